@@ -177,7 +177,10 @@ def decoder_run(sources, lengths, W, hp, decoder="DualSourceTransformerDecoder",
             term = (nn.sigmoid(stop[:, 0]) > 0.5) & (t > MIN_ITERS)
             newly = term & (stop_steps < 0)
             stop_steps[newly] = t
-            finished = bool(np.all(term)) if stop_mode == "all_rows" else bool(np.all(stop_steps >= 0))
+            if stop_mode == "never":
+                finished = False
+            else:
+                finished = bool(np.all(term)) if stop_mode == "all_rows" else bool(np.all(stop_steps >= 0))
             x = out[:, -M * nf:]
         t += 1
         if finished:

@@ -1,0 +1,149 @@
+// common.cuh -- host-side plumbing shared by every translation unit of libsat.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <cstdarg>
+#include <string>
+#include <vector>
+#include <map>
+#include <stdexcept>
+#include <memory>
+#include "../../include/sat.h"
+
+namespace sat {
+
+// ---- error plumbing: C++ exceptions inside, int codes at the ABI ----------
+struct Error : std::runtime_error {
+  int code;
+  Error(int c, const std::string& m) : std::runtime_error(m), code(c) {}
+};
+void set_last_error(const std::string& m);
+[[noreturn]] void fail(int code, const char* fmt, ...);
+
+#define SAT_CUDA(expr)                                                                   \
+  do {                                                                                   \
+    cudaError_t e__ = (expr);                                                            \
+    if (e__ != cudaSuccess)                                                              \
+      ::sat::fail(SAT_ECUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, __LINE__); \
+  } while (0)
+
+#define SAT_REQUIRE(cond, ...)                        \
+  do {                                                \
+    if (!(cond)) ::sat::fail(SAT_EINVAL, __VA_ARGS__); \
+  } while (0)
+
+// Wraps an ABI body: catches everything, records the message, returns a code.
+template <class F>
+int guarded(F&& f) {
+  try {
+    f();
+    return SAT_OK;
+  } catch (const Error& e) {
+    set_last_error(e.what());
+    return e.code;
+  } catch (const std::exception& e) {
+    set_last_error(e.what());
+    return SAT_EINVAL;
+  }
+}
+
+// every kernel launch of the library goes through this counter (bench: gpu_launches)
+void count_launch(int n = 1);
+void check_launch(const char* what);
+
+// ---- weight blob lookup -----------------------------------------------------
+struct Blob {
+  std::map<std::string, std::pair<const float*, int64_t>> t;
+  Blob(const sat_tensor* w, int n) {
+    for (int i = 0; i < n; ++i) t[w[i].name] = {w[i].data, w[i].numel};
+  }
+  bool has(const std::string& name) const { return t.count(name) != 0; }
+  const float* get(const std::string& name, int64_t numel) const {
+    auto it = t.find(name);
+    if (it == t.end()) fail(SAT_EMISSING, "weight '%s' missing from the blob", name.c_str());
+    if (it->second.second != numel)
+      fail(SAT_EINVAL, "weight '%s' has %lld elements, expected %lld", name.c_str(),
+           (long long)it->second.second, (long long)numel);
+    return it->second.first;
+  }
+};
+
+// ---- device memory owned by a handle ---------------------------------------
+struct DevPool {
+  std::vector<void*> ptrs;
+  size_t bytes = 0;
+  ~DevPool() { release(); }
+  void release() {
+    for (void* p : ptrs) cudaFree(p);
+    ptrs.clear();
+    bytes = 0;
+  }
+  template <class T>
+  T* alloc(size_t n, bool zero = true) {
+    void* p = nullptr;
+    size_t b = (n ? n : 1) * sizeof(T);
+    SAT_CUDA(cudaMalloc(&p, b));
+    if (zero) SAT_CUDA(cudaMemset(p, 0, b));
+    ptrs.push_back(p);
+    bytes += b;
+    return (T*)p;
+  }
+  float* upload(const float* host, size_t n) {
+    float* d = alloc<float>(n, false);
+    SAT_CUDA(cudaMemcpy(d, host, n * sizeof(float), cudaMemcpyHostToDevice));
+    return d;
+  }
+  float* upload(const std::vector<float>& v) { return upload(v.data(), v.size()); }
+};
+
+// grow-only scratch buffer (re-used across calls of a handle)
+struct Scratch {
+  void* p = nullptr;
+  size_t cap = 0;
+  ~Scratch() {
+    if (p) cudaFree(p);
+  }
+  template <class T>
+  T* get(size_t n) {
+    size_t b = (n ? n : 1) * sizeof(T);
+    if (b > cap) {
+      if (p) SAT_CUDA(cudaFree(p));
+      p = nullptr;
+      SAT_CUDA(cudaMalloc(&p, b));
+      cap = b;
+    }
+    return (T*)p;
+  }
+};
+
+inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }
+
+enum Act { ACT_NONE = 0, ACT_RELU = 1, ACT_TANH = 2, ACT_SIGMOID = 3, ACT_SOFTSIGN = 4 };
+
+// ---- row-major GEMM / implicit conv1d (gemm.cu) -----------------------------
+// C[(b,t), n] = act( (sum_tap sum_c X[b, t + tap - pad_left, c] * W[tap][c][n]) * scale[n] + shift[n] ) (+ R[(b,t), n])
+// X is [Bn, T, ldx] with Cin <= ldx used columns starting at x_col0; zero outside [0,T).
+// Output row stride ldc, column offset c_col0.  scale may be null (=1), shift may be null (=0).
+struct GemmArgs {
+  const float* X = nullptr;
+  int Bn = 1, T = 1, Cin = 0, ldx = 0;
+  const float* W = nullptr;  // device [taps][Cin][N]
+  int taps = 1, pad_left = 0, N = 0;
+  const float* scale = nullptr;
+  const float* shift = nullptr;
+  int act = ACT_NONE;
+  const float* R = nullptr;  // residual, row stride ldr
+  int ldr = 0;
+  float* C = nullptr;
+  int ldc = 0;
+  const int64_t* row_lengths = nullptr;  // optional [Bn]: rows with t >= length read as zero input (values mask)
+  const int64_t* gather_ids = nullptr;   // optional [Bn*T] int64: X row index = ids - gather_offset (embedding lookup); T-shift disabled
+  int64_t gather_offset = 0;
+  int maxpool2 = 0;                      // 1: input element = max(X[t], X[t+1]) (MaxPooling1D k2 s1 SAME) fused on load
+};
+void gemm_launch(const GemmArgs& a, cudaStream_t st);
+
+}  // namespace sat

@@ -1,0 +1,419 @@
+// decoder.cu -- host side of sat_decoder_*: weight repacking, workspace layout, launch.
+#include "common.cuh"
+#include "decoder_kernel.cuh"
+
+namespace sat {
+using namespace dec;
+
+namespace {
+
+struct PackedDense {
+  float* Wp = nullptr;
+  float* bias = nullptr;
+  int K = 0, N = 0, n_tiles = 0;
+  DenseDesc desc() const { return DenseDesc{Wp, bias, K, N, n_tiles, -1, 0}; }
+};
+
+// generic column-tile packing: column c of tile i comes from source column colmap[i*8+c] (or -1 = zero)
+PackedDense pack_cols(DevPool& pool, const float* W, const float* bias, int K, int Nsrc, const std::vector<int>& colmap) {
+  PackedDense d;
+  d.K = K;
+  d.N = (int)colmap.size();
+  d.n_tiles = ceil_div(d.N, TILE_N);
+  std::vector<float> wp((size_t)d.n_tiles * K * TILE_N, 0.f), bp((size_t)d.n_tiles * TILE_N, 0.f);
+  for (int n = 0; n < d.N; ++n) {
+    const int src = colmap[n];
+    if (src < 0) continue;
+    const int tile = n / TILE_N, c = n % TILE_N;
+    for (int k = 0; k < K; ++k) wp[((size_t)tile * K + k) * TILE_N + c] = W[(size_t)k * Nsrc + src];
+    if (bias) bp[n] = bias[src];
+  }
+  d.Wp = pool.upload(wp);
+  d.bias = pool.upload(bp);
+  return d;
+}
+PackedDense pack_dense(DevPool& pool, const float* W, const float* bias, int K, int N) {
+  std::vector<int> cm(N);
+  for (int n = 0; n < N; ++n) cm[n] = n;
+  return pack_cols(pool, W, bias, K, N, cm);
+}
+// LSTM kernel [K][4*units] gate order i,j,f,o -> tiles of 2 units x 4 gates
+PackedDense pack_lstm(DevPool& pool, const float* W, const float* bias, int K, int units) {
+  const int tiles = ceil_div(units, 2);
+  std::vector<int> cm((size_t)tiles * TILE_N, -1);
+  for (int u = 0; u < units; ++u)
+    for (int g = 0; g < 4; ++g) cm[(u / 2) * TILE_N + (u % 2) * 4 + g] = g * units + u;
+  PackedDense d = pack_cols(pool, W, bias, K, 4 * units, cm);
+  d.N = tiles * TILE_N;
+  return d;
+}
+
+__global__ void init_state_kernel(float* alpha0, float* alpha1, float* u0, float* u1, int B, int T) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  if (alpha0) alpha0[(size_t)b * T] = 1.f;
+  if (alpha1) alpha1[(size_t)b * T] = 1.f;
+  if (u0) u0[b] = 0.5f;
+  if (u1) u1[b] = 0.5f;
+}
+
+// spk_term[n][b] = softsign(speaker_embed[b] . Ws[:, n] + bs[n])   (multi_speaker_modules.py:29)
+__global__ void spk_term_kernel(const float* spk, const float* Ws, const float* bs, int B, int E, int N, int ld, float* out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * N) return;
+  const int n = i / B, b = i % B;
+  float v = bs[n];
+  for (int e = 0; e < E; ++e) v = fmaf(spk[(size_t)b * E + e], Ws[(size_t)e * N + n], v);
+  out[(size_t)n * ld + b] = v / (1.f + fabsf(v));
+}
+
+// sample ids: argmax over M per r-slot (modules/helpers.py:49-52); first maximum wins like tf.argmax
+__global__ void argmax_kernel(const float* mel, long long rows, int M, int* ids) {
+  const long long row = (long long)blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32;
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  float best = -INFINITY;
+  int bi = 0x7fffffff;
+  for (int i = lane; i < M; i += 32) {
+    const float v = mel[row * M + i];
+    if (v > best) { best = v; bi = i; }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+  }
+  if (lane == 0) ids[row] = bi;
+}
+
+}  // namespace
+}  // namespace sat
+
+using namespace sat;
+
+struct sat_decoder {
+  sat_hparams hp;
+  DevPool pool;
+  Scratch ws;
+  PackedDense pre0, msd, pre1, lstm_a, lstm_1, lstm_2, outp, dq[2];
+  PackedDense sa_qkv[MAX_HOPS], sa_o[MAX_HOPS], sa_tr[MAX_HOPS];
+  float* mem_layer[2] = {nullptr, nullptr};  // [Dm][Up]
+  float *att_v[2], *att_ba[2], *conv_w[2], *conv_b[2], *Wl[2], *Wt[2];
+  float bt[2] = {0.f, 0.f};
+  float *ms_Ws = nullptr, *ms_bs = nullptr;
+  int Up[2] = {0, 0};
+  int n_mech = 1, hops = 0, sm_count = 0, grid = 0;
+  int P0 = 0, P1 = 0, Dctx = 0, Mr = 0, Mnf = 0;
+  unsigned* barrier = nullptr;
+  long long* prof = nullptr;
+  size_t max_dyn_smem = 0;
+};
+
+extern "C" int sat_decoder_create(const sat_hparams* hpp, const sat_tensor* weights, int32_t n_weights, sat_decoder** out) {
+  return guarded([&] {
+    SAT_REQUIRE(hpp && weights && out, "null argument");
+    const sat_hparams& hp = *hpp;
+    Blob W(weights, n_weights);
+    auto* h = new sat_decoder();
+    std::unique_ptr<sat_decoder> guard(h);
+    h->hp = hp;
+    const int M = hp.num_mels, r = hp.outputs_per_step, nf = hp.n_feed_frame;
+    const int A = hp.attention_out_units, Dd = hp.decoder_out_units;
+    SAT_REQUIRE(nf >= 1 && nf <= r, "n_feed_frame must be in [1, outputs_per_step]");
+    h->n_mech = hp.decoder_kind == SAT_DEC_EXTENDED ? 1 : 2;
+    h->hops = hp.decoder_kind == SAT_DEC_DUAL_SOURCE_TRANSFORMER ? hp.decoder_self_attention_num_hop : 0;
+    SAT_REQUIRE(h->hops <= MAX_HOPS, "at most %d decoder self-attention hops are supported", MAX_HOPS);
+    h->Mr = M * r;
+    h->Mnf = M * nf;
+    h->P0 = hp.decoder_prenet_units[0];
+    h->P1 = hp.decoder_prenet_units[1];
+    h->Dctx = 0;
+    for (int i = 0; i < h->n_mech; ++i) h->Dctx += hp.memory_dim[i];
+    DevPool& pool = h->pool;
+    const std::string D = "decoder/";
+    // prenet (modules/module.py:1511-1517)
+    if (hp.multi_speaker_prenet) {
+      const int E = hp.speaker_embedding_dim;
+      h->pre0 = pack_dense(pool, W.get(D + "prenet/ms/dense0/kernel", (int64_t)h->Mnf * h->P0),
+                           W.get(D + "prenet/ms/dense0/bias", h->P0), h->Mnf, h->P0);
+      h->msd = pack_dense(pool, W.get(D + "prenet/ms/dense/kernel", (int64_t)h->P0 * h->P0),
+                          W.get(D + "prenet/ms/dense/bias", h->P0), h->P0, h->P0);
+      h->ms_Ws = pool.upload(W.get(D + "prenet/ms/speaker_projection/kernel", (int64_t)E * h->P0), (size_t)E * h->P0);
+      h->ms_bs = pool.upload(W.get(D + "prenet/ms/speaker_projection/bias", h->P0), h->P0);
+    } else {
+      h->pre0 = pack_dense(pool, W.get(D + "prenet/dense_0/kernel", (int64_t)h->Mnf * h->P0),
+                           W.get(D + "prenet/dense_0/bias", h->P0), h->Mnf, h->P0);
+    }
+    h->pre1 = pack_dense(pool, W.get(D + "prenet/dense_1/kernel", (int64_t)h->P0 * h->P1),
+                         W.get(D + "prenet/dense_1/bias", h->P1), h->P0, h->P1);
+    // cells
+    const int Ka = h->P1 + h->Dctx + A, K1 = A + h->Dctx + Dd, K2 = 2 * Dd;
+    h->lstm_a = pack_lstm(pool, W.get(D + "attention_lstm/kernel", (int64_t)Ka * 4 * A), W.get(D + "attention_lstm/bias", 4 * A), Ka, A);
+    h->lstm_1 = pack_lstm(pool, W.get(D + "lstm_1/kernel", (int64_t)K1 * 4 * Dd), W.get(D + "lstm_1/bias", 4 * Dd), K1, Dd);
+    h->lstm_2 = pack_lstm(pool, W.get(D + "lstm_2/kernel", (int64_t)K2 * 4 * Dd), W.get(D + "lstm_2/bias", 4 * Dd), K2, Dd);
+    // attention mechanisms
+    for (int i = 0; i < h->n_mech; ++i) {
+      const std::string P = D + "attention" + std::to_string(i + 1) + "/";
+      const int U = hp.attention_units[i], Dm = hp.memory_dim[i], Up = (U + 3) / 4 * 4;
+      const int kind = hp.attention_kind[i];
+      SAT_REQUIRE(U <= 256, "attention num_units > 256 unsupported (got %d)", U);
+      SAT_REQUIRE(Dm <= NT, "attention memory depth > %d unsupported", NT);
+      h->Up[i] = Up;
+      auto padU = [&](const float* src, int rows) {  // [rows][U] -> [rows][Up]
+        std::vector<float> v((size_t)rows * Up, 0.f);
+        for (int rr = 0; rr < rows; ++rr)
+          for (int u = 0; u < U; ++u) v[(size_t)rr * Up + u] = src[(size_t)rr * U + u];
+        return pool.upload(v);
+      };
+      h->mem_layer[i] = padU(W.get(P + "memory_layer/kernel", (int64_t)Dm * U), Dm);
+      {
+        std::vector<int> cm(Up, -1);
+        for (int u = 0; u < U; ++u) cm[u] = u;
+        h->dq[i] = pack_cols(pool, W.get(P + "query_layer/kernel", (int64_t)A * U), nullptr, A, U, cm);
+      }
+      h->att_v[i] = padU(W.get(P + "attention_v", U), 1);
+      std::vector<float> zeros(Up, 0.f);
+      h->att_ba[i] = pool.upload(zeros);
+      h->conv_w[i] = h->conv_b[i] = h->Wl[i] = h->Wt[i] = nullptr;
+      if (kind == SAT_ATT_FORWARD || kind == SAT_ATT_LOCATION_SENSITIVE) {
+        const int Kc = hp.attention_kernel, F = hp.attention_filters;
+        SAT_REQUIRE(Kc <= 2 * HALO && F <= 32, "attention_kernel <= %d and attention_filters <= 32 required", 2 * HALO);
+        h->att_ba[i] = padU(W.get(P + "attention_bias", U), 1);
+        h->conv_w[i] = pool.upload(W.get(P + "location_conv/kernel", (int64_t)Kc * F), (size_t)Kc * F);
+        h->conv_b[i] = pool.upload(W.get(P + "location_conv/bias", F), F);
+        h->Wl[i] = padU(W.get(P + "location_layer/kernel", (int64_t)F * U), F);
+        if (kind == SAT_ATT_FORWARD && hp.use_transition_agent) {
+          h->Wt[i] = pool.upload(W.get(P + "transition/kernel", Dm + U), Dm + U);
+          h->bt[i] = W.get(P + "transition/bias", 1)[0];
+        }
+      }
+    }
+    // decoder self-attention hops (modules/module.py:363-371 inside rnn_wrappers.py:111-124)
+    int d_out = Dd;
+    for (int i = 0; i < h->hops; ++i) {
+      const int Ds = hp.decoder_self_attention_out_units;
+      SAT_REQUIRE(Ds == Dd, "decoder self-attention units must equal decoder_out_units");
+      SAT_REQUIRE(Ds % hp.decoder_self_attention_num_heads == 0 && (Ds / hp.decoder_self_attention_num_heads) % 4 == 0 &&
+                      Ds / hp.decoder_self_attention_num_heads <= 512, "unsupported head size");
+      const std::string P = D + "sa_" + std::to_string(i) + "/";
+      std::vector<float> w((size_t)Dd * 3 * Ds), b(3 * Ds);
+      const char* names[3] = {"key", "value", "query"};
+      for (int j = 0; j < 3; ++j) {
+        const float* k = W.get(P + "mha/" + names[j] + "/kernel", (int64_t)Dd * Ds);
+        const float* bb = W.get(P + "mha/" + names[j] + "/bias", Ds);
+        for (int kk = 0; kk < Dd; ++kk)
+          for (int n = 0; n < Ds; ++n) w[(size_t)kk * 3 * Ds + j * Ds + n] = k[(size_t)kk * Ds + n];
+        for (int n = 0; n < Ds; ++n) b[j * Ds + n] = bb[n];
+      }
+      h->sa_qkv[i] = pack_dense(pool, w.data(), b.data(), Dd, 3 * Ds);
+      h->sa_o[i] = pack_dense(pool, W.get(P + "mha/output/kernel", (int64_t)Ds * Ds), W.get(P + "mha/output/bias", Ds), Ds, Ds);
+      h->sa_tr[i] = pack_dense(pool, W.get(P + "transform/kernel", (int64_t)Ds * Ds), W.get(P + "transform/bias", Ds), Ds, Ds);
+      d_out = Ds;
+    }
+    // frame + stop projection fused into one [d_out][Mr + 1] layer
+    {
+      const float* ko = W.get(D + "out_projection/kernel", (int64_t)d_out * h->Mr);
+      const float* bo = W.get(D + "out_projection/bias", h->Mr);
+      const float* ks = W.get(D + "stop_token_projection/kernel", d_out);
+      const float* bs = W.get(D + "stop_token_projection/bias", 1);
+      const int N = h->Mr + 1;
+      std::vector<float> w((size_t)d_out * N), b(N);
+      for (int k = 0; k < d_out; ++k) {
+        for (int n = 0; n < h->Mr; ++n) w[(size_t)k * N + n] = ko[(size_t)k * h->Mr + n];
+        w[(size_t)k * N + h->Mr] = ks[k];
+      }
+      for (int n = 0; n < h->Mr; ++n) b[n] = bo[n];
+      b[h->Mr] = bs[0];
+      h->outp = pack_dense(pool, w.data(), b.data(), d_out, N);
+    }
+    // launch geometry
+    int dev = 0;
+    SAT_CUDA(cudaGetDevice(&dev));
+    cudaDeviceProp prop;
+    SAT_CUDA(cudaGetDeviceProperties(&prop, dev));
+    SAT_REQUIRE(prop.cooperativeLaunch, "device lacks cooperative launch");
+    h->sm_count = prop.multiProcessorCount;
+    h->max_dyn_smem = prop.sharedMemPerBlockOptin - 4096;
+    SAT_CUDA(cudaFuncSetAttribute(decoder_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->max_dyn_smem));
+    h->grid = h->sm_count;
+    h->barrier = pool.alloc<unsigned>(1);
+    h->prof = pool.alloc<long long>(N_PROF);
+    guard.release();
+    *out = h;
+  });
+}
+
+extern "C" void sat_decoder_destroy(sat_decoder* h) { delete h; }
+
+extern "C" double sat_decoder_step_bytes(const sat_decoder* h, int32_t B, int32_t T, int32_t avg_cache_len) {
+  // weights once per step + per-utterance attention memory (keys + values of every
+  // source) + average KV-cache read + state/io.
+  if (!h) return 0.0;
+  const sat_hparams& hp = h->hp;
+  auto wbytes = [](const PackedDense& d) { return (double)d.K * d.N * 4.0; };
+  double w = wbytes(h->pre0) + wbytes(h->pre1) + wbytes(h->lstm_a) + wbytes(h->lstm_1) + wbytes(h->lstm_2) + wbytes(h->outp);
+  if (hp.multi_speaker_prenet) w += wbytes(h->msd);
+  double per_utt = 0;
+  for (int i = 0; i < h->n_mech; ++i) {
+    w += wbytes(h->dq[i]);
+    per_utt += (double)T * (hp.attention_units[i] + hp.memory_dim[i]) * 4.0;
+  }
+  for (int i = 0; i < h->hops; ++i) {
+    w += wbytes(h->sa_qkv[i]) + wbytes(h->sa_o[i]) + wbytes(h->sa_tr[i]);
+    per_utt += (double)avg_cache_len * 2.0 * hp.decoder_self_attention_out_units * 4.0;
+  }
+  const double state = 4.0 * (2.0 * (hp.attention_out_units + 2 * hp.decoder_out_units) * 2 + h->Dctx + 3.0 * T * h->n_mech);
+  const double io = 4.0 * (h->Mnf + h->Mr + 1);
+  return w + B * (per_utt + state + io);
+}
+
+extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* stream) {
+  return guarded([&] {
+    SAT_REQUIRE(h && iop, "null argument");
+    const sat_decoder_io& io = *iop;
+    const sat_hparams& hp = h->hp;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int B = io.B, T = io.T_enc;
+    SAT_REQUIRE(B >= 1 && B <= MAX_B, "batch must be in [1, %d] per call (got %d); split larger batches", MAX_B, B);
+    SAT_REQUIRE(T >= 1 && T <= MAX_T, "T_enc must be in [1, %d] (got %d)", MAX_T, T);
+    SAT_REQUIRE(io.max_steps >= 1 && io.max_steps <= 8192, "max_steps must be in [1, 8192]");
+    SAT_REQUIRE(io.memory_lengths && io.mel && io.stop && io.stop_steps && io.n_steps, "missing required buffer");
+    SAT_REQUIRE(io.feed_mode != SAT_FEED_TEACHER || (io.target && io.target_steps >= 1), "teacher feed needs target");
+    SAT_REQUIRE(!hp.multi_speaker_prenet || io.speaker_embed, "multi-speaker prenet needs speaker_embed");
+    const int Bp = (B + 3) / 4 * 4, ld = Bp;
+    const int R = ceil_div(Bp, ROWS_PER_GROUP);
+    const int A = hp.attention_out_units, Dd = hp.decoder_out_units, Ds = hp.decoder_self_attention_out_units;
+    const int S = io.max_steps;
+
+    DecParams p;
+    memset(&p, 0, sizeof(p));
+    p.B = B; p.Bp = Bp; p.ld = ld; p.R = R; p.T = T;
+    p.M = hp.num_mels; p.r = hp.outputs_per_step; p.nf = hp.n_feed_frame; p.Mnf = h->Mnf; p.Mr = h->Mr;
+    p.P0 = h->P0; p.P1 = h->P1; p.A = A; p.Dd = Dd; p.Dctx = h->Dctx; p.n_mech = h->n_mech;
+    p.hops = h->hops; p.heads = hp.decoder_self_attention_num_heads; p.Ds = Ds; p.ms = hp.multi_speaker_prenet;
+    p.feed_mode = io.feed_mode; p.stop_mode = io.stop_mode; p.max_steps = S; p.min_iters = io.min_iters;
+    p.S_target = io.target_steps; p.Smax = S;
+    p.zc = hp.zoneout_factor_cell; p.zh = hp.zoneout_factor_output;
+    p.pre0 = h->pre0.desc(); p.pre1 = h->pre1.desc(); p.outp = h->outp.desc();
+    if (p.ms) p.msd = h->msd.desc();
+    p.lstm_a = h->lstm_a.desc(); p.lstm_1 = h->lstm_1.desc(); p.lstm_2 = h->lstm_2.desc();
+
+    // ---- shared-memory plan: keep as many LSTM tiles resident as fit ----
+    size_t smem_floats = SCRATCH_FLOATS;
+    DenseDesc* lst[3] = {&p.lstm_a, &p.lstm_1, &p.lstm_2};
+    for (DenseDesc* d : lst) {
+      const int slots = ceil_div(d->n_tiles * R, h->grid);
+      const size_t need = (size_t)slots * d->K * TILE_N;
+      if ((smem_floats + need) * sizeof(float) <= h->max_dyn_smem) {
+        d->smem_off = (int)(smem_floats - SCRATCH_FLOATS);
+        d->slots = slots;
+        smem_floats += need;
+      }
+    }
+
+    // ---- workspace carve-up (floats) ----
+    const int Ka = p.P1 + p.Dctx + A, K1 = A + p.Dctx + Dd, K2 = 2 * Dd;
+    size_t off = 0;
+    auto take = [&](size_t n) { size_t o = off; off += (n + 63) / 64 * 64; return o; };
+    const size_t o_xin = take((size_t)p.Mnf * ld), o_p0 = take((size_t)p.P0 * ld), o_p0b = take((size_t)p.P0 * ld);
+    const size_t o_att0 = take((size_t)Ka * ld), o_att1 = take((size_t)Ka * ld);
+    const size_t o_l10 = take((size_t)K1 * ld), o_l11 = take((size_t)K1 * ld);
+    const size_t o_l20 = take((size_t)K2 * ld), o_l21 = take((size_t)K2 * ld);
+    const size_t o_ca = take((size_t)A * ld), o_c1 = take((size_t)Dd * ld), o_c2 = take((size_t)Dd * ld);
+    const size_t o_dout = take((size_t)Dd * ld);
+    const size_t o_saq = take((size_t)Ds * ld), o_sactx = take((size_t)Ds * ld), o_saa = take((size_t)Ds * ld);
+    const size_t o_say0 = take((size_t)Ds * ld), o_say1 = take((size_t)Ds * ld);
+    const size_t o_spk = take((size_t)p.P0 * ld);
+    size_t o_pq[2], o_sal[2], o_sap[2], o_su[2], o_keys[2];
+    for (int i = 0; i < 2; ++i) {
+      o_pq[i] = take((size_t)256 * ld);
+      o_sal[i] = take((size_t)B * T);
+      o_sap[i] = take((size_t)B * T);
+      o_su[i] = take((size_t)B);
+    }
+    const size_t state_floats = off;  // everything up to here is zeroed per run
+    for (int i = 0; i < h->n_mech; ++i) o_keys[i] = take((size_t)B * T * h->Up[i]);
+    size_t o_kc[MAX_HOPS], o_vc[MAX_HOPS];
+    for (int i = 0; i < h->hops; ++i) {
+      o_kc[i] = take((size_t)B * Ds * S);
+      o_vc[i] = take((size_t)B * Ds * S);
+    }
+    float* ws = h->ws.get<float>(off);
+    SAT_CUDA(cudaMemsetAsync(ws, 0, state_floats * sizeof(float), st));
+    SAT_CUDA(cudaMemsetAsync(h->barrier, 0, sizeof(unsigned), st));
+    SAT_CUDA(cudaMemsetAsync(io.stop_steps, 0xff, sizeof(int32_t) * B, st));
+
+    p.xin = ws + o_xin; p.p0 = ws + o_p0; p.p0b = ws + o_p0b;
+    p.att_in[0] = ws + o_att0; p.att_in[1] = ws + o_att1;
+    p.l1_in[0] = ws + o_l10; p.l1_in[1] = ws + o_l11;
+    p.l2_in[0] = ws + o_l20; p.l2_in[1] = ws + o_l21;
+    p.c_a = ws + o_ca; p.c_1 = ws + o_c1; p.c_2 = ws + o_c2; p.dout = ws + o_dout;
+    p.sa_q = ws + o_saq; p.sa_ctx = ws + o_sactx; p.sa_a = ws + o_saa; p.sa_y[0] = ws + o_say0; p.sa_y[1] = ws + o_say1;
+    p.target = io.target; p.lengths = (const long long*)io.memory_lengths;
+    p.mel = io.mel; p.stop = io.stop; p.dec_out = io.decoder_outputs; p.stop_steps = io.stop_steps; p.n_steps = io.n_steps;
+    p.barrier = h->barrier; p.prof = h->prof;
+
+    if (p.ms) {
+      spk_term_kernel<<<ceil_div(B * p.P0, 256), 256, 0, st>>>(io.speaker_embed, h->ms_Ws, h->ms_bs, B, hp.speaker_embedding_dim,
+                                                              p.P0, ld, ws + o_spk);
+      count_launch();
+      p.spk_term = ws + o_spk;
+    }
+    for (int i = 0; i < h->n_mech; ++i) {
+      int kind = hp.attention_kind[i];
+      if (io.forced_alignment) kind = SAT_ATT_TEACHER_FORCING;
+      SAT_REQUIRE(io.memory[i], "memory[%d] is null", i);
+      AttMech& m = p.mech[i];
+      m.kind = kind; m.U = hp.attention_units[i]; m.Up = h->Up[i]; m.Dv = hp.memory_dim[i];
+      m.F = hp.attention_filters; m.Kc = hp.attention_kernel; m.pad_left = (hp.attention_kernel - 1) / 2;
+      m.cumulative = hp.cumulative_weights; m.agent = (h->Wt[i] != nullptr);
+      m.values = io.memory[i];
+      m.v = h->att_v[i]; m.ba = h->att_ba[i]; m.conv_w = h->conv_w[i]; m.conv_b = h->conv_b[i]; m.Wl = h->Wl[i];
+      m.Wt = h->Wt[i]; m.bt = h->bt[i];
+      m.pq = ws + o_pq[i]; m.pq_su = ld; m.pq_sb = 1;
+      m.st_align = ws + o_sal[i]; m.st_alpha = ws + o_sap[i]; m.st_u = ws + o_su[i];
+      m.out_align = io.alignments[i]; m.out_S = S;
+      p.dq[i] = h->dq[i].desc();
+      if (kind == SAT_ATT_TEACHER_FORCING) {
+        SAT_REQUIRE(io.teacher_alignments[i] && io.target_steps >= 1, "teacher-forcing attention needs teacher_alignments[%d]", i);
+        m.teacher = io.teacher_alignments[i];
+        m.teacher_S = io.target_steps;
+      } else {
+        // keys = (memory * mask) @ memory_layer  (TF BahdanauAttention; computed once per batch)
+        GemmArgs g;
+        g.X = io.memory[i]; g.Bn = B; g.T = T; g.Cin = m.Dv; g.ldx = m.Dv;
+        g.W = h->mem_layer[i]; g.N = m.Up; g.C = ws + o_keys[i]; g.ldc = m.Up;
+        g.row_lengths = io.memory_lengths;
+        gemm_launch(g, st);
+        m.keys = ws + o_keys[i];
+      }
+    }
+    init_state_kernel<<<ceil_div(B, 128), 128, 0, st>>>(ws + o_sap[0], ws + o_sap[1], ws + o_su[0], ws + o_su[1], B, T);
+    count_launch();
+    for (int i = 0; i < h->hops; ++i) {
+      p.hop[i].qkv = h->sa_qkv[i].desc(); p.hop[i].o = h->sa_o[i].desc(); p.hop[i].tr = h->sa_tr[i].desc();
+      p.hop[i].kcache = ws + o_kc[i]; p.hop[i].vcache = ws + o_vc[i];
+    }
+
+    void* args[] = {&p};
+    SAT_CUDA(cudaLaunchCooperativeKernel((const void*)decoder_persistent_kernel, dim3(h->grid), dim3(NT), args,
+                                         smem_floats * sizeof(float), st));
+    count_launch();
+    if (io.sample_ids) {
+      const long long rows = (long long)B * S * p.r;
+      argmax_kernel<<<(unsigned)ceil_div64(rows, 8), 256, 0, st>>>(io.mel, rows, p.M, io.sample_ids);
+      count_launch();
+    }
+    check_launch("decoder_persistent_kernel");
+  });
+}
+
+// cycles per phase accumulated by CTA 0 over all runs since the last reset (debug / profiling aid)
+extern "C" int sat_decoder_profile(sat_decoder* h, int64_t* out16, int32_t reset) {
+  return guarded([&] {
+    SAT_REQUIRE(h && out16, "null argument");
+    SAT_CUDA(cudaDeviceSynchronize());
+    SAT_CUDA(cudaMemcpy(out16, h->prof, sizeof(long long) * N_PROF, cudaMemcpyDeviceToHost));
+    if (reset) SAT_CUDA(cudaMemset(h->prof, 0, sizeof(long long) * N_PROF));
+  });
+}

@@ -1,0 +1,339 @@
+// decoder_kernel.cuh -- the persistent autoregressive decoder kernel.
+//
+// One cooperative launch runs ALL decoder steps.  Per step:
+//   A  prenet layer 0 (+ MultiSpeakerPreNet speaker term)       column-split dense
+//   A2 MultiSpeakerPreNet second dense (multi-speaker only)      column-split dense
+//   B  prenet layer 1                                            column-split dense
+//   C  attention ZoneoutLSTM                                     weight-stationary LSTM tiles
+//   D  query layers of the attention mechanisms                  column-split dense
+//   E  attention mechanisms: energies, softmax, alpha recursion, context   row-split
+//   F  decoder ZoneoutLSTM 1                                     weight-stationary LSTM tiles
+//   G  decoder ZoneoutLSTM 2                                     weight-stationary LSTM tiles
+//   H-K decoder self-attention hops with a KV cache (transformer decoder only)
+//   L  frame + stop-token projection, feedback frame, stop rule
+// with one grid-wide barrier between consecutive phases.
+#pragma once
+#include "decoder_attn.cuh"
+
+namespace sat {
+namespace dec {
+
+constexpr int N_PROF = 16;
+constexpr int SCRATCH_FLOATS = (RED_FLOATS > ATT_SMEM_FLOATS ? RED_FLOATS : ATT_SMEM_FLOATS);
+
+struct SaHop {
+  DenseDesc qkv, o, tr;
+  float* kcache;  // [B][H][Smax][dh]
+  float* vcache;
+};
+
+struct DecParams {
+  int B, Bp, ld, R, T;
+  int M, r, nf, Mnf, Mr, P0, P1, A, Dd, Dctx, n_mech, hops, heads, Ds, ms;
+  int feed_mode, stop_mode, max_steps, min_iters, S_target, Smax;
+  float zc, zh;
+  DenseDesc pre0, msd, pre1, lstm_a, lstm_1, lstm_2, outp;
+  DenseDesc dq[2];
+  AttMech mech[2];
+  SaHop hop[MAX_HOPS];
+  float *xin, *p0, *p0b, *att_in[2], *l1_in[2], *l2_in[2], *c_a, *c_1, *c_2, *dout;
+  float *sa_q, *sa_ctx, *sa_a, *sa_y[2];
+  const float* spk_term;  // [P0][ld] softsign(Ws spk + bs), feature-major
+  const float* target;    // [B][S_target][Mr]
+  const long long* lengths;
+  float *mel, *stop, *dec_out;
+  int *stop_steps, *n_steps;
+  unsigned* barrier;
+  long long* prof;  // [N_PROF] accumulated SM cycles per phase (CTA 0), may be null
+};
+
+struct DenseEpi {
+  const float* bias; int N, ld, act;
+  float* dst; float* dst2; const float* addend;  // feature-major [n][ld]
+  __device__ __forceinline__ void operator()(int b, int tile, int ul, const float* g) const {
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const int n = tile * TILE_N + ul * 4 + c;
+      if (n >= N) continue;
+      float v = g[c] + __ldg(bias + n);
+      if (act == 1) v = fmaxf(v, 0.f);
+      else if (act == 2) v = tanhf(v);
+      if (addend) v += __ldcg(addend + (size_t)n * ld + b);
+      dst[(size_t)n * ld + b] = v;
+      if (dst2) dst2[(size_t)n * ld + b] = v;
+    }
+  }
+};
+
+struct LstmEpi {
+  const float* bias; int units, ld, B;
+  float* c; const float* hprev; float* out; float* hz;
+  float* rm_out; int rm_stride; int rm_off;  // optional row-major copy of the output: rm_out[b*rm_stride + rm_off + u]
+  float zc, zh;
+  __device__ __forceinline__ void operator()(int b, int tile, int ul, const float* g) const {
+    const int u = tile * 2 + ul;
+    if (u >= units) return;
+    const float* bb = bias + tile * TILE_N + ul * 4;
+    const float gi = g[0] + __ldg(bb + 0), gj = g[1] + __ldg(bb + 1), gf = g[2] + __ldg(bb + 2), go = g[3] + __ldg(bb + 3);
+    const size_t idx = (size_t)u * ld + b;
+    const float cp = c[idx], hp = __ldcg(hprev + idx);
+    const float cn = sigmoidf_(gf + 1.0f) * cp + sigmoidf_(gi) * tanhf(gj);
+    const float hn = sigmoidf_(go) * tanhf(cn);
+    c[idx] = cn - zc * (cn - cp);
+    hz[idx] = hn - zh * (hn - hp);
+    out[idx] = hn;
+    if (rm_out && b < B) rm_out[(size_t)b * rm_stride + rm_off + u] = hn;
+  }
+};
+
+struct QkvEpi {
+  const float* bias; int Ds, dh, H, Smax, t, ld, B;
+  float *kc, *vc, *q;
+  __device__ __forceinline__ void operator()(int b, int tile, int ul, const float* g) const {
+    const int n0 = tile * TILE_N + ul * 4;
+    if (n0 >= 3 * Ds) return;
+    float v[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) v[c] = g[c] + __ldg(bias + n0 + c);
+    const int which = n0 / Ds, d = n0 % Ds;
+    if (which == 2) {
+#pragma unroll
+      for (int c = 0; c < 4; ++c) q[(size_t)(d + c) * ld + b] = v[c];
+    } else if (b < B) {
+      const int hd = d / dh, dd = d % dh;
+      float* dst = (which == 0 ? kc : vc) + (((size_t)b * H + hd) * Smax + t) * dh + dd;
+      *(float4*)dst = make_float4(v[0], v[1], v[2], v[3]);
+    }
+  }
+};
+
+struct OutEpi {
+  const float* bias; int Mr, Mnf, ld, B, t, maxS, feed_self;
+  float *mel, *stop, *xin;
+  __device__ __forceinline__ void operator()(int b, int tile, int ul, const float* g) const {
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const int n = tile * TILE_N + ul * 4 + c;
+      if (n > Mr) continue;
+      const float v = g[c] + __ldg(bias + n);
+      if (n == Mr) {
+        if (b < B) stop[(size_t)b * maxS + t] = v;
+      } else {
+        if (b < B) mel[((size_t)b * maxS + t) * Mr + n] = v;
+        if (feed_self && n >= Mr - Mnf) xin[(size_t)(n - (Mr - Mnf)) * ld + b] = v;
+      }
+    }
+  }
+};
+
+// decoder self-attention over the KV cache for one (row, head): last-row causal attention
+__device__ inline void sa_item(const DecParams& p, const SaHop& h, int b, int hd, int t, float* sm) {
+  const int dh = p.Ds / p.heads, n = t + 1, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  float* sc = sm;             // [n]
+  float* q = sm + 8192;       // [dh]
+  float* part = q + 512;      // [NT]
+  float* s32 = part + NT;
+  for (int d = tid; d < dh; d += NT) q[d] = __ldcg(p.sa_q + (size_t)(hd * dh + d) * p.ld + b);
+  __syncthreads();
+  const float* kb = h.kcache + ((size_t)b * p.heads + hd) * p.Smax * dh;
+  const float* vb = h.vcache + ((size_t)b * p.heads + hd) * p.Smax * dh;
+  const float scale = 1.f / sqrtf((float)dh);
+  for (int j = warp; j < n; j += NW) {
+    float s = 0.f;
+    for (int d = lane; d < dh; d += 32) s = fmaf(q[d], __ldcg(kb + (size_t)j * dh + d), s);
+    s = warp_sum(s);
+    if (lane == 0) sc[j] = s * scale;
+  }
+  __syncthreads();
+  float mx = -INFINITY;
+  for (int j = tid; j < n; j += NT) mx = fmaxf(mx, sc[j]);
+  mx = block_max(mx, s32);
+  float sum = 0.f;
+  for (int j = tid; j < n; j += NT) {
+    const float e = expf(sc[j] - mx);
+    sc[j] = e;
+    sum += e;
+  }
+  sum = block_sum(sum, s32);
+  const float inv = 1.f / sum;
+  const int G = max(1, NT / dh), d = tid % dh, grp = tid / dh;
+  float c = 0.f;
+  if (tid < G * dh)
+    for (int j = grp; j < n; j += G) c = fmaf(sc[j], __ldcg(vb + (size_t)j * dh + d), c);
+  part[tid] = c;
+  __syncthreads();
+  if (tid < dh) {
+    float ctx = 0.f;
+    for (int g = 0; g < G; ++g) ctx += part[g * dh + tid];
+    p.sa_ctx[(size_t)(hd * dh + tid) * p.ld + b] = ctx * inv;
+  }
+  __syncthreads();
+}
+
+// softmax feedback of the code decoders (modules/helpers.py:98-106) for one row
+__device__ inline void softmax_feed_item(const DecParams& p, int b, int t, float* sm) {
+  float* s32 = sm;
+  for (int s = p.r - p.nf; s < p.r; ++s) {
+    const float* row = p.mel + ((size_t)b * p.max_steps + t) * p.Mr + (size_t)s * p.M;
+    float mx = -INFINITY;
+    for (int i = threadIdx.x; i < p.M; i += NT) mx = fmaxf(mx, __ldcg(row + i));
+    mx = block_max(mx, s32);
+    float sum = 0.f;
+    for (int i = threadIdx.x; i < p.M; i += NT) sum += expf(__ldcg(row + i) - mx);
+    sum = block_sum(sum, s32);
+    for (int i = threadIdx.x; i < p.M; i += NT)
+      p.xin[(size_t)((s - (p.r - p.nf)) * p.M + i) * p.ld + b] = expf(__ldcg(row + i) - mx) / sum;
+    __syncthreads();
+  }
+}
+
+__global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_constant__ DecParams p) {
+  extern __shared__ __align__(16) float smem[];
+  float* scratch = smem;                  // SCRATCH_FLOATS: reduction / row-phase scratch
+  float* wres = smem + SCRATCH_FLOATS;    // resident LSTM tiles
+  __shared__ int s_stopped[MAX_B];
+  GridBarrier bar{p.barrier, 0u};
+  const int tid = threadIdx.x;
+  const int ld = p.ld;
+
+  load_resident(p.lstm_a, p.R, wres);
+  load_resident(p.lstm_1, p.R, wres);
+  load_resident(p.lstm_2, p.R, wres);
+  for (int i = tid; i < MAX_B; i += NT) s_stopped[i] = -1;
+  __syncthreads();
+
+  long long tprev = 0;
+  int ph = 0;
+  auto phase_end = [&]() {
+    bar.sync();
+    if (p.prof && blockIdx.x == 0 && tid == 0) {
+      const long long now = clock64();
+      p.prof[ph] += now - tprev;
+      tprev = now;
+    }
+    ++ph;
+  };
+
+  int t = 0;
+  for (; t < p.max_steps; ++t) {
+    const int cur = t & 1, nxt = cur ^ 1;
+    ph = 0;
+    if (p.prof && blockIdx.x == 0 && tid == 0) tprev = clock64();
+    // ---- A: prenet layer 0 ----
+    dense_phase(p.pre0, p.xin, ld, p.Bp, p.R, wres, scratch,
+                DenseEpi{p.pre0.bias, p.pre0.N, ld, 1, p.p0, nullptr, p.ms ? p.spk_term : nullptr});
+    phase_end();
+    const float* pin = p.p0;
+    if (p.ms) {
+      dense_phase(p.msd, p.p0, ld, p.Bp, p.R, wres, scratch,
+                  DenseEpi{p.msd.bias, p.msd.N, ld, 1, p.p0b, nullptr, nullptr});
+      phase_end();
+      pin = p.p0b;
+    }
+    // ---- B: prenet layer 1 -> attention-LSTM input rows [0, P1) ----
+    dense_phase(p.pre1, pin, ld, p.Bp, p.R, wres, scratch,
+                DenseEpi{p.pre1.bias, p.pre1.N, ld, 1, p.att_in[cur], nullptr, nullptr});
+    phase_end();
+    // ---- C: attention LSTM ----
+    {
+      const size_t hoff = (size_t)(p.P1 + p.Dctx) * ld;
+      dense_phase(p.lstm_a, p.att_in[cur], ld, p.Bp, p.R, wres, scratch,
+                  LstmEpi{p.lstm_a.bias, p.A, ld, p.B, p.c_a, p.att_in[cur] + hoff, p.l1_in[cur],
+                          p.att_in[nxt] + hoff, nullptr, 0, 0, p.zc, p.zh});
+    }
+    phase_end();
+    // ---- D: query layers ----
+    bool any_q = false;
+    for (int mi = 0; mi < p.n_mech; ++mi)
+      if (p.mech[mi].kind != SAT_ATT_TEACHER_FORCING) {
+        any_q = true;
+        dense_phase(p.dq[mi], p.l1_in[cur], ld, p.Bp, p.R, wres, scratch,
+                    DenseEpi{p.dq[mi].bias, p.dq[mi].N, ld, 0, const_cast<float*>(p.mech[mi].pq), nullptr, nullptr});
+      }
+    if (any_q) phase_end();
+    // ---- E: attention mechanisms (row split) ----
+    for (int item = blockIdx.x; item < p.B * p.n_mech; item += gridDim.x) {
+      const int b = item / p.n_mech, mi = item % p.n_mech;
+      AttMech m = p.mech[mi];
+      m.ctx_dst[0] = p.att_in[nxt] + (size_t)(p.P1 + (mi ? p.mech[0].Dv : 0)) * ld;
+      m.ctx_dst[1] = p.l1_in[cur] + (size_t)(p.A + (mi ? p.mech[0].Dv : 0)) * ld;
+      m.ctx_sd = ld;
+      m.ctx_sb = 1;
+      attention_item(m, b, t, p.T, (int)p.lengths[b], scratch);
+    }
+    phase_end();
+    // ---- F: decoder LSTM 1 ----
+    {
+      const size_t hoff = (size_t)(p.A + p.Dctx) * ld;
+      dense_phase(p.lstm_1, p.l1_in[cur], ld, p.Bp, p.R, wres, scratch,
+                  LstmEpi{p.lstm_1.bias, p.Dd, ld, p.B, p.c_1, p.l1_in[cur] + hoff, p.l2_in[cur],
+                          p.l1_in[nxt] + hoff, nullptr, 0, 0, p.zc, p.zh});
+    }
+    phase_end();
+    // ---- G: decoder LSTM 2 ----
+    {
+      const size_t hoff = (size_t)p.Dd * ld;
+      dense_phase(p.lstm_2, p.l2_in[cur], ld, p.Bp, p.R, wres, scratch,
+                  LstmEpi{p.lstm_2.bias, p.Dd, ld, p.B, p.c_2, p.l2_in[cur] + hoff, p.dout,
+                          p.l2_in[nxt] + hoff, p.dec_out, p.max_steps * p.Dd, t * p.Dd, p.zc, p.zh});
+    }
+    phase_end();
+    // ---- H-K: decoder self-attention hops over the KV cache ----
+    const float* y = p.dout;
+    for (int hi = 0; hi < p.hops; ++hi) {
+      const SaHop& h = p.hop[hi];
+      dense_phase(h.qkv, y, ld, p.Bp, p.R, wres, scratch,
+                  QkvEpi{h.qkv.bias, p.Ds, p.Ds / p.heads, p.heads, p.Smax, t, ld, p.B, h.kcache, h.vcache, p.sa_q});
+      phase_end();
+      for (int item = blockIdx.x; item < p.B * p.heads; item += gridDim.x)
+        sa_item(p, h, item / p.heads, item % p.heads, t, scratch);
+      phase_end();
+      dense_phase(h.o, p.sa_ctx, ld, p.Bp, p.R, wres, scratch,
+                  DenseEpi{h.o.bias, h.o.N, ld, 0, p.sa_a, nullptr, nullptr});
+      phase_end();
+      dense_phase(h.tr, p.sa_a, ld, p.Bp, p.R, wres, scratch,
+                  DenseEpi{h.tr.bias, h.tr.N, ld, 2, p.sa_y[hi & 1], nullptr, y});
+      phase_end();
+      y = p.sa_y[hi & 1];
+    }
+    // ---- L: frame + stop projections; next input frame ----
+    if (p.feed_mode == SAT_FEED_TEACHER) {
+      const int ts = min(t, p.S_target - 1);
+      for (int i = blockIdx.x * NT + tid; i < p.Mnf * p.B; i += gridDim.x * NT) {
+        const int f = i / p.B, b = i % p.B;
+        p.xin[(size_t)f * ld + b] = __ldg(p.target + ((size_t)b * p.S_target + ts) * p.Mr + (p.Mr - p.Mnf) + f);
+      }
+    }
+    dense_phase(p.outp, y, ld, p.Bp, p.R, wres, scratch,
+                OutEpi{p.outp.bias, p.Mr, p.Mnf, ld, p.B, t, p.max_steps, p.feed_mode == SAT_FEED_SELF,
+                       p.mel, p.stop, p.xin});
+    phase_end();
+    if (p.feed_mode == SAT_FEED_SELF_SOFTMAX) {
+      for (int b = blockIdx.x; b < p.B; b += gridDim.x) softmax_feed_item(p, b, t, scratch);
+      phase_end();
+    }
+    // ---- stop rule (every CTA evaluates the same data -> same decision) ----
+    if (p.stop_mode != SAT_STOP_FIXED) {
+      bool term = true, stopped = true;
+      if (tid < p.B) {
+        const float logit = __ldcg(p.stop + (size_t)tid * p.max_steps + t);
+        term = (sigmoidf_(logit) > 0.5f) && (t > p.min_iters);
+        if (term && s_stopped[tid] < 0) {
+          s_stopped[tid] = t;
+          if (blockIdx.x == 0) p.stop_steps[tid] = t;
+        }
+        stopped = s_stopped[tid] >= 0;
+      }
+      const int all_term = __syncthreads_and(term ? 1 : 0);
+      const int all_stopped = __syncthreads_and(stopped ? 1 : 0);
+      if (p.stop_mode == SAT_STOP_ALL_ROWS ? all_term : all_stopped) {
+        ++t;
+        break;
+      }
+    }
+  }
+  if (blockIdx.x == 0 && tid == 0) *p.n_steps = t;
+}
+
+}  // namespace dec
+}  // namespace sat

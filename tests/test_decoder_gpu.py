@@ -1,0 +1,197 @@
+"""GPU parity of the persistent decoder kernel (through the C ABI) against the oracle.
+
+Tolerance: BASELINE.json north_star -- teacher-forced mel / stop / alignments within 1e-3
+relative (max|d| / max|ref|); free-run: identical stop step and alignment argmax.
+The oracle runs in float64 on the same float32 weights and inputs.
+"""
+import numpy as np
+import pytest
+
+import sat_b200
+from tests.util import rel_err, small_hp, decoder_inputs, oracle_decoder
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-3
+
+
+def _torch():
+    import torch
+    return torch
+
+
+def run_cuda(hp, W, mems, lengths, **kw):
+    torch = _torch()
+    from sat_b200.engine import DecoderHandle
+    dev = torch.device("cuda:0")
+    h = DecoderHandle(hp, W)
+    t = lambda a: None if a is None else torch.from_numpy(np.ascontiguousarray(a)).to(dev)  # noqa: E731
+    if "teacher_alignments" in kw and kw["teacher_alignments"] is not None:
+        kw["teacher_alignments"] = [t(a) for a in kw["teacher_alignments"]]
+    for k in ("target", "speaker_embed"):
+        if k in kw:
+            kw[k] = t(kw[k])
+    out = h.run([t(m) for m in mems], t(lengths), **kw)
+    torch.cuda.synchronize()
+    n = int(out["n_steps"].item())
+    res = {"n_steps": n, "stop_steps": out["stop_steps"].cpu().numpy(),
+           "mel": out["mel"].cpu().numpy()[:, :n * hp.outputs_per_step],
+           "stop": out["stop"].cpu().numpy()[:, :n, None],
+           "alignments": [a.cpu().numpy()[:, :n] for a in out["alignments"] if a is not None]}
+    if out["sample_ids"] is not None:
+        res["sample_ids"] = out["sample_ids"].cpu().numpy()[:, :n]
+    if out["decoder_outputs"] is not None:
+        res["decoder_outputs"] = out["decoder_outputs"].cpu().numpy()[:, :n]
+    return res
+
+
+def check_close(got, ref, keys=("mel", "stop"), tol=TOL):
+    assert got["n_steps"] == ref["n_steps"]
+    for k in keys:
+        assert got[k].shape == ref[k].shape, (k, got[k].shape, ref[k].shape)
+        e = rel_err(got[k], ref[k])
+        assert e <= tol, f"{k}: rel err {e:.3e} > {tol}"
+    for i, (a, b) in enumerate(zip(got["alignments"], ref["alignments"])):
+        e = rel_err(a, b)
+        assert e <= tol, f"alignment{i}: rel err {e:.3e} > {tol}"
+
+
+SMALL = dict(attention_out_units=32, decoder_out_units=32, decoder_self_attention_out_units=32,
+             attention1_out_units=24, attention2_out_units=8, cbhg_out_units=16, self_attention_out_units=8,
+             decoder_prenet_out_units=(24, 16), num_mels=12)
+
+
+@pytest.mark.parametrize("B,T,S", [(1, 7, 5), (3, 23, 12), (16, 40, 9)])
+def test_extended_decoder_teacher_forced_small(B, T, S):
+    hp = small_hp("ljspeech_tacotron", **SMALL)
+    W = sat_b200.init_weights(hp, seed=B, stress=True)
+    mems, lengths, target, _ = decoder_inputs(hp, B, T, S, seed=B)
+    ref = oracle_decoder(hp, W, mems, lengths, target=target, is_validation=True, teacher_forcing=True)
+    got = run_cuda(hp, W, mems, lengths, target=target, feed_mode=0, stop_mode=0, max_steps=S,
+                   want_decoder_outputs=True)
+    check_close(got, ref)
+    assert rel_err(got["decoder_outputs"], ref["decoder_outputs"]) <= TOL
+
+
+def test_extended_decoder_full_dims_teacher_forced():
+    hp = small_hp("ljspeech_tacotron")
+    W = sat_b200.init_weights(hp, seed=7, stress=True)
+    mems, lengths, target, _ = decoder_inputs(hp, 2, 150, 40, seed=7)
+    ref = oracle_decoder(hp, W, mems, lengths, target=target, is_validation=True, teacher_forcing=True)
+    got = run_cuda(hp, W, mems, lengths, target=target, feed_mode=0, stop_mode=0, max_steps=40)
+    check_close(got, ref)
+
+
+@pytest.mark.parametrize("B", [130, 256])
+def test_extended_decoder_two_row_groups(B):
+    hp = small_hp("ljspeech_tacotron", **SMALL)
+    W = sat_b200.init_weights(hp, seed=3, stress=True)
+    mems, lengths, target, _ = decoder_inputs(hp, B, 19, 6, seed=3)
+    ref = oracle_decoder(hp, W, mems, lengths, target=target, is_validation=True, teacher_forcing=True)
+    got = run_cuda(hp, W, mems, lengths, target=target, feed_mode=0, stop_mode=0, max_steps=6)
+    check_close(got, ref)
+
+
+@pytest.mark.parametrize("stop_mode", ["all_rows", "per_row"])
+def test_extended_decoder_free_run_stop(stop_mode):
+    hp = small_hp("ljspeech_tacotron", **SMALL)
+    W = sat_b200.init_weights(hp, seed=11, stress=True)
+    W["decoder/stop_token_projection/kernel"] *= 8.0
+    mems, lengths, _, _ = decoder_inputs(hp, 6, 21, 1, seed=11)
+    # the stop logit does not feed back: shift its bias so the rows stop at spread-out steps
+    probe = oracle_decoder(hp, W, mems, lengths, stop_mode="never", max_iters=40)
+    W["decoder/stop_token_projection/bias"] -= np.float32(np.quantile(probe["stop"][:, 11:], 0.9))
+    ref = oracle_decoder(hp, W, mems, lengths, stop_mode=stop_mode, max_iters=40)
+    got = run_cuda(hp, W, mems, lengths, feed_mode=1, stop_mode=1 if stop_mode == "all_rows" else 2, max_steps=40)
+    assert got["n_steps"] == ref["n_steps"]
+    np.testing.assert_array_equal(got["stop_steps"], ref["stop_steps"])
+    check_close(got, ref)
+    n = got["n_steps"]
+    np.testing.assert_array_equal(np.argmax(got["alignments"][0][:, :n], -1), np.argmax(ref["alignments"][0][:, :n], -1))
+
+
+@pytest.mark.parametrize("kind,cumulative,agent", [("location_sensitive", False, False),
+                                                   ("location_sensitive", True, False),
+                                                   ("additive", False, False),
+                                                   ("forward", True, True),
+                                                   ("forward", False, True)])
+def test_attention_kinds(kind, cumulative, agent):
+    hp = small_hp("ljspeech_tacotron", attention=kind, cumulative_weights=cumulative,
+                  use_forward_attention_transition_agent=agent, attention_kernel=7, attention_filters=3, **SMALL)
+    W = sat_b200.init_weights(hp, seed=5, stress=True)
+    mems, lengths, target, _ = decoder_inputs(hp, 4, 18, 10, seed=5)
+    ref = oracle_decoder(hp, W, mems, lengths, target=target, is_validation=True, teacher_forcing=True)
+    got = run_cuda(hp, W, mems, lengths, target=target, feed_mode=0, stop_mode=0, max_steps=10)
+    check_close(got, ref)
+
+
+def test_generic_location_filters():
+    hp = small_hp("ljspeech_tacotron", attention="forward", attention_kernel=31, attention_filters=32, **SMALL)
+    W = sat_b200.init_weights(hp, seed=6, stress=True)
+    mems, lengths, target, _ = decoder_inputs(hp, 3, 20, 6, seed=6)
+    ref = oracle_decoder(hp, W, mems, lengths, target=target, is_validation=True, teacher_forcing=True)
+    got = run_cuda(hp, W, mems, lengths, target=target, feed_mode=0, stop_mode=0, max_steps=6)
+    check_close(got, ref)
+
+
+@pytest.mark.parametrize("B,T,S", [(2, 9, 6), (5, 30, 14)])
+def test_dual_source_transformer_teacher_forced(B, T, S):
+    hp = small_hp("ljspeech_self_attention", **SMALL)
+    W = sat_b200.init_weights(hp, seed=B, stress=True)
+    mems, lengths, target, _ = decoder_inputs(hp, B, T, S, seed=B)
+    ref = oracle_decoder(hp, W, mems, lengths, target=target, is_validation=True, teacher_forcing=True)
+    got = run_cuda(hp, W, mems, lengths, target=target, feed_mode=0, stop_mode=0, max_steps=S, want_sample_ids=True)
+    check_close(got, ref)
+    np.testing.assert_array_equal(got["sample_ids"], ref["sample_ids"])
+
+
+def test_dual_source_transformer_full_dims():
+    hp = small_hp("ljspeech_self_attention")
+    W = sat_b200.init_weights(hp, seed=9, stress=True)
+    mems, lengths, target, _ = decoder_inputs(hp, 2, 60, 30, seed=9)
+    ref = oracle_decoder(hp, W, mems, lengths, target=target, is_validation=True, teacher_forcing=True)
+    got = run_cuda(hp, W, mems, lengths, target=target, feed_mode=0, stop_mode=0, max_steps=30)
+    check_close(got, ref)
+
+
+def test_dual_source_decoder_no_transformer():
+    hp = small_hp("ljspeech_self_attention", decoder="DualSourceDecoder", **SMALL)
+    W = sat_b200.init_weights(hp, seed=2, stress=True)
+    mems, lengths, target, _ = decoder_inputs(hp, 3, 15, 8, seed=2)
+    ref = oracle_decoder(hp, W, mems, lengths, target=target, is_validation=True, teacher_forcing=True)
+    got = run_cuda(hp, W, mems, lengths, target=target, feed_mode=0, stop_mode=0, max_steps=8)
+    check_close(got, ref)
+
+
+def test_code_decoder_softmax_feedback():
+    """cfg 5 form: r=1, validation without teacher forcing feeds softmax probs (helpers.py:98-106);
+    argmax code ids must match exactly."""
+    hp = small_hp("codes_self_attention", **dict(SMALL, num_mels=37))
+    W = sat_b200.init_weights(hp, seed=4, stress=True)
+    mems, lengths, target, _ = decoder_inputs(hp, 4, 16, 12, seed=4)
+    ref = oracle_decoder(hp, W, mems, lengths, target=target, is_validation=True, teacher_forcing=False)
+    got = run_cuda(hp, W, mems, lengths, target=target, feed_mode=2, stop_mode=0, max_steps=12, want_sample_ids=True)
+    check_close(got, ref)
+    np.testing.assert_array_equal(got["sample_ids"], ref["sample_ids"])
+
+
+def test_multi_speaker_prenet():
+    hp = small_hp("vctk_self_attention", **SMALL)
+    W = sat_b200.init_weights(hp, seed=8, stress=True)
+    mems, lengths, target, spk = decoder_inputs(hp, 5, 14, 7, seed=8)
+    ref = oracle_decoder(hp, W, mems, lengths, target=target, is_validation=True, teacher_forcing=True, speaker_embed=spk)
+    got = run_cuda(hp, W, mems, lengths, target=target, speaker_embed=spk, feed_mode=0, stop_mode=0, max_steps=7)
+    check_close(got, ref)
+
+
+def test_forced_alignment_second_pass():
+    """models/models.py:118-134: pass 2 replays pass-1 alignments, feeding its own output."""
+    hp = small_hp("ljspeech_self_attention", **SMALL)
+    W = sat_b200.init_weights(hp, seed=10, stress=True)
+    mems, lengths, target, _ = decoder_inputs(hp, 3, 13, 9, seed=10)
+    p1 = oracle_decoder(hp, W, mems, lengths, target=target, is_validation=True, teacher_forcing=True)
+    ta = [a.astype(np.float32) for a in p1["alignments"]]
+    ref = oracle_decoder(hp, W, mems, lengths, target=target, is_validation=True, teacher_forcing=False,
+                         teacher_alignments=ta, forced_alignment=True)
+    got = run_cuda(hp, W, mems, lengths, target=target, teacher_alignments=ta, forced_alignment=True,
+                   feed_mode=2, stop_mode=0, max_steps=9)
+    check_close(got, ref)
