@@ -15,7 +15,7 @@
  *   sat_sat_forward SelfAttentionTransformer.call  modules/module.py:363-371
  *   sat_attention_step  ForwardAttention.__call__  modules/forward_attention.py:88-122
  *                       (+ additive / location_sensitive, modules/attentions.py:35-57)
- *   sat_prenet_forward  PreNet stack / MultiSpeakerPreNet  modules/multi_speaker_modules.py:27-32
+ *   sat_dense_forward   tf.layers.Dense (PreNet, MultiSpeakerPreNet modules/multi_speaker_modules.py:27-32)
  *   sat_postnet_*   tacotron2 PostNetV2 (models/models.py:4)
  *
  * Conventions: all tensors fp32 row-major in TensorFlow layouts ([B,T,C]
@@ -97,6 +97,9 @@ int sat_encoder_create(const sat_hparams* hp, const sat_tensor* weights, int32_t
  * [hops*heads,B,T,T] may be NULL (must be NULL for SAT_ENC_ZONEOUT_V1). */
 int sat_encoder_forward(sat_encoder* h, const int64_t* ids, const int64_t* lengths, int32_t B, int32_t T,
                         float* lstm_out, float* sa_out, float* sa_probs, void* stream);
+/* same, for callers that did the embedding lookup themselves: embedded [B,T,embedding_dim] (device) */
+int sat_encoder_forward_embedded(sat_encoder* h, const float* embedded, const int64_t* lengths, int32_t B, int32_t T,
+                                 float* lstm_out, float* sa_out, float* sa_probs, void* stream);
 void sat_encoder_destroy(sat_encoder* h);
 
 /* ---- decoder ---------------------------------------------------------- */
@@ -155,6 +158,11 @@ int sat_attention_prepare(const sat_tensor* weights, int32_t n_weights, const ch
 /* y = act(x @ kernel + bias); act: 0 none, 1 relu, 2 tanh, 3 sigmoid, 4 softsign */
 int sat_dense_forward(const float* kernel_host, const float* bias_host, int32_t K, int32_t N, int32_t act,
                       const float* x, int64_t rows, float* y, void* stream);
+/* table[ids - index_offset]  (tacotron2 Embedding; models/models.py:28,43-50): table host [rows,dim], ids device [n] */
+int sat_embedding_lookup(const float* table_host, int64_t table_rows, int32_t dim, int64_t index_offset,
+                         const int64_t* ids, int64_t n, float* out, void* stream);
+/* cycles per phase accumulated by CTA 0 of the persistent decoder kernel (profiling aid); out16 host */
+int sat_decoder_profile(sat_decoder* h, int64_t* out16, int32_t reset);
 
 /* ---- post-net --------------------------------------------------------- */
 int sat_postnet_create(const sat_hparams* hp, const sat_tensor* weights, int32_t n_weights, sat_postnet** out);

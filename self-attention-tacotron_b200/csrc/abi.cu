@@ -33,6 +33,15 @@ __global__ void __launch_bounds__(NT) attention_step_kernel(AttMech m, int B, in
   for (int b = blockIdx.x; b < B; b += gridDim.x) attention_item(m, b, 0, T, (int)lengths[b], sm);
 }
 
+__global__ void embedding_kernel(const float* table, long long rows, int dim, long long offset, const long long* ids,
+                                 long long n, float* out, int* bad) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n * dim) return;
+  const long long r = ids[i / dim] - offset;
+  if (r < 0 || r >= rows) { *bad = 1; out[i] = 0.f; return; }
+  out[i] = table[r * dim + i % dim];
+}
+
 __global__ void mask_rows_kernel(const float* x, const long long* lengths, int B, int T, int D, float* y) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= (long long)B * T * D) return;
@@ -150,5 +159,26 @@ extern "C" int sat_attention_step(const sat_tensor* weights, int32_t n_weights, 
     count_launch();
     check_launch("attention_step_kernel");
     SAT_CUDA(cudaStreamSynchronize(st));
+  });
+}
+
+extern "C" int sat_embedding_lookup(const float* table_host, int64_t table_rows, int32_t dim, int64_t index_offset,
+                                    const int64_t* ids, int64_t n, float* out, void* stream) {
+  return guarded([&] {
+    SAT_REQUIRE(table_host && ids && out && table_rows > 0 && dim > 0 && n >= 0, "bad argument");
+    cudaStream_t st = (cudaStream_t)stream;
+    DevPool pool;
+    float* table = pool.upload(table_host, (size_t)table_rows * dim);
+    int* bad = pool.alloc<int>(1);
+    if (n > 0) {
+      embedding_kernel<<<(unsigned)ceil_div64(n * dim, 256), 256, 0, st>>>(table, table_rows, dim, index_offset,
+                                                                          (const long long*)ids, n, out, bad);
+      count_launch();
+      check_launch("embedding_kernel");
+    }
+    int hbad = 0;
+    SAT_CUDA(cudaMemcpyAsync(&hbad, bad, sizeof(int), cudaMemcpyDeviceToHost, st));
+    SAT_CUDA(cudaStreamSynchronize(st));
+    SAT_REQUIRE(!hbad, "embedding id out of range [%lld, %lld)", (long long)index_offset, (long long)(index_offset + table_rows));
   });
 }

@@ -143,7 +143,31 @@ struct GemmArgs {
   const int64_t* gather_ids = nullptr;   // optional [Bn*T] int64: X row index = ids - gather_offset (embedding lookup); T-shift disabled
   int64_t gather_offset = 0;
   int maxpool2 = 0;                      // 1: input element = max(X[t], X[t+1]) (MaxPooling1D k2 s1 SAME) fused on load
+  int highway = 0;                       // 1: HighwayNet epilogue over interleaved (H_u, T_u) column pairs; R = layer input; writes N/2 columns
 };
 void gemm_launch(const GemmArgs& a, cudaStream_t st);
+
+// ---- multi-head self-attention (mha.cu) --------------------------------------
+// Device copy of one MultiHeadAttention (modules/self_attention.py:89-128) and, optionally, the
+// tanh transform layer of the enclosing SelfAttentionTransformer (modules/module.py:358).
+struct MhaDev {
+  float* Wqkv = nullptr;  // [Din][3D], column blocks key | value | query
+  float* bqkv = nullptr;  // [3D]
+  float* Wo = nullptr;    // [D][D]
+  float* bo = nullptr;
+  float* Wt = nullptr;    // [D][D] transform (null when absent)
+  float* bt = nullptr;
+  int Din = 0, D = 0, H = 1;
+};
+// mha_prefix: ".../mha" holding {key,value,query,output}/{kernel,bias}; transform_prefix may be empty
+MhaDev mha_upload(DevPool& pool, const Blob& W, const std::string& mha_prefix, const std::string& transform_prefix,
+                  int Din, int D, int H);
+size_t mha_scratch_floats(const MhaDev& m, int64_t rows);
+// out [B,T,D] = output Dense(attention(x)); probs [B,H,T,T] or null; pad_lengths != null enables the padding mask
+void mha_forward(const MhaDev& m, const float* x, int B, int T, int causal, const int64_t* pad_lengths,
+                 float* out, float* probs, float* scratch, cudaStream_t st);
+// SelfAttentionTransformer: out = x + tanh(Dense(mha(x)))   (needs Din == D and a transform layer)
+void sat_layer_forward(const MhaDev& m, const float* x, int B, int T, int causal, const int64_t* pad_lengths,
+                       float* out, float* probs, float* scratch, cudaStream_t st);
 
 }  // namespace sat

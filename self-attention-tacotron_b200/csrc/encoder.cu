@@ -1,0 +1,350 @@
+// encoder.cu -- sat_encoder_*: embedding lookup + encoder prenet + ZoneoutCBHG (+ self-attention branch).
+//
+// Restates (citations into /root/reference):
+//   Embedding lookup                  models/models.py:28,54 (tacotron2 Embedding)
+//   ZoneoutEncoderV1.call             modules/module.py:336-339
+//   SelfAttentionCBHGEncoder.call     modules/module.py:425-438
+//   ZoneoutCBHG.call                  modules/module.py:77-110
+//     conv bank K=1..max (Conv1d = conv -> BN(inference) -> relu, A.2) -> concat -> MaxPooling1D(2,1,SAME)
+//     -> proj1 (k3, relu) -> proj2 (k3, linear) -> + input -> [adjustment Dense] -> highway x n (A.3)
+//     -> bidirectional ZoneoutLSTM with sequence_length (A.4, A.12)
+//
+// Dense / conv stages are implicit-GEMM launches (gemm.cu) with BN folded into scale/shift, the
+// embedding gather and the max-pool fused on load and the highway gate fused into the epilogue.
+// The BiLSTM input projection is one time-batched GEMM; the recurrence runs in a kernel where each
+// CTA owns a few (row, direction) sequences for all T steps (rows are independent -> no grid sync).
+#include "common.cuh"
+
+namespace sat {
+namespace {
+
+constexpr int LSTM_NT = 512;
+constexpr int LSTM_ROWS = 4;  // sequences per CTA
+
+__device__ __forceinline__ float sigm(float x) { return 1.f / (1.f + expf(-x)); }
+
+// xproj [B][T][2][U][4] (bias included); Wh [2][U(k)][U][4]; out [B][T][2U] (fw | bw), zero past the length.
+// grid = (ceil(B / LSTM_ROWS), 2).  Thread (u, kpart): partial gate sums of unit u over k in its quarter.
+template <int U>
+__global__ void __launch_bounds__(LSTM_NT) bilstm_kernel(const float* __restrict__ xproj, const float* __restrict__ Wh,
+                                                         const long long* __restrict__ lengths, int B, int T,
+                                                         float zc, float zh, float* __restrict__ out) {
+  constexpr int KP = LSTM_NT / U;  // k partitions
+  constexpr int KQ = U / KP;       // k values per partition
+  __shared__ __align__(16) float h_s[LSTM_ROWS][U];
+  __shared__ __align__(16) float part[KP][LSTM_ROWS][U][4];
+  const int tid = threadIdx.x, u = tid % U, kp = tid / U;
+  const int dir = blockIdx.y, b0 = blockIdx.x * LSTM_ROWS;
+  const float4* W4 = (const float4*)(Wh + (size_t)dir * U * U * 4);
+  int maxlen = 0;
+#pragma unroll
+  for (int r = 0; r < LSTM_ROWS; ++r)
+    maxlen = max(maxlen, (b0 + r < B) ? min((int)lengths[b0 + r], T) : 0);
+  for (int i = tid; i < LSTM_ROWS * U; i += LSTM_NT) (&h_s[0][0])[i] = 0.f;
+  // the thread that finalises (row r, unit u) keeps that cell's c and zoned h in registers
+  float c_reg = 0.f, h_reg = 0.f;
+  const int fr = kp;  // finalising thread of row r has kp == r (needs KP >= LSTM_ROWS)
+  static_assert(KP >= LSTM_ROWS, "one finalising k-partition per row");
+  const int my_len = (fr < LSTM_ROWS && b0 + fr < B) ? min((int)lengths[b0 + fr], T) : 0;
+  __syncthreads();
+  for (int s = 0; s < maxlen; ++s) {
+    float acc[LSTM_ROWS][4];
+#pragma unroll
+    for (int r = 0; r < LSTM_ROWS; ++r)
+#pragma unroll
+      for (int g = 0; g < 4; ++g) acc[r][g] = 0.f;
+#pragma unroll 4
+    for (int kk = 0; kk < KQ; ++kk) {
+      const int k = kp * KQ + kk;
+      const float4 w = __ldg(W4 + (size_t)k * U + u);
+#pragma unroll
+      for (int r = 0; r < LSTM_ROWS; ++r) {
+        const float hv = h_s[r][k];
+        acc[r][0] = fmaf(hv, w.x, acc[r][0]); acc[r][1] = fmaf(hv, w.y, acc[r][1]);
+        acc[r][2] = fmaf(hv, w.z, acc[r][2]); acc[r][3] = fmaf(hv, w.w, acc[r][3]);
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < LSTM_ROWS; ++r) *(float4*)part[kp][r][u] = make_float4(acc[r][0], acc[r][1], acc[r][2], acc[r][3]);
+    __syncthreads();
+    if (s < my_len) {
+      const int r = fr, b = b0 + r;
+      const int pos = dir == 0 ? s : my_len - 1 - s;  // backward direction walks the row reversed by its own length
+      float4 g = __ldg((const float4*)(xproj + ((((size_t)b * T + pos) * 2 + dir) * U + u) * 4));
+#pragma unroll
+      for (int q = 0; q < KP; ++q) {
+        const float4 pp = *(const float4*)part[q][r][u];
+        g.x += pp.x; g.y += pp.y; g.z += pp.z; g.w += pp.w;
+      }
+      const float cn = sigm(g.z + 1.0f) * c_reg + sigm(g.x) * tanhf(g.y);
+      const float hn = sigm(g.w) * tanhf(cn);
+      c_reg = cn - zc * (cn - c_reg);
+      h_reg = hn - zh * (hn - h_reg);
+      out[((size_t)b * T + pos) * (2 * U) + dir * U + u] = hn;  // cell output is the un-zoned h (A.4)
+      h_s[r][u] = h_reg;  // every thread is past this step's h_s reads (barrier above)
+    }
+    __syncthreads();
+  }
+}
+
+struct Conv {
+  float* w = nullptr;      // [k][cin][cout]
+  float* scale = nullptr;  // folded BN
+  float* shift = nullptr;
+  int k = 1, cin = 0, cout = 0;
+};
+
+Conv upload_conv_bn(DevPool& pool, const Blob& W, const std::string& P, int k, int cin, int cout) {
+  Conv c;
+  c.k = k; c.cin = cin; c.cout = cout;
+  c.w = pool.upload(W.get(P + "/kernel", (int64_t)k * cin * cout), (size_t)k * cin * cout);
+  const float* gamma = W.get(P + "/bn/gamma", cout);
+  const float* beta = W.get(P + "/bn/beta", cout);
+  const float* mean = W.get(P + "/bn/mean", cout);
+  const float* var = W.get(P + "/bn/var", cout);
+  std::vector<float> sc(cout), sh(cout);
+  for (int i = 0; i < cout; ++i) {
+    // tf.layers.batch_normalization(training=False), epsilon 1e-3
+    const float s = gamma[i] / sqrtf(var[i] + 1e-3f);
+    sc[i] = s;
+    sh[i] = beta[i] - mean[i] * s;
+  }
+  c.scale = pool.upload(sc);
+  c.shift = pool.upload(sh);
+  return c;
+}
+
+}  // namespace
+
+// shared with postnet.cu
+void conv_bn_act_launch(const float* x, int B, int T, int ldx, const float* w, const float* scale, const float* shift,
+                        int k, int cin, int cout, int act, int maxpool2, const float* R, int ldr, float* y, int ldy,
+                        cudaStream_t st) {
+  GemmArgs g;
+  g.X = x; g.Bn = B; g.T = T; g.Cin = cin; g.ldx = ldx;
+  g.W = w; g.taps = k; g.pad_left = (k - 1) / 2; g.N = cout;
+  g.scale = scale; g.shift = shift; g.act = act; g.maxpool2 = maxpool2;
+  g.R = R; g.ldr = ldr; g.C = y; g.ldc = ldy;
+  gemm_launch(g, st);
+}
+
+}  // namespace sat
+
+using namespace sat;
+
+struct sat_encoder {
+  sat_hparams hp;
+  DevPool pool;
+  Scratch ws;
+  float* emb = nullptr;
+  float *pre_w[2], *pre_b[2];
+  std::vector<Conv> bank;
+  Conv proj1, proj2;
+  float *adj_w = nullptr, *adj_b = nullptr;
+  std::vector<float*> hw_w, hw_b;  // [half][2*half] interleaved (H_u, T_u), bias [2*half]
+  float *lstm_wx = nullptr, *lstm_bx = nullptr, *lstm_wh = nullptr;
+  float *sap_w = nullptr, *sap_b = nullptr;
+  std::vector<MhaDev> hops;
+  int half = 0, cin = 0;
+};
+
+extern "C" int sat_encoder_create(const sat_hparams* hpp, const sat_tensor* weights, int32_t n_weights, sat_encoder** out) {
+  return guarded([&] {
+    SAT_REQUIRE(hpp && weights && out, "null argument");
+    const sat_hparams& hp = *hpp;
+    SAT_REQUIRE(hp.encoder_kind == SAT_ENC_ZONEOUT_V1 || hp.encoder_kind == SAT_ENC_SELF_ATTENTION_CBHG, "Unknown encoder");
+    Blob W(weights, n_weights);
+    auto* h = new sat_encoder();
+    std::unique_ptr<sat_encoder> guard(h);
+    h->hp = hp;
+    DevPool& pool = h->pool;
+    const int E = hp.embedding_dim;
+    SAT_REQUIRE(hp.encoder_prenet_units[0] > 0 && hp.encoder_prenet_units[1] > 0, "encoder prenet needs two layers");
+    h->emb = pool.upload(W.get("embedding", (int64_t)hp.num_symbols * E), (size_t)hp.num_symbols * E);
+    int d = E;
+    for (int i = 0; i < 2; ++i) {
+      const int u = hp.encoder_prenet_units[i];
+      const std::string P = "encoder/prenet/dense_" + std::to_string(i);
+      h->pre_w[i] = pool.upload(W.get(P + "/kernel", (int64_t)d * u), (size_t)d * u);
+      h->pre_b[i] = pool.upload(W.get(P + "/bias", u), u);
+      d = u;
+    }
+    h->cin = d;
+    h->half = hp.cbhg_out_units / 2;
+    SAT_REQUIRE(hp.cbhg_out_units % 2 == 0, "cbhg_out_units must be even");
+    SAT_REQUIRE(h->half == 128, "the BiLSTM kernel is built for 128 units per direction (cbhg_out_units=256), got %d", h->half);
+    const std::string C = "encoder/cbhg/";
+    for (int k = 1; k <= hp.max_filter_width; ++k)
+      h->bank.push_back(upload_conv_bn(pool, W, C + "conv1d_K" + std::to_string(k), k, d, hp.conv_channels));
+    h->proj1 = upload_conv_bn(pool, W, C + "proj1", 3, hp.max_filter_width * hp.conv_channels, hp.projection1_out_channels);
+    h->proj2 = upload_conv_bn(pool, W, C + "proj2", 3, hp.projection1_out_channels, hp.projection2_out_channels);
+    SAT_REQUIRE(hp.projection2_out_channels == d, "CBHG residual needs projection2_out_channels == prenet output units");
+    const int half = h->half;
+    if (hp.projection2_out_channels != half) {
+      h->adj_w = pool.upload(W.get(C + "adjustment/kernel", (int64_t)d * half), (size_t)d * half);
+      h->adj_b = pool.upload(W.get(C + "adjustment/bias", half), half);
+    }
+    for (int i = 0; i < hp.num_highway; ++i) {
+      const std::string P = C + "highway_" + std::to_string(i);
+      const float* wh = W.get(P + "/H/kernel", (int64_t)half * half);
+      const float* bh = W.get(P + "/H/bias", half);
+      const float* wt = W.get(P + "/T/kernel", (int64_t)half * half);
+      const float* bt = W.get(P + "/T/bias", half);
+      std::vector<float> w((size_t)half * 2 * half), b((size_t)2 * half);
+      for (int k = 0; k < half; ++k)
+        for (int u = 0; u < half; ++u) {
+          w[(size_t)k * 2 * half + 2 * u] = wh[(size_t)k * half + u];
+          w[(size_t)k * 2 * half + 2 * u + 1] = wt[(size_t)k * half + u];
+        }
+      for (int u = 0; u < half; ++u) { b[2 * u] = bh[u]; b[2 * u + 1] = bt[u]; }
+      h->hw_w.push_back(pool.upload(w));
+      h->hw_b.push_back(pool.upload(b));
+    }
+    // BiLSTM: TF kernel [in + U][4U] gate blocks i,j,f,o -> input part [in][dir][u][g], recurrent part [dir][k][u][g]
+    {
+      const int U = half, in = half;
+      std::vector<float> wx((size_t)in * 2 * U * 4), bx((size_t)2 * U * 4), wh((size_t)2 * U * U * 4);
+      const char* names[2] = {"lstm_fw", "lstm_bw"};
+      for (int dir = 0; dir < 2; ++dir) {
+        const float* k = W.get(C + names[dir] + "/kernel", (int64_t)(in + U) * 4 * U);
+        const float* b = W.get(C + names[dir] + "/bias", 4 * U);
+        for (int u = 0; u < U; ++u)
+          for (int g = 0; g < 4; ++g) {
+            const int src = g * U + u;
+            bx[((size_t)dir * U + u) * 4 + g] = b[src];
+            for (int kk = 0; kk < in; ++kk) wx[(size_t)kk * 2 * U * 4 + ((size_t)dir * U + u) * 4 + g] = k[(size_t)kk * 4 * U + src];
+            for (int kk = 0; kk < U; ++kk) wh[(((size_t)dir * U + kk) * U + u) * 4 + g] = k[(size_t)(in + kk) * 4 * U + src];
+          }
+      }
+      h->lstm_wx = pool.upload(wx);
+      h->lstm_bx = pool.upload(bx);
+      h->lstm_wh = pool.upload(wh);
+    }
+    if (hp.encoder_kind == SAT_ENC_SELF_ATTENTION_CBHG) {
+      const int Ds = hp.self_attention_out_units;
+      h->sap_w = pool.upload(W.get("encoder/sa_projection/kernel", (int64_t)hp.cbhg_out_units * Ds), (size_t)hp.cbhg_out_units * Ds);
+      h->sap_b = pool.upload(W.get("encoder/sa_projection/bias", Ds), Ds);
+      for (int i = 0; i < hp.self_attention_num_hop; ++i) {
+        const std::string P = "encoder/sa_" + std::to_string(i);
+        h->hops.push_back(mha_upload(pool, W, P + "/mha", P + "/transform", Ds, Ds, hp.self_attention_num_heads));
+      }
+    }
+    guard.release();
+    *out = h;
+  });
+}
+
+extern "C" void sat_encoder_destroy(sat_encoder* h) { delete h; }
+
+static int encoder_forward_impl(sat_encoder* h, const int64_t* ids, const float* embedded, const int64_t* lengths,
+                                int32_t B, int32_t T, float* lstm_out, float* sa_out, float* sa_probs, void* stream) {
+  return guarded([&] {
+    SAT_REQUIRE(h && (ids || embedded) && lengths && lstm_out && B >= 1 && T >= 1, "bad argument");
+    const sat_hparams& hp = h->hp;
+    const bool sa = hp.encoder_kind == SAT_ENC_SELF_ATTENTION_CBHG;
+    SAT_REQUIRE(sa || (!sa_out && !sa_probs), "ZoneoutEncoderV1 has no self-attention outputs");
+    SAT_REQUIRE(!sa || sa_out, "SelfAttentionCBHGEncoder needs sa_out");
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t rows = (size_t)B * T;
+    const int P0 = hp.encoder_prenet_units[0], P1 = hp.encoder_prenet_units[1];
+    const int Cb = hp.conv_channels, KW = hp.max_filter_width, half = h->half;
+    const int Ds = hp.self_attention_out_units;
+    // ---- workspace ----
+    size_t off = 0;
+    auto take = [&](size_t n) { size_t o = off; off += (n + 63) / 64 * 64; return o; };
+    const size_t o_p0 = take(rows * P0), o_p1 = take(rows * P1), o_bank = take(rows * (size_t)KW * Cb);
+    const size_t o_q1 = take(rows * hp.projection1_out_channels), o_q2 = take(rows * hp.projection2_out_channels);
+    const size_t o_ha = take(rows * half), o_hb = take(rows * half), o_xp = take(rows * 8 * (size_t)half);
+    size_t o_sa0 = 0, o_sa1 = 0, o_mha = 0;
+    if (sa) {
+      o_sa0 = take(rows * Ds);
+      o_sa1 = take(rows * Ds);
+      o_mha = take(mha_scratch_floats(h->hops.empty() ? MhaDev() : h->hops[0], (int64_t)rows));
+    }
+    float* ws = h->ws.get<float>(off);
+    // ---- embedding gather fused into prenet layer 0 ----
+    {
+      GemmArgs g;
+      g.X = ids ? h->emb : embedded; g.Bn = 1; g.T = (int)rows; g.Cin = hp.embedding_dim; g.ldx = hp.embedding_dim;
+      g.gather_ids = ids; g.gather_offset = 0;
+      g.W = h->pre_w[0]; g.N = P0; g.shift = h->pre_b[0]; g.act = ACT_RELU; g.C = ws + o_p0; g.ldc = P0;
+      gemm_launch(g, st);
+      GemmArgs g1;
+      g1.X = ws + o_p0; g1.Bn = 1; g1.T = (int)rows; g1.Cin = P0; g1.ldx = P0;
+      g1.W = h->pre_w[1]; g1.N = P1; g1.shift = h->pre_b[1]; g1.act = ACT_RELU; g1.C = ws + o_p1; g1.ldc = P1;
+      gemm_launch(g1, st);
+    }
+    // ---- conv bank -> concat buffer [rows][KW*Cb] ----
+    const int ldb = KW * Cb;
+    for (int k = 1; k <= KW; ++k) {
+      const Conv& c = h->bank[k - 1];
+      conv_bn_act_launch(ws + o_p1, B, T, P1, c.w, c.scale, c.shift, k, P1, Cb, ACT_RELU, 0, nullptr, 0,
+                         ws + o_bank + (size_t)(k - 1) * Cb, ldb, st);
+    }
+    // ---- maxpool (fused on load) + proj1, proj2 + residual ----
+    conv_bn_act_launch(ws + o_bank, B, T, ldb, h->proj1.w, h->proj1.scale, h->proj1.shift, 3, ldb, h->proj1.cout, ACT_RELU, 1,
+                       nullptr, 0, ws + o_q1, h->proj1.cout, st);
+    conv_bn_act_launch(ws + o_q1, B, T, h->proj1.cout, h->proj2.w, h->proj2.scale, h->proj2.shift, 3, h->proj1.cout,
+                       h->proj2.cout, ACT_NONE, 0, ws + o_p1, P1, ws + o_q2, h->proj2.cout, st);
+    const float* hw_in = ws + o_q2;
+    float* ping = ws + o_ha;
+    float* pong = ws + o_hb;
+    if (h->adj_w) {
+      GemmArgs g;
+      g.X = hw_in; g.Bn = 1; g.T = (int)rows; g.Cin = h->proj2.cout; g.ldx = h->proj2.cout;
+      g.W = h->adj_w; g.N = half; g.shift = h->adj_b; g.C = ping; g.ldc = half;
+      gemm_launch(g, st);
+      hw_in = ping;
+      std::swap(ping, pong);
+    }
+    for (size_t i = 0; i < h->hw_w.size(); ++i) {
+      GemmArgs g;
+      g.X = hw_in; g.Bn = 1; g.T = (int)rows; g.Cin = half; g.ldx = half;
+      g.W = h->hw_w[i]; g.N = 2 * half; g.shift = h->hw_b[i]; g.highway = 1; g.R = hw_in; g.ldr = half; g.C = ping; g.ldc = half;
+      gemm_launch(g, st);
+      hw_in = ping;
+      std::swap(ping, pong);
+    }
+    // ---- BiLSTM: time-batched input projection, then the recurrence ----
+    {
+      GemmArgs g;
+      g.X = hw_in; g.Bn = 1; g.T = (int)rows; g.Cin = half; g.ldx = half;
+      g.W = h->lstm_wx; g.N = 8 * half; g.shift = h->lstm_bx; g.C = ws + o_xp; g.ldc = 8 * half;
+      gemm_launch(g, st);
+      SAT_CUDA(cudaMemsetAsync(lstm_out, 0, rows * 2 * half * sizeof(float), st));
+      dim3 grid((unsigned)ceil_div(B, LSTM_ROWS), 2);
+      bilstm_kernel<128><<<grid, LSTM_NT, 0, st>>>(ws + o_xp, h->lstm_wh, (const long long*)lengths, B, T,
+                                                   hp.zoneout_factor_cell, hp.zoneout_factor_output, lstm_out);
+      count_launch();
+      check_launch("bilstm_kernel");
+    }
+    // ---- self-attention branch (modules/module.py:429-437); the padding mask is OFF in the reference ----
+    if (sa) {
+      GemmArgs g;
+      g.X = lstm_out; g.Bn = 1; g.T = (int)rows; g.Cin = 2 * half; g.ldx = 2 * half;
+      g.W = h->sap_w; g.N = Ds; g.shift = h->sap_b; g.C = ws + o_sa0; g.ldc = Ds;
+      gemm_launch(g, st);
+      const float* x = ws + o_sa0;
+      const int H = hp.self_attention_num_heads;
+      for (size_t i = 0; i < h->hops.size(); ++i) {
+        float* y = (i + 1 == h->hops.size()) ? sa_out : ws + ((i & 1) ? o_sa0 : o_sa1);
+        float* pr = sa_probs ? sa_probs + i * (size_t)H * B * T * T : nullptr;
+        sat_layer_forward(h->hops[i], x, B, T, 0, nullptr, y, pr, ws + o_mha, st);
+        x = y;
+      }
+      if (h->hops.empty()) SAT_CUDA(cudaMemcpyAsync(sa_out, x, rows * Ds * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    }
+  });
+}
+
+extern "C" int sat_encoder_forward(sat_encoder* h, const int64_t* ids, const int64_t* lengths, int32_t B, int32_t T,
+                                   float* lstm_out, float* sa_out, float* sa_probs, void* stream) {
+  if (!ids) { set_last_error("ids is null"); return SAT_EINVAL; }
+  return encoder_forward_impl(h, ids, nullptr, lengths, B, T, lstm_out, sa_out, sa_probs, stream);
+}
+
+extern "C" int sat_encoder_forward_embedded(sat_encoder* h, const float* embedded, const int64_t* lengths, int32_t B,
+                                            int32_t T, float* lstm_out, float* sa_out, float* sa_probs, void* stream) {
+  if (!embedded) { set_last_error("embedded is null"); return SAT_EINVAL; }
+  return encoder_forward_impl(h, nullptr, embedded, lengths, B, T, lstm_out, sa_out, sa_probs, stream);
+}

@@ -35,6 +35,7 @@ struct GemmDev {
   float* C; int ldc;
   const int64_t* row_lengths; const int64_t* gather_ids; long long gather_offset;
   int maxpool2; int vecA; int vecB; long long M;
+  int highway;
 };
 
 // source row pointer for global output row g at tap; nullptr when the tap falls in the zero padding
@@ -136,6 +137,26 @@ __global__ void __launch_bounds__(NT) gemm_kernel(GemmDev p) {
     }
   }
   // ---- epilogue ----
+  if (p.highway) {
+    // HighwayNet (tacotron2): columns are interleaved (2u = H_u, 2u+1 = T_u);
+    // y_u = relu(H) * sigmoid(T) + x_u * (1 - sigmoid(T)), x = R
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      long long g = m0 + ty * 8 + i;
+      if (g >= p.M) continue;
+#pragma unroll
+      for (int j = 0; j < 4; j += 2) {
+        int n = n0 + tx * 4 + j;
+        if (n + 1 >= p.N) continue;
+        const int u = n >> 1;
+        const float hh = fmaxf(acc[i][j] + __ldg(p.shift + n), 0.f);
+        const float tt = 1.f / (1.f + expf(-(acc[i][j + 1] + __ldg(p.shift + n + 1))));
+        const float x = p.R[g * p.ldr + u];
+        p.C[g * p.ldc + u] = hh * tt + x * (1.f - tt);
+      }
+    }
+    return;
+  }
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     long long g = m0 + ty * 8 + i;
@@ -163,6 +184,7 @@ void gemm_launch(const GemmArgs& a, cudaStream_t st) {
   p.R = a.R; p.ldr = a.ldr; p.C = a.C; p.ldc = a.ldc;
   p.row_lengths = a.row_lengths; p.gather_ids = a.gather_ids; p.gather_offset = a.gather_offset;
   p.maxpool2 = a.maxpool2;
+  p.highway = a.highway;
   p.M = (long long)a.Bn * a.T;
   p.vecA = ((a.ldx % 4) == 0) && ((((uintptr_t)a.X) & 15) == 0);
   p.vecB = ((a.N % 4) == 0) && ((((uintptr_t)a.W) & 15) == 0);

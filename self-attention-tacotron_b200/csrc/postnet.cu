@@ -1,0 +1,78 @@
+// postnet.cu -- sat_postnet_*: tacotron2 PostNetV2 (imported models/models.py:4; hparams hparams.py:146-150;
+// consumer predict_mel.py:50,60).  Its definition is absent from /root/reference; the form here is
+// n x [Conv1d(k, C, no bias) -> BN -> tanh (last layer: none)] -> Dense(num_mels) -> + input.
+#include "common.cuh"
+
+namespace sat {
+void conv_bn_act_launch(const float* x, int B, int T, int ldx, const float* w, const float* scale, const float* shift,
+                        int k, int cin, int cout, int act, int maxpool2, const float* R, int ldr, float* y, int ldy,
+                        cudaStream_t st);
+}
+using namespace sat;
+
+struct sat_postnet {
+  sat_hparams hp;
+  DevPool pool;
+  Scratch ws;
+  std::vector<float*> w, scale, shift;
+  float *pw = nullptr, *pb = nullptr;
+};
+
+extern "C" int sat_postnet_create(const sat_hparams* hpp, const sat_tensor* weights, int32_t n_weights, sat_postnet** out) {
+  return guarded([&] {
+    SAT_REQUIRE(hpp && weights && out, "null argument");
+    const sat_hparams& hp = *hpp;
+    SAT_REQUIRE(hp.num_postnet_layers >= 1, "post-net needs at least one layer");
+    Blob W(weights, n_weights);
+    auto* h = new sat_postnet();
+    std::unique_ptr<sat_postnet> guard(h);
+    h->hp = hp;
+    const int M = hp.num_mels, C = hp.postnet_channels, k = hp.postnet_kernel_size;
+    for (int i = 0; i < hp.num_postnet_layers; ++i) {
+      const std::string P = "postnet/conv_" + std::to_string(i);
+      const int cin = i == 0 ? M : C;
+      h->w.push_back(h->pool.upload(W.get(P + "/kernel", (int64_t)k * cin * C), (size_t)k * cin * C));
+      const float* gamma = W.get(P + "/bn/gamma", C);
+      const float* beta = W.get(P + "/bn/beta", C);
+      const float* mean = W.get(P + "/bn/mean", C);
+      const float* var = W.get(P + "/bn/var", C);
+      std::vector<float> sc(C), sh(C);
+      for (int c = 0; c < C; ++c) {
+        sc[c] = gamma[c] / sqrtf(var[c] + 1e-3f);
+        sh[c] = beta[c] - mean[c] * sc[c];
+      }
+      h->scale.push_back(h->pool.upload(sc));
+      h->shift.push_back(h->pool.upload(sh));
+    }
+    h->pw = h->pool.upload(W.get("postnet/projection/kernel", (int64_t)C * M), (size_t)C * M);
+    h->pb = h->pool.upload(W.get("postnet/projection/bias", M), M);
+    guard.release();
+    *out = h;
+  });
+}
+
+extern "C" void sat_postnet_destroy(sat_postnet* h) { delete h; }
+
+extern "C" int sat_postnet_forward(sat_postnet* h, const float* mel, int32_t B, int32_t T, float* mel_postnet, void* stream) {
+  return guarded([&] {
+    SAT_REQUIRE(h && mel && mel_postnet && B >= 1 && T >= 1, "bad argument");
+    const sat_hparams& hp = h->hp;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int M = hp.num_mels, C = hp.postnet_channels, k = hp.postnet_kernel_size, n = hp.num_postnet_layers;
+    const size_t rows = (size_t)B * T;
+    float* ws = h->ws.get<float>(2 * rows * C);
+    float* buf[2] = {ws, ws + rows * C};
+    const float* x = mel;
+    int ldx = M, cin = M;
+    for (int i = 0; i < n; ++i) {
+      conv_bn_act_launch(x, B, T, ldx, h->w[i], h->scale[i], h->shift[i], k, cin, C, i < n - 1 ? ACT_TANH : ACT_NONE, 0,
+                         nullptr, 0, buf[i & 1], C, st);
+      x = buf[i & 1];
+      ldx = cin = C;
+    }
+    GemmArgs g;
+    g.X = x; g.Bn = 1; g.T = (int)rows; g.Cin = C; g.ldx = C;
+    g.W = h->pw; g.N = M; g.shift = h->pb; g.R = mel; g.ldr = M; g.C = mel_postnet; g.ldc = M;
+    gemm_launch(g, st);
+  });
+}
