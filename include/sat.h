@@ -163,6 +163,9 @@ int sat_embedding_lookup(const float* table_host, int64_t table_rows, int32_t di
                          const int64_t* ids, int64_t n, float* out, void* stream);
 /* cycles per phase accumulated by CTA 0 of the persistent decoder kernel (profiling aid); out16 host */
 int sat_decoder_profile(sat_decoder* h, int64_t* out16, int32_t reset);
+/* device time (ms) of the persistent decoder kernel of the last sat_decoder_run, from CUDA events recorded on the
+ * launching stream around that launch; blocks until the kernel has finished */
+int sat_decoder_kernel_ms(sat_decoder* h, float* ms);
 
 /* ---- post-net --------------------------------------------------------- */
 int sat_postnet_create(const sat_hparams* hp, const sat_tensor* weights, int32_t n_weights, sat_postnet** out);

@@ -63,6 +63,7 @@ def lib():
         L.sat_decoder_step_bytes.restype = C.c_double
         L.sat_decoder_step_bytes.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32]
         for n in ("sat_encoder_destroy", "sat_decoder_destroy", "sat_postnet_destroy", "sat_launch_count_reset"):
+            getattr(L, n).argtypes = [C.c_void_p] if n != "sat_launch_count_reset" else []
             if hasattr(L, n):
                 getattr(L, n).restype = None
         _lib = L

@@ -165,9 +165,9 @@ MhaDev mha_upload(DevPool& pool, const Blob& W, const std::string& mha_prefix, c
 size_t mha_scratch_floats(const MhaDev& m, int64_t rows);
 // out [B,T,D] = output Dense(attention(x)); probs [B,H,T,T] or null; pad_lengths != null enables the padding mask
 void mha_forward(const MhaDev& m, const float* x, int B, int T, int causal, const int64_t* pad_lengths,
-                 float* out, float* probs, float* scratch, cudaStream_t st);
+                 float* out, float* probs, float* scratch, cudaStream_t st, int head_major = 0);
 // SelfAttentionTransformer: out = x + tanh(Dense(mha(x)))   (needs Din == D and a transform layer)
 void sat_layer_forward(const MhaDev& m, const float* x, int B, int T, int causal, const int64_t* pad_lengths,
-                       float* out, float* probs, float* scratch, cudaStream_t st);
+                       float* out, float* probs, float* scratch, cudaStream_t st, int head_major = 0);
 
 }  // namespace sat

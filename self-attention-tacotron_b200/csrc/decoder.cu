@@ -107,6 +107,12 @@ struct sat_decoder {
   unsigned* barrier = nullptr;
   long long* prof = nullptr;
   size_t max_dyn_smem = 0;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;  // bracket the persistent launch of the last run
+  int last_B = 0, last_T = 0, last_S = 0;
+  ~sat_decoder() {
+    if (ev0) cudaEventDestroy(ev0);
+    if (ev1) cudaEventDestroy(ev1);
+  }
 };
 
 extern "C" int sat_decoder_create(const sat_hparams* hpp, const sat_tensor* weights, int32_t n_weights, sat_decoder** out) {
@@ -238,6 +244,8 @@ extern "C" int sat_decoder_create(const sat_hparams* hpp, const sat_tensor* weig
     h->grid = h->sm_count;
     h->barrier = pool.alloc<unsigned>(1);
     h->prof = pool.alloc<long long>(N_PROF);
+    SAT_CUDA(cudaEventCreate(&h->ev0));
+    SAT_CUDA(cudaEventCreate(&h->ev1));
     guard.release();
     *out = h;
   });
@@ -396,8 +404,11 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
     }
 
     void* args[] = {&p};
+    SAT_CUDA(cudaEventRecord(h->ev0, st));
     SAT_CUDA(cudaLaunchCooperativeKernel((const void*)decoder_persistent_kernel, dim3(h->grid), dim3(NT), args,
                                          smem_floats * sizeof(float), st));
+    SAT_CUDA(cudaEventRecord(h->ev1, st));
+    h->last_B = B; h->last_T = T; h->last_S = S;
     count_launch();
     if (io.sample_ids) {
       const long long rows = (long long)B * S * p.r;
@@ -415,5 +426,15 @@ extern "C" int sat_decoder_profile(sat_decoder* h, int64_t* out16, int32_t reset
     SAT_CUDA(cudaDeviceSynchronize());
     SAT_CUDA(cudaMemcpy(out16, h->prof, sizeof(long long) * N_PROF, cudaMemcpyDeviceToHost));
     if (reset) SAT_CUDA(cudaMemset(h->prof, 0, sizeof(long long) * N_PROF));
+  });
+}
+
+// device time of the persistent kernel of the last sat_decoder_run (CUDA events on the launching stream); blocks
+// until that kernel has finished
+extern "C" int sat_decoder_kernel_ms(sat_decoder* h, float* ms) {
+  return guarded([&] {
+    SAT_REQUIRE(h && ms, "null argument");
+    SAT_CUDA(cudaEventSynchronize(h->ev1));
+    SAT_CUDA(cudaEventElapsedTime(ms, h->ev0, h->ev1));
   });
 }

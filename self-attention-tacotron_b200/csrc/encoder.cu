@@ -329,7 +329,7 @@ static int encoder_forward_impl(sat_encoder* h, const int64_t* ids, const float*
       for (size_t i = 0; i < h->hops.size(); ++i) {
         float* y = (i + 1 == h->hops.size()) ? sa_out : ws + ((i & 1) ? o_sa0 : o_sa1);
         float* pr = sa_probs ? sa_probs + i * (size_t)H * B * T * T : nullptr;
-        sat_layer_forward(h->hops[i], x, B, T, 0, nullptr, y, pr, ws + o_mha, st);
+        sat_layer_forward(h->hops[i], x, B, T, 0, nullptr, y, pr, ws + o_mha, st, 1);
         x = y;
       }
       if (h->hops.empty()) SAT_CUDA(cudaMemcpyAsync(sa_out, x, rows * Ds * sizeof(float), cudaMemcpyDeviceToDevice, st));

@@ -30,7 +30,8 @@ __device__ __forceinline__ float wmax(float v) {
 // grid = (ceil(T / MHA_WARPS), B*H); dynamic smem = MHA_WARPS * (Tpad + dh) floats.
 __global__ void __launch_bounds__(MHA_WARPS * 32) mha_attn_kernel(const float* __restrict__ qkv, int T, int D, int H,
                                                                   int causal, const long long* __restrict__ lengths,
-                                                                  float* __restrict__ ctx, float* __restrict__ probs) {
+                                                                  float* __restrict__ ctx, float* __restrict__ probs,
+                                                                  int head_major) {
   extern __shared__ __align__(16) float sm[];
   const int dh = D / H, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int b = blockIdx.y / H, h = blockIdx.y % H;
@@ -77,7 +78,8 @@ __global__ void __launch_bounds__(MHA_WARPS * 32) mha_attn_kernel(const float* _
   const float inv = 1.f / sum;
   __syncwarp();
   if (probs) {
-    float* pr = probs + (((size_t)b * H + h) * T + i) * T;
+    // [B][H][T][T], or [H][B][T][T] when head_major (one tensor per head, models/models.py:104)
+    float* pr = probs + ((head_major ? (size_t)h * gridDim.y / H + b : (size_t)b * H + h) * T + i) * T;
     for (int j = lane; j < T; j += 32) pr[j] = j < nk ? sc[j] * inv : 0.f;
   }
   float* out = ctx + ((size_t)b * T + i) * D + (size_t)h * dh;
@@ -134,7 +136,7 @@ MhaDev mha_upload(DevPool& pool, const Blob& W, const std::string& P, const std:
 size_t mha_scratch_floats(const MhaDev& m, int64_t rows) { return (size_t)rows * (size_t)(3 * m.D + 2 * m.D) + 64; }
 
 static void attention_core(const MhaDev& m, const float* x, int B, int T, int causal, const int64_t* pad_lengths,
-                           float* ctx, float* qkv, float* probs, cudaStream_t st) {
+                           float* ctx, float* qkv, float* probs, int head_major, cudaStream_t st) {
   GemmArgs g;
   g.X = x; g.Bn = 1; g.T = B * T; g.Cin = m.Din; g.ldx = m.Din;
   g.W = m.Wqkv; g.N = 3 * m.D; g.shift = m.bqkv; g.C = qkv; g.ldc = 3 * m.D;
@@ -144,17 +146,18 @@ static void attention_core(const MhaDev& m, const float* x, int B, int T, int ca
   SAT_REQUIRE(smem <= 200 * 1024, "sequence too long for the SIMT attention kernel (T=%d)", T);
   SAT_CUDA(cudaFuncSetAttribute(mha_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   dim3 grid((unsigned)ceil_div(T, MHA_WARPS), (unsigned)(B * m.H));
-  mha_attn_kernel<<<grid, MHA_WARPS * 32, smem, st>>>(qkv, T, m.D, m.H, causal, (const long long*)pad_lengths, ctx, probs);
+  mha_attn_kernel<<<grid, MHA_WARPS * 32, smem, st>>>(qkv, T, m.D, m.H, causal, (const long long*)pad_lengths, ctx, probs,
+                                                       head_major);
   count_launch();
   check_launch("mha_attn_kernel");
 }
 
 void mha_forward(const MhaDev& m, const float* x, int B, int T, int causal, const int64_t* pad_lengths,
-                 float* out, float* probs, float* scratch, cudaStream_t st) {
+                 float* out, float* probs, float* scratch, cudaStream_t st, int head_major) {
   const size_t rows = (size_t)B * T;
   float* qkv = scratch;
   float* ctx = qkv + rows * 3 * m.D;
-  attention_core(m, x, B, T, causal, pad_lengths, ctx, qkv, probs, st);
+  attention_core(m, x, B, T, causal, pad_lengths, ctx, qkv, probs, head_major, st);
   GemmArgs g;
   g.X = ctx; g.Bn = 1; g.T = (int)rows; g.Cin = m.D; g.ldx = m.D;
   g.W = m.Wo; g.N = m.D; g.shift = m.bo; g.C = out; g.ldc = m.D;
@@ -162,11 +165,11 @@ void mha_forward(const MhaDev& m, const float* x, int B, int T, int causal, cons
 }
 
 void sat_layer_forward(const MhaDev& m, const float* x, int B, int T, int causal, const int64_t* pad_lengths,
-                       float* out, float* probs, float* scratch, cudaStream_t st) {
+                       float* out, float* probs, float* scratch, cudaStream_t st, int head_major) {
   SAT_REQUIRE(m.Wt && m.Din == m.D, "SelfAttentionTransformer needs a transform layer and Din == D");
   const size_t rows = (size_t)B * T;
   float* a = scratch + rows * 4 * m.D;
-  mha_forward(m, x, B, T, causal, pad_lengths, a, probs, scratch, st);
+  mha_forward(m, x, B, T, causal, pad_lengths, a, probs, scratch, st, head_major);
   GemmArgs g;
   g.X = a; g.Bn = 1; g.T = (int)rows; g.Cin = m.D; g.ldx = m.D;
   g.W = m.Wt; g.N = m.D; g.shift = m.bt; g.act = ACT_TANH; g.R = x; g.ldr = m.D; g.C = out; g.ldc = m.D;

@@ -89,7 +89,176 @@ class DecoderHandle:
     def step_bytes(self, B, T, avg_cache_len=0):
         return lib().sat_decoder_step_bytes(self._h, B, T, avg_cache_len)
 
+    def kernel_ms(self):
+        ms = C.c_float()
+        check(lib().sat_decoder_kernel_ms(self._h, C.byref(ms)))
+        return ms.value
+
     def profile(self, reset=True):
         out = (C.c_int64 * 16)()
         check(lib().sat_decoder_profile(self._h, out, int(reset)))
         return list(out)
+
+
+class EncoderHandle:
+    """sat_encoder_* (ZoneoutEncoderV1 modules/module.py:336-339, SelfAttentionCBHGEncoder :425-438,
+    embedding lookup models/models.py:28,54)."""
+
+    def __init__(self, hp, weights):
+        self.hp = hp
+        self._h = C.c_void_p()
+        keep = {k: v for k, v in weights.items() if k.startswith("encoder/") or k == "embedding"}
+        arr, n, _keep = _lib.tensor_list(keep)
+        s = _lib.make_hparams(hp)
+        check(lib().sat_encoder_create(C.byref(s), arr, n, C.byref(self._h)))
+        self.self_attention = hp.encoder == "SelfAttentionCBHGEncoder"
+
+    def __del__(self):
+        if getattr(self, "_h", None) and self._h.value:
+            lib().sat_encoder_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def forward(self, ids_or_embedded, lengths, want_probs=False, stream=None):
+        hp = self.hp
+        x = ids_or_embedded
+        _need_cuda(x, lengths)
+        dev = x.device
+        B, T = x.shape[0], x.shape[1]
+        lengths = lengths.to(device=dev, dtype=torch.int64).contiguous()
+        lstm_out = torch.empty((B, T, hp.cbhg_out_units), device=dev, dtype=torch.float32)
+        sa_out = probs = None
+        if self.self_attention:
+            sa_out = torch.empty((B, T, hp.self_attention_out_units), device=dev, dtype=torch.float32)
+            if want_probs:
+                probs = torch.empty((hp.self_attention_num_hop * hp.self_attention_num_heads, B, T, T),
+                                    device=dev, dtype=torch.float32)
+        if x.dtype in (torch.int64, torch.int32):
+            x = x.to(torch.int64).contiguous()
+            check(lib().sat_encoder_forward(self._h, ptr(x), ptr(lengths), B, T, ptr(lstm_out), ptr(sa_out), ptr(probs),
+                                            stream_ptr(stream)))
+        else:
+            x = x.contiguous().float()
+            if x.shape[2] != hp.embedding_dim:
+                raise ValueError(f"encoder input depth {x.shape[2]} != embedding_dim {hp.embedding_dim}")
+            check(lib().sat_encoder_forward_embedded(self._h, ptr(x), ptr(lengths), B, T, ptr(lstm_out), ptr(sa_out),
+                                                     ptr(probs), stream_ptr(stream)))
+        self._keep = (x, lengths)
+        return lstm_out, sa_out, probs
+
+
+class PostnetHandle:
+    """sat_postnet_* (tacotron2 PostNetV2, models/models.py:4)."""
+
+    def __init__(self, hp, weights):
+        self.hp = hp
+        self._h = C.c_void_p()
+        arr, n, _keep = _lib.tensor_list({k: v for k, v in weights.items() if k.startswith("postnet/")})
+        s = _lib.make_hparams(hp)
+        check(lib().sat_postnet_create(C.byref(s), arr, n, C.byref(self._h)))
+
+    def __del__(self):
+        if getattr(self, "_h", None) and self._h.value:
+            lib().sat_postnet_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def forward(self, mel, stream=None):
+        _need_cuda(mel)
+        mel = mel.contiguous().float()
+        out = torch.empty_like(mel)
+        check(lib().sat_postnet_forward(self._h, ptr(mel), mel.shape[0], mel.shape[1], ptr(out), stream_ptr(stream)))
+        self._keep = mel
+        return out
+
+
+# ---- stand-alone module entry points (unit parity; each call uploads its weights) ----
+
+def dense_forward(x, kernel, bias=None, act=None, stream=None):
+    """tf.layers.Dense on the last axis through sat_dense_forward."""
+    import numpy as np
+    _need_cuda(x)
+    x = x.contiguous().float()
+    K, N = kernel.shape
+    if x.shape[-1] != K:
+        raise ValueError(f"Dense: input depth {x.shape[-1]} != kernel rows {K}")
+    k = np.ascontiguousarray(kernel, dtype=np.float32)
+    b = np.ascontiguousarray(bias, dtype=np.float32) if bias is not None else None
+    y = torch.empty(x.shape[:-1] + (N,), device=x.device, dtype=torch.float32)
+    rows = x.numel() // K
+    check(lib().sat_dense_forward(C.c_void_p(k.ctypes.data), C.c_void_p(b.ctypes.data if b is not None else 0),
+                                  K, N, _lib.ACT[act], ptr(x), C.c_int64(rows), ptr(y), stream_ptr(stream)))
+    return y
+
+
+def embedding_lookup(table, ids, index_offset=0, stream=None):
+    import numpy as np
+    _need_cuda(ids)
+    t = np.ascontiguousarray(table, dtype=np.float32)
+    ids = ids.to(torch.int64).contiguous()
+    out = torch.empty(tuple(ids.shape) + (t.shape[1],), device=ids.device, dtype=torch.float32)
+    check(lib().sat_embedding_lookup(C.c_void_p(t.ctypes.data), C.c_int64(t.shape[0]), t.shape[1],
+                                     C.c_int64(index_offset), ptr(ids), C.c_int64(ids.numel()), ptr(out),
+                                     stream_ptr(stream)))
+    return out
+
+
+def mha_forward(weights, prefix, x, num_heads, model_dim, causal=False, lengths=None, want_probs=True, stream=None):
+    """MultiHeadAttention with K=V=Q=x (SelfAttention, modules/self_attention.py:131-144)."""
+    _need_cuda(x, lengths)
+    x = x.contiguous().float()
+    B, T, Din = x.shape
+    arr, n, _keep = _lib.tensor_list({k: v for k, v in weights.items() if k.startswith(prefix + "/")})
+    out = torch.empty((B, T, model_dim), device=x.device, dtype=torch.float32)
+    probs = torch.empty((B, num_heads, T, T), device=x.device, dtype=torch.float32) if want_probs else None
+    if lengths is not None:
+        lengths = lengths.to(device=x.device, dtype=torch.int64).contiguous()
+    check(lib().sat_mha_forward(arr, n, prefix.encode(), ptr(x), B, T, Din, model_dim, num_heads, int(causal),
+                                ptr(lengths), ptr(out), ptr(probs), stream_ptr(stream)))
+    return out, probs
+
+
+def sat_forward(weights, prefix, x, num_heads, causal=False, want_probs=True, stream=None):
+    """SelfAttentionTransformer (modules/module.py:363-371): x + tanh(Dense(SelfAttention(x)))."""
+    _need_cuda(x)
+    x = x.contiguous().float()
+    B, T, D = x.shape
+    arr, n, _keep = _lib.tensor_list({k: v for k, v in weights.items() if k.startswith(prefix + "/")})
+    out = torch.empty_like(x)
+    probs = torch.empty((B, num_heads, T, T), device=x.device, dtype=torch.float32) if want_probs else None
+    check(lib().sat_sat_forward(arr, n, prefix.encode(), ptr(x), B, T, D, num_heads, int(causal), ptr(out), ptr(probs),
+                                stream_ptr(stream)))
+    return out, probs
+
+
+def attention_prepare(weights, prefix, memory, lengths, num_units, stream=None):
+    """keys = (memory * mask) @ memory_layer, values = memory * mask (TF BahdanauAttention)."""
+    _need_cuda(memory, lengths)
+    memory = memory.contiguous().float()
+    B, T, Dm = memory.shape
+    lengths = lengths.to(device=memory.device, dtype=torch.int64).contiguous()
+    arr, n, _keep = _lib.tensor_list({k: v for k, v in weights.items() if k.startswith(prefix + "/")})
+    keys = torch.empty((B, T, num_units), device=memory.device, dtype=torch.float32)
+    values = torch.empty_like(memory)
+    check(lib().sat_attention_prepare(arr, n, prefix.encode(), ptr(memory), ptr(lengths), B, T, Dm, num_units,
+                                      ptr(keys), ptr(values), stream_ptr(stream)))
+    return keys, values
+
+
+def attention_step(weights, prefix, kind, options, keys, values, lengths, query, state, stream=None):
+    """One AttentionMechanism.__call__ (+ context) through sat_attention_step.
+    state = dict(alignments [B,T], alpha [B,T] | None, u [B] | None) -- updated IN PLACE."""
+    _need_cuda(keys, values, lengths, query)
+    B, T, U = keys.shape
+    Dv, A = values.shape[2], query.shape[1]
+    query = query.contiguous().float()
+    lengths = lengths.to(device=keys.device, dtype=torch.int64).contiguous()
+    arr, n, _keep = _lib.tensor_list({k: v for k, v in weights.items() if k.startswith(prefix + "/")})
+    align = torch.empty((B, T), device=keys.device, dtype=torch.float32)
+    ctx = torch.empty((B, Dv), device=keys.device, dtype=torch.float32)
+    check(lib().sat_attention_step(arr, n, prefix.encode(), _lib.SAT_ATT[kind], B, T, U, Dv, A,
+                                   int(options.get("attention_kernel", 1)), int(options.get("attention_filters", 1)),
+                                   int(bool(options.get("cumulative_weights", False))),
+                                   int(bool(options.get("use_transition_agent", False))),
+                                   ptr(keys), ptr(values), ptr(lengths), ptr(query),
+                                   ptr(state.get("alignments")), ptr(state.get("alpha")), ptr(state.get("u")),
+                                   ptr(align), ptr(ctx), stream_ptr(stream)))
+    return align, ctx

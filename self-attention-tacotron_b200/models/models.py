@@ -1,0 +1,140 @@
+"""The wiring of /root/reference/models/models.py:28-148 (embedding -> encoder -> speaker embedding ->
+decoder -> forced-alignment second pass -> post-net) as a plain callable, without tf.estimator.
+
+``SynthesisModel.predict`` is what ``estimator.predict`` yields per batch in the reference
+(models/models.py:252-277 / predict_mel.py:49-54): mel, mel_postnet, alignments, ..."""
+import torch
+
+from ..modules.module import (ZoneoutEncoderV1, SelfAttentionCBHGEncoder, ExtendedDecoder, DualSourceDecoder,
+                              DualSourceTransformerDecoder, PostNetV2, Embedding)
+from .attention_factories import (attention_factory, dual_source_attention_factory,
+                                  force_alignment_attention_factory, force_alignment_dual_source_attention_factory)
+
+
+def encoder_factory(params, is_training, weights):
+    """models/models.py:325-346 (+ ZoneoutEncoderV1 for the baseline-Tacotron JSONs)."""
+    if params.encoder == "SelfAttentionCBHGEncoder":
+        return SelfAttentionCBHGEncoder(is_training, cbhg_out_units=params.cbhg_out_units,
+                                        conv_channels=params.conv_channels, max_filter_width=params.max_filter_width,
+                                        projection1_out_channels=params.projection1_out_channels,
+                                        projection2_out_channels=params.projection2_out_channels,
+                                        num_highway=params.num_highway,
+                                        self_attention_out_units=params.self_attention_out_units,
+                                        self_attention_num_heads=params.self_attention_num_heads,
+                                        self_attention_num_hop=params.self_attention_num_hop,
+                                        prenet_out_units=params.encoder_prenet_out_units,
+                                        drop_rate=params.encoder_prenet_drop_rate,
+                                        zoneout_factor_cell=params.zoneout_factor_cell,
+                                        zoneout_factor_output=params.zoneout_factor_output,
+                                        self_attention_drop_rate=params.self_attention_drop_rate, weights=weights)
+    if params.encoder == "ZoneoutEncoderV1":
+        return ZoneoutEncoderV1(is_training, cbhg_out_units=params.cbhg_out_units, conv_channels=params.conv_channels,
+                                max_filter_width=params.max_filter_width,
+                                projection1_out_channels=params.projection1_out_channels,
+                                projection2_out_channels=params.projection2_out_channels,
+                                num_highway=params.num_highway, prenet_out_units=params.encoder_prenet_out_units,
+                                drop_rate=params.encoder_prenet_drop_rate, use_zoneout=True,
+                                zoneout_factor_cell=params.zoneout_factor_cell,
+                                zoneout_factor_output=params.zoneout_factor_output, weights=weights)
+    raise ValueError(f"Unknown encoder: {params.encoder}")
+
+
+def decoder_factory(params, weights):
+    """models/models.py:349-368 (+ ExtendedDecoder / DualSourceDecoder)."""
+    kw = dict(prenet_out_units=params.decoder_prenet_out_units, drop_rate=params.decoder_prenet_drop_rate,
+              attention_out_units=params.attention_out_units, decoder_version=params.decoder_version,
+              decoder_out_units=params.decoder_out_units, num_mels=params.num_mels,
+              outputs_per_step=params.outputs_per_step, max_iters=params.max_iters, n_feed_frame=params.n_feed_frame,
+              zoneout_factor_cell=params.zoneout_factor_cell, zoneout_factor_output=params.zoneout_factor_output,
+              weights=weights)
+    if params.decoder == "DualSourceTransformerDecoder":
+        return DualSourceTransformerDecoder(self_attention_out_units=params.decoder_self_attention_out_units,
+                                            self_attention_num_heads=params.decoder_self_attention_num_heads,
+                                            self_attention_num_hop=params.decoder_self_attention_num_hop,
+                                            self_attention_drop_rate=params.decoder_self_attention_drop_rate, **kw)
+    if params.decoder == "DualSourceDecoder":
+        return DualSourceDecoder(**kw)
+    if params.decoder == "ExtendedDecoder":
+        return ExtendedDecoder(**kw)
+    raise ValueError(f"Unknown decoder: {params.decoder}")
+
+
+class SynthesisModel:
+    """PREDICT / EVAL branch of model_fn (models/models.py:23-148, 252-277)."""
+
+    def __init__(self, params, weights):
+        self.params, self.weights = params, weights
+        self.encoder = encoder_factory(params, False, weights)
+        self.decoder = decoder_factory(params, weights)
+        self.dual = params.decoder != "ExtendedDecoder"
+        self.speaker_embedding = None
+        if params.use_speaker_embedding:
+            self.speaker_embedding = Embedding(params.num_speakers, params.speaker_embedding_dim,
+                                               index_offset=params.speaker_embedding_offset, weights=weights,
+                                               name="speaker_embedding")
+        self.postnet = PostNetV2(params.num_mels, params.num_postnet_v2_layers, params.postnet_v2_kernel_size,
+                                 params.postnet_v2_out_channels, False, weights=weights) if params.use_postnet_v2 else None
+
+    def predict(self, source, source_length, target=None, speaker_id=None, is_validation=False,
+                teacher_forcing=False, want_encoder_alignments=False):
+        """source int64 ids [B,T_enc] (device), source_length [B]; target [B,T_dec,M] for validation /
+        forced alignment.  Returns a dict of device tensors."""
+        p = self.params
+        if self.dual:
+            lstm_out, sa_out, enc_align = self.encoder(source, input_lengths=source_length,
+                                                       want_alignments=want_encoder_alignments)
+            sources = (lstm_out, sa_out)
+        else:
+            sources = self.encoder(source, input_lengths=source_length)
+            enc_align = []
+        spk = None
+        if self.speaker_embedding is not None:
+            ids = speaker_id
+            if p.speaker_for_synthesis > -1:
+                ids = torch.full_like(speaker_id, p.speaker_for_synthesis)
+            spk = self.speaker_embedding(ids)
+            if p.speaker_embedd_to_decoder:
+                raise NotImplementedError("speaker_embedd_to_decoder (tile+concat onto encoder outputs)")
+        spk_prenet = spk if p.speaker_embedd_to_prenet else None
+        forced = p.use_forced_alignment_mode
+        kw = dict(speaker_embed=spk_prenet, is_training=False, is_validation=is_validation or forced,
+                  teacher_forcing=teacher_forcing or forced, target=target,
+                  apply_dropout_on_inference=p.apply_dropout_on_inference)
+        if self.dual:
+            a1, a2 = dual_source_attention_factory(p)
+            res = self.decoder(sources, attention1_fn=a1, attention2_fn=a2, memory_sequence_length=source_length,
+                               memory2_sequence_length=source_length, **kw)
+        else:
+            res = self.decoder(sources, attention_fn=attention_factory(p), memory_sequence_length=source_length, **kw)
+        state = res[-1]
+        if forced:
+            # second pass: replay pass-1 alignments, feed back own outputs (models/models.py:118-134)
+            kw.update(is_validation=True, teacher_forcing=False)
+            ta = tuple(state.alignment_history)
+            if self.dual:
+                f1, f2 = force_alignment_dual_source_attention_factory(p)
+                res = self.decoder(sources, attention1_fn=f1, attention2_fn=f2, memory_sequence_length=source_length,
+                                   memory2_sequence_length=source_length, teacher_alignments=ta, **kw)
+            else:
+                res = self.decoder(sources, attention_fn=force_alignment_attention_factory(p),
+                                   memory_sequence_length=source_length, teacher_alignments=ta[0], **kw)
+            state = res[-1]
+        mel, stop = res[0], res[1]
+        out = {"mel": mel, "stop_token": stop, "stop_steps": state.stop_steps, "n_steps": state.n_steps,
+               "source": source, "encoder_alignments": enc_align}
+        # alignments arranged (B, T_memory, T_query) like models/models.py:104-115
+        for i, a in enumerate(state.alignment_history):
+            out["alignment" if i == 0 else f"alignment{i + 1}"] = a.transpose(1, 2)
+        if len(res) == 4:
+            out["predicted_samples"] = res[2]
+        if self.postnet is not None:
+            out["mel_postnet"] = self.postnet(mel)
+        return out
+
+
+def tacotron_model_factory(hparams, weights):
+    """models/models.py:371-378: model selection by name; returns the synthesis callable."""
+    if hparams.tacotron_model in ("DualSourceSelfAttentionTacotronModel", "ExtendedTacotronV1Model",
+                                  "DualSourceTacotronModel"):
+        return SynthesisModel(hparams, weights)
+    raise ValueError(f"Unknown Tacotron model: {hparams.tacotron_model}")

@@ -1,0 +1,107 @@
+"""predict_mel entry point: the surface of /root/reference/predict_mel.py (``PredictedMel`` fields :28-33,
+``predict`` :36-74, raw little-endian float32 ``.mfbsp`` output :58-62) fed by the CUDA hot path.
+
+Differences from the reference: batched (the reference forces batch_size=1, :43-44), utterances are
+length-bucketed and sharded over the GPUs of one box (``sharding.py``), inputs arrive as arrays
+(the TFRecord reader is a "next" row), and no PNG plot is written (no plotting stack)."""
+import os
+from collections import namedtuple
+
+import numpy as np
+import torch
+
+from .models import tacotron_model_factory
+from .sharding import make_buckets
+
+
+class PredictedMel(
+    namedtuple("PredictedMel",
+               ["id", "key", "predicted_mel", "predicted_mel_postnet", "predicted_mel_width", "predicted_target_length",
+                "ground_truth_mel", "alignment", "alignment2", "alignment3", "alignment4", "alignment5", "alignment6",
+                "source", "text", "accent_type"])):
+    pass
+
+
+class Utterance(namedtuple("Utterance", ["id", "key", "source", "text", "mel", "speaker_id"])):
+    """One synthesis request: ``source`` int64 symbol ids [T_enc]; ``mel`` optional ground truth [T_dec, M]."""
+
+    def __new__(cls, id, key, source, text="", mel=None, speaker_id=None):
+        return super().__new__(cls, id, key, np.asarray(source, dtype=np.int64), text, mel, speaker_id)
+
+
+def _pad_batch(utts, hp, device):
+    B = len(utts)
+    T = max(len(u.source) for u in utts)
+    ids = np.zeros((B, T), dtype=np.int64)  # batch padding id 0 (datasets/ljspeech/dataset.py:268)
+    lengths = np.zeros(B, dtype=np.int64)
+    for i, u in enumerate(utts):
+        ids[i, :len(u.source)] = u.source
+        lengths[i] = len(u.source)
+    target = None
+    if all(u.mel is not None for u in utts):
+        r = hp.outputs_per_step
+        Td = max(u.mel.shape[0] for u in utts)
+        Td = (Td + r - 1) // r * r
+        # r-padding with silence (datasets/ljspeech/dataset.py:134-135,275)
+        tgt = np.full((B, Td, hp.num_mels), hp.silence_mel_level_db, dtype=np.float32)
+        for i, u in enumerate(utts):
+            tgt[i, :u.mel.shape[0]] = u.mel
+        target = torch.from_numpy(tgt).pin_memory().to(device, non_blocking=True)
+    spk = None
+    if hp.use_speaker_embedding:
+        spk = torch.tensor([int(u.speaker_id) for u in utts], dtype=torch.int64).to(device)
+    return (torch.from_numpy(ids).pin_memory().to(device, non_blocking=True),
+            torch.from_numpy(lengths).pin_memory().to(device, non_blocking=True), target, spk)
+
+
+def predict(hparams, weights, utterances, output_dir=None, batch_size=None, device=None, rank=0, world_size=1,
+            mode="free_run", model=None):
+    """Synthesise ``utterances`` (list of Utterance) -> list[PredictedMel] for the ones this rank owns.
+
+    mode: 'free_run' (stop-token inference, PREDICT), 'validation' / 'teacher_forced' (EVAL forms).
+    With ``hparams.use_forced_alignment_mode`` the two-pass forced alignment of models/models.py:118-134 runs.
+    """
+    device = device or torch.device("cuda", torch.cuda.current_device())
+    if device.type != "cuda":
+        raise RuntimeError("predict_mel runs on CUDA devices only (no CPU fallback)")
+    model = model or tacotron_model_factory(hparams, weights)
+    batch_size = batch_size or hparams.batch_size
+    r = hparams.outputs_per_step
+    results = []
+    buckets = make_buckets([len(u.source) for u in utterances], batch_size, world_size,
+                           bucket_width=hparams.batch_bucket_width)
+    for idxs in buckets[rank]:
+        utts = [utterances[i] for i in idxs]
+        ids, lengths, target, spk = _pad_batch(utts, hparams, device)
+        need_target = mode != "free_run" or hparams.use_forced_alignment_mode
+        if need_target and target is None:
+            raise ValueError(f"mode {mode!r} needs ground-truth mel for every utterance")
+        out = model.predict(ids, lengths, target=target if need_target else None, speaker_id=spk,
+                            is_validation=mode != "free_run", teacher_forcing=mode == "teacher_forced")
+        mel = out["mel"].cpu().numpy()
+        post = out["mel_postnet"].cpu().numpy() if "mel_postnet" in out else None
+        stop_steps = out["stop_steps"].cpu().numpy()
+        aligns = [out[k].cpu().numpy() for k in ("alignment", "alignment2") if k in out]
+        for i, u in enumerate(utts):
+            # frames kept per utterance: up to and including its own stop step (free run), else all steps
+            n = out["n_steps"] if (mode != "free_run" or stop_steps[i] < 0) else int(stop_steps[i]) + 1
+            L = int(lengths[i].item())
+            al = [a[i, :L, :n] for a in aligns] + [None] * (6 - len(aligns))
+            m = mel[i, :n * r]
+            pm = PredictedMel(u.id, u.key, m, post[i, :n * r] if post is not None else None, m.shape[1], m.shape[0],
+                              u.mel, al[0], al[1], al[2], al[3], al[4], al[5], u.source, u.text, None)
+            results.append(pm)
+            if output_dir is not None:
+                write_predicted_mel(pm, hparams, output_dir)
+    return results
+
+
+def write_predicted_mel(v, hparams, output_dir):
+    """predict_mel.py:56-62: ``<key>.<predicted_mel_extension>`` holding raw '<f4' frames [T_dec, num_mels]."""
+    key = v.key.decode("utf-8") if isinstance(v.key, bytes) else str(v.key)
+    mel = v.predicted_mel_postnet if hparams.use_postnet_v2 else v.predicted_mel
+    assert mel.shape[1] == hparams.num_mels
+    os.makedirs(output_dir, exist_ok=True)
+    path = os.path.join(output_dir, f"{key}.{hparams.predicted_mel_extension}")
+    np.ascontiguousarray(mel, dtype="<f4").tofile(path)
+    return path

@@ -1,0 +1,100 @@
+"""End-to-end GPU parity: SynthesisModel / predict_mel (embedding -> encoder -> decoder -> post-net, wiring of
+models/models.py:28-148) against oracle.postnet.synthesize on the same seeded weights and inputs."""
+import numpy as np
+import pytest
+
+import sat_b200
+from oracle.postnet import synthesize
+from tests.util import rel_err, small_hp
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-3
+
+
+def _t(a):
+    import torch
+    return None if a is None else torch.from_numpy(np.ascontiguousarray(a)).to("cuda:0")
+
+
+def _w64(W):
+    return {k: v.astype(np.float64) for k, v in W.items()}
+
+
+def _inputs(hp, B, T, S, seed):
+    rng = np.random.default_rng(seed)
+    lengths = np.full(B, T, dtype=np.int64)
+    if B > 1:
+        lengths[1:] = rng.integers(T // 2, T + 1, size=B - 1)
+    ids = rng.integers(1, 71, size=(B, T)).astype(np.int64)
+    for b in range(B):
+        ids[b, lengths[b]:] = 0
+    target = rng.normal(0, 1, size=(B, S * hp.outputs_per_step, hp.num_mels)).astype(np.float32)
+    return ids, lengths, target
+
+
+@pytest.mark.parametrize("cfg,extra", [("ljspeech_self_attention", dict(use_postnet_v2=True)),
+                                       ("ljspeech_tacotron", {}),
+                                       ("vctk_self_attention", {})])
+def test_teacher_forced_end_to_end(cfg, extra):
+    from sat_b200.models import tacotron_model_factory
+    hp = small_hp(cfg, **extra)
+    W = sat_b200.init_weights(hp, seed=21, stress=True)
+    ids, lengths, target = _inputs(hp, 3, 31, 14, seed=21)
+    spk = np.array([226, 230, 300], dtype=np.int64) if hp.use_speaker_embedding else None
+    ref = synthesize(ids, lengths, _w64(W), hp, target=target.astype(np.float64), speaker_ids=spk, mode="teacher_forced")
+    model = tacotron_model_factory(hp, W)
+    out = model.predict(_t(ids), _t(lengths), target=_t(target), speaker_id=_t(spk), is_validation=True,
+                        teacher_forcing=True)
+    assert out["n_steps"] == ref["n_steps"]
+    assert rel_err(out["mel"].cpu().numpy(), ref["mel"]) <= TOL
+    assert rel_err(out["stop_token"].cpu().numpy(), ref["stop"]) <= TOL
+    assert rel_err(out["alignment"].cpu().numpy(), ref["alignments"][0].transpose(0, 2, 1)) <= TOL
+    if "alignment2" in out:
+        assert rel_err(out["alignment2"].cpu().numpy(), ref["alignments"][1].transpose(0, 2, 1)) <= TOL
+    if hp.use_postnet_v2:
+        assert rel_err(out["mel_postnet"].cpu().numpy(), ref["mel_postnet"]) <= TOL
+
+
+def test_forced_alignment_mode_end_to_end():
+    from sat_b200.models import tacotron_model_factory
+    hp = small_hp("ljspeech_self_attention", use_forced_alignment_mode=True)
+    W = sat_b200.init_weights(hp, seed=22, stress=True)
+    ids, lengths, target = _inputs(hp, 2, 23, 10, seed=22)
+    ref = synthesize(ids, lengths, _w64(W), hp, target=target.astype(np.float64), mode="forced_alignment")
+    out = tacotron_model_factory(hp, W).predict(_t(ids), _t(lengths), target=_t(target))
+    assert rel_err(out["mel"].cpu().numpy(), ref["mel"]) <= TOL
+    assert rel_err(out["alignment"].cpu().numpy(), ref["alignments"][0].transpose(0, 2, 1)) <= TOL
+
+
+def test_predict_mel_free_run_writes_mfbsp(tmp_path):
+    """predict_mel surface: PredictedMel fields, raw '<f4' .mfbsp output (predict_mel.py:28-33,58-62);
+    free run with per-utterance stop steps equal to the oracle's."""
+    from sat_b200.predict_mel import predict, Utterance
+    hp = small_hp("ljspeech_tacotron", max_iters=40)
+    W = sat_b200.init_weights(hp, seed=23, stress=True)
+    W["decoder/stop_token_projection/kernel"] *= 8.0
+    rng = np.random.default_rng(23)
+    utts = [Utterance(i, f"utt{i}", rng.integers(1, 71, size=n), text="x") for i, n in enumerate([17, 25, 21, 9])]
+    # oracle on the same padded batch order predict() forms (single rank, batch_size >= n: sorted longest first)
+    order = sorted(range(4), key=lambda i: -len(utts[i].source))
+    T = max(len(u.source) for u in utts)
+    ids = np.zeros((4, T), np.int64)
+    lengths = np.zeros(4, np.int64)
+    for row, i in enumerate(order):
+        ids[row, :len(utts[i].source)] = utts[i].source
+        lengths[row] = len(utts[i].source)
+    probe = synthesize(ids, lengths, _w64(W), hp, mode="free_run", stop_mode="never", max_iters=40)
+    W["decoder/stop_token_projection/bias"] -= np.float32(np.quantile(probe["stop"][:, 11:], 0.9))
+    ref = synthesize(ids, lengths, _w64(W), hp, mode="free_run", stop_mode="all_rows", max_iters=40)
+    res = predict(hp, W, utts, output_dir=str(tmp_path), batch_size=8)
+    assert len(res) == 4
+    for row, v in enumerate(res):
+        i = order[row]
+        assert v.id == i and v.key == f"utt{i}"
+        n = ref["n_steps"] if ref["stop_steps"][row] < 0 else ref["stop_steps"][row] + 1
+        assert v.predicted_mel.shape == (n * hp.outputs_per_step, hp.num_mels)
+        assert v.predicted_mel_width == hp.num_mels and v.predicted_target_length == n * hp.outputs_per_step
+        assert rel_err(v.predicted_mel, ref["mel"][row, :n * hp.outputs_per_step]) <= TOL
+        assert v.alignment.shape == (lengths[row], n)
+        raw = np.fromfile(tmp_path / f"utt{i}.mfbsp", dtype="<f4").reshape(-1, hp.num_mels)
+        np.testing.assert_array_equal(raw, v.predicted_mel)
