@@ -1,0 +1,316 @@
+"""bench.py -- mel frames/s of the synthesis hot path (BASELINE.json metric) on N B200s of one node.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    torchrun ... bench.py --gpus N ...          (one rank per GPU, NCCL)
+
+A "step" is ONE pass of the whole hot path (embedding -> encoder -> autoregressive decoder) over one
+synthetic batch of BASELINE.json configs[1]: LJSpeech baseline Tacotron (examples/ljspeech/tacotron.json:
+ZoneoutEncoderV1 + ExtendedDecoder, forward attention, r=2), free-running decode with the reference stop
+rule, batch 256 per GPU, T_enc ~ U[100,200], max_iters=500.  With random-init weights the reference's
+`reduce_all` stop rule never fires, so every step emits 256 x 500 x 2 mel frames per GPU.
+
+Prints ONE JSON line (rank 0).  `value` = frames/s with inputs resident in HBM; `e2e` = the same through the
+public API (sat_b200.models.SynthesisModel.predict) with pinned HOST buffers in and out; `roofline` = the
+persistent decoder kernel against the measured HBM peak; `cpu_baseline` = the torch-CPU port of the oracle on a
+bounded sample.  `--impl reference` times that CPU port alone (TensorFlow 1.x, the reference's own runtime, is
+not installable here -- see BASELINE.md).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "mel_frames_per_sec_free_run"
+UNIT = "frames/s"
+WORKLOAD = "cfg2: LJSpeech baseline Tacotron (tacotron.json), free-run decode, stop rule all_rows, B=256/GPU, " \
+           "T_enc~U[100,200], max_iters=500, r=2"
+B_PER_GPU, T_MIN, T_MAX, SEED = 256, 100, 200, 12345
+
+
+def workload(hp, rank=0):
+    """Synthetic batch of cfg 2: ids uniform in [1,70], padding id 0, lengths ~ U[100,200]."""
+    rng = np.random.default_rng(SEED + rank)
+    lengths = rng.integers(T_MIN, T_MAX + 1, size=B_PER_GPU).astype(np.int64)
+    lengths[0] = T_MAX
+    T = int(lengths.max())
+    ids = rng.integers(1, 71, size=(B_PER_GPU, T)).astype(np.int64)
+    ids[np.arange(T)[None, :] >= lengths[:, None]] = 0
+    return ids, lengths
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(index), "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        self.th.join(timeout=2)
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) >= 6 and r[2 + i].lower() == "active" for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------------------
+# CPU baseline: the torch-CPU port of the oracle (oracle/torch_cpu.py), the one place bench.py runs oracle/ code
+# ---------------------------------------------------------------------------------------------------------
+CPU_SAMPLE_STEPS = 50
+_cpu_warm = False
+
+
+def cpu_sample(hp, W, ids, lengths, threads):
+    """One bounded sample of the workload on the host cores: the whole encoder for the full batch plus the first
+    CPU_SAMPLE_STEPS of the 500 decoder steps; the decoder part is scaled to 500 steps (cfg 2 has no KV cache, so
+    every step costs the same).  -> (frames/s of the whole workload, seconds spent)."""
+    import torch
+    from oracle import torch_cpu
+    global _cpu_warm
+    torch.set_num_threads(threads)
+    torch.set_flush_denormal(True)  # forward-attention tails underflow; TF's CPU kernels flush denormals too
+    S = hp.max_iters
+    with torch.no_grad():
+        Wt = torch_cpu._t(W)
+        if not _cpu_warm:  # one-time oneDNN / thread-pool initialisation, outside the timed sample
+            torch_cpu.decoder_free_run(torch_cpu.encoder(ids[:4], lengths[:4], Wt, hp), lengths[:4], Wt, hp, 2)
+            _cpu_warm = True
+        t0 = time.perf_counter()
+        src = torch_cpu.encoder(ids, lengths, Wt, hp)
+        t1 = time.perf_counter()
+        torch_cpu.decoder_free_run(src, lengths, Wt, hp, CPU_SAMPLE_STEPS)
+        t2 = time.perf_counter()
+    est = (t1 - t0) + (t2 - t1) * S / CPU_SAMPLE_STEPS
+    frames = ids.shape[0] * S * hp.outputs_per_step
+    return frames / est, t2 - t0
+
+
+def cpu_sample_text():
+    return (f"full batch (B={B_PER_GPU}): whole encoder + first {CPU_SAMPLE_STEPS} of 500 decoder steps, decoder time "
+            f"scaled x{500 // CPU_SAMPLE_STEPS}; torch-CPU fp32 port of the oracle (TF 1.x reference not installable)")
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU implementation of the path = the oracle port, all host threads."""
+    if rank != 0:
+        return
+    import sat_b200
+    hp = sat_b200.config("ljspeech_tacotron")
+    W = sat_b200.init_weights(hp, seed=SEED)
+    ids, lengths = workload(hp)
+    threads = os.cpu_count() or 1
+    for _ in range(min(args.warmup, 1)):
+        cpu_sample(hp, W, ids, lengths, threads)
+    vals, secs = [], []
+    for _ in range(args.steps):
+        v, s = cpu_sample(hp, W, ids, lengths, threads)
+        vals.append(v)
+        secs.append(s)
+    value = float(np.mean(vals))
+    frames = B_PER_GPU * hp.max_iters * hp.outputs_per_step
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * frames / value,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "note": "ms_per_step = estimated CPU time of one full workload step"},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": cpu_sample_text()},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "sample_seconds": float(np.mean(secs))}
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# our arm: libsat.so on the GPU(s)
+# ---------------------------------------------------------------------------------------------------------
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    import sat_b200
+    from sat_b200 import _lib
+    from sat_b200.engine import EncoderHandle, DecoderHandle
+    from sat_b200.models import tacotron_model_factory
+
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    lib = _lib.lib()  # raises if libsat.so is missing
+    hp = sat_b200.config("ljspeech_tacotron")
+    W = sat_b200.init_weights(hp, seed=SEED)
+    ids_np, len_np = workload(hp, rank)
+    B, T = ids_np.shape
+    S, r, M = hp.max_iters, hp.outputs_per_step, hp.num_mels
+    frames_per_step = B * S * r
+
+    enc, dec = EncoderHandle(hp, W), DecoderHandle(hp, W)
+    ids, lengths = torch.from_numpy(ids_np).to(dev), torch.from_numpy(len_np).to(dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    def step():
+        """one pass of the hot path, inputs resident in HBM"""
+        flush.fill_(1)
+        mem, _, _ = enc.forward(ids, lengths)
+        return dec.run([mem], lengths, feed_mode=_lib.FEED_SELF, stop_mode=_lib.STOP_ALL_ROWS, max_steps=S)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        out = step()
+    barrier()
+    assert int(out["n_steps"].item()) == S, "the all_rows stop rule fired: frames/step would be wrong"
+    assert bool(torch.isfinite(out["mel"]).all()), "non-finite mel frames"
+
+    # ---- timed region: EXACTLY K steps between barrier + synchronize ----
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    lib.sat_launch_count_reset()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    barrier()
+    launches = int(lib.sat_launch_count())
+    clocks = sampler.stop() if sampler else None
+    ms = e0.elapsed_time(e1)
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    value = world * frames_per_step * args.steps / (ms * 1e-3)
+
+    # ---- dominant kernel: persistent decoder kernel, CUDA events recorded around its launch inside libsat ----
+    kms = []
+    for _ in range(max(3, min(args.steps, 5))):
+        step()
+        kms.append(dec.kernel_ms())
+    k_ms = float(np.mean(kms))
+    bytes_step = dec.step_bytes(B, int(round(float(len_np.mean()))), 0)  # SURVEY.md 8d formula, mean memory length
+    peak, peak_src = peaks()
+    achieved = bytes_step * S / (k_ms * 1e-3) / 1e9
+
+    # ---- e2e: public API with HOST buffers; H2D of the step's inputs and D2H of its result inside the region ----
+    model = tacotron_model_factory(hp, W)
+    ids_h, len_h = torch.from_numpy(ids_np).pin_memory(), torch.from_numpy(len_np).pin_memory()
+    mel_h = torch.empty((B, S * r, M), dtype=torch.float32).pin_memory()
+
+    def e2e_step():
+        flush.fill_(1)
+        o = model.predict(ids_h.to(dev, non_blocking=True), len_h.to(dev, non_blocking=True))
+        mel_h.copy_(o["mel"], non_blocking=True)
+        return o
+
+    for _ in range(max(1, min(args.warmup, 2))):
+        e2e_step()
+    k2 = max(1, min(args.steps, 5))
+    barrier()
+    e0.record()
+    for _ in range(k2):
+        e2e_step()
+    e1.record()
+    barrier()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = world * frames_per_step * k2 / (float(t.item()) * 1e-3)
+    assert bool(np.isfinite(mel_h.numpy()[:, -1]).all())
+
+    if rank != 0:
+        return
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        v, secs = cpu_sample(hp, W, ids_np, len_np, threads)
+        cpu = {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": cpu_sample_text(),
+               "sample_seconds": secs}
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "frames_per_step_per_gpu": frames_per_step, "T_enc_padded": T,
+                       "l2": "256 MiB flush buffer written before every step (inside the timed region)",
+                       "weights": "random-init seed 12345", "rtf": ms / args.steps * 1e-3 / (frames_per_step * world * 0.0125)},
+            "clocks": clocks, "gpu_launches": launches,
+            "e2e": {"value": e2e_value, "unit": UNIT, "steps": k2,
+                    "h2d_bytes_per_step": int(ids_np.nbytes + len_np.nbytes), "d2h_bytes_per_step": int(mel_h.numel() * 4)},
+            "roofline": {"kernel": "decoder_persistent_kernel", "bound": "hbm", "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "bytes_per_decoder_step": bytes_step, "decoder_steps_per_launch": S, "kernel_ms": k_ms,
+                         "kernel_share_of_step": k_ms / (ms / args.steps)},
+            "cpu_baseline": cpu}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    elif args.gpus > 1:
+        # launched without torchrun: re-exec under torch.distributed.run, one rank per GPU
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", str(29500 + os.getpid() % 1000)] + sys.argv
+        sys.exit(subprocess.call(cmd))
+    try:
+        run_ours(args, rank, world, local_rank)
+    finally:
+        if world > 1:
+            import torch.distributed as dist
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -254,25 +254,34 @@ extern "C" int sat_decoder_create(const sat_hparams* hpp, const sat_tensor* weig
 extern "C" void sat_decoder_destroy(sat_decoder* h) { delete h; }
 
 extern "C" double sat_decoder_step_bytes(const sat_decoder* h, int32_t B, int32_t T, int32_t avg_cache_len) {
-  // weights once per step + per-utterance attention memory (keys + values of every
-  // source) + average KV-cache read + state/io.
+  // bytes_step(B) = W * 4 + B * [T * sum_i (U_i + D_i) * 4 + avg_cache * 2 * d_sa * 4 + state + io]
+  // W = decoder parameters actually read by a step (counted once per step, un-padded); T = (mean) memory length.
   if (!h) return 0.0;
   const sat_hparams& hp = h->hp;
-  auto wbytes = [](const PackedDense& d) { return (double)d.K * d.N * 4.0; };
-  double w = wbytes(h->pre0) + wbytes(h->pre1) + wbytes(h->lstm_a) + wbytes(h->lstm_1) + wbytes(h->lstm_2) + wbytes(h->outp);
-  if (hp.multi_speaker_prenet) w += wbytes(h->msd);
+  const int A = hp.attention_out_units, Dd = hp.decoder_out_units;
+  double w = (double)h->Mnf * h->P0 + h->P0 + (double)h->P0 * h->P1 + h->P1;
+  if (hp.multi_speaker_prenet) w += (double)h->P0 * h->P0 + h->P0;
+  w += (double)(h->P1 + h->Dctx + A) * 4 * A + 4 * A;
+  w += (double)(A + h->Dctx + Dd) * 4 * Dd + 4 * Dd + (double)2 * Dd * 4 * Dd + 4 * Dd;
   double per_utt = 0;
   for (int i = 0; i < h->n_mech; ++i) {
-    w += wbytes(h->dq[i]);
-    per_utt += (double)T * (hp.attention_units[i] + hp.memory_dim[i]) * 4.0;
+    const int U = hp.attention_units[i];
+    w += (double)A * U + U;
+    if (hp.attention_kind[i] == SAT_ATT_FORWARD || hp.attention_kind[i] == SAT_ATT_LOCATION_SENSITIVE)
+      w += U + (double)hp.attention_kernel * hp.attention_filters + hp.attention_filters + (double)hp.attention_filters * U;
+    per_utt += (double)T * (U + hp.memory_dim[i]) * 4.0;
   }
+  int d_out = Dd;
   for (int i = 0; i < h->hops; ++i) {
-    w += wbytes(h->sa_qkv[i]) + wbytes(h->sa_o[i]) + wbytes(h->sa_tr[i]);
-    per_utt += (double)avg_cache_len * 2.0 * hp.decoder_self_attention_out_units * 4.0;
+    const int Ds = hp.decoder_self_attention_out_units;
+    w += 5.0 * ((double)Ds * Ds + Ds);
+    per_utt += (double)avg_cache_len * 2.0 * Ds * 4.0;
+    d_out = Ds;
   }
-  const double state = 4.0 * (2.0 * (hp.attention_out_units + 2 * hp.decoder_out_units) * 2 + h->Dctx + 3.0 * T * h->n_mech);
+  w += (double)d_out * (h->Mr + 1) + h->Mr + 1;
+  const double state = 4.0 * (2.0 * (A + 2 * Dd) * 2 + h->Dctx + 3.0 * T * h->n_mech);
   const double io = 4.0 * (h->Mnf + h->Mr + 1);
-  return w + B * (per_utt + state + io);
+  return w * 4.0 + B * (per_utt + state + io);
 }
 
 extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* stream) {
