@@ -30,9 +30,15 @@ def run(cfg, B, T, S, feed, reps=3):
     by = h.step_bytes(B, T, S // 2)
     print(f"{cfg} B={B} T={T} S={S} feed={feed}: {ms:.2f} ms/run, {ms*1e3/S:.1f} us/step, "
           f"{B*S*hp.outputs_per_step/ms*1e3:.3e} frames/s, bytes/step {by/1e6:.1f} MB -> {by/(ms*1e-3/S)/1e9:.0f} GB/s")
-    print("  phase share:", " ".join(f"{100*p/tot:.0f}%" for p in prof if p))
+    tot = sum(prof[:16]) or 1
+    clk = 1.9e3  # cycles per us (approx)
+    print("  phase us/step:", " ".join(f"{p/clk/S/reps:.1f}" for p in prof[:16] if p))
+    print("  attention stages us/step (CTA0):", " ".join(f"{p/clk/S/reps:.1f}" for p in prof[16:24]))
+    print("  tc lstm (3 phases summed) us/step: producer %.1f, until accumulator ready %.1f, cell update %.1f" % tuple(p/clk/S/reps for p in prof[24:27]))
 
-if __name__ == "__main__":
+if __name__ == "__main__" and len(sys.argv) > 1:
+    run(sys.argv[1], int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4]), int(sys.argv[5]), reps=1)
+elif __name__ == "__main__":
     run("ljspeech_tacotron", 256, 200, 500, 1)
     run("ljspeech_tacotron", 16, 150, 400, 0)
     run("ljspeech_self_attention", 16, 150, 400, 0)

@@ -110,7 +110,8 @@ extern "C" int sat_attention_step(const sat_tensor* weights, int32_t n_weights, 
     SAT_REQUIRE(weights && prefix && keys && values && lengths && query && alignments && context, "null argument");
     SAT_REQUIRE(kind == SAT_ATT_ADDITIVE || kind == SAT_ATT_LOCATION_SENSITIVE || kind == SAT_ATT_FORWARD,
                 "sat_attention_step handles additive / location_sensitive / forward");
-    SAT_REQUIRE(U % 4 == 0 && U <= 256 && Dv <= dec::NT && T <= dec::MAX_T, "unsupported shape (U%%4==0, U<=256, Dv<=512, T<=1024)");
+    SAT_REQUIRE(U >= 1 && U <= 256 && Dv <= dec::NT && T <= dec::MAX_T, "unsupported shape (U<=256, Dv<=512, T<=1024)");
+    const int Up = dec::att_padded_units(U);
     cudaStream_t st = (cudaStream_t)stream;
     Blob W(weights, n_weights);
     const std::string P = std::string(prefix) + "/";
@@ -124,20 +125,31 @@ extern "C" int sat_attention_step(const sat_tensor* weights, int32_t n_weights, 
     gemm_launch(g, st);
     dec::AttMech m;
     memset(&m, 0, sizeof(m));
-    m.kind = kind; m.U = U; m.Up = U; m.Dv = Dv; m.F = attention_filters; m.Kc = attention_kernel;
+    m.kind = kind; m.U = U; m.Up = Up; m.Dv = Dv; m.F = attention_filters; m.Kc = attention_kernel;
     m.pad_left = (attention_kernel - 1) / 2; m.cumulative = cumulative_weights;
-    m.keys = keys; m.values = values;
-    m.v = pool.upload(W.get(P + "attention_v", U), U);
-    std::vector<float> zeros(U, 0.f);
+    // keys and per-unit vectors padded to the kernel's unit axis (zeros in the padding)
+    float* keys_p = pool.alloc<float>((size_t)B * T * Up);
+    SAT_CUDA(cudaMemcpy2DAsync(keys_p, (size_t)Up * 4, keys, (size_t)U * 4, (size_t)U * 4, (size_t)B * T,
+                               cudaMemcpyDeviceToDevice, st));
+    auto padU = [&](const float* src, int rows) {
+      std::vector<float> v((size_t)rows * Up, 0.f);
+      for (int r = 0; r < rows; ++r)
+        for (int u = 0; u < U; ++u) v[(size_t)r * Up + u] = src[(size_t)r * U + u];
+      return pool.upload(v);
+    };
+    m.keys = keys_p; m.values = values;
+    m.v = padU(W.get(P + "attention_v", U), 1);
+    std::vector<float> zeros(Up, 0.f);
     m.ba = pool.upload(zeros);
     if (kind != SAT_ATT_ADDITIVE) {
       SAT_REQUIRE(state_alignments, "location-sensitive kinds need state_alignments");
       SAT_REQUIRE(attention_kernel <= 2 * dec::HALO && attention_filters <= 32, "attention_kernel/filters too large");
-      m.ba = pool.upload(W.get(P + "attention_bias", U), U);
+      SAT_REQUIRE(attention_filters <= 8 || (128 / std::min(Up, 128)) * attention_filters <= 512, "too many filters");
+      m.ba = padU(W.get(P + "attention_bias", U), 1);
       m.conv_w = pool.upload(W.get(P + "location_conv/kernel", (int64_t)attention_kernel * attention_filters),
                              (size_t)attention_kernel * attention_filters);
       m.conv_b = pool.upload(W.get(P + "location_conv/bias", attention_filters), attention_filters);
-      m.Wl = pool.upload(W.get(P + "location_layer/kernel", (int64_t)attention_filters * U), (size_t)attention_filters * U);
+      m.Wl = padU(W.get(P + "location_layer/kernel", (int64_t)attention_filters * U), attention_filters);
     }
     if (kind == SAT_ATT_FORWARD) {
       SAT_REQUIRE(state_alpha && state_u, "forward attention needs alpha and u state");
@@ -152,7 +164,7 @@ extern "C" int sat_attention_step(const sat_tensor* weights, int32_t n_weights, 
     m.st_align = state_alignments ? state_alignments : dummy_state;
     m.st_alpha = state_alpha; m.st_u = state_u;
     m.out_align = alignments; m.out_S = 1;
-    m.ctx_dst[0] = context; m.ctx_dst[1] = nullptr; m.ctx_sd = 1; m.ctx_sb = Dv;
+    m.ctx_dst[0] = context; m.ctx_dst[1] = nullptr; m.ctx_sd[0] = 1; m.ctx_sb[0] = Dv;
     const size_t smem = dec::ATT_SMEM_FLOATS * sizeof(float);
     SAT_CUDA(cudaFuncSetAttribute(attention_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attention_step_kernel<<<B < 148 ? B : 148, dec::NT, smem, st>>>(m, B, T, (const long long*)lengths);

@@ -10,6 +10,7 @@
 #include <map>
 #include <stdexcept>
 #include <memory>
+#include <algorithm>
 #include "../../include/sat.h"
 
 namespace sat {

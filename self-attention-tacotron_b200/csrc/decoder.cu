@@ -1,6 +1,7 @@
 // decoder.cu -- host side of sat_decoder_*: weight repacking, workspace layout, launch.
 #include "common.cuh"
 #include "decoder_kernel.cuh"
+#include <cstdlib>
 
 namespace sat {
 using namespace dec;
@@ -107,6 +108,9 @@ struct sat_decoder {
   unsigned* barrier = nullptr;
   long long* prof = nullptr;
   size_t max_dyn_smem = 0;
+  CUtensorMap hmaps[6];
+  CUtensorMap* dmaps = nullptr;  // device copy, 64-byte aligned
+  int last_tc = 0;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;  // bracket the persistent launch of the last run
   int last_B = 0, last_T = 0, last_S = 0;
   ~sat_decoder() {
@@ -160,7 +164,7 @@ extern "C" int sat_decoder_create(const sat_hparams* hpp, const sat_tensor* weig
     // attention mechanisms
     for (int i = 0; i < h->n_mech; ++i) {
       const std::string P = D + "attention" + std::to_string(i + 1) + "/";
-      const int U = hp.attention_units[i], Dm = hp.memory_dim[i], Up = (U + 3) / 4 * 4;
+      const int U = hp.attention_units[i], Dm = hp.memory_dim[i], Up = att_padded_units(U);
       const int kind = hp.attention_kind[i];
       SAT_REQUIRE(U <= 256, "attention num_units > 256 unsupported (got %d)", U);
       SAT_REQUIRE(Dm <= NT, "attention memory depth > %d unsupported", NT);
@@ -184,6 +188,7 @@ extern "C" int sat_decoder_create(const sat_hparams* hpp, const sat_tensor* weig
       if (kind == SAT_ATT_FORWARD || kind == SAT_ATT_LOCATION_SENSITIVE) {
         const int Kc = hp.attention_kernel, F = hp.attention_filters;
         SAT_REQUIRE(Kc <= 2 * HALO && F <= 32, "attention_kernel <= %d and attention_filters <= 32 required", 2 * HALO);
+        SAT_REQUIRE(F <= 8 || (128 / std::min(Up, 128)) * F <= 512, "attention_filters %d too large for %d attention units", F, U);
         h->att_ba[i] = padU(W.get(P + "attention_bias", U), 1);
         h->conv_w[i] = pool.upload(W.get(P + "location_conv/kernel", (int64_t)Kc * F), (size_t)Kc * F);
         h->conv_b[i] = pool.upload(W.get(P + "location_conv/bias", F), F);
@@ -244,6 +249,7 @@ extern "C" int sat_decoder_create(const sat_hparams* hpp, const sat_tensor* weig
     h->grid = h->sm_count;
     h->barrier = pool.alloc<unsigned>(1);
     h->prof = pool.alloc<long long>(N_PROF);
+    h->dmaps = (CUtensorMap*)(((uintptr_t)pool.alloc<uint8_t>(6 * sizeof(CUtensorMap) + 64) + 63) & ~(uintptr_t)63);
     SAT_CUDA(cudaEventCreate(&h->ev0));
     SAT_CUDA(cudaEventCreate(&h->ev1));
     guard.release();
@@ -315,10 +321,43 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
     if (p.ms) p.msd = h->msd.desc();
     p.lstm_a = h->lstm_a.desc(); p.lstm_1 = h->lstm_1.desc(); p.lstm_2 = h->lstm_2.desc();
 
-    // ---- shared-memory plan: keep as many LSTM tiles resident as fit ----
+    const int Ka = p.P1 + p.Dctx + A, K1 = A + p.Dctx + Dd, K2 = 2 * Dd;
+    // ---- tensor-core mode for the gate GEMMs once the batch makes them a real contraction ----
+    bool use_tc = B >= 64;
+    if (const char* e = getenv("SAT_TC")) use_tc = atoi(e) != 0;
+    use_tc = use_tc && (A % 4 == 0) && (Dd % 4 == 0);
+    const int RB = ceil_div(Bp, TC_M);
     size_t smem_floats = SCRATCH_FLOATS;
+    size_t smem_bytes = 0;
+    if (use_tc) {
+      TcLstmDesc* td[3] = {&p.tc_a, &p.tc_1, &p.tc_2};
+      const PackedDense* src[3] = {&h->lstm_a, &h->lstm_1, &h->lstm_2};
+      const int Ks[3] = {Ka, K1, K2}, us[3] = {A, Dd, Dd};
+      int off = 0;
+      for (int i = 0; i < 3; ++i) {
+        TcLstmDesc& d = *td[i];
+        d.Wp = src[i]->Wp; d.bias = src[i]->bias; d.K = Ks[i]; d.units = us[i];
+        d.n_tiles = us[i] / 4;
+        d.kchunks = ceil_div(Ks[i], tc::CHUNK_K);
+        d.slots = ceil_div(d.n_tiles * RB, h->grid);
+        d.img_off = off;
+        off += d.slots * d.kchunks * 2048;
+      }
+      p.scratch_floats = std::max((int)SCRATCH_FLOATS, (int)TC_SCRATCH_FLOATS);
+      smem_bytes = p.scratch_floats * sizeof(float) + 1024 + (size_t)off;
+      if (smem_bytes > h->max_dyn_smem) use_tc = false;  // resident images do not fit: SIMT form
+    }
+    p.tc = use_tc ? 1 : 0;
+    if (!use_tc) p.scratch_floats = SCRATCH_FLOATS;
+    p.RB = RB;
+    p.Ka_pad = ceil_div(Ka, tc::CHUNK_K) * tc::CHUNK_K;
+    p.K1_pad = ceil_div(K1, tc::CHUNK_K) * tc::CHUNK_K;
+    p.K2_pad = ceil_div(K2, tc::CHUNK_K) * tc::CHUNK_K;
+    h->last_tc = p.tc;
+    // ---- shared-memory plan (SIMT form): keep as many LSTM tiles resident as fit ----
     DenseDesc* lst[3] = {&p.lstm_a, &p.lstm_1, &p.lstm_2};
     for (DenseDesc* d : lst) {
+      if (use_tc) break;
       const int slots = ceil_div(d->n_tiles * R, h->grid);
       const size_t need = (size_t)slots * d->K * TILE_N;
       if ((smem_floats + need) * sizeof(float) <= h->max_dyn_smem) {
@@ -327,15 +366,19 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
         smem_floats += need;
       }
     }
+    if (!use_tc) smem_bytes = smem_floats * sizeof(float);
 
     // ---- workspace carve-up (floats) ----
-    const int Ka = p.P1 + p.Dctx + A, K1 = A + p.Dctx + Dd, K2 = 2 * Dd;
     size_t off = 0;
     auto take = [&](size_t n) { size_t o = off; off += (n + 63) / 64 * 64; return o; };
     const size_t o_xin = take((size_t)p.Mnf * ld), o_p0 = take((size_t)p.P0 * ld), o_p0b = take((size_t)p.P0 * ld);
-    const size_t o_att0 = take((size_t)Ka * ld), o_att1 = take((size_t)Ka * ld);
-    const size_t o_l10 = take((size_t)K1 * ld), o_l11 = take((size_t)K1 * ld);
-    const size_t o_l20 = take((size_t)K2 * ld), o_l21 = take((size_t)K2 * ld);
+    const size_t rows_tc = (size_t)RB * TC_M;  // row-major [rows_tc][K*_pad] in tensor-core mode, else [K][ld]
+    const size_t n_att = use_tc ? rows_tc * p.Ka_pad : (size_t)Ka * ld, n_l1 = use_tc ? rows_tc * p.K1_pad : (size_t)K1 * ld;
+    const size_t n_l2 = use_tc ? rows_tc * p.K2_pad : (size_t)K2 * ld;
+    const size_t o_att0 = take(n_att), o_att1 = take(n_att);
+    const size_t o_l10 = take(n_l1), o_l11 = take(n_l1);
+    const size_t o_l20 = take(n_l2), o_l21 = take(n_l2);
+    const size_t o_qfm = take((size_t)A * ld);
     const size_t o_ca = take((size_t)A * ld), o_c1 = take((size_t)Dd * ld), o_c2 = take((size_t)Dd * ld);
     const size_t o_dout = take((size_t)Dd * ld);
     const size_t o_saq = take((size_t)Ds * ld), o_sactx = take((size_t)Ds * ld), o_saa = take((size_t)Ds * ld);
@@ -364,6 +407,7 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
     p.att_in[0] = ws + o_att0; p.att_in[1] = ws + o_att1;
     p.l1_in[0] = ws + o_l10; p.l1_in[1] = ws + o_l11;
     p.l2_in[0] = ws + o_l20; p.l2_in[1] = ws + o_l21;
+    p.qfm = ws + o_qfm;
     p.c_a = ws + o_ca; p.c_1 = ws + o_c1; p.c_2 = ws + o_c2; p.dout = ws + o_dout;
     p.sa_q = ws + o_saq; p.sa_ctx = ws + o_sactx; p.sa_a = ws + o_saa; p.sa_y[0] = ws + o_say0; p.sa_y[1] = ws + o_say1;
     p.target = io.target; p.lengths = (const long long*)io.memory_lengths;
@@ -412,10 +456,18 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
       p.hop[i].kcache = ws + o_kc[i]; p.hop[i].vcache = ws + o_vc[i];
     }
 
+    if (use_tc) {
+      float* bufs[6] = {p.att_in[0], p.att_in[1], p.l1_in[0], p.l1_in[1], p.l2_in[0], p.l2_in[1]};
+      const int pads[6] = {p.Ka_pad, p.Ka_pad, p.K1_pad, p.K1_pad, p.K2_pad, p.K2_pad};
+      for (int i = 0; i < 6; ++i)
+        make_tensor_map_2d(&h->hmaps[i], bufs[i], rows_tc, (uint64_t)pads[i], (uint64_t)pads[i], TC_M);
+      SAT_CUDA(cudaMemcpyAsync(h->dmaps, h->hmaps, sizeof(h->hmaps), cudaMemcpyHostToDevice, st));
+      p.maps = h->dmaps;
+    }
     void* args[] = {&p};
     SAT_CUDA(cudaEventRecord(h->ev0, st));
     SAT_CUDA(cudaLaunchCooperativeKernel((const void*)decoder_persistent_kernel, dim3(h->grid), dim3(NT), args,
-                                         smem_floats * sizeof(float), st));
+                                         smem_bytes, st));
     SAT_CUDA(cudaEventRecord(h->ev1, st));
     h->last_B = B; h->last_T = T; h->last_S = S;
     count_launch();
@@ -429,7 +481,7 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
 }
 
 // cycles per phase accumulated by CTA 0 over all runs since the last reset (debug / profiling aid)
-extern "C" int sat_decoder_profile(sat_decoder* h, int64_t* out16, int32_t reset) {
+extern "C" int sat_decoder_profile(sat_decoder* h, int64_t* out16 /* N_PROF = 32 slots */, int32_t reset) {
   return guarded([&] {
     SAT_REQUIRE(h && out16, "null argument");
     SAT_CUDA(cudaDeviceSynchronize());

@@ -10,6 +10,7 @@
 //   context            _calculate_context modules/forward_attention.py:29-41
 #pragma once
 #include "decoder_dev.cuh"
+#include "tc.cuh"
 #include "../../include/sat.h"
 
 namespace sat {
@@ -17,7 +18,16 @@ namespace dec {
 
 constexpr int HALO = 32;         // zero halo each side of the previous alignments (attention_kernel <= 64)
 constexpr int MAX_T = 1024;      // padded memory length bound of the row phase
-constexpr int ATT_SMEM_FLOATS = 11 * MAX_T + 2 * HALO + NT + 64;
+constexpr int MAX_DV = 512;       // attention memory depth bound (context staging)
+constexpr int ATT_SMEM_FLOATS = 13 * MAX_T + 2 * HALO + NT + MAX_DV + 64;
+
+// unit axis padding of keys / per-unit vectors: 4 * 2^k lanes-worth for U <= 128, else 256 (two warps per row)
+inline int att_padded_units(int U) {
+  if (U > 128) return 256;
+  int c = 1;
+  while (4 * c < U) c <<= 1;
+  return 4 * c;
+}
 
 struct AttMech {
   int kind;             // SAT_ATT_*
@@ -40,96 +50,269 @@ struct AttMech {
   int teacher_S;
   float* out_align;     // [B][out_S][T] or null
   int out_S;
-  float* ctx_dst[2];    // context element (d, b) written at ctx_dst[i][d * ctx_sd + b * ctx_sb]; may be null
-  int ctx_sd, ctx_sb;
+  long long* prof;      // optional stage cycle counters (8 slots), CTA 0 only
+  float* ctx_dst[2];    // context element (d, b) written at ctx_dst[i][d * ctx_sd[i] + b * ctx_sb[i]]; may be null
+  int ctx_sd[2], ctx_sb[2];
+  int ctx_tf32;         // 1: context destinations feed tensor-core GEMMs -> store rounded (RN) to tf32
 };
 
-__device__ __forceinline__ float fast_tanh(float x) {
-  // 1 - 2 / (exp(2x) + 1); abs error ~1e-6 (ex2.approx + fast divide), saturates cleanly
-  const float e = __expf(2.f * x);
-  return 1.f - __fdividef(2.f, e + 1.f);
+// exp2 / reciprocal on the MUFU pipe
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
 }
 
-// F_T: 0 = no location term (additive); 5 / 8 = location filters held in registers
-// (8 = zero-padded for 6..8); -1 = generic (any F, location features recomputed per row).
+// Energies of one row.  v . tanh(x) = sum(v) - 2 sum_u v_u / (exp(2 x_u) + 1); the constant sum(v) is the same
+// for every j of the row and cancels in the softmax, so the kernel evaluates
+//     e'_j = sum_u (-2 v_u) * rcp(ex2(C x_u) + 1),  C = 2 log2(e)
+// with C folded into the processed query / bias / location weights (registers) and applied to the key with the
+// FFMA that adds it.  Abs error of the implied tanh ~1e-7 (ex2.approx, rcp.approx); saturates cleanly.
+//
+// Lane mapping: one lane owns ONE float4 of the unit axis (keeps the per-lane constants at 8 + 4 F registers).
+// Up = 4 * lpr with lpr a power of two <= 32 lanes per memory row (32 / lpr rows per warp pass), or Up = 256:
+// two warps per memory row (units [0,128) and [128,256)), partial sums combined through e2.
+// F_T: 0 = no location term (additive); 5 / 8 = location filters held in registers (8 = zero-padded 6..8);
+// -1 = generic (any F <= 32, location features recomputed per row).
 template <int F_T>
 __device__ void attention_energies(const AttMech& m, int b, int T, int len, const float* aprev,
-                                   const float* fbuf, float* e) {
+                                   const float* fbuf, float* e, float* e2) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  constexpr int NCH = 2;
+  constexpr float C2 = 2.8853900817779268f;  // 2 * log2(e)
   constexpr int FR = F_T > 0 ? F_T : 1;
-  float pqb[NCH][4], vv[NCH][4], wl[FR][NCH][4];
+  const int halves = m.Up > 128 ? 2 : 1;
+  const int lpr = halves == 2 ? 32 : (m.Up >> 2);  // lanes per memory row
+  const int G = 32 / lpr;                          // memory rows per warp pass
+  const int half = halves == 2 ? (warp & 1) : 0;
+  const int wrow = halves == 2 ? (warp >> 1) : warp;
+  const int nwr = halves == 2 ? NW / 2 : NW;       // warps along the row axis
+  const int u0 = half * 128 + 4 * (lane % lpr);
+  const int g = lane / lpr;
+  float pqb[4], vv[4], wl[FR][4];
 #pragma unroll
-  for (int ch = 0; ch < NCH; ++ch) {
-    const int u0 = ch * 128 + 4 * lane;
+  for (int i = 0; i < 4; ++i) {
+    const int u = u0 + i;
+    pqb[i] = u < m.U ? C2 * (__ldcg(m.pq + (size_t)u * m.pq_su + (size_t)b * m.pq_sb) + __ldg(m.ba + u)) : 0.f;
+    vv[i] = -2.f * __ldg(m.v + u);  // zero in the padding
+    if (F_T > 0) {
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int u = u0 + i;
-      const bool ok = u < m.Up;
-      pqb[ch][i] = (ok && u < m.U) ? __ldcg(m.pq + (size_t)u * m.pq_su + (size_t)b * m.pq_sb) + __ldg(m.ba + u) : 0.f;
-      vv[ch][i] = ok ? __ldg(m.v + u) : 0.f;
-      if (F_T > 0) {
-#pragma unroll
-        for (int c = 0; c < FR; ++c) wl[c][ch][i] = (ok && c < m.F) ? __ldg(m.Wl + c * m.Up + u) : 0.f;
-      }
+      for (int c = 0; c < FR; ++c) wl[c][i] = c < m.F ? C2 * __ldg(m.Wl + c * m.Up + u) : 0.f;
     }
   }
-  const float* kbase = m.keys + (size_t)b * T * m.Up;
-  float4 kn[NCH];
-  auto load_keys = [&](int j) {
+  long long c0 = 0, c1 = 0, c2 = 0;
+  const bool prof_on = m.prof && blockIdx.x == 0 && threadIdx.x == 0;
+  if (prof_on) {
+    float dep = pqb[0] + vv[0] + wl[0][0] + wl[FR - 1][3];
+    asm volatile("mov.u64 %0, %%clock64;" : "=l"(c0) : "f"(dep));
+  }
+  const float* kbase = m.keys + (size_t)b * T * m.Up + u0;
+  const int stride = nwr * G;
+  constexpr int PF = 4;  // key rows in flight per lane
+  float4 kq[PF];
+  const int jbase = wrow * G + g;
 #pragma unroll
-    for (int ch = 0; ch < NCH; ++ch) {
-      const int u0 = ch * 128 + 4 * lane;
-      kn[ch] = (j < len && u0 < m.Up) ? __ldg((const float4*)(kbase + (size_t)j * m.Up + u0)) : make_float4(0, 0, 0, 0);
-    }
-  };
-  load_keys(warp);
-  for (int j = warp; j < T; j += NW) {
-    float4 kc[NCH];
+  for (int s = 0; s < PF; ++s) {
+    const int j = jbase + s * stride;
+    kq[s] = j < len ? __ldg((const float4*)(kbase + (size_t)j * m.Up)) : make_float4(0, 0, 0, 0);
+  }
+  if (prof_on) {
+    float dep = kq[0].x + kq[PF - 1].w;
+    asm volatile("mov.u64 %0, %%clock64;" : "=l"(c1) : "f"(dep));
+  }
+  float* eo = half ? e2 : e;
+  for (int j0 = jbase; j0 - g < T; j0 += PF * stride) {
 #pragma unroll
-    for (int ch = 0; ch < NCH; ++ch) kc[ch] = kn[ch];
-    if (j + NW < T) load_keys(j + NW);
-    float s = 0.f;
-    if (j < len) {
-      float fj[FR];
+    for (int s = 0; s < PF; ++s) {
+      const int j = j0 + s * stride;
+      if (j - g >= T) break;  // warp-uniform
+      const float4 kc = kq[s];
+      {
+        const int jn = j + PF * stride;
+        kq[s] = jn < len ? __ldg((const float4*)(kbase + (size_t)jn * m.Up)) : make_float4(0, 0, 0, 0);
+      }
+      float sum = 0.f;
+      float x[4] = {fmaf(kc.x, C2, pqb[0]), fmaf(kc.y, C2, pqb[1]), fmaf(kc.z, C2, pqb[2]), fmaf(kc.w, C2, pqb[3])};
       if (F_T > 0) {
-#pragma unroll
-        for (int c = 0; c < FR; ++c) fj[c] = fbuf[j * 8 + c];
-      }
-      float fc = 0.f;
-      if (F_T < 0 && lane < m.F) {
-        // generic: recompute the location features of row j, lane c holds f[j][c] (F <= 32)
-        fc = __ldg(m.conv_b + lane);
-        for (int i = 0; i < m.Kc; ++i) fc = fmaf(__ldg(m.conv_w + i * m.F + lane), aprev[HALO + j + i - m.pad_left], fc);
-      }
-#pragma unroll
-      for (int ch = 0; ch < NCH; ++ch) {
-        const int u0 = ch * 128 + 4 * lane;
-        const bool ok = u0 < m.Up;  // lane-divergent: only guards loads/accumulation, never a shuffle
-        float x[4] = {kc[ch].x + pqb[ch][0], kc[ch].y + pqb[ch][1], kc[ch].z + pqb[ch][2], kc[ch].w + pqb[ch][3]};
-        if (F_T > 0) {
+        if (j < len) {
+          const float4 f0 = *(const float4*)(fbuf + j * 8);
+          const float4 f1 = FR > 4 ? *(const float4*)(fbuf + j * 8 + 4) : make_float4(0, 0, 0, 0);
+          const float fj[8] = {f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w};
 #pragma unroll
           for (int c = 0; c < FR; ++c)
 #pragma unroll
-            for (int i = 0; i < 4; ++i) x[i] = fmaf(fj[c], wl[c][ch][i], x[i]);
-        } else if (F_T < 0) {
-          for (int c = 0; c < m.F; ++c) {
-            const float f = __shfl_sync(0xffffffffu, fc, c);
-            if (ok) {
-#pragma unroll
-              for (int i = 0; i < 4; ++i) x[i] = fmaf(f, __ldg(m.Wl + c * m.Up + u0 + i), x[i]);
-            }
-          }
+            for (int i = 0; i < 4; ++i) x[i] = fmaf(fj[c], wl[c][i], x[i]);
         }
-        if (ok) {
-#pragma unroll
-          for (int i = 0; i < 4; ++i) s = fmaf(vv[ch][i], fast_tanh(x[i]), s);
+      } else if (F_T < 0) {
+        // generic (9..32 filters): the warp first computes the location features of the G rows of this pass
+        // into its private stash (fbuf is free in this mode), then every lane reads its row's features.
+        float* stash = const_cast<float*>(fbuf) + warp * 512;  // G * F <= 512 enforced at create time
+        __syncwarp();
+        for (int idx = lane; idx < G * m.F; idx += 32) {
+          const int gg = idx / m.F, c = idx % m.F;
+          const int jj = j - g + gg;
+          float fc = 0.f;
+          if (jj < T) {
+            fc = __ldg(m.conv_b + c);
+            for (int i = 0; i < m.Kc; ++i) fc = fmaf(__ldg(m.conv_w + i * m.F + c), aprev[HALO + jj + i - m.pad_left], fc);
+          }
+          stash[idx] = fc * C2;
+        }
+        __syncwarp();
+        for (int c2 = 0; c2 < m.F; ++c2) {
+          const float f = stash[g * m.F + c2];
+          const float4 w = __ldg((const float4*)(m.Wl + c2 * m.Up + u0));
+          x[0] = fmaf(f, w.x, x[0]); x[1] = fmaf(f, w.y, x[1]); x[2] = fmaf(f, w.z, x[2]); x[3] = fmaf(f, w.w, x[3]);
         }
       }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) sum = fmaf(vv[i], rcp_approx(ex2_approx(x[i]) + 1.f), sum);
+      for (int o = 1; o < lpr; o <<= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+      if ((lane % lpr) == 0 && j < T) eo[j] = (j < len) ? sum : (half ? 0.f : -INFINITY);
     }
-    s = warp_sum(s);
-    if (lane == 0) e[j] = (j < len) ? s : -INFINITY;
   }
+  if (prof_on) {
+    asm volatile("mov.u64 %0, %%clock64;" : "=l"(c2));
+    m.prof[6] += c1 - c0;  // first key rows landed
+    m.prof[7] += c2 - c1;  // main loop of warp 0
+  }
+}
+
+// Fast path of the energies for Up = 128 or 256 (a full warp spans 128 units; Up = 256: two warps per row).
+// Four memory rows per pass and lane, software-pipelined key loads (next four rows in flight while the current
+// four are evaluated), and ONE transpose-reduction per four rows (6 shuffles instead of 20).
+// Only rows j < len are visited; the masked tail is filled by the caller.
+template <int F_T>
+__device__ void attention_energies_w32(const AttMech& m, int b, int T, int len, const float* fbuf, float* e, float* e2) {
+  static_assert(F_T >= 0 && F_T <= 8, "register-resident location filters");
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  constexpr float C2 = 2.8853900817779268f;  // 2 * log2(e)
+  constexpr int FR = F_T > 0 ? F_T : 1;
+  const bool two = m.Up > 128;
+  const int half = two ? (warp & 1) : 0;
+  const int wrow = two ? (warp >> 1) : warp;
+  const int nwr = two ? NW / 2 : NW;
+  const int u0 = half * 128 + 4 * lane;
+  float pqb[4], vv[4], wl[FR][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int u = u0 + i;
+    pqb[i] = u < m.U ? C2 * (__ldcg(m.pq + (size_t)u * m.pq_su + (size_t)b * m.pq_sb) + __ldg(m.ba + u)) : 0.f;
+    vv[i] = -2.f * __ldg(m.v + u);
+    if (F_T > 0) {
+#pragma unroll
+      for (int c = 0; c < FR; ++c) wl[c][i] = c < m.F ? C2 * __ldg(m.Wl + c * m.Up + u) : 0.f;
+    }
+  }
+  const float* kbase = m.keys + (size_t)b * T * m.Up + u0;
+  const size_t rstride = (size_t)nwr * m.Up;  // floats between consecutive rows of this warp
+  const int last = len - 1;
+  float* eo = half ? e2 : e;
+  // rows of this warp: j = wrow + nwr * r, r = 0, 1, ...; out-of-range rows are clamped to `last` and discarded
+  auto row_ptr = [&](int r) { return kbase + (size_t)min(wrow + nwr * r, last) * m.Up; };
+  float4 kn[4];
+#pragma unroll
+  for (int s = 0; s < 4; ++s) kn[s] = __ldg((const float4*)row_ptr(s));
+  for (int r0 = 0; wrow + nwr * r0 < len; r0 += 4) {
+    float4 kc[4];
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+      kc[s] = kn[s];
+      kn[s] = __ldg((const float4*)row_ptr(r0 + 4 + s));
+    }
+    float sum[4];
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+      const int j = min(wrow + nwr * (r0 + s), last);
+      float x[4] = {fmaf(kc[s].x, C2, pqb[0]), fmaf(kc[s].y, C2, pqb[1]), fmaf(kc[s].z, C2, pqb[2]), fmaf(kc[s].w, C2, pqb[3])};
+      if (F_T > 0) {
+        const float4 f0 = *(const float4*)(fbuf + j * 8);
+        const float4 f1 = FR > 4 ? *(const float4*)(fbuf + j * 8 + 4) : make_float4(0, 0, 0, 0);
+        const float fj[8] = {f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w};
+#pragma unroll
+        for (int c = 0; c < FR; ++c)
+#pragma unroll
+          for (int i = 0; i < 4; ++i) x[i] = fmaf(fj[c], wl[c][i], x[i]);
+      }
+      float acc = 0.f;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) acc = fmaf(vv[i], rcp_approx(ex2_approx(x[i]) + 1.f), acc);
+      sum[s] = acc;
+    }
+    // transpose-reduce 4 rows x 32 lanes: afterwards lanes [8q, 8q+8) hold the total of row q
+    const bool b4 = lane & 16, b3 = lane & 8;
+    float a0 = b4 ? sum[2] : sum[0], a1 = b4 ? sum[3] : sum[1];
+    a0 += __shfl_xor_sync(0xffffffffu, b4 ? sum[0] : sum[2], 16);
+    a1 += __shfl_xor_sync(0xffffffffu, b4 ? sum[1] : sum[3], 16);
+    float c = b3 ? a1 : a0;
+    c += __shfl_xor_sync(0xffffffffu, b3 ? a0 : a1, 8);
+    c += __shfl_xor_sync(0xffffffffu, c, 4);
+    c += __shfl_xor_sync(0xffffffffu, c, 2);
+    c += __shfl_xor_sync(0xffffffffu, c, 1);
+    const int jq = wrow + nwr * (r0 + (lane >> 3));
+    if ((lane & 7) == 0 && jq < len) eo[jq] = c;
+  }
+}
+
+// context = alignments @ values for one row: warp per memory row, lanes over float4 chunks of the depth.
+// CH = float4 chunks per lane per memory row (Dv = 4 * Cq; Cq <= 32: CH = 1 and 32 / Cq rows per warp pass;
+// Cq = 64 / 128: CH = 2 / 4).  part = NW * Dv floats of shared memory.
+template <int CH>
+__device__ void attention_context_vec(const float* __restrict__ vb, const float* align, int len, int Dv,
+                                      float* part, float* ctx_out /* smem [Dv] */) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int Cq = Dv >> 2;
+  const int lpr = CH > 1 ? 32 : Cq;      // lanes per memory row
+  const int G = 32 / lpr;                // memory rows per warp pass
+  const int c0 = lane % lpr, g = lane / lpr;
+  float4 acc[CH];
+#pragma unroll
+  for (int c = 0; c < CH; ++c) acc[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+  constexpr int UN = CH > 1 ? 4 : 8;     // rows in flight per lane
+  const int stride = NW * G;
+  for (int j0 = warp * G + g; j0 < len; j0 += UN * stride) {
+    float4 v[UN][CH];
+    float a[UN];
+#pragma unroll
+    for (int s = 0; s < UN; ++s) {
+      const int j = j0 + s * stride;
+      const bool ok = j < len;
+      a[s] = ok ? align[j] : 0.f;
+#pragma unroll
+      for (int c = 0; c < CH; ++c)
+        v[s][c] = ok ? __ldg((const float4*)(vb + (size_t)j * Dv) + c0 + 32 * c) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int s = 0; s < UN; ++s)
+#pragma unroll
+      for (int c = 0; c < CH; ++c) {
+        acc[c].x = fmaf(a[s], v[s][c].x, acc[c].x); acc[c].y = fmaf(a[s], v[s][c].y, acc[c].y);
+        acc[c].z = fmaf(a[s], v[s][c].z, acc[c].z); acc[c].w = fmaf(a[s], v[s][c].w, acc[c].w);
+      }
+  }
+  for (int o = lpr; o < 32; o <<= 1) {
+#pragma unroll
+    for (int c = 0; c < CH; ++c) {
+      acc[c].x += __shfl_xor_sync(0xffffffffu, acc[c].x, o); acc[c].y += __shfl_xor_sync(0xffffffffu, acc[c].y, o);
+      acc[c].z += __shfl_xor_sync(0xffffffffu, acc[c].z, o); acc[c].w += __shfl_xor_sync(0xffffffffu, acc[c].w, o);
+    }
+  }
+  if (g == 0) {
+#pragma unroll
+    for (int c = 0; c < CH; ++c) *((float4*)(part + (size_t)warp * Dv) + c0 + 32 * c) = acc[c];
+  }
+  __syncthreads();
+  for (int d = threadIdx.x; d < Dv; d += NT) {
+    float s = 0.f;
+#pragma unroll
+    for (int w = 0; w < NW; ++w) s += part[w * Dv + d];
+    ctx_out[d] = s;
+  }
+  __syncthreads();
 }
 
 // One (row, mechanism) item.  `sm` = ATT_SMEM_FLOATS floats of shared memory.  t = decoder step.
@@ -137,13 +320,28 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
   float* e = sm;                         // [MAX_T] energies -> softmax probs a
   float* aprev = e + MAX_T;              // [MAX_T + 2*HALO]
   float* alpha = aprev + MAX_T + 2 * HALO;  // [MAX_T]
-  float* fbuf = alpha + MAX_T;           // [MAX_T * 8] location features; later scratch
-  float* part = fbuf + 8 * MAX_T;        // [NT] context partials
-  float* s32 = part + NT;                // [32] block-reduce scratch
+  float* fbuf = alpha + MAX_T;           // [MAX_T * 8] location features; later the context partials [NW * Dv]
+  float* nal = fbuf + 8 * MAX_T;         // [MAX_T] normalised forward variable
+  float* e2 = nal + MAX_T;               // [MAX_T] partial energies of units [128,256)
+  float* part = e2 + MAX_T;              // [NT] context partials of the scalar path
+  float* ctxs = part + NT;               // [MAX_DV] context of this row
+  float* s32 = ctxs + MAX_DV;            // [32] block-reduce scratch
   const int tid = threadIdx.x;
   const bool loc = (m.kind == SAT_ATT_FORWARD || m.kind == SAT_ATT_LOCATION_SENSITIVE);
   const bool fwd = (m.kind == SAT_ATT_FORWARD);
   float* align = e;  // the alignments handed to the context / history
+  long long tp = 0;
+  int ps = 0;
+  const bool profiling = m.prof && blockIdx.x == 0 && tid == 0;
+  if (profiling) tp = clock64();
+  auto stamp = [&]() {
+    if (profiling) {
+      const long long now = clock64();
+      m.prof[ps] += now - tp;
+      tp = now;
+    }
+    ++ps;
+  };
 
   if (m.kind == SAT_ATT_TEACHER_FORCING) {
     // index = prev_index + 1 = t ; alignments = teacher_alignments[:, index]
@@ -158,6 +356,7 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
     if (fwd)
       for (int j = tid; j < T; j += NT) alpha[j] = __ldcg(m.st_alpha + (size_t)b * T + j);
     __syncthreads();
+    stamp();
     if (loc && m.F <= 8) {
       for (int i = tid; i < T * 8; i += NT) {
         const int j = i >> 3, c = i & 7;
@@ -170,11 +369,25 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
       }
       __syncthreads();
     }
-    if (!loc) attention_energies<0>(m, b, T, len, aprev, fbuf, e);
-    else if (m.F == 5) attention_energies<5>(m, b, T, len, aprev, fbuf, e);
-    else if (m.F <= 8) attention_energies<8>(m, b, T, len, aprev, fbuf, e);
-    else attention_energies<-1>(m, b, T, len, aprev, fbuf, e);
+    stamp();
+    if (m.Up >= 128 && (!loc || m.F <= 8)) {
+      if (!loc) attention_energies_w32<0>(m, b, T, len, fbuf, e, e2);
+      else if (m.F <= 4) attention_energies_w32<4>(m, b, T, len, fbuf, e, e2);
+      else if (m.F == 5) attention_energies_w32<5>(m, b, T, len, fbuf, e, e2);
+      else attention_energies_w32<8>(m, b, T, len, fbuf, e, e2);
+      for (int j = len + tid; j < T; j += NT) {  // masked tail
+        e[j] = -INFINITY;
+        e2[j] = 0.f;
+      }
+    } else if (!loc) attention_energies<0>(m, b, T, len, aprev, fbuf, e, e2);
+    else if (m.F <= 4) attention_energies<4>(m, b, T, len, aprev, fbuf, e, e2);
+    else if (m.F == 5) attention_energies<5>(m, b, T, len, aprev, fbuf, e, e2);
+    else if (m.F <= 8) attention_energies<8>(m, b, T, len, aprev, fbuf, e, e2);
+    else attention_energies<-1>(m, b, T, len, aprev, fbuf, e, e2);
     __syncthreads();
+    if (m.Up > 128)
+      for (int j = tid; j < T; j += NT) e[j] += e2[j];
+    stamp();
     // masked softmax (TF: softmax(where(j < len, score, -inf)))
     float mx = -INFINITY;
     for (int j = tid; j < T; j += NT) mx = fmaxf(mx, e[j]);
@@ -191,7 +404,6 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
     if (fwd) {
       // alpha' = ((1-u) alpha + u shift(alpha) + 1e-7) * a ; alpha = alpha' / sum(alpha')
       const float u = __ldcg(m.st_u + b);
-      float* nal = fbuf;
       float s2 = 0.f;
       for (int j = tid; j < T; j += NT) {
         const float sh = j > 0 ? alpha[j - 1] : 0.f;
@@ -212,35 +424,53 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
   }
   if (m.out_align)
     for (int j = tid; j < T; j += NT) m.out_align[((size_t)b * m.out_S + t) * T + j] = align[j];
+  ps = 3;
+  stamp();
 
-  // context = alignments @ values  (threads: d fastest, groups split j)
-  const int Dv = m.Dv;
-  const int G = max(1, NT / Dv);
-  const int d = tid % Dv, grp = tid / Dv;
-  float c = 0.f;
-  if (grp < G && tid < G * Dv) {
-    const float* vb = m.values + (size_t)b * T * Dv + d;
+  // context = alignments @ values
+  const int Dv = m.Dv, Cq = Dv >> 2;
+  const float* vb = m.values + (size_t)b * T * Dv;
+  const bool vec = (Dv & 3) == 0 && (Cq & (Cq - 1)) == 0 && Cq <= 128 && ((((size_t)vb) & 15) == 0);
+  if (vec) {
+    float* cpart = fbuf;  // location features are dead by now
+    if (Cq <= 32) attention_context_vec<1>(vb, align, len, Dv, cpart, ctxs);
+    else if (Cq == 64) attention_context_vec<2>(vb, align, len, Dv, cpart, ctxs);
+    else attention_context_vec<4>(vb, align, len, Dv, cpart, ctxs);
+  } else {
+    const int G = max(1, NT / Dv);
+    const int d = tid % Dv, grp = tid / Dv;
+    float c = 0.f;
+    if (grp < G && tid < G * Dv) {
 #pragma unroll 4
-    for (int j = grp; j < len; j += G) c = fmaf(align[j], __ldg(vb + (size_t)j * Dv), c);
+      for (int j = grp; j < len; j += G) c = fmaf(align[j], __ldg(vb + (size_t)j * Dv + d), c);
+    }
+    part[tid] = c;
+    __syncthreads();
+    if (tid < Dv) {
+      float ctx = 0.f;
+      for (int g = 0; g < G; ++g) ctx += part[g * Dv + tid];
+      ctxs[tid] = ctx;
+    }
+    __syncthreads();
   }
-  part[tid] = c;
-  __syncthreads();
-  float ctx = 0.f;
-  if (tid < Dv) {
-    for (int g = 0; g < G; ++g) ctx += part[g * Dv + tid];
+  stamp();
+  for (int d = tid; d < Dv; d += NT) {
+    const float ctx = ctxs[d];
 #pragma unroll
     for (int i = 0; i < 2; ++i)
-      if (m.ctx_dst[i]) m.ctx_dst[i][(size_t)tid * m.ctx_sd + (size_t)b * m.ctx_sb] = ctx;
+      if (m.ctx_dst[i]) m.ctx_dst[i][(size_t)d * m.ctx_sd[i] + (size_t)b * m.ctx_sb[i]] = m.ctx_tf32 ? tc::round_tf32(ctx) : ctx;
   }
   if (fwd && m.agent) {
     // u = sigmoid([context, processed_query] . Wt + bt)   forward_attention.py:111-114
-    float z = (tid < Dv) ? ctx * __ldg(m.Wt + tid) : 0.f;
+    float z = 0.f;
+    for (int d = tid; d < Dv; d += NT) z = fmaf(ctxs[d], __ldg(m.Wt + d), z);
     for (int u = tid; u < m.U; u += NT)
       z = fmaf(__ldcg(m.pq + (size_t)u * m.pq_su + (size_t)b * m.pq_sb), __ldg(m.Wt + Dv + u), z);
     z = block_sum(z, s32);
     if (tid == 0) m.st_u[b] = sigmoidf_(z + m.bt);
   }
   __syncthreads();
+  stamp();
 }
 
 }  // namespace dec

@@ -14,12 +14,14 @@
 // with one grid-wide barrier between consecutive phases.
 #pragma once
 #include "decoder_attn.cuh"
+#include "decoder_tc.cuh"
 
 namespace sat {
 namespace dec {
 
-constexpr int N_PROF = 16;
+constexpr int N_PROF = 32;  // [0,16) phases of a step, [16,24) stages of the attention item (CTA 0)
 constexpr int SCRATCH_FLOATS = (RED_FLOATS > ATT_SMEM_FLOATS ? RED_FLOATS : ATT_SMEM_FLOATS);
+constexpr int TC_SCRATCH_FLOATS = (TC_STAGES * TC_STAGE_BYTES + 1024) / 4;  // ring + alignment slack
 
 struct SaHop {
   DenseDesc qkv, o, tr;
@@ -45,11 +47,17 @@ struct DecParams {
   int *stop_steps, *n_steps;
   unsigned* barrier;
   long long* prof;  // [N_PROF] accumulated SM cycles per phase (CTA 0), may be null
+  // ---- tensor-core mode (B >= 64): LSTM inputs att_in / l1_in / l2_in are ROW-major [RB*128][K*_pad] ----
+  int tc, RB, Ka_pad, K1_pad, K2_pad;
+  int scratch_floats;       // phase scratch at the head of dynamic smem (>= SCRATCH_FLOATS; holds the TMA ring in tc mode)
+  TcLstmDesc tc_a, tc_1, tc_2;
+  const CUtensorMap* maps;  // [6]: att_in[0,1], l1_in[0,1], l2_in[0,1]
+  float* qfm;               // feature-major copy of the attention-LSTM output (query) for the SIMT query layers
 };
 
 struct DenseEpi {
   const float* bias; int N, ld, act;
-  float* dst; float* dst2; const float* addend;  // feature-major [n][ld]
+  Act2D dst; float* dst2; const float* addend;  // dst2 / addend feature-major [n][ld]
   __device__ __forceinline__ void operator()(int b, int tile, int ul, const float* g) const {
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
@@ -59,7 +67,7 @@ struct DenseEpi {
       if (act == 1) v = fmaxf(v, 0.f);
       else if (act == 2) v = tanhf(v);
       if (addend) v += __ldcg(addend + (size_t)n * ld + b);
-      dst[(size_t)n * ld + b] = v;
+      dst.put(n, b, v);
       if (dst2) dst2[(size_t)n * ld + b] = v;
     }
   }
@@ -190,15 +198,43 @@ __device__ inline void softmax_feed_item(const DecParams& p, int b, int t, float
 __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_constant__ DecParams p) {
   extern __shared__ __align__(16) float smem[];
   float* scratch = smem;                  // SCRATCH_FLOATS: reduction / row-phase scratch
-  float* wres = smem + SCRATCH_FLOATS;    // resident LSTM tiles
+  float* wres = smem + p.scratch_floats;  // resident LSTM tiles / tensor-core weight images
   __shared__ int s_stopped[MAX_B];
   GridBarrier bar{p.barrier, 0u};
   const int tid = threadIdx.x;
   const int ld = p.ld;
 
-  load_resident(p.lstm_a, p.R, wres);
-  load_resident(p.lstm_1, p.R, wres);
-  load_resident(p.lstm_2, p.R, wres);
+  __shared__ __align__(8) uint64_t s_tcbar[2 * TC_STAGES + 1];
+  __shared__ uint32_t s_tmem;
+  TcState tcs;
+  tcs.ring = (uint8_t*)(((uintptr_t)scratch + 1023) & ~(uintptr_t)1023);
+  tcs.wimg = (uint8_t*)(((uintptr_t)wres + 1023) & ~(uintptr_t)1023);
+  tcs.full = s_tcbar;
+  tcs.empty = s_tcbar + TC_STAGES;
+  tcs.done = s_tcbar + 2 * TC_STAGES;
+  tcs.tmem = 0;
+  tcs.n_chunks = 0;
+  tcs.n_items = 0;
+  tcs.prof = p.prof ? p.prof + 24 : nullptr;
+  if (p.tc) {
+    if (tid == 0) {
+      for (int i = 0; i < 2 * TC_STAGES + 1; ++i) tc::mbar_init(s_tcbar + i, 1);
+      tc::fence_mbar_init();
+    }
+    if (tid < 32) tc::tmem_alloc(&s_tmem, 32);
+    tc_load_resident(p.tc_a, p.RB, tcs);
+    tc_load_resident(p.tc_1, p.RB, tcs);
+    tc_load_resident(p.tc_2, p.RB, tcs);
+    tc::fence_proxy_async();
+    tc::tc_fence_before();
+    __syncthreads();
+    tc::tc_fence_after();
+    tcs.tmem = s_tmem;
+  } else {
+    load_resident(p.lstm_a, p.R, wres);
+    load_resident(p.lstm_1, p.R, wres);
+    load_resident(p.lstm_2, p.R, wres);
+  }
   for (int i = tid; i < MAX_B; i += NT) s_stopped[i] = -1;
   __syncthreads();
 
@@ -221,21 +257,28 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
     if (p.prof && blockIdx.x == 0 && tid == 0) tprev = clock64();
     // ---- A: prenet layer 0 ----
     dense_phase(p.pre0, p.xin, ld, p.Bp, p.R, wres, scratch,
-                DenseEpi{p.pre0.bias, p.pre0.N, ld, 1, p.p0, nullptr, p.ms ? p.spk_term : nullptr});
+                DenseEpi{p.pre0.bias, p.pre0.N, ld, 1, Act2D{p.p0, ld, 1, 0}, nullptr, p.ms ? p.spk_term : nullptr});
     phase_end();
     const float* pin = p.p0;
     if (p.ms) {
       dense_phase(p.msd, p.p0, ld, p.Bp, p.R, wres, scratch,
-                  DenseEpi{p.msd.bias, p.msd.N, ld, 1, p.p0b, nullptr, nullptr});
+                  DenseEpi{p.msd.bias, p.msd.N, ld, 1, Act2D{p.p0b, ld, 1, 0}, nullptr, nullptr});
       phase_end();
       pin = p.p0b;
     }
     // ---- B: prenet layer 1 -> attention-LSTM input rows [0, P1) ----
     dense_phase(p.pre1, pin, ld, p.Bp, p.R, wres, scratch,
-                DenseEpi{p.pre1.bias, p.pre1.N, ld, 1, p.att_in[cur], nullptr, nullptr});
+                DenseEpi{p.pre1.bias, p.pre1.N, ld, 1, Act2D{p.att_in[cur], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc}, nullptr, nullptr});
     phase_end();
     // ---- C: attention LSTM ----
-    {
+    if (p.tc) {
+      const int h0 = p.P1 + p.Dctx;
+      TcLstmIO io{p.maps + cur, Act2D{p.att_in[cur] + h0, 1, p.Ka_pad, 1}, Act2D{p.l1_in[cur], 1, p.K1_pad, 1},
+                  Act2D{p.qfm, ld, 1, 0}, Act2D{p.att_in[nxt] + h0, 1, p.Ka_pad, 1}, p.c_a, nullptr, 0, 0};
+      tc::fence_proxy_async();
+      __syncthreads();
+      lstm_phase_tc(p.tc_a, io, p.B, p.Bp, ld, p.RB, p.zc, p.zh, tcs);
+    } else {
       const size_t hoff = (size_t)(p.P1 + p.Dctx) * ld;
       dense_phase(p.lstm_a, p.att_in[cur], ld, p.Bp, p.R, wres, scratch,
                   LstmEpi{p.lstm_a.bias, p.A, ld, p.B, p.c_a, p.att_in[cur] + hoff, p.l1_in[cur],
@@ -247,23 +290,41 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
     for (int mi = 0; mi < p.n_mech; ++mi)
       if (p.mech[mi].kind != SAT_ATT_TEACHER_FORCING) {
         any_q = true;
-        dense_phase(p.dq[mi], p.l1_in[cur], ld, p.Bp, p.R, wres, scratch,
-                    DenseEpi{p.dq[mi].bias, p.dq[mi].N, ld, 0, const_cast<float*>(p.mech[mi].pq), nullptr, nullptr});
+        dense_phase(p.dq[mi], p.tc ? p.qfm : p.l1_in[cur], ld, p.Bp, p.R, wres, scratch,
+                    DenseEpi{p.dq[mi].bias, p.dq[mi].N, ld, 0, Act2D{const_cast<float*>(p.mech[mi].pq), ld, 1, 0}, nullptr, nullptr});
       }
     if (any_q) phase_end();
     // ---- E: attention mechanisms (row split) ----
     for (int item = blockIdx.x; item < p.B * p.n_mech; item += gridDim.x) {
       const int b = item / p.n_mech, mi = item % p.n_mech;
       AttMech m = p.mech[mi];
-      m.ctx_dst[0] = p.att_in[nxt] + (size_t)(p.P1 + (mi ? p.mech[0].Dv : 0)) * ld;
-      m.ctx_dst[1] = p.l1_in[cur] + (size_t)(p.A + (mi ? p.mech[0].Dv : 0)) * ld;
-      m.ctx_sd = ld;
-      m.ctx_sb = 1;
+      const int coff = mi ? p.mech[0].Dv : 0;
+      if (p.tc) {
+        m.ctx_dst[0] = p.att_in[nxt] + p.P1 + coff;
+        m.ctx_dst[1] = p.l1_in[cur] + p.A + coff;
+        m.ctx_sd[0] = m.ctx_sd[1] = 1;
+        m.ctx_sb[0] = p.Ka_pad;
+        m.ctx_sb[1] = p.K1_pad;
+        m.ctx_tf32 = 1;
+      } else {
+        m.ctx_dst[0] = p.att_in[nxt] + (size_t)(p.P1 + coff) * ld;
+        m.ctx_dst[1] = p.l1_in[cur] + (size_t)(p.A + coff) * ld;
+        m.ctx_sd[0] = m.ctx_sd[1] = ld;
+        m.ctx_sb[0] = m.ctx_sb[1] = 1;
+      }
+      m.prof = p.prof ? p.prof + 16 : nullptr;
       attention_item(m, b, t, p.T, (int)p.lengths[b], scratch);
     }
     phase_end();
     // ---- F: decoder LSTM 1 ----
-    {
+    if (p.tc) {
+      const int h0 = p.A + p.Dctx;
+      TcLstmIO io{p.maps + 2 + cur, Act2D{p.l1_in[cur] + h0, 1, p.K1_pad, 1}, Act2D{p.l2_in[cur], 1, p.K2_pad, 1},
+                  Act2D{nullptr, 0, 0, 0}, Act2D{p.l1_in[nxt] + h0, 1, p.K1_pad, 1}, p.c_1, nullptr, 0, 0};
+      tc::fence_proxy_async();
+      __syncthreads();
+      lstm_phase_tc(p.tc_1, io, p.B, p.Bp, ld, p.RB, p.zc, p.zh, tcs);
+    } else {
       const size_t hoff = (size_t)(p.A + p.Dctx) * ld;
       dense_phase(p.lstm_1, p.l1_in[cur], ld, p.Bp, p.R, wres, scratch,
                   LstmEpi{p.lstm_1.bias, p.Dd, ld, p.B, p.c_1, p.l1_in[cur] + hoff, p.l2_in[cur],
@@ -271,7 +332,15 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
     }
     phase_end();
     // ---- G: decoder LSTM 2 ----
-    {
+    if (p.tc) {
+      const int h0 = p.Dd;
+      TcLstmIO io{p.maps + 4 + cur, Act2D{p.l2_in[cur] + h0, 1, p.K2_pad, 1}, Act2D{p.dout, ld, 1, 0},
+                  Act2D{nullptr, 0, 0, 0}, Act2D{p.l2_in[nxt] + h0, 1, p.K2_pad, 1}, p.c_2, p.dec_out,
+                  p.max_steps * p.Dd, t * p.Dd};
+      tc::fence_proxy_async();
+      __syncthreads();
+      lstm_phase_tc(p.tc_2, io, p.B, p.Bp, ld, p.RB, p.zc, p.zh, tcs);
+    } else {
       const size_t hoff = (size_t)p.Dd * ld;
       dense_phase(p.lstm_2, p.l2_in[cur], ld, p.Bp, p.R, wres, scratch,
                   LstmEpi{p.lstm_2.bias, p.Dd, ld, p.B, p.c_2, p.l2_in[cur] + hoff, p.dout,
@@ -289,10 +358,10 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
         sa_item(p, h, item / p.heads, item % p.heads, t, scratch);
       phase_end();
       dense_phase(h.o, p.sa_ctx, ld, p.Bp, p.R, wres, scratch,
-                  DenseEpi{h.o.bias, h.o.N, ld, 0, p.sa_a, nullptr, nullptr});
+                  DenseEpi{h.o.bias, h.o.N, ld, 0, Act2D{p.sa_a, ld, 1, 0}, nullptr, nullptr});
       phase_end();
       dense_phase(h.tr, p.sa_a, ld, p.Bp, p.R, wres, scratch,
-                  DenseEpi{h.tr.bias, h.tr.N, ld, 2, p.sa_y[hi & 1], nullptr, y});
+                  DenseEpi{h.tr.bias, h.tr.N, ld, 2, Act2D{p.sa_y[hi & 1], ld, 1, 0}, nullptr, y});
       phase_end();
       y = p.sa_y[hi & 1];
     }
@@ -333,6 +402,11 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
     }
   }
   if (blockIdx.x == 0 && tid == 0) *p.n_steps = t;
+  if (p.tc) {
+    tc::tc_fence_before();
+    __syncthreads();
+    if (tid < 32) tc::tmem_dealloc(tcs.tmem, 32);
+  }
 }
 
 }  // namespace dec

@@ -95,7 +95,7 @@ class DecoderHandle:
         return ms.value
 
     def profile(self, reset=True):
-        out = (C.c_int64 * 16)()
+        out = (C.c_int64 * 32)()
         check(lib().sat_decoder_profile(self._h, out, int(reset)))
         return list(out)
 
