@@ -31,9 +31,13 @@ def run(cfg, B, T, S, feed, reps=3):
     print(f"{cfg} B={B} T={T} S={S} feed={feed}: {ms:.2f} ms/run, {ms*1e3/S:.1f} us/step, "
           f"{B*S*hp.outputs_per_step/ms*1e3:.3e} frames/s, bytes/step {by/1e6:.1f} MB -> {by/(ms*1e-3/S)/1e9:.0f} GB/s")
     tot = sum(prof[:16]) or 1
-    clk = 1.9e3  # cycles per us (approx)
+    clk = sum(prof[:16]) / (ms * 1e3 * reps)  # SM cycles per us, from CTA 0's phase counters over the event time
+    print(f"  SM clock ~{clk:.0f} MHz")
     print("  phase us/step:", " ".join(f"{p/clk/S/reps:.1f}" for p in prof[:16] if p))
     print("  attention stages us/step (CTA0):", " ".join(f"{p/clk/S/reps:.1f}" for p in prof[16:24]))
+    if prof[30]:
+        nb = int(os.environ.get("SAT_BENCH_BARRIERS", "0"))
+        print("  empty grid barrier: %.2f us each" % (prof[30] / clk / nb / reps))
     print("  tc lstm (3 phases summed) us/step: producer %.1f, until accumulator ready %.1f, cell update %.1f" % tuple(p/clk/S/reps for p in prof[24:27]))
 
 if __name__ == "__main__" and len(sys.argv) > 1:

@@ -347,6 +347,7 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
       smem_bytes = p.scratch_floats * sizeof(float) + 1024 + (size_t)off;
       if (smem_bytes > h->max_dyn_smem) use_tc = false;  // resident images do not fit: SIMT form
     }
+    if (const char* e = getenv("SAT_BENCH_BARRIERS")) p.bench_barriers = atoi(e);
     p.tc = use_tc ? 1 : 0;
     if (!use_tc) p.scratch_floats = SCRATCH_FLOATS;
     p.RB = RB;
@@ -431,7 +432,7 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
       m.values = io.memory[i];
       m.v = h->att_v[i]; m.ba = h->att_ba[i]; m.conv_w = h->conv_w[i]; m.conv_b = h->conv_b[i]; m.Wl = h->Wl[i];
       m.Wt = h->Wt[i]; m.bt = h->bt[i];
-      m.pq = ws + o_pq[i]; m.pq_su = ld; m.pq_sb = 1;
+      m.pq = ws + o_pq[i]; m.pq_su = 1; m.pq_sb = m.Up;  // row-major [b][Up]: one 16-byte load per lane
       m.st_align = ws + o_sal[i]; m.st_alpha = ws + o_sap[i]; m.st_u = ws + o_su[i];
       m.out_align = io.alignments[i]; m.out_S = S;
       p.dq[i] = h->dq[i].desc();

@@ -198,18 +198,34 @@ __device__ void attention_energies_w32(const AttMech& m, int b, int T, int len, 
   const int nwr = two ? NW / 2 : NW;
   const int u0 = half * 128 + 4 * lane;
   float pqb[4], vv[4], wl[FR][4];
+  {
+    // per-unit constants: one 16-byte load each (all arrays are padded to Up with zeros)
+    float4 q4;
+    if (m.pq_su == 1) {
+      q4 = __ldcg((const float4*)(m.pq + (size_t)b * m.pq_sb + u0));
+    } else {
+      q4.x = __ldcg(m.pq + (size_t)(u0 + 0) * m.pq_su + (size_t)b * m.pq_sb);
+      q4.y = __ldcg(m.pq + (size_t)(u0 + 1) * m.pq_su + (size_t)b * m.pq_sb);
+      q4.z = __ldcg(m.pq + (size_t)(u0 + 2) * m.pq_su + (size_t)b * m.pq_sb);
+      q4.w = __ldcg(m.pq + (size_t)(u0 + 3) * m.pq_su + (size_t)b * m.pq_sb);
+    }
+    const float4 b4 = __ldg((const float4*)(m.ba + u0)), v4 = __ldg((const float4*)(m.v + u0));
+    const float q[4] = {q4.x, q4.y, q4.z, q4.w}, bb[4] = {b4.x, b4.y, b4.z, b4.w}, v[4] = {v4.x, v4.y, v4.z, v4.w};
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int u = u0 + i;
-    pqb[i] = u < m.U ? C2 * (__ldcg(m.pq + (size_t)u * m.pq_su + (size_t)b * m.pq_sb) + __ldg(m.ba + u)) : 0.f;
-    vv[i] = -2.f * __ldg(m.v + u);
+    for (int i = 0; i < 4; ++i) {
+      pqb[i] = u0 + i < m.U ? C2 * (q[i] + bb[i]) : 0.f;
+      vv[i] = -2.f * v[i];
+    }
     if (F_T > 0) {
 #pragma unroll
-      for (int c = 0; c < FR; ++c) wl[c][i] = c < m.F ? C2 * __ldg(m.Wl + c * m.Up + u) : 0.f;
+      for (int c = 0; c < FR; ++c) {
+        float4 w4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (c < m.F) w4 = __ldg((const float4*)(m.Wl + c * m.Up + u0));
+        wl[c][0] = C2 * w4.x; wl[c][1] = C2 * w4.y; wl[c][2] = C2 * w4.z; wl[c][3] = C2 * w4.w;
+      }
     }
   }
   const float* kbase = m.keys + (size_t)b * T * m.Up + u0;
-  const size_t rstride = (size_t)nwr * m.Up;  // floats between consecutive rows of this warp
   const int last = len - 1;
   float* eo = half ? e2 : e;
   // rows of this warp: j = wrow + nwr * r, r = 0, 1, ...; out-of-range rows are clamped to `last` and discarded
@@ -358,14 +374,31 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
     __syncthreads();
     stamp();
     if (loc && m.F <= 8) {
-      for (int i = tid; i < T * 8; i += NT) {
-        const int j = i >> 3, c = i & 7;
-        float f = 0.f;
-        if (c < m.F) {
-          f = __ldg(m.conv_b + c);
-          for (int k = 0; k < m.Kc; ++k) f = fmaf(__ldg(m.conv_w + k * m.F + c), aprev[HALO + j + k - m.pad_left], f);
+      // location features f[j][c] = b_c + sum_k w[k][c] a[j - pad + k]: a thread owns filter c = tid & 7 and four
+      // consecutive positions, sliding a 4-wide register window over the taps (1 weight + 1 alignment LDS per tap)
+      float* wsm = part;  // [Kc * 8] taps, zero-filled for c >= F
+      for (int i = tid; i < m.Kc * 8; i += NT) wsm[i] = (i & 7) < m.F ? __ldg(m.conv_w + (i >> 3) * m.F + (i & 7)) : 0.f;
+      __syncthreads();
+      const int c = tid & 7;
+      const float cb = c < m.F ? __ldg(m.conv_b + c) : 0.f;
+      for (int j0 = 4 * (tid >> 3); j0 < T; j0 += 4 * (NT / 8)) {
+        const float* a = aprev + HALO + j0 - m.pad_left;
+        float f0 = cb, f1 = cb, f2 = cb, f3 = cb;
+        float x0 = a[0], x1 = a[1], x2 = a[2];
+        for (int k = 0; k < m.Kc; ++k) {
+          const float x3 = a[k + 3], w = wsm[k * 8 + c];
+          f0 = fmaf(w, x0, f0);
+          f1 = fmaf(w, x1, f1);
+          f2 = fmaf(w, x2, f2);
+          f3 = fmaf(w, x3, f3);
+          x0 = x1;
+          x1 = x2;
+          x2 = x3;
         }
-        fbuf[i] = f;
+        fbuf[j0 * 8 + c] = f0;
+        if (j0 + 1 < T) fbuf[(j0 + 1) * 8 + c] = f1;
+        if (j0 + 2 < T) fbuf[(j0 + 2) * 8 + c] = f2;
+        if (j0 + 3 < T) fbuf[(j0 + 3) * 8 + c] = f3;
       }
       __syncthreads();
     }

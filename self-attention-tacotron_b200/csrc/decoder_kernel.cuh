@@ -49,6 +49,7 @@ struct DecParams {
   long long* prof;  // [N_PROF] accumulated SM cycles per phase (CTA 0), may be null
   // ---- tensor-core mode (B >= 64): LSTM inputs att_in / l1_in / l2_in are ROW-major [RB*128][K*_pad] ----
   int tc, RB, Ka_pad, K1_pad, K2_pad;
+  int bench_barriers;       // diagnostic: time this many empty grid barriers before the loop (prof[30])
   int scratch_floats;       // phase scratch at the head of dynamic smem (>= SCRATCH_FLOATS; holds the TMA ring in tc mode)
   TcLstmDesc tc_a, tc_1, tc_2;
   const CUtensorMap* maps;  // [6]: att_in[0,1], l1_in[0,1], l2_in[0,1]
@@ -134,23 +135,69 @@ struct OutEpi {
   }
 };
 
-// decoder self-attention over the KV cache for one (row, head): last-row causal attention
+// decoder self-attention over the KV cache for one (row, head): last-row causal attention.
+// Scores: a lane owns one float4 of the head dimension, 32 / (dh/4) cache rows per warp pass, four passes in
+// flight; dh = 128 uses the 4-row transpose-reduction.  Context: attention_context_vec (warp per cache row).
 __device__ inline void sa_item(const DecParams& p, const SaHop& h, int b, int hd, int t, float* sm) {
   const int dh = p.Ds / p.heads, n = t + 1, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  float* sc = sm;             // [n]
+  float* sc = sm;             // [n] scores -> probabilities (n <= 8192)
   float* q = sm + 8192;       // [dh]
-  float* part = q + 512;      // [NT]
-  float* s32 = part + NT;
-  for (int d = tid; d < dh; d += NT) q[d] = __ldcg(p.sa_q + (size_t)(hd * dh + d) * p.ld + b);
+  float* part = q + 512;      // [NW * dh] context partials / [NT] scalar-path partials
+  float* ctxs = part + NW * 128;  // [dh] (vector path needs dh <= 128)
+  float* s32 = ctxs + 512;
+  const float scale = 1.f / sqrtf((float)dh);
+  for (int d = tid; d < dh; d += NT) q[d] = __ldcg(p.sa_q + (size_t)(hd * dh + d) * p.ld + b) * scale;
   __syncthreads();
   const float* kb = h.kcache + ((size_t)b * p.heads + hd) * p.Smax * dh;
   const float* vb = h.vcache + ((size_t)b * p.heads + hd) * p.Smax * dh;
-  const float scale = 1.f / sqrtf((float)dh);
-  for (int j = warp; j < n; j += NW) {
-    float s = 0.f;
-    for (int d = lane; d < dh; d += 32) s = fmaf(q[d], __ldcg(kb + (size_t)j * dh + d), s);
-    s = warp_sum(s);
-    if (lane == 0) sc[j] = s * scale;
+  const int Cq = dh >> 2;
+  const bool vec = (dh & 3) == 0 && (Cq & (Cq - 1)) == 0 && Cq <= 32;
+  if (vec) {
+    const int G = 32 / Cq, c0 = lane % Cq, g = lane / Cq;
+    const float4 q4 = *(const float4*)(q + 4 * c0);
+    const int stride = NW * G, last = n - 1;
+    const float* kl = kb + 4 * c0;
+    auto rowp = [&](int r) { return (const float4*)(kl + (size_t)min(warp * G + g + stride * r, last) * dh); };
+    float4 kn[4];
+#pragma unroll
+    for (int s = 0; s < 4; ++s) kn[s] = __ldcg(rowp(s));
+    for (int r0 = 0; warp * G + stride * r0 < n; r0 += 4) {
+      float sum[4];
+#pragma unroll
+      for (int s = 0; s < 4; ++s) {
+        const float4 k4 = kn[s];
+        kn[s] = __ldcg(rowp(r0 + 4 + s));
+        sum[s] = fmaf(q4.x, k4.x, fmaf(q4.y, k4.y, fmaf(q4.z, k4.z, q4.w * k4.w)));
+      }
+      if (Cq == 32) {
+        const bool b4 = lane & 16, b3 = lane & 8;
+        float a0 = b4 ? sum[2] : sum[0], a1 = b4 ? sum[3] : sum[1];
+        a0 += __shfl_xor_sync(0xffffffffu, b4 ? sum[0] : sum[2], 16);
+        a1 += __shfl_xor_sync(0xffffffffu, b4 ? sum[1] : sum[3], 16);
+        float c = b3 ? a1 : a0;
+        c += __shfl_xor_sync(0xffffffffu, b3 ? a0 : a1, 8);
+        c += __shfl_xor_sync(0xffffffffu, c, 4);
+        c += __shfl_xor_sync(0xffffffffu, c, 2);
+        c += __shfl_xor_sync(0xffffffffu, c, 1);
+        const int jq = warp + stride * (r0 + (lane >> 3));
+        if ((lane & 7) == 0 && jq < n) sc[jq] = c;
+      } else {
+#pragma unroll
+        for (int s = 0; s < 4; ++s) {
+          float c = sum[s];
+          for (int o = 1; o < Cq; o <<= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+          const int jq = warp * G + g + stride * (r0 + s);
+          if (c0 == 0 && jq < n) sc[jq] = c;
+        }
+      }
+    }
+  } else {
+    for (int j = warp; j < n; j += NW) {
+      float s = 0.f;
+      for (int d = lane; d < dh; d += 32) s = fmaf(q[d], __ldcg(kb + (size_t)j * dh + d), s);
+      s = warp_sum(s);
+      if (lane == 0) sc[j] = s;
+    }
   }
   __syncthreads();
   float mx = -INFINITY;
@@ -164,16 +211,22 @@ __device__ inline void sa_item(const DecParams& p, const SaHop& h, int b, int hd
   }
   sum = block_sum(sum, s32);
   const float inv = 1.f / sum;
-  const int G = max(1, NT / dh), d = tid % dh, grp = tid / dh;
-  float c = 0.f;
-  if (tid < G * dh)
-    for (int j = grp; j < n; j += G) c = fmaf(sc[j], __ldcg(vb + (size_t)j * dh + d), c);
-  part[tid] = c;
   __syncthreads();
-  if (tid < dh) {
-    float ctx = 0.f;
-    for (int g = 0; g < G; ++g) ctx += part[g * dh + tid];
-    p.sa_ctx[(size_t)(hd * dh + tid) * p.ld + b] = ctx * inv;
+  if (vec && ((((size_t)vb) & 15) == 0)) {
+    attention_context_vec<1>(vb, sc, n, dh, part, ctxs);
+    for (int d = tid; d < dh; d += NT) p.sa_ctx[(size_t)(hd * dh + d) * p.ld + b] = ctxs[d] * inv;
+  } else {
+    const int G = max(1, NT / dh), d = tid % dh, grp = tid / dh;
+    float c = 0.f;
+    if (tid < G * dh)
+      for (int j = grp; j < n; j += G) c = fmaf(sc[j], __ldcg(vb + (size_t)j * dh + d), c);
+    part[tid] = c;
+    __syncthreads();
+    if (tid < dh) {
+      float ctx = 0.f;
+      for (int g = 0; g < G; ++g) ctx += part[g * dh + tid];
+      p.sa_ctx[(size_t)(hd * dh + tid) * p.ld + b] = ctx * inv;
+    }
   }
   __syncthreads();
 }
@@ -238,6 +291,12 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
   for (int i = tid; i < MAX_B; i += NT) s_stopped[i] = -1;
   __syncthreads();
 
+  if (p.bench_barriers > 0 && p.prof) {
+    bar.sync();
+    const long long c0 = clock64();
+    for (int i = 0; i < p.bench_barriers; ++i) bar.sync();
+    if (blockIdx.x == 0 && tid == 0) p.prof[30] += clock64() - c0;
+  }
   long long tprev = 0;
   int ph = 0;
   auto phase_end = [&]() {
@@ -291,7 +350,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
       if (p.mech[mi].kind != SAT_ATT_TEACHER_FORCING) {
         any_q = true;
         dense_phase(p.dq[mi], p.tc ? p.qfm : p.l1_in[cur], ld, p.Bp, p.R, wres, scratch,
-                    DenseEpi{p.dq[mi].bias, p.dq[mi].N, ld, 0, Act2D{const_cast<float*>(p.mech[mi].pq), ld, 1, 0}, nullptr, nullptr});
+                    DenseEpi{p.dq[mi].bias, p.dq[mi].N, ld, 0, Act2D{const_cast<float*>(p.mech[mi].pq), p.mech[mi].pq_su, p.mech[mi].pq_sb, 0}, nullptr, nullptr});
       }
     if (any_q) phase_end();
     // ---- E: attention mechanisms (row split) ----

@@ -131,22 +131,38 @@ __device__ inline void lstm_phase_tc(const TcLstmDesc& d, const TcLstmIO& io, in
       }
       const int b = row0 + q * 32 + lane;
       if (b < Bp) {
+        // 4 consecutive units of one row: the row-major buffers take one 16-byte access each
+        const int u0 = tile * 4;
+        const float4 hp4 = __ldcg((const float4*)io.hprev.at(u0, b));  // hprev / hz are always row-major here
+        const float hpv[4] = {hp4.x, hp4.y, hp4.z, hp4.w};
+        float hzv[4], hnv[4];
 #pragma unroll
         for (int ul = 0; ul < 4; ++ul) {
-          const int u = tile * 4 + ul;
-          if (u >= d.units) continue;
-          const float* bb = d.bias + (size_t)(2 * tile + (ul >> 1)) * TILE_N + (ul & 1) * 4;
-          const float gi = g[ul * 4 + 0] + __ldg(bb + 0), gj = g[ul * 4 + 1] + __ldg(bb + 1);
-          const float gf = g[ul * 4 + 2] + __ldg(bb + 2), go = g[ul * 4 + 3] + __ldg(bb + 3);
-          const size_t idx = (size_t)u * ld + b;
-          const float cp = io.c[idx], hp = __ldcg(io.hprev.at(u, b));
+          const float4 bb = __ldg((const float4*)(d.bias + (size_t)(2 * tile + (ul >> 1)) * TILE_N + (ul & 1) * 4));
+          const float gi = g[ul * 4 + 0] + bb.x, gj = g[ul * 4 + 1] + bb.y, gf = g[ul * 4 + 2] + bb.z, go = g[ul * 4 + 3] + bb.w;
+          const size_t idx = (size_t)(u0 + ul) * ld + b;
+          const float cp = io.c[idx];
           const float cn = sigmoidf_(gf + 1.0f) * cp + sigmoidf_(gi) * tanhf(gj);
           const float hn = sigmoidf_(go) * tanhf(cn);
           io.c[idx] = cn - zc * (cn - cp);
-          io.hz.put(u, b, hn - zh * (hn - hp));
-          io.out0.put(u, b, hn);
-          if (io.out1.p) io.out1.put(u, b, hn);
-          if (io.rm_out && b < B) io.rm_out[(size_t)b * io.rm_stride + io.rm_off + u] = hn;
+          hnv[ul] = hn;
+          hzv[ul] = tc::round_tf32(hn - zh * (hn - hpv[ul]));
+        }
+        *(float4*)io.hz.at(u0, b) = make_float4(hzv[0], hzv[1], hzv[2], hzv[3]);
+        if (io.out0.sd == 1) {
+          *(float4*)io.out0.at(u0, b) = make_float4(tc::round_tf32(hnv[0]), tc::round_tf32(hnv[1]),
+                                                    tc::round_tf32(hnv[2]), tc::round_tf32(hnv[3]));
+        } else {
+#pragma unroll
+          for (int ul = 0; ul < 4; ++ul) io.out0.put(u0 + ul, b, hnv[ul]);
+        }
+        if (io.out1.p) {
+#pragma unroll
+          for (int ul = 0; ul < 4; ++ul) io.out1.put(u0 + ul, b, hnv[ul]);
+        }
+        if (io.rm_out && b < B) {
+#pragma unroll
+          for (int ul = 0; ul < 4; ++ul) io.rm_out[(size_t)b * io.rm_stride + io.rm_off + u0 + ul] = hnv[ul];
         }
       }
       tc::tc_fence_before();
