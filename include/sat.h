@@ -161,12 +161,15 @@ int sat_dense_forward(const float* kernel_host, const float* bias_host, int32_t 
 /* table[ids - index_offset]  (tacotron2 Embedding; models/models.py:28,43-50): table host [rows,dim], ids device [n] */
 int sat_embedding_lookup(const float* table_host, int64_t table_rows, int32_t dim, int64_t index_offset,
                          const int64_t* ids, int64_t n, float* out, void* stream);
-/* cycles accumulated by CTA 0 of the persistent decoder kernel (profiling aid): 32 host slots,
- * [0,16) phases of a step, [16,24) stages of the attention item */
+/* cycles accumulated by CTA 0 of the persistent decoder kernel (profiling aid): 48 host slots,
+ * [0,16) phases of a step, [16,24) stages of the attention item, [24,27) tensor-core LSTM, [32,40) frame-item stages */
 int sat_decoder_profile(sat_decoder* h, int64_t* out16, int32_t reset);
 /* device time (ms) of the persistent decoder kernel of the last sat_decoder_run, from CUDA events recorded on the
  * launching stream around that launch; blocks until the kernel has finished */
 int sat_decoder_kernel_ms(sat_decoder* h, float* ms);
+/* 1 if the last sat_decoder_run computed the LSTM gate GEMMs on the tensor cores (tcgen05, fp16 operands, fp32
+ * accumulation; batch >= 64), 0 if it used the fp32 SIMT form */
+int sat_decoder_used_tensor_cores(sat_decoder* h, int32_t* used);
 
 /* diagnostic: one-CTA self-test of the tcgen05 / TMA / TMEM building blocks (csrc/tc.cuh):
  * D[128,16] = A[128,K] . Wt[16,K]^T in TF32 with fp32 accumulation; all pointers device, K % 32 == 0, K <= 1024 */

@@ -35,6 +35,7 @@ def run(cfg, B, T, S, feed, reps=3):
     print(f"  SM clock ~{clk:.0f} MHz")
     print("  phase us/step:", " ".join(f"{p/clk/S/reps:.1f}" for p in prof[:16] if p))
     print("  attention stages us/step (CTA0):", " ".join(f"{p/clk/S/reps:.1f}" for p in prof[16:24]))
+    print("  frame stages us/step (CTA0): load y, out proj, stores+feed, prenet0, prenet1(+ms), store:", " ".join(f"{p/clk/S/reps:.1f}" for p in prof[32:38]))
     if prof[30]:
         nb = int(os.environ.get("SAT_BENCH_BARRIERS", "0"))
         print("  empty grid barrier: %.2f us each" % (prof[30] / clk / nb / reps))

@@ -11,8 +11,10 @@ namespace {
 struct PackedDense {
   float* Wp = nullptr;
   float* bias = nullptr;
-  int K = 0, N = 0, n_tiles = 0;
-  DenseDesc desc() const { return DenseDesc{Wp, bias, K, N, n_tiles, -1, 0}; }
+  float* Wrm = nullptr;   // row-major [K][Np] copy (pack_dense only)
+  void* Wrm16 = nullptr;  // row-major fp16 [K][Np8] copy
+  int K = 0, N = 0, n_tiles = 0, Np = 0, Np8 = 0;
+  DenseDesc desc() const { return DenseDesc{Wp, bias, K, N, n_tiles, -1, 0, Wrm, Np, Wrm16, Np8, 0, 0}; }
 };
 
 // generic column-tile packing: column c of tile i comes from source column colmap[i*8+c] (or -1 = zero)
@@ -36,7 +38,18 @@ PackedDense pack_cols(DevPool& pool, const float* W, const float* bias, int K, i
 PackedDense pack_dense(DevPool& pool, const float* W, const float* bias, int K, int N) {
   std::vector<int> cm(N);
   for (int n = 0; n < N; ++n) cm[n] = n;
-  return pack_cols(pool, W, bias, K, N, cm);
+  PackedDense d = pack_cols(pool, W, bias, K, N, cm);
+  d.Np = (N + 3) / 4 * 4;
+  std::vector<float> rm((size_t)K * d.Np, 0.f);
+  for (int k = 0; k < K; ++k)
+    for (int n = 0; n < N; ++n) rm[(size_t)k * d.Np + n] = W[(size_t)k * N + n];
+  d.Wrm = pool.upload(rm);
+  d.Np8 = (N + 7) / 8 * 8;
+  std::vector<__half> rh((size_t)K * d.Np8 + 8, __float2half(0.f));
+  for (int k = 0; k < K; ++k)
+    for (int n = 0; n < N; ++n) rh[(size_t)k * d.Np8 + n] = __float2half_rn(W[(size_t)k * N + n]);
+  d.Wrm16 = pool.upload((const float*)rh.data(), (rh.size() + 1) / 2);
+  return d;
 }
 // LSTM kernel [K][4*units] gate order i,j,f,o -> tiles of 2 units x 4 gates
 PackedDense pack_lstm(DevPool& pool, const float* W, const float* bias, int K, int units) {
@@ -338,28 +351,50 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
         TcLstmDesc& d = *td[i];
         d.Wp = src[i]->Wp; d.bias = src[i]->bias; d.K = Ks[i]; d.units = us[i];
         d.n_tiles = us[i] / 4;
-        d.kchunks = ceil_div(Ks[i], tc::CHUNK_K);
+        d.kchunks = ceil_div(Ks[i], tc::CHUNK_K16);
         d.slots = ceil_div(d.n_tiles * RB, h->grid);
         d.img_off = off;
         off += d.slots * d.kchunks * 2048;
+      }
+      for (int i = 0; i < 3; ++i) {  // cell state of the CTA's own items, after the images
+        td[i]->st_off = off;
+        off += td[i]->slots * TC_STATE_BYTES;
       }
       p.scratch_floats = std::max((int)SCRATCH_FLOATS, (int)TC_SCRATCH_FLOATS);
       smem_bytes = p.scratch_floats * sizeof(float) + 1024 + (size_t)off;
       if (smem_bytes > h->max_dyn_smem) use_tc = false;  // resident images do not fit: SIMT form
     }
+    {
+      const int need = frame_smem_floats(p.outp.K, p.outp.Np, p.Mnf, p.pre0.Np, p.pre1.Np);
+      SAT_REQUIRE(need <= (int)SCRATCH_FLOATS, "frame phase needs %d floats of shared memory (limit %d): layer sizes too large",
+                  need, (int)SCRATCH_FLOATS);
+      SAT_REQUIRE(p.outp.Np <= 4 * NT && p.pre0.Np <= 4 * NT && p.pre1.Np <= 4 * NT,
+                  "prenet / projection widths must be <= %d", 4 * NT);
+    }
     if (const char* e = getenv("SAT_BENCH_BARRIERS")) p.bench_barriers = atoi(e);
     p.tc = use_tc ? 1 : 0;
     if (!use_tc) p.scratch_floats = SCRATCH_FLOATS;
     p.RB = RB;
-    p.Ka_pad = ceil_div(Ka, tc::CHUNK_K) * tc::CHUNK_K;
-    p.K1_pad = ceil_div(K1, tc::CHUNK_K) * tc::CHUNK_K;
-    p.K2_pad = ceil_div(K2, tc::CHUNK_K) * tc::CHUNK_K;
+    p.Ka_pad = ceil_div(Ka, tc::CHUNK_K16) * tc::CHUNK_K16;
+    p.K1_pad = ceil_div(K1, tc::CHUNK_K16) * tc::CHUNK_K16;
+    p.K2_pad = ceil_div(K2, tc::CHUNK_K16) * tc::CHUNK_K16;
     h->last_tc = p.tc;
     // ---- shared-memory plan (SIMT form): keep as many LSTM tiles resident as fit ----
+    // rows per work item: the finest split of {128, 64, 32} whose items still fit one wave of the grid
+    auto plan_rows = [&](DenseDesc& d, bool fixed128) {
+      d.rpg = ROWS_PER_GROUP;
+      if (!fixed128)
+        for (int rpg : {64, 32})
+          if (d.n_tiles * ceil_div(Bp, rpg) <= h->grid) d.rpg = rpg;
+      d.R = ceil_div(Bp, d.rpg);
+    };
     DenseDesc* lst[3] = {&p.lstm_a, &p.lstm_1, &p.lstm_2};
+    for (DenseDesc* d : lst) plan_rows(*d, true);
+    plan_rows(p.pre0, false); plan_rows(p.pre1, false); plan_rows(p.outp, false);
+    if (p.ms) plan_rows(p.msd, false);
     for (DenseDesc* d : lst) {
       if (use_tc) break;
-      const int slots = ceil_div(d->n_tiles * R, h->grid);
+      const int slots = ceil_div(d->n_tiles * d->R, h->grid);
       const size_t need = (size_t)slots * d->K * TILE_N;
       if ((smem_floats + need) * sizeof(float) <= h->max_dyn_smem) {
         d->smem_off = (int)(smem_floats - SCRATCH_FLOATS);
@@ -373,9 +408,10 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
     size_t off = 0;
     auto take = [&](size_t n) { size_t o = off; off += (n + 63) / 64 * 64; return o; };
     const size_t o_xin = take((size_t)p.Mnf * ld), o_p0 = take((size_t)p.P0 * ld), o_p0b = take((size_t)p.P0 * ld);
-    const size_t rows_tc = (size_t)RB * TC_M;  // row-major [rows_tc][K*_pad] in tensor-core mode, else [K][ld]
-    const size_t n_att = use_tc ? rows_tc * p.Ka_pad : (size_t)Ka * ld, n_l1 = use_tc ? rows_tc * p.K1_pad : (size_t)K1 * ld;
-    const size_t n_l2 = use_tc ? rows_tc * p.K2_pad : (size_t)K2 * ld;
+    // fp16 row-major [rows_tc][K*_pad] in tensor-core mode (two halves per float slot), else fp32 [K][ld]
+    const size_t rows_tc = (size_t)RB * TC_M;
+    const size_t n_att = use_tc ? rows_tc * p.Ka_pad / 2 : (size_t)Ka * ld, n_l1 = use_tc ? rows_tc * p.K1_pad / 2 : (size_t)K1 * ld;
+    const size_t n_l2 = use_tc ? rows_tc * p.K2_pad / 2 : (size_t)K2 * ld;
     const size_t o_att0 = take(n_att), o_att1 = take(n_att);
     const size_t o_l10 = take(n_l1), o_l11 = take(n_l1);
     const size_t o_l20 = take(n_l2), o_l21 = take(n_l2);
@@ -436,6 +472,7 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
       m.st_align = ws + o_sal[i]; m.st_alpha = ws + o_sap[i]; m.st_u = ws + o_su[i];
       m.out_align = io.alignments[i]; m.out_S = S;
       p.dq[i] = h->dq[i].desc();
+      plan_rows(p.dq[i], false);
       if (kind == SAT_ATT_TEACHER_FORCING) {
         SAT_REQUIRE(io.teacher_alignments[i] && io.target_steps >= 1, "teacher-forcing attention needs teacher_alignments[%d]", i);
         m.teacher = io.teacher_alignments[i];
@@ -454,6 +491,7 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
     count_launch();
     for (int i = 0; i < h->hops; ++i) {
       p.hop[i].qkv = h->sa_qkv[i].desc(); p.hop[i].o = h->sa_o[i].desc(); p.hop[i].tr = h->sa_tr[i].desc();
+      plan_rows(p.hop[i].qkv, false); plan_rows(p.hop[i].o, false); plan_rows(p.hop[i].tr, false);
       p.hop[i].kcache = ws + o_kc[i]; p.hop[i].vcache = ws + o_vc[i];
     }
 
@@ -461,7 +499,7 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
       float* bufs[6] = {p.att_in[0], p.att_in[1], p.l1_in[0], p.l1_in[1], p.l2_in[0], p.l2_in[1]};
       const int pads[6] = {p.Ka_pad, p.Ka_pad, p.K1_pad, p.K1_pad, p.K2_pad, p.K2_pad};
       for (int i = 0; i < 6; ++i)
-        make_tensor_map_2d(&h->hmaps[i], bufs[i], rows_tc, (uint64_t)pads[i], (uint64_t)pads[i], TC_M);
+        make_tensor_map_2d_f16(&h->hmaps[i], bufs[i], rows_tc, (uint64_t)pads[i], (uint64_t)pads[i], TC_M);
       SAT_CUDA(cudaMemcpyAsync(h->dmaps, h->hmaps, sizeof(h->hmaps), cudaMemcpyHostToDevice, st));
       p.maps = h->dmaps;
     }
@@ -482,7 +520,7 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
 }
 
 // cycles per phase accumulated by CTA 0 over all runs since the last reset (debug / profiling aid)
-extern "C" int sat_decoder_profile(sat_decoder* h, int64_t* out16 /* N_PROF = 32 slots */, int32_t reset) {
+extern "C" int sat_decoder_profile(sat_decoder* h, int64_t* out16 /* N_PROF = 48 slots */, int32_t reset) {
   return guarded([&] {
     SAT_REQUIRE(h && out16, "null argument");
     SAT_CUDA(cudaDeviceSynchronize());
@@ -493,6 +531,13 @@ extern "C" int sat_decoder_profile(sat_decoder* h, int64_t* out16 /* N_PROF = 32
 
 // device time of the persistent kernel of the last sat_decoder_run (CUDA events on the launching stream); blocks
 // until that kernel has finished
+extern "C" int sat_decoder_used_tensor_cores(sat_decoder* h, int32_t* used) {
+  return guarded([&] {
+    SAT_REQUIRE(h && used, "null argument");
+    *used = h->last_tc;
+  });
+}
+
 extern "C" int sat_decoder_kernel_ms(sat_decoder* h, float* ms) {
   return guarded([&] {
     SAT_REQUIRE(h && ms, "null argument");

@@ -51,9 +51,9 @@ struct AttMech {
   float* out_align;     // [B][out_S][T] or null
   int out_S;
   long long* prof;      // optional stage cycle counters (8 slots), CTA 0 only
-  float* ctx_dst[2];    // context element (d, b) written at ctx_dst[i][d * ctx_sd[i] + b * ctx_sb[i]]; may be null
+  void* ctx_dst[2];     // context element (d, b) written at ctx_dst[i][d * ctx_sd[i] + b * ctx_sb[i]]; may be null
   int ctx_sd[2], ctx_sb[2];
-  int ctx_tf32;         // 1: context destinations feed tensor-core GEMMs -> store rounded (RN) to tf32
+  int ctx_f16;          // 1: the context destinations are fp16 buffers feeding tensor-core GEMMs, 0: fp32
 };
 
 // exp2 / reciprocal on the MUFU pipe
@@ -491,7 +491,11 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
     const float ctx = ctxs[d];
 #pragma unroll
     for (int i = 0; i < 2; ++i)
-      if (m.ctx_dst[i]) m.ctx_dst[i][(size_t)d * m.ctx_sd[i] + (size_t)b * m.ctx_sb[i]] = m.ctx_tf32 ? tc::round_tf32(ctx) : ctx;
+      if (m.ctx_dst[i]) {
+        const size_t o = (size_t)d * m.ctx_sd[i] + (size_t)b * m.ctx_sb[i];
+        if (m.ctx_f16) ((__half*)m.ctx_dst[i])[o] = tc::to_f16(ctx);
+        else ((float*)m.ctx_dst[i])[o] = ctx;
+      }
   }
   if (fwd && m.agent) {
     // u = sigmoid([context, processed_query] . Wt + bt)   forward_attention.py:111-114

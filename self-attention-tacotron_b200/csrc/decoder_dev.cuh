@@ -28,6 +28,12 @@ struct DenseDesc {
   int K, N, n_tiles;
   int smem_off;       // float offset of this layer's resident slots in dynamic smem, -1 = streamed
   int slots;          // resident slots per CTA
+  const float* Wrm;   // row-major copy [K][Np] (Np = N padded to 4) for the row-split frame phase; may be null
+  int Np;
+  const void* Wrm16;  // the same in fp16 [K][Np8] (Np8 = N padded to 8), used in tensor-core mode
+  int Np8;
+  int rpg, R;         // rows per work item (32 / 64 / 128) and row groups = ceil(Bp / rpg): small layers split rows
+                      // finer so that n_tiles * R work items cover the grid
 };
 
 // ---- small math helpers (accurate versions: parity first) ------------------
@@ -94,15 +100,15 @@ struct GridBarrier {
 // Items are dealt round-robin: item = tile * R + rg -> CTA item % gridDim.x; the j-th
 // item of a CTA uses resident slot j when the layer is resident.
 template <class Epi>
-__device__ void dense_phase(const DenseDesc& d, const float* X, int ld, int Bp, int R,
-                            float* smem, float* red, Epi epi) {
+__device__ void dense_phase(const DenseDesc& d, const float* X, int ld, int Bp, float* smem, float* red, Epi epi) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int R = d.R;
   const int n_items = d.n_tiles * R;
   int slot = 0;
   for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++slot) {
     const int tile = item / R, rg = item % R;
-    const int r0 = rg * ROWS_PER_GROUP;
-    const int nrows = min(ROWS_PER_GROUP, Bp - r0);
+    const int r0 = rg * d.rpg;
+    const int nrows = min(d.rpg, Bp - r0);
     const int nq = nrows >> 2;
     int qpw = 1;
     while (qpw < nq) qpw <<= 1;  // quads per warp (power of two, <= 32)
@@ -161,8 +167,9 @@ __device__ void dense_phase(const DenseDesc& d, const float* X, int ld, int Bp, 
 }
 
 // copy this CTA's resident tiles of a layer into shared memory (once, before the loop)
-__device__ inline void load_resident(const DenseDesc& d, int R, float* smem) {
+__device__ inline void load_resident(const DenseDesc& d, float* smem) {
   if (d.smem_off < 0) return;
+  const int R = d.R;
   const int n_items = d.n_tiles * R;
   int slot = 0;
   for (int item = blockIdx.x; item < n_items && slot < d.slots; item += gridDim.x, ++slot) {

@@ -1,17 +1,15 @@
 // decoder_kernel.cuh -- the persistent autoregressive decoder kernel.
 //
 // One cooperative launch runs ALL decoder steps.  Per step:
-//   A  prenet layer 0 (+ MultiSpeakerPreNet speaker term)       column-split dense
-//   A2 MultiSpeakerPreNet second dense (multi-speaker only)      column-split dense
-//   B  prenet layer 1                                            column-split dense
 //   C  attention ZoneoutLSTM                                     weight-stationary LSTM tiles
 //   D  query layers of the attention mechanisms                  column-split dense
 //   E  attention mechanisms: energies, softmax, alpha recursion, context   row-split
 //   F  decoder ZoneoutLSTM 1                                     weight-stationary LSTM tiles
 //   G  decoder ZoneoutLSTM 2                                     weight-stationary LSTM tiles
 //   H-K decoder self-attention hops with a KV cache (transformer decoder only)
-//   L  frame + stop-token projection, feedback frame, stop rule
-// with one grid-wide barrier between consecutive phases.
+//   L  frame + stop-token projection, fed-back frame, prenet of the NEXT step (MultiSpeakerPreNet included),
+//      stop rule                                                 row split, no barrier inside
+// with one grid-wide barrier between consecutive phases.  The prenet of the <GO> frame runs before the loop.
 #pragma once
 #include "decoder_attn.cuh"
 #include "decoder_tc.cuh"
@@ -19,7 +17,7 @@
 namespace sat {
 namespace dec {
 
-constexpr int N_PROF = 32;  // [0,16) phases of a step, [16,24) stages of the attention item (CTA 0)
+constexpr int N_PROF = 48;  // [0,16) phases of a step, [16,24) attention-item stages, [24,27) tc, [32,40) frame-item stages (CTA 0)
 constexpr int SCRATCH_FLOATS = (RED_FLOATS > ATT_SMEM_FLOATS ? RED_FLOATS : ATT_SMEM_FLOATS);
 constexpr int TC_SCRATCH_FLOATS = (TC_STAGES * TC_STAGE_BYTES + 1024) / 4;  // ring + alignment slack
 
@@ -47,7 +45,7 @@ struct DecParams {
   int *stop_steps, *n_steps;
   unsigned* barrier;
   long long* prof;  // [N_PROF] accumulated SM cycles per phase (CTA 0), may be null
-  // ---- tensor-core mode (B >= 64): LSTM inputs att_in / l1_in / l2_in are ROW-major [RB*128][K*_pad] ----
+  // ---- tensor-core mode (B >= 64): LSTM inputs att_in / l1_in / l2_in are ROW-major fp16 [RB*128][K*_pad] ----
   int tc, RB, Ka_pad, K1_pad, K2_pad;
   int bench_barriers;       // diagnostic: time this many empty grid barriers before the loop (prof[30])
   int scratch_floats;       // phase scratch at the head of dynamic smem (>= SCRATCH_FLOATS; holds the TMA ring in tc mode)
@@ -112,25 +110,6 @@ struct QkvEpi {
       const int hd = d / dh, dd = d % dh;
       float* dst = (which == 0 ? kc : vc) + (((size_t)b * H + hd) * Smax + t) * dh + dd;
       *(float4*)dst = make_float4(v[0], v[1], v[2], v[3]);
-    }
-  }
-};
-
-struct OutEpi {
-  const float* bias; int Mr, Mnf, ld, B, t, maxS, feed_self;
-  float *mel, *stop, *xin;
-  __device__ __forceinline__ void operator()(int b, int tile, int ul, const float* g) const {
-#pragma unroll
-    for (int c = 0; c < 4; ++c) {
-      const int n = tile * TILE_N + ul * 4 + c;
-      if (n > Mr) continue;
-      const float v = g[c] + __ldg(bias + n);
-      if (n == Mr) {
-        if (b < B) stop[(size_t)b * maxS + t] = v;
-      } else {
-        if (b < B) mel[((size_t)b * maxS + t) * Mr + n] = v;
-        if (feed_self && n >= Mr - Mnf) xin[(size_t)(n - (Mr - Mnf)) * ld + b] = v;
-      }
     }
   }
 };
@@ -231,20 +210,189 @@ __device__ inline void sa_item(const DecParams& p, const SaHop& h, int b, int hd
   __syncthreads();
 }
 
-// softmax feedback of the code decoders (modules/helpers.py:98-106) for one row
-__device__ inline void softmax_feed_item(const DecParams& p, int b, int t, float* sm) {
-  float* s32 = sm;
-  for (int s = p.r - p.nf; s < p.r; ++s) {
-    const float* row = p.mel + ((size_t)b * p.max_steps + t) * p.Mr + (size_t)s * p.M;
-    float mx = -INFINITY;
-    for (int i = threadIdx.x; i < p.M; i += NT) mx = fmaxf(mx, __ldcg(row + i));
-    mx = block_max(mx, s32);
-    float sum = 0.f;
-    for (int i = threadIdx.x; i < p.M; i += NT) sum += expf(__ldcg(row + i) - mx);
-    sum = block_sum(sum, s32);
-    for (int i = threadIdx.x; i < p.M; i += NT)
-      p.xin[(size_t)((s - (p.r - p.nf)) * p.M + i) * p.ld + b] = expf(__ldcg(row + i) - mx) / sum;
+// ---- row-split frame phase -------------------------------------------------------------------------------
+// Everything between the last recurrent layer of step t and the attention LSTM of step t+1 is local to an utterance
+// row: frame + stop projection, the fed-back frame, and the prenet.  One CTA takes (up to) two rows through all of
+// it without a grid barrier in between; the weights (row-major [K][Np]) stream from L2 with 16-byte loads.
+
+// outs[r][n] = act(bias[n] + sum_k xs[r][k] W[k][n]) for RR rows held in shared memory.
+// H = false: fp32 weights [K][Np], a lane owns 4 columns; H = true: fp16 weights [K][Np8] (tensor-core mode, where
+// the LSTM operands are fp16 as well), a lane owns 8 columns -- half the L2 -> SM bytes, which bound this phase.
+template <int RR, bool H>
+__device__ inline void row_dense(const DenseDesc& d, const float* xs, int xs_stride, float* part, float* outs, int act) {
+  constexpr int CW = H ? 8 : 4;  // columns per lane
+  const int tid = threadIdx.x;
+  const int Np = H ? d.Np8 : d.Np, Cn = Np / CW, K = d.K;
+  const int kparts = min(NT / Cn, K), kper = (K + kparts - 1) / kparts;
+  const int kp = tid / Cn, cl = tid - kp * Cn;
+  if (kp < kparts) {
+    float acc[RR][CW];
+#pragma unroll
+    for (int r = 0; r < RR; ++r)
+#pragma unroll
+      for (int c = 0; c < CW; ++c) acc[r][c] = 0.f;
+    const int k0 = kp * kper, k1 = min(K, k0 + kper);
+    const uint4* w = (H ? (const uint4*)d.Wrm16 : (const uint4*)d.Wrm) + (size_t)k0 * Cn + cl;
+    for (int k = k0; k < k1; k += 8, w += 8 * Cn) {
+      uint4 wv[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) wv[j] = (k + j < k1) ? __ldg(w + (size_t)j * Cn) : make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float wf[CW];
+        if (H) {
+          const float2 a = __half22float2(*(const __half2*)&wv[j].x), b = __half22float2(*(const __half2*)&wv[j].y);
+          const float2 c = __half22float2(*(const __half2*)&wv[j].z), e = __half22float2(*(const __half2*)&wv[j].w);
+          wf[0] = a.x; wf[1] = a.y; wf[2] = b.x; wf[3] = b.y;
+          if (CW == 8) { wf[4 % CW] = c.x; wf[5 % CW] = c.y; wf[6 % CW] = e.x; wf[7 % CW] = e.y; }
+        } else {
+          wf[0] = __uint_as_float(wv[j].x); wf[1] = __uint_as_float(wv[j].y);
+          wf[2] = __uint_as_float(wv[j].z); wf[3] = __uint_as_float(wv[j].w);
+        }
+#pragma unroll
+        for (int r = 0; r < RR; ++r) {
+          const float x = (k + j < k1) ? xs[r * xs_stride + k + j] : 0.f;
+#pragma unroll
+          for (int c = 0; c < CW; ++c) acc[r][c] = fmaf(x, wf[c], acc[r][c]);
+        }
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < RR; ++r)
+#pragma unroll
+      for (int c = 0; c < CW; c += 4)
+        *(float4*)(part + (size_t)(kp * RR + r) * Np + CW * cl + c) =
+            make_float4(acc[r][c], acc[r][c + 1], acc[r][c + 2], acc[r][c + 3]);
+  }
+  __syncthreads();
+  const int No = d.Np;  // output row stride (bias is zero-padded to n_tiles * 8 >= Np)
+  for (int i = tid; i < RR * No; i += NT) {
+    const int r = i / No, n = i - r * No;
+    float v = 0.f;
+    for (int q = 0; q < kparts; ++q) v += part[(size_t)(q * RR + r) * Np + n];
+    v += __ldg(d.bias + n);
+    if (act == 1) v = fmaxf(v, 0.f);
+    outs[r * No + n] = v;
+  }
+  __syncthreads();
+}
+
+// shared-memory floats the frame phase needs (checked against the phase scratch on the host)
+__host__ __device__ inline int al4(int x) { return (x + 3) & ~3; }
+__host__ __device__ inline int frame_smem_floats(int Dy, int Np_out, int Mnf, int P0p, int P1p) {
+  return al4(2 * Dy) + 2 * Np_out + al4(2 * Mnf) + 4 * P0p + 2 * P1p + 2 * NT * 8 + 64;
+}
+
+// rows b[0..RR): (unless `prologue`) project y -> frame + stop token of step t, form the next input frame, and run
+// the prenet on it into the attention-LSTM input buffer of step t+1
+template <int RR, bool H>
+__device__ inline void frame_item(const DecParams& p, const int* b, int t, const float* y, int Dy, Act2D p1_dst,
+                                  bool prologue, float* sm) {
+  const int tid = threadIdx.x, ld = p.ld;
+  const int Npo = p.outp.Np, P0p = p.pre0.Np, P1p = p.pre1.Np;
+  float* ys = sm;                   // [RR][Dy]        (every region starts 16-byte aligned)
+  float* os = ys + al4(2 * Dy);     // [RR][Npo] projection outputs
+  float* fr = os + 2 * Npo;         // [RR][Mnf] next input frame
+  float* p0s = fr + al4(2 * p.Mnf); // [RR][P0p]
+  float* p0b = p0s + 2 * P0p;       // [RR][P0p] (multi-speaker second dense)
+  float* p1s = p0b + 2 * P0p;       // [RR][P1p]
+  float* s32 = p1s + 2 * P1p;       // [64]
+  float* part = s32 + 64;           // [2 * NT * 8]
+  long long tp = 0;
+  int ps = 32;
+  const bool profiling = p.prof && blockIdx.x == 0 && tid == 0 && !prologue;
+  if (profiling) tp = clock64();
+  auto stamp = [&]() {
+    if (profiling) {
+      const long long now = clock64();
+      p.prof[ps] += now - tp;
+      tp = now;
+    }
+    ++ps;
+  };
+  if (!prologue) {
+    for (int i = tid; i < RR * Dy; i += NT) {
+      const int r = i / Dy, k = i - r * Dy;
+      ys[r * Dy + k] = __ldcg(y + (size_t)k * ld + b[r]);
+    }
     __syncthreads();
+    stamp();
+    row_dense<RR, H>(p.outp, ys, Dy, part, os, 0);
+    stamp();
+    for (int i = tid; i < RR * (p.Mr + 1); i += NT) {
+      const int r = i / (p.Mr + 1), n = i - r * (p.Mr + 1);
+      const float v = os[r * Npo + n];
+      if (n == p.Mr) p.stop[(size_t)b[r] * p.max_steps + t] = v;
+      else p.mel[((size_t)b[r] * p.max_steps + t) * p.Mr + n] = v;
+    }
+    const int f0 = p.Mr - p.Mnf;
+    if (p.feed_mode == SAT_FEED_TEACHER) {
+      const int ts = min(t, p.S_target - 1);
+      for (int i = tid; i < RR * p.Mnf; i += NT) {
+        const int r = i / p.Mnf, f = i - r * p.Mnf;
+        fr[r * p.Mnf + f] = __ldg(p.target + ((size_t)b[r] * p.S_target + ts) * p.Mr + f0 + f);
+      }
+    } else if (p.feed_mode == SAT_FEED_SELF) {
+      for (int i = tid; i < RR * p.Mnf; i += NT) {
+        const int r = i / p.Mnf, f = i - r * p.Mnf;
+        fr[r * p.Mnf + f] = os[r * Npo + f0 + f];
+      }
+    } else {
+      // softmax feedback of the code decoders (modules/helpers.py:98-106): per fed-back frame over its M bins
+      for (int r = 0; r < RR; ++r)
+        for (int s = 0; s < p.nf; ++s) {
+          const float* row = os + r * Npo + f0 + s * p.M;
+          float mx = -INFINITY;
+          for (int i = tid; i < p.M; i += NT) mx = fmaxf(mx, row[i]);
+          mx = block_max(mx, s32);
+          float sum = 0.f;
+          for (int i = tid; i < p.M; i += NT) sum += expf(row[i] - mx);
+          sum = block_sum(sum, s32);
+          for (int i = tid; i < p.M; i += NT) fr[r * p.Mnf + s * p.M + i] = expf(row[i] - mx) / sum;
+          __syncthreads();
+        }
+    }
+  } else {
+    for (int i = tid; i < RR * p.Mnf; i += NT) fr[i] = 0.f;  // <GO> frame
+  }
+  __syncthreads();
+  ps = 34;
+  stamp();
+  row_dense<RR, H>(p.pre0, fr, p.Mnf, part, p0s, 1);
+  stamp();
+  const float* pin = p0s;
+  if (p.ms) {
+    // MultiSpeakerPreNet: relu(dense0(x)) + softsign(speaker projection), then a second relu dense
+    for (int i = tid; i < RR * p.P0; i += NT) {
+      const int r = i / p.P0, n = i - r * p.P0;
+      p0s[r * P0p + n] += __ldg(p.spk_term + (size_t)n * ld + b[r]);
+    }
+    __syncthreads();
+    row_dense<RR, H>(p.msd, p0s, P0p, part, p0b, 1);
+    pin = p0b;
+  }
+  row_dense<RR, H>(p.pre1, pin, P0p, part, p1s, 1);
+  ps = 36;
+  stamp();
+  for (int i = tid; i < RR * p.P1; i += NT) {
+    const int r = i / p.P1, n = i - r * p.P1;
+    p1_dst.put(n, b[r], p1s[r * P1p + n]);
+  }
+  __syncthreads();
+  stamp();
+}
+
+// all rows of the batch through frame_item, two per pass
+__device__ inline void frame_phase(const DecParams& p, int t, const float* y, int Dy, Act2D p1_dst, bool prologue, float* sm) {
+  for (int b0 = blockIdx.x; b0 < p.B; b0 += 2 * gridDim.x) {
+    int b[2] = {b0, b0 + (int)gridDim.x};
+    if (p.tc) {
+      if (b[1] < p.B) frame_item<2, true>(p, b, t, y, Dy, p1_dst, prologue, sm);
+      else frame_item<1, true>(p, b, t, y, Dy, p1_dst, prologue, sm);
+    } else {
+      if (b[1] < p.B) frame_item<2, false>(p, b, t, y, Dy, p1_dst, prologue, sm);
+      else frame_item<1, false>(p, b, t, y, Dy, p1_dst, prologue, sm);
+    }
   }
 }
 
@@ -284,9 +432,9 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
     tc::tc_fence_after();
     tcs.tmem = s_tmem;
   } else {
-    load_resident(p.lstm_a, p.R, wres);
-    load_resident(p.lstm_1, p.R, wres);
-    load_resident(p.lstm_2, p.R, wres);
+    load_resident(p.lstm_a, wres);
+    load_resident(p.lstm_1, wres);
+    load_resident(p.lstm_2, wres);
   }
   for (int i = tid; i < MAX_B; i += NT) s_stopped[i] = -1;
   __syncthreads();
@@ -309,37 +457,27 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
     ++ph;
   };
 
+  // prenet of the <GO> frame -> attention-LSTM input of step 0
+  frame_phase(p, 0, nullptr, 0, Act2D{p.att_in[0], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc}, true, scratch);
+  bar.sync();
+
   int t = 0;
   for (; t < p.max_steps; ++t) {
     const int cur = t & 1, nxt = cur ^ 1;
     ph = 0;
     if (p.prof && blockIdx.x == 0 && tid == 0) tprev = clock64();
-    // ---- A: prenet layer 0 ----
-    dense_phase(p.pre0, p.xin, ld, p.Bp, p.R, wres, scratch,
-                DenseEpi{p.pre0.bias, p.pre0.N, ld, 1, Act2D{p.p0, ld, 1, 0}, nullptr, p.ms ? p.spk_term : nullptr});
-    phase_end();
-    const float* pin = p.p0;
-    if (p.ms) {
-      dense_phase(p.msd, p.p0, ld, p.Bp, p.R, wres, scratch,
-                  DenseEpi{p.msd.bias, p.msd.N, ld, 1, Act2D{p.p0b, ld, 1, 0}, nullptr, nullptr});
-      phase_end();
-      pin = p.p0b;
-    }
-    // ---- B: prenet layer 1 -> attention-LSTM input rows [0, P1) ----
-    dense_phase(p.pre1, pin, ld, p.Bp, p.R, wres, scratch,
-                DenseEpi{p.pre1.bias, p.pre1.N, ld, 1, Act2D{p.att_in[cur], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc}, nullptr, nullptr});
-    phase_end();
     // ---- C: attention LSTM ----
     if (p.tc) {
+      // fp16 row-major buffers: att_in = [prenet | context | zoned h], l1_in = [h_a | context | zoned h1]
       const int h0 = p.P1 + p.Dctx;
-      TcLstmIO io{p.maps + cur, Act2D{p.att_in[cur] + h0, 1, p.Ka_pad, 1}, Act2D{p.l1_in[cur], 1, p.K1_pad, 1},
-                  Act2D{p.qfm, ld, 1, 0}, Act2D{p.att_in[nxt] + h0, 1, p.Ka_pad, 1}, p.c_a, nullptr, 0, 0};
+      TcLstmIO io{p.maps + cur, Act2D{p.l1_in[cur], 1, p.K1_pad, 1}, Act2D{p.qfm, ld, 1, 0},
+                  Act2D{(__half*)p.att_in[nxt] + h0, 1, p.Ka_pad, 1}, nullptr, 0, 0};
       tc::fence_proxy_async();
       __syncthreads();
-      lstm_phase_tc(p.tc_a, io, p.B, p.Bp, ld, p.RB, p.zc, p.zh, tcs);
+      lstm_phase_tc(p.tc_a, io, p.B, p.Bp, p.RB, p.zc, p.zh, tcs);
     } else {
       const size_t hoff = (size_t)(p.P1 + p.Dctx) * ld;
-      dense_phase(p.lstm_a, p.att_in[cur], ld, p.Bp, p.R, wres, scratch,
+      dense_phase(p.lstm_a, p.att_in[cur], ld, p.Bp, wres, scratch,
                   LstmEpi{p.lstm_a.bias, p.A, ld, p.B, p.c_a, p.att_in[cur] + hoff, p.l1_in[cur],
                           p.att_in[nxt] + hoff, nullptr, 0, 0, p.zc, p.zh});
     }
@@ -349,7 +487,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
     for (int mi = 0; mi < p.n_mech; ++mi)
       if (p.mech[mi].kind != SAT_ATT_TEACHER_FORCING) {
         any_q = true;
-        dense_phase(p.dq[mi], p.tc ? p.qfm : p.l1_in[cur], ld, p.Bp, p.R, wres, scratch,
+        dense_phase(p.dq[mi], p.tc ? p.qfm : p.l1_in[cur], ld, p.Bp, wres, scratch,
                     DenseEpi{p.dq[mi].bias, p.dq[mi].N, ld, 0, Act2D{const_cast<float*>(p.mech[mi].pq), p.mech[mi].pq_su, p.mech[mi].pq_sb, 0}, nullptr, nullptr});
       }
     if (any_q) phase_end();
@@ -359,13 +497,14 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
       AttMech m = p.mech[mi];
       const int coff = mi ? p.mech[0].Dv : 0;
       if (p.tc) {
-        m.ctx_dst[0] = p.att_in[nxt] + p.P1 + coff;
-        m.ctx_dst[1] = p.l1_in[cur] + p.A + coff;
+        m.ctx_dst[0] = (__half*)p.att_in[nxt] + p.P1 + coff;
+        m.ctx_dst[1] = (__half*)p.l1_in[cur] + p.A + coff;
         m.ctx_sd[0] = m.ctx_sd[1] = 1;
         m.ctx_sb[0] = p.Ka_pad;
         m.ctx_sb[1] = p.K1_pad;
-        m.ctx_tf32 = 1;
+        m.ctx_f16 = 1;
       } else {
+        m.ctx_f16 = 0;
         m.ctx_dst[0] = p.att_in[nxt] + (size_t)(p.P1 + coff) * ld;
         m.ctx_dst[1] = p.l1_in[cur] + (size_t)(p.A + coff) * ld;
         m.ctx_sd[0] = m.ctx_sd[1] = ld;
@@ -378,14 +517,14 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
     // ---- F: decoder LSTM 1 ----
     if (p.tc) {
       const int h0 = p.A + p.Dctx;
-      TcLstmIO io{p.maps + 2 + cur, Act2D{p.l1_in[cur] + h0, 1, p.K1_pad, 1}, Act2D{p.l2_in[cur], 1, p.K2_pad, 1},
-                  Act2D{nullptr, 0, 0, 0}, Act2D{p.l1_in[nxt] + h0, 1, p.K1_pad, 1}, p.c_1, nullptr, 0, 0};
+      TcLstmIO io{p.maps + 2 + cur, Act2D{p.l2_in[cur], 1, p.K2_pad, 1}, Act2D{nullptr, 0, 0, 0},
+                  Act2D{(__half*)p.l1_in[nxt] + h0, 1, p.K1_pad, 1}, nullptr, 0, 0};
       tc::fence_proxy_async();
       __syncthreads();
-      lstm_phase_tc(p.tc_1, io, p.B, p.Bp, ld, p.RB, p.zc, p.zh, tcs);
+      lstm_phase_tc(p.tc_1, io, p.B, p.Bp, p.RB, p.zc, p.zh, tcs);
     } else {
       const size_t hoff = (size_t)(p.A + p.Dctx) * ld;
-      dense_phase(p.lstm_1, p.l1_in[cur], ld, p.Bp, p.R, wres, scratch,
+      dense_phase(p.lstm_1, p.l1_in[cur], ld, p.Bp, wres, scratch,
                   LstmEpi{p.lstm_1.bias, p.Dd, ld, p.B, p.c_1, p.l1_in[cur] + hoff, p.l2_in[cur],
                           p.l1_in[nxt] + hoff, nullptr, 0, 0, p.zc, p.zh});
     }
@@ -393,15 +532,14 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
     // ---- G: decoder LSTM 2 ----
     if (p.tc) {
       const int h0 = p.Dd;
-      TcLstmIO io{p.maps + 4 + cur, Act2D{p.l2_in[cur] + h0, 1, p.K2_pad, 1}, Act2D{p.dout, ld, 1, 0},
-                  Act2D{nullptr, 0, 0, 0}, Act2D{p.l2_in[nxt] + h0, 1, p.K2_pad, 1}, p.c_2, p.dec_out,
-                  p.max_steps * p.Dd, t * p.Dd};
+      TcLstmIO io{p.maps + 4 + cur, Act2D{p.dout, ld, 1, 0}, Act2D{nullptr, 0, 0, 0},
+                  Act2D{(__half*)p.l2_in[nxt] + h0, 1, p.K2_pad, 1}, p.dec_out, p.max_steps * p.Dd, t * p.Dd};
       tc::fence_proxy_async();
       __syncthreads();
-      lstm_phase_tc(p.tc_2, io, p.B, p.Bp, ld, p.RB, p.zc, p.zh, tcs);
+      lstm_phase_tc(p.tc_2, io, p.B, p.Bp, p.RB, p.zc, p.zh, tcs);
     } else {
       const size_t hoff = (size_t)p.Dd * ld;
-      dense_phase(p.lstm_2, p.l2_in[cur], ld, p.Bp, p.R, wres, scratch,
+      dense_phase(p.lstm_2, p.l2_in[cur], ld, p.Bp, wres, scratch,
                   LstmEpi{p.lstm_2.bias, p.Dd, ld, p.B, p.c_2, p.l2_in[cur] + hoff, p.dout,
                           p.l2_in[nxt] + hoff, p.dec_out, p.max_steps * p.Dd, t * p.Dd, p.zc, p.zh});
     }
@@ -410,36 +548,23 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
     const float* y = p.dout;
     for (int hi = 0; hi < p.hops; ++hi) {
       const SaHop& h = p.hop[hi];
-      dense_phase(h.qkv, y, ld, p.Bp, p.R, wres, scratch,
+      dense_phase(h.qkv, y, ld, p.Bp, wres, scratch,
                   QkvEpi{h.qkv.bias, p.Ds, p.Ds / p.heads, p.heads, p.Smax, t, ld, p.B, h.kcache, h.vcache, p.sa_q});
       phase_end();
       for (int item = blockIdx.x; item < p.B * p.heads; item += gridDim.x)
         sa_item(p, h, item / p.heads, item % p.heads, t, scratch);
       phase_end();
-      dense_phase(h.o, p.sa_ctx, ld, p.Bp, p.R, wres, scratch,
+      dense_phase(h.o, p.sa_ctx, ld, p.Bp, wres, scratch,
                   DenseEpi{h.o.bias, h.o.N, ld, 0, Act2D{p.sa_a, ld, 1, 0}, nullptr, nullptr});
       phase_end();
-      dense_phase(h.tr, p.sa_a, ld, p.Bp, p.R, wres, scratch,
+      dense_phase(h.tr, p.sa_a, ld, p.Bp, wres, scratch,
                   DenseEpi{h.tr.bias, h.tr.N, ld, 2, Act2D{p.sa_y[hi & 1], ld, 1, 0}, nullptr, y});
       phase_end();
       y = p.sa_y[hi & 1];
     }
-    // ---- L: frame + stop projections; next input frame ----
-    if (p.feed_mode == SAT_FEED_TEACHER) {
-      const int ts = min(t, p.S_target - 1);
-      for (int i = blockIdx.x * NT + tid; i < p.Mnf * p.B; i += gridDim.x * NT) {
-        const int f = i / p.B, b = i % p.B;
-        p.xin[(size_t)f * ld + b] = __ldg(p.target + ((size_t)b * p.S_target + ts) * p.Mr + (p.Mr - p.Mnf) + f);
-      }
-    }
-    dense_phase(p.outp, y, ld, p.Bp, p.R, wres, scratch,
-                OutEpi{p.outp.bias, p.Mr, p.Mnf, ld, p.B, t, p.max_steps, p.feed_mode == SAT_FEED_SELF,
-                       p.mel, p.stop, p.xin});
+    // ---- L+A+B: frame + stop projection of step t, fed-back frame, prenet of step t+1 (row split) ----
+    frame_phase(p, t, y, p.outp.K, Act2D{p.att_in[nxt], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc}, false, scratch);
     phase_end();
-    if (p.feed_mode == SAT_FEED_SELF_SOFTMAX) {
-      for (int b = blockIdx.x; b < p.B; b += gridDim.x) softmax_feed_item(p, b, t, scratch);
-      phase_end();
-    }
     // ---- stop rule (every CTA evaluates the same data -> same decision) ----
     if (p.stop_mode != SAT_STOP_FIXED) {
       bool term = true, stopped = true;

@@ -6,6 +6,7 @@
 // CU_TENSOR_MAP_SWIZZLE_128B writes.  D[M=128, N] accumulates in TMEM (row i = lane i, column j = column j).
 #pragma once
 #include <cuda.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <cstdint>
 
@@ -90,7 +91,23 @@ __host__ __device__ constexpr uint32_t idesc_tf32(int M, int N) {
   return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
+// kind::f16 with fp16 operands, fp32 accumulate, A and B K-major, dense.  fp16 carries the same 11-bit significand
+// as tf32 in half the bytes, so the fp16 form halves the L2 -> shared-memory stream of a K-major operand.
+__host__ __device__ constexpr uint32_t idesc_f16(int M, int N) {
+  return (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+constexpr int CHUNK_K16 = 64;  // fp16 elements per 128-byte swizzle row
+constexpr int UMMA_K16 = 16;   // K of one tcgen05.mma kind::f16
+
 // D[tmem] (+)= A[smem] * B[smem]^T ; issued by ONE thread
+__device__ __forceinline__ void mma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 __device__ __forceinline__ void mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
@@ -119,6 +136,21 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
   for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
 
+// 4 consecutive fp32 columns of this thread's TMEM lane
+__device__ __forceinline__ void tmem_ld4(uint32_t taddr, float* v) {
+  uint32_t r[4];
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(taddr)
+               : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 4; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// fp32 -> fp16, round to nearest, saturating at the largest finite half instead of overflowing to inf
+__device__ __forceinline__ __half to_f16(float x) { return __float2half_rn(fminf(fmaxf(x, -65504.f), 65504.f)); }
+
 // round-to-nearest fp32 -> tf32 (the tensor core itself TRUNCATES fp32 operands, which biases every product
 // towards zero; operands stored pre-rounded make the error unbiased and half as large)
 __device__ __forceinline__ float round_tf32(float x) {
@@ -132,11 +164,19 @@ __device__ __forceinline__ uint32_t sw128_offset(int n, int kk) {
   return (uint32_t)(n * 128 + ((((kk >> 2) ^ (n & 7)) << 4) | ((kk & 3) << 2)));
 }
 
+// the same for an fp16 operand: 64-k chunk image, 2-byte elements
+__device__ __forceinline__ uint32_t sw128_offset16(int n, int kk) {
+  return (uint32_t)(n * 128 + ((((kk >> 3) ^ (n & 7)) << 4) | ((kk & 7) << 1)));
+}
+
 }  // namespace tc
 
 // host: 2-D tensor map over a row-major fp32 matrix [rows][cols] (cols contiguous), box = {32 floats, box_rows},
 // 128-byte swizzle (tc_host.cu)
 void make_tensor_map_2d(CUtensorMap* map, const float* base, uint64_t rows, uint64_t cols, uint64_t row_stride_floats,
                         uint32_t box_rows);
+// the same over a row-major fp16 matrix, box = {64 halves, box_rows}
+void make_tensor_map_2d_f16(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t row_stride_elems,
+                            uint32_t box_rows);
 
 }  // namespace sat

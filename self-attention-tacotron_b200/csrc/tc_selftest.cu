@@ -5,16 +5,46 @@
 
 namespace sat {
 
+// cuTensorMapEncodeTiled is resolved through the runtime (cudaGetDriverEntryPoint) instead of linking libcuda, so
+// that libsat.so still loads -- and its symbol table can be checked -- on a machine without a GPU driver.
+namespace {
+using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn encode_tiled() {
+  static EncodeTiledFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      p = nullptr;
+    return (EncodeTiledFn)p;
+  }();
+  if (!fn) fail(SAT_ECUDA, "cuTensorMapEncodeTiled is not available from the installed CUDA driver");
+  return fn;
+}
+
+void encode_2d(CUtensorMap* map, CUtensorMapDataType dt, size_t elem, uint32_t box_k, const void* base, uint64_t rows,
+               uint64_t cols, uint64_t row_stride_elems, uint32_t box_rows) {
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {row_stride_elems * elem};
+  cuuint32_t box[2] = {box_k, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = encode_tiled()(map, dt, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) fail(SAT_ECUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+}
+}  // namespace
+
 void make_tensor_map_2d(CUtensorMap* map, const float* base, uint64_t rows, uint64_t cols, uint64_t row_stride_floats,
                         uint32_t box_rows) {
-  cuuint64_t dims[2] = {cols, rows};
-  cuuint64_t strides[1] = {row_stride_floats * sizeof(float)};
-  cuuint32_t box[2] = {(cuuint32_t)tc::CHUNK_K, box_rows};
-  cuuint32_t estr[2] = {1, 1};
-  CUresult r = cuTensorMapEncodeTiled(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)base, dims, strides, box, estr,
-                                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                                      CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) fail(SAT_ECUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+  encode_2d(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, tc::CHUNK_K, base, rows, cols, row_stride_floats, box_rows);
+}
+
+void make_tensor_map_2d_f16(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t row_stride_elems,
+                            uint32_t box_rows) {
+  encode_2d(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, tc::CHUNK_K16, base, rows, cols, row_stride_elems, box_rows);
 }
 
 namespace {

@@ -94,8 +94,13 @@ class DecoderHandle:
         check(lib().sat_decoder_kernel_ms(self._h, C.byref(ms)))
         return ms.value
 
+    def used_tensor_cores(self):
+        used = C.c_int32()
+        check(lib().sat_decoder_used_tensor_cores(self._h, C.byref(used)))
+        return bool(used.value)
+
     def profile(self, reset=True):
-        out = (C.c_int64 * 32)()
+        out = (C.c_int64 * 48)()
         check(lib().sat_decoder_profile(self._h, out, int(reset)))
         return list(out)
 

@@ -33,7 +33,7 @@ def run_cuda(hp, W, mems, lengths, **kw):
     out = h.run([t(m) for m in mems], t(lengths), **kw)
     torch.cuda.synchronize()
     n = int(out["n_steps"].item())
-    res = {"n_steps": n, "stop_steps": out["stop_steps"].cpu().numpy(),
+    res = {"n_steps": n, "tensor_cores": h.used_tensor_cores(), "stop_steps": out["stop_steps"].cpu().numpy(),
            "mel": out["mel"].cpu().numpy()[:, :n * hp.outputs_per_step],
            "stop": out["stop"].cpu().numpy()[:, :n, None],
            "alignments": [a.cpu().numpy()[:, :n] for a in out["alignments"] if a is not None]}
@@ -89,6 +89,30 @@ def test_extended_decoder_two_row_groups(B):
     ref = oracle_decoder(hp, W, mems, lengths, target=target, is_validation=True, teacher_forcing=True)
     got = run_cuda(hp, W, mems, lengths, target=target, feed_mode=0, stop_mode=0, max_steps=6)
     check_close(got, ref)
+
+
+@pytest.mark.parametrize("name,B,T,S", [("ljspeech_tacotron", 64, 50, 12), ("ljspeech_tacotron", 200, 37, 8),
+                                        ("ljspeech_self_attention", 96, 41, 10)])
+def test_tensor_core_gate_gemms_full_dims(name, B, T, S):
+    """B >= 64 switches the three ZoneoutLSTM gate GEMMs to tcgen05 (fp16 operands, fp32 accumulation, TMA-fed);
+    same 1e-3 bar as the fp32 path, at the real layer sizes."""
+    hp = small_hp(name)
+    W = sat_b200.init_weights(hp, seed=11, stress=True)
+    mems, lengths, target, _ = decoder_inputs(hp, B, T, S, seed=11)
+    ref = oracle_decoder(hp, W, mems, lengths, target=target, is_validation=True, teacher_forcing=True)
+    got = run_cuda(hp, W, mems, lengths, target=target, feed_mode=0, stop_mode=0, max_steps=S)
+    assert got["tensor_cores"]
+    check_close(got, ref)
+    errs = {k: rel_err(got[k], ref[k]) for k in ("mel", "stop")}
+    print("tensor-core path rel err", name, B, errs)
+
+
+def test_small_batch_uses_fp32_simt():
+    hp = small_hp("ljspeech_tacotron", **SMALL)
+    W = sat_b200.init_weights(hp, seed=1)
+    mems, lengths, target, _ = decoder_inputs(hp, 8, 11, 4, seed=1)
+    got = run_cuda(hp, W, mems, lengths, target=target, feed_mode=0, stop_mode=0, max_steps=4)
+    assert not got["tensor_cores"]
 
 
 @pytest.mark.parametrize("stop_mode", ["all_rows", "per_row"])
