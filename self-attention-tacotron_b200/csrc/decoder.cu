@@ -62,6 +62,11 @@ PackedDense pack_lstm(DevPool& pool, const float* W, const float* bias, int K, i
   return d;
 }
 
+__global__ void f32_to_f16_kernel(const float* __restrict__ src, __half* __restrict__ dst, size_t n) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    dst[i] = tc::to_f16(src[i]);
+}
+
 __global__ void init_state_kernel(float* alpha0, float* alpha1, float* u0, float* u1, int B, int T) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= B) return;
@@ -356,6 +361,30 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
         d.img_off = off;
         off += d.slots * d.kchunks * 2048;
       }
+      // chunk order: columns produced at least two phases before the LSTM first (requested behind the grid barrier)
+      {
+        struct Range { int lo, hi; };
+        const Range old_a[1] = {{p.P1, Ka}}, old_1[2] = {{0, A}, {A + p.Dctx, K1}}, old_2[1] = {{Dd, K2}};
+        const Range* olds[3] = {old_a, old_1, old_2};
+        const int nold[3] = {1, 2, 1};
+        for (int i = 0; i < 3; ++i) {
+          TcLstmDesc& d = *td[i];
+          if (d.kchunks > 48) { use_tc = false; break; }
+          int n = 0, n_old = 0;
+          for (int pass = 0; pass < 2; ++pass)
+            for (int c = 0; c < d.kchunks; ++c) {
+              const int lo = c * tc::CHUNK_K16, hi = std::min(lo + tc::CHUNK_K16, Ks[i]);
+              bool old = false;
+              for (int r = 0; r < nold[i]; ++r) old = old || (lo >= olds[i][r].lo && hi <= olds[i][r].hi);
+              if (old == (pass == 0)) { d.order[n++] = (unsigned char)c; n_old += pass == 0; }
+            }
+          // measured on B200 (cfg 2, B=256): requesting these chunks behind the grid barrier shortens the LSTM phases by
+          // ~0.7 us each but lengthens the phases whose barrier hosts the requests by as much (net 0), so it is
+          // off unless SAT_TC_PREFILL=<chunks> asks for it
+          d.n_pre = 0;
+          if (const char* e = getenv("SAT_TC_PREFILL")) d.n_pre = std::min(std::min(n_old, (int)TC_STAGES), atoi(e));
+        }
+      }
       for (int i = 0; i < 3; ++i) {  // cell state of the CTA's own items, after the images
         td[i]->st_off = off;
         off += td[i]->slots * TC_STATE_BYTES;
@@ -430,6 +459,9 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
     }
     const size_t state_floats = off;  // everything up to here is zeroed per run
     for (int i = 0; i < h->n_mech; ++i) o_keys[i] = take((size_t)B * T * h->Up[i]);
+    size_t o_v16[2] = {0, 0};
+    if (use_tc)
+      for (int i = 0; i < h->n_mech; ++i) o_v16[i] = take(((size_t)B * T * hp.memory_dim[i] + 1) / 2);
     size_t o_kc[MAX_HOPS], o_vc[MAX_HOPS];
     for (int i = 0; i < h->hops; ++i) {
       o_kc[i] = take((size_t)B * Ds * S);
@@ -466,6 +498,14 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
       m.F = hp.attention_filters; m.Kc = hp.attention_kernel; m.pad_left = (hp.attention_kernel - 1) / 2;
       m.cumulative = hp.cumulative_weights; m.agent = (h->Wt[i] != nullptr);
       m.values = io.memory[i];
+      if (use_tc && m.Dv % 8 == 0) {
+        // fp16 copy of the attention values: halves the bytes of the context reduction (see attention_context_h8)
+        const size_t n = (size_t)B * T * m.Dv;
+        __half* v16 = (__half*)(ws + o_v16[i]);
+        f32_to_f16_kernel<<<(unsigned)std::min<size_t>(ceil_div64((long long)n, 256), 148 * 8), 256, 0, st>>>(io.memory[i], v16, n);
+        count_launch();
+        m.values16 = v16;
+      }
       m.v = h->att_v[i]; m.ba = h->att_ba[i]; m.conv_w = h->conv_w[i]; m.conv_b = h->conv_b[i]; m.Wl = h->Wl[i];
       m.Wt = h->Wt[i]; m.bt = h->bt[i];
       m.pq = ws + o_pq[i]; m.pq_su = 1; m.pq_sb = m.Up;  // row-major [b][Up]: one 16-byte load per lane

@@ -51,6 +51,7 @@ struct AttMech {
   float* out_align;     // [B][out_S][T] or null
   int out_S;
   long long* prof;      // optional stage cycle counters (8 slots), CTA 0 only
+  const __half* values16;  // optional fp16 copy of `values` (tensor-core mode)
   void* ctx_dst[2];     // context element (d, b) written at ctx_dst[i][d * ctx_sd[i] + b * ctx_sb[i]]; may be null
   int ctx_sd[2], ctx_sb[2];
   int ctx_f16;          // 1: the context destinations are fp16 buffers feeding tensor-core GEMMs, 0: fp32
@@ -274,6 +275,124 @@ __device__ void attention_energies_w32(const AttMech& m, int b, int T, int len, 
   }
 }
 
+// ---- energies with the location term on the tensor cores (mma.sync m16n8k8, 3xTF32) ---------------------------
+// x[j][u] = C2 * (key[j][u] + pq[u] + b[u] + sum_c f[j][c] Wl[c][u]) is a [T x 8] . [8 x Up] product added to the keys:
+// A = [f[j][0..F) | 1 | 0..] (the constant-1 slot carries pq + b), B = C2 * [Wl ; pq + b ; 0], C = C2 * keys.  Both
+// operands are split hi + lo (3 MMAs per tile) so the result keeps fp32 accuracy.  That leaves ex2 / rcp / a handful
+// of FMAs per element for the SIMT pipes, and four reciprocals share one MUFU.RCP:
+//   v0/y0 + v1/y1 + v2/y2 + v3/y3 = ((v0 y1 + v1 y0) y2 y3 + (v2 y3 + v3 y2) y0 y1) / (y0 y1 y2 y3),  y = 2^x + 1 <= 2^30 + 1.
+// Warp w owns units [32 (w % NUG), +32) and row blocks of 16 positions; partial row sums over the warp's 32 units go
+// to epart[w % NUG][j] and are summed by the softmax pass.
+__device__ __forceinline__ void mma_tf32_16x8x8(float* c, const uint32_t* a, const uint32_t* b) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
+__device__ __forceinline__ void split_tf32(float x, uint32_t& hi, uint32_t& lo) {
+  hi = __float_as_uint(x) & 0xffffe000u;
+  lo = __float_as_uint(x - __uint_as_float(hi));
+}
+__device__ __forceinline__ float quad_recip_dot(float y0, float y1, float y2, float y3, float v0, float v1, float v2,
+                                                float v3) {
+  const float ab = y0 * y1, cd = y2 * y3;
+  const float nab = fmaf(v0, y1, v1 * y0), ncd = fmaf(v2, y3, v3 * y2);
+  return fmaf(nab, cd, ncd * ab) * rcp_approx(ab * cd);
+}
+
+template <int NUG>
+__device__ void attention_energies_mma(const AttMech& m, int b, int T, int len, const float* fbuf, float* epart, int Tpad) {
+  constexpr float C2 = 2.8853900817779268f;  // 2 * log2(e)
+  constexpr int NRG = NW / NUG;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int g = lane >> 2, t = lane & 3;
+  const int ug = warp % NUG, rg = warp / NUG;
+  const int ubase = 32 * ug;
+  // first key block in flight before anything else (rows past the end are clamped to the last valid row)
+  const float* kb = m.keys + (size_t)b * T * m.Up + ubase + 2 * t;
+  const int last = len - 1;
+  auto kptr = [&](int jb, int h) { return (const float2*)(kb + (size_t)min(16 * jb + g + 8 * h, last) * m.Up); };
+  float2 kn[4][2];
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const float2* kp = kptr(rg, h);
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) kn[nt][h] = __ldg(kp + 4 * nt);
+  }
+  // per-warp constants: all loads are issued unconditionally and up front (one L2 round trip), selected afterwards
+  uint32_t bh[4][2], bl[4][2];
+  float vv[4][2];
+  {
+    float wraw[4][2], qraw[4], braw[4];
+    float2 vraw[4];
+    const int k0 = min(t, max(m.F - 1, 0)), k1 = min(t + 4, max(m.F - 1, 0));
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) {
+      const int ub = ubase + 8 * nt + g;  // B fragment: feature slot k = t (+4), unit n = g
+      wraw[nt][0] = __ldg(m.Wl + k0 * m.Up + ub);
+      wraw[nt][1] = __ldg(m.Wl + k1 * m.Up + ub);
+      qraw[nt] = __ldcg(m.pq + (size_t)ub * m.pq_su + (size_t)b * m.pq_sb);
+      braw[nt] = __ldg(m.ba + ub);
+      vraw[nt] = __ldg((const float2*)(m.v + ubase + 8 * nt + 2 * t));  // C fragment columns 2t, 2t+1
+    }
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) {
+      const int ub = ubase + 8 * nt + g;
+      const float pqb = ub < m.U ? C2 * (qraw[nt] + braw[nt]) : 0.f;
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int k = t + 4 * h;
+        const float w = k < m.F ? C2 * wraw[nt][h] : (k == m.F ? pqb : 0.f);
+        split_tf32(w, bh[nt][h], bl[nt][h]);
+      }
+      vv[nt][0] = -2.f * vraw[nt].x;
+      vv[nt][1] = -2.f * vraw[nt].y;
+    }
+  }
+  for (int jb = rg; 16 * jb < len; jb += NRG) {
+    float c[4][4];
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) {
+      c[nt][0] = C2 * kn[nt][0].x; c[nt][1] = C2 * kn[nt][0].y;
+      c[nt][2] = C2 * kn[nt][1].x; c[nt][3] = C2 * kn[nt][1].y;
+    }
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const float2* kp = kptr(jb + NRG, h);
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) kn[nt][h] = __ldg(kp + 4 * nt);
+    }
+    // A fragment: rows g / g+8 of the block, feature slots t / t+4
+    const float* fa = fbuf + (16 * jb + g) * 8 + t;
+    uint32_t ah[4], al[4];
+    split_tf32(fa[0], ah[0], al[0]);
+    split_tf32(fa[64], ah[1], al[1]);
+    split_tf32(fa[4], ah[2], al[2]);
+    split_tf32(fa[68], ah[3], al[3]);
+    float y[4][4];
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) {
+      mma_tf32_16x8x8(c[nt], al, bh[nt]);
+      mma_tf32_16x8x8(c[nt], ah, bl[nt]);
+      mma_tf32_16x8x8(c[nt], ah, bh[nt]);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) y[nt][i] = ex2_approx(fminf(c[nt][i], 30.f)) + 1.f;
+    }
+    // row g: elements [nt][0..1], row g+8: elements [nt][2..3]
+    float r0 = quad_recip_dot(y[0][0], y[0][1], y[1][0], y[1][1], vv[0][0], vv[0][1], vv[1][0], vv[1][1]) +
+               quad_recip_dot(y[2][0], y[2][1], y[3][0], y[3][1], vv[2][0], vv[2][1], vv[3][0], vv[3][1]);
+    float r1 = quad_recip_dot(y[0][2], y[0][3], y[1][2], y[1][3], vv[0][0], vv[0][1], vv[1][0], vv[1][1]) +
+               quad_recip_dot(y[2][2], y[2][3], y[3][2], y[3][3], vv[2][0], vv[2][1], vv[3][0], vv[3][1]);
+    // reduce over the 4 lanes of a quad: odd t ends up with row g+8, even t with row g
+    const bool odd = t & 1;
+    float s = odd ? r1 : r0;
+    s += __shfl_xor_sync(0xffffffffu, odd ? r0 : r1, 1);
+    s += __shfl_xor_sync(0xffffffffu, s, 2);
+    const int j = 16 * jb + g + (odd ? 8 : 0);
+    if (t < 2 && j < len) epart[ug * Tpad + j] = s;
+  }
+}
+
 // context = alignments @ values for one row: warp per memory row, lanes over float4 chunks of the depth.
 // CH = float4 chunks per lane per memory row (Dv = 4 * Cq; Cq <= 32: CH = 1 and 32 / Cq rows per warp pass;
 // Cq = 64 / 128: CH = 2 / 4).  part = NW * Dv floats of shared memory.
@@ -331,6 +450,57 @@ __device__ void attention_context_vec(const float* __restrict__ vb, const float*
   __syncthreads();
 }
 
+// The same over an fp16 copy of the values (tensor-core mode: the context is rounded to fp16 on its way into the
+// LSTM inputs anyway, and this phase is bound by the L2 -> SM bytes): a lane owns 8 halves, Dv / 8 lanes per row.
+__device__ inline void attention_context_h8(const __half* __restrict__ vb, const float* align, int len, int Dv, float* part,
+                                            float* ctx_out /* smem [Dv] */) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int lpr = Dv >> 3, G = 32 / lpr;
+  const int c0 = lane % lpr, g = lane / lpr;
+  float acc[8];
+#pragma unroll
+  for (int c = 0; c < 8; ++c) acc[c] = 0.f;
+  constexpr int UN = 8;
+  const int stride = NW * G;
+  for (int j0 = warp * G + g; j0 < len; j0 += UN * stride) {
+    uint4 v[UN];
+    float a[UN];
+#pragma unroll
+    for (int s = 0; s < UN; ++s) {
+      const int j = j0 + s * stride;
+      const bool ok = j < len;
+      a[s] = ok ? align[j] : 0.f;
+      v[s] = ok ? __ldg((const uint4*)(vb + (size_t)j * Dv) + c0) : make_uint4(0u, 0u, 0u, 0u);
+    }
+#pragma unroll
+    for (int s = 0; s < UN; ++s) {
+      const float2 f0 = __half22float2(*(const __half2*)&v[s].x), f1 = __half22float2(*(const __half2*)&v[s].y);
+      const float2 f2 = __half22float2(*(const __half2*)&v[s].z), f3 = __half22float2(*(const __half2*)&v[s].w);
+      acc[0] = fmaf(a[s], f0.x, acc[0]); acc[1] = fmaf(a[s], f0.y, acc[1]);
+      acc[2] = fmaf(a[s], f1.x, acc[2]); acc[3] = fmaf(a[s], f1.y, acc[3]);
+      acc[4] = fmaf(a[s], f2.x, acc[4]); acc[5] = fmaf(a[s], f2.y, acc[5]);
+      acc[6] = fmaf(a[s], f3.x, acc[6]); acc[7] = fmaf(a[s], f3.y, acc[7]);
+    }
+  }
+  for (int o = lpr; o < 32; o <<= 1) {
+#pragma unroll
+    for (int c = 0; c < 8; ++c) acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], o);
+  }
+  if (g == 0) {
+    float4* dst = (float4*)(part + (size_t)warp * Dv + 8 * c0);
+    dst[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+    dst[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+  }
+  __syncthreads();
+  for (int d = threadIdx.x; d < Dv; d += NT) {
+    float s = 0.f;
+#pragma unroll
+    for (int w = 0; w < NW; ++w) s += part[w * Dv + d];
+    ctx_out[d] = s;
+  }
+  __syncthreads();
+}
+
 // One (row, mechanism) item.  `sm` = ATT_SMEM_FLOATS floats of shared memory.  t = decoder step.
 __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int len, float* sm) {
   float* e = sm;                         // [MAX_T] energies -> softmax probs a
@@ -346,6 +516,8 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
   const bool loc = (m.kind == SAT_ATT_FORWARD || m.kind == SAT_ATT_LOCATION_SENSITIVE);
   const bool fwd = (m.kind == SAT_ATT_FORWARD);
   float* align = e;  // the alignments handed to the context / history
+  const int lane = tid & 31, warp = tid >> 5;
+  float u_prev = 0.f;
   long long tp = 0;
   int ps = 0;
   const bool profiling = m.prof && blockIdx.x == 0 && tid == 0;
@@ -369,8 +541,10 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
       const int jj = j - HALO;
       aprev[j] = (loc && jj >= 0 && jj < T) ? __ldcg(m.st_align + (size_t)b * T + jj) : 0.f;
     }
-    if (fwd)
+    if (fwd) {
       for (int j = tid; j < T; j += NT) alpha[j] = __ldcg(m.st_alpha + (size_t)b * T + j);
+      u_prev = __ldcg(m.st_u + b);
+    }
     __syncthreads();
     stamp();
     if (loc && m.F <= 8) {
@@ -380,7 +554,7 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
       for (int i = tid; i < m.Kc * 8; i += NT) wsm[i] = (i & 7) < m.F ? __ldg(m.conv_w + (i >> 3) * m.F + (i & 7)) : 0.f;
       __syncthreads();
       const int c = tid & 7;
-      const float cb = c < m.F ? __ldg(m.conv_b + c) : 0.f;
+      const float cb = c < m.F ? __ldg(m.conv_b + c) : (c == m.F ? 1.f : 0.f);  // slot F = 1: carries pq + b in the MMA form
       for (int j0 = 4 * (tid >> 3); j0 < T; j0 += 4 * (NT / 8)) {
         const float* a = aprev + HALO + j0 - m.pad_left;
         float f0 = cb, f1 = cb, f2 = cb, f3 = cb;
@@ -403,57 +577,98 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
       __syncthreads();
     }
     stamp();
-    if (m.Up >= 128 && (!loc || m.F <= 8)) {
+    const int Tpad = (T + 15) & ~15;
+    const int nug = m.Up >> 5;
+    // partial energies per 32-unit group live in the (dead) nal .. ctxs region: 3 * MAX_T floats
+    const bool use_mma = loc && m.F <= 7 && (m.Up == 128 || m.Up == 256) && nug * Tpad <= 3 * MAX_T;
+    float* epart = nal;
+    if (use_mma) {
+      if (m.Up == 256) attention_energies_mma<8>(m, b, T, len, fbuf, epart, Tpad);
+      else attention_energies_mma<4>(m, b, T, len, fbuf, epart, Tpad);
+    } else if (m.Up >= 128 && (!loc || m.F <= 8)) {
       if (!loc) attention_energies_w32<0>(m, b, T, len, fbuf, e, e2);
       else if (m.F <= 4) attention_energies_w32<4>(m, b, T, len, fbuf, e, e2);
       else if (m.F == 5) attention_energies_w32<5>(m, b, T, len, fbuf, e, e2);
       else attention_energies_w32<8>(m, b, T, len, fbuf, e, e2);
-      for (int j = len + tid; j < T; j += NT) {  // masked tail
-        e[j] = -INFINITY;
-        e2[j] = 0.f;
-      }
     } else if (!loc) attention_energies<0>(m, b, T, len, aprev, fbuf, e, e2);
     else if (m.F <= 4) attention_energies<4>(m, b, T, len, aprev, fbuf, e, e2);
     else if (m.F == 5) attention_energies<5>(m, b, T, len, aprev, fbuf, e, e2);
     else if (m.F <= 8) attention_energies<8>(m, b, T, len, aprev, fbuf, e, e2);
     else attention_energies<-1>(m, b, T, len, aprev, fbuf, e, e2);
     __syncthreads();
-    if (m.Up > 128)
-      for (int j = tid; j < T; j += NT) e[j] += e2[j];
     stamp();
-    // masked softmax (TF: softmax(where(j < len, score, -inf)))
+    // masked softmax (TF: softmax(where(j < len, score, -inf))), the forward-variable recursion and the state update
+    // with every element in registers (T <= 2 * NT) and one CTA barrier per reduction
+    constexpr int NJ = MAX_T / NT;
+    float x[NJ], pr[NJ];
     float mx = -INFINITY;
-    for (int j = tid; j < T; j += NT) mx = fmaxf(mx, e[j]);
-    mx = block_max(mx, s32);
-    float sum = 0.f;
-    for (int j = tid; j < T; j += NT) {
-      const float ex = (j < len) ? expf(e[j] - mx) : 0.f;
-      e[j] = ex;
-      sum += ex;
+#pragma unroll
+    for (int i = 0; i < NJ; ++i) {
+      const int j = tid + i * NT;
+      x[i] = -INFINITY;
+      if (j < len) {
+        if (use_mma) {
+          float a = 0.f;
+          for (int q = 0; q < nug; ++q) a += epart[q * Tpad + j];
+          x[i] = a;
+        } else {
+          x[i] = m.Up > 128 ? e[j] + e2[j] : e[j];
+        }
+      }
+      mx = fmaxf(mx, x[i]);
     }
-    sum = block_sum(sum, s32);
-    for (int j = tid; j < T; j += NT) e[j] = e[j] / sum;
+    mx = warp_max(mx);
+    if (lane == 0) s32[warp] = mx;
     __syncthreads();
+    mx = warp_max(lane < NW ? s32[lane] : -INFINITY);
+    float sum = 0.f;
+#pragma unroll
+    for (int i = 0; i < NJ; ++i) {
+      pr[i] = (tid + i * NT < len) ? expf(x[i] - mx) : 0.f;
+      sum += pr[i];
+    }
+    sum = warp_sum(sum);
+    if (lane == 0) s32[NW + warp] = sum;
+    __syncthreads();
+    sum = warp_sum(lane < NW ? s32[NW + lane] : 0.f);
+#pragma unroll
+    for (int i = 0; i < NJ; ++i) {
+      const int j = tid + i * NT;
+      pr[i] = pr[i] / sum;
+      if (j < T) {
+        e[j] = pr[i];
+        m.st_align[(size_t)b * T + j] = m.cumulative ? pr[i] + aprev[HALO + j] : pr[i];
+      }
+    }
     if (fwd) {
       // alpha' = ((1-u) alpha + u shift(alpha) + 1e-7) * a ; alpha = alpha' / sum(alpha')
-      const float u = __ldcg(m.st_u + b);
-      float s2 = 0.f;
-      for (int j = tid; j < T; j += NT) {
-        const float sh = j > 0 ? alpha[j - 1] : 0.f;
-        const float val = (((1.f - u) * alpha[j] + u * sh) + 1e-7f) * e[j];
-        nal[j] = val;
-        s2 += val;
+      float val[NJ], s2 = 0.f;
+#pragma unroll
+      for (int i = 0; i < NJ; ++i) {
+        const int j = tid + i * NT;
+        val[i] = 0.f;
+        if (j < T) {
+          const float sh = j > 0 ? alpha[j - 1] : 0.f;
+          val[i] = (((1.f - u_prev) * alpha[j] + u_prev * sh) + 1e-7f) * pr[i];
+        }
+        s2 += val[i];
       }
-      s2 = block_sum(s2, s32);
-      for (int j = tid; j < T; j += NT) nal[j] = nal[j] / s2;
+      s2 = warp_sum(s2);
+      if (lane == 0) s32[2 * NW + warp] = s2;
       __syncthreads();
+      s2 = warp_sum(lane < NW ? s32[2 * NW + lane] : 0.f);
+#pragma unroll
+      for (int i = 0; i < NJ; ++i) {
+        const int j = tid + i * NT;
+        if (j < T) {
+          const float a = val[i] / s2;
+          nal[j] = a;
+          m.st_alpha[(size_t)b * T + j] = a;
+        }
+      }
       align = nal;
     }
-    // next state
-    for (int j = tid; j < T; j += NT) {
-      m.st_align[(size_t)b * T + j] = m.cumulative ? e[j] + aprev[HALO + j] : e[j];
-      if (fwd) m.st_alpha[(size_t)b * T + j] = align[j];
-    }
+    __syncthreads();
   }
   if (m.out_align)
     for (int j = tid; j < T; j += NT) m.out_align[((size_t)b * m.out_S + t) * T + j] = align[j];
@@ -464,7 +679,10 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
   const int Dv = m.Dv, Cq = Dv >> 2;
   const float* vb = m.values + (size_t)b * T * Dv;
   const bool vec = (Dv & 3) == 0 && (Cq & (Cq - 1)) == 0 && Cq <= 128 && ((((size_t)vb) & 15) == 0);
-  if (vec) {
+  const int C8 = Dv >> 3;
+  if (m.values16 && (Dv & 7) == 0 && (C8 & (C8 - 1)) == 0 && C8 <= 32) {
+    attention_context_h8(m.values16 + (size_t)b * T * Dv, align, len, Dv, fbuf, ctxs);
+  } else if (vec) {
     float* cpart = fbuf;  // location features are dead by now
     if (Cq <= 32) attention_context_vec<1>(vb, align, len, Dv, cpart, ctxs);
     else if (Cq == 64) attention_context_vec<2>(vb, align, len, Dv, cpart, ctxs);

@@ -76,12 +76,19 @@ struct GridBarrier {
   unsigned* counter;
   unsigned gen;
   __device__ __forceinline__ void sync() {
+    sync([] {});
+  }
+  // `between` runs on thread 0 after this CTA has arrived and before it starts waiting for the others: work that only
+  // needs data from earlier phases (e.g. TMA prefetch for the next phase) hides behind the barrier latency
+  template <class F>
+  __device__ __forceinline__ void sync(F&& between) {
     __syncthreads();
     if (threadIdx.x == 0) {
       gen += 1;
       const unsigned target = gen * gridDim.x;
       __threadfence();
       atomicAdd(counter, 1u);
+      between();
       unsigned seen;
       do {
         asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(counter) : "memory");

@@ -416,6 +416,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
   tcs.tmem = 0;
   tcs.n_chunks = 0;
   tcs.n_items = 0;
+  tcs.prefilled = 0;
   tcs.prof = p.prof ? p.prof + 24 : nullptr;
   if (p.tc) {
     if (tid == 0) {
@@ -447,8 +448,15 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
   }
   long long tprev = 0;
   int ph = 0;
-  auto phase_end = [&]() {
-    bar.sync();
+  // next_lstm / next_map: the tensor-core LSTM phase that follows this barrier (null: none) -- its "old" input
+  // columns are requested while the CTA waits for the other CTAs
+  auto phase_end = [&](const TcLstmDesc* next_lstm = nullptr, const CUtensorMap* next_map = nullptr) {
+    if (next_lstm) {
+      tc::fence_proxy_async();  // every thread: its generic-proxy writes to the scratch precede the TMA writes
+      bar.sync([&] { tc_prefill(*next_lstm, next_map, p.RB, tcs); });
+    } else {
+      bar.sync();
+    }
     if (p.prof && blockIdx.x == 0 && tid == 0) {
       const long long now = clock64();
       p.prof[ph] += now - tprev;
@@ -459,7 +467,12 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
 
   // prenet of the <GO> frame -> attention-LSTM input of step 0
   frame_phase(p, 0, nullptr, 0, Act2D{p.att_in[0], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc}, true, scratch);
-  bar.sync();
+  if (p.tc) {
+    tc::fence_proxy_async();
+    bar.sync([&] { tc_prefill(p.tc_a, p.maps, p.RB, tcs); });
+  } else {
+    bar.sync();
+  }
 
   int t = 0;
   for (; t < p.max_steps; ++t) {
@@ -513,7 +526,8 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
       m.prof = p.prof ? p.prof + 16 : nullptr;
       attention_item(m, b, t, p.T, (int)p.lengths[b], scratch);
     }
-    phase_end();
+    if (p.tc) phase_end(&p.tc_1, p.maps + 2 + cur);
+    else phase_end();
     // ---- F: decoder LSTM 1 ----
     if (p.tc) {
       const int h0 = p.A + p.Dctx;
@@ -528,7 +542,8 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
                   LstmEpi{p.lstm_1.bias, p.Dd, ld, p.B, p.c_1, p.l1_in[cur] + hoff, p.l2_in[cur],
                           p.l1_in[nxt] + hoff, nullptr, 0, 0, p.zc, p.zh});
     }
-    phase_end();
+    if (p.tc) phase_end(&p.tc_2, p.maps + 4 + cur);
+    else phase_end();
     // ---- G: decoder LSTM 2 ----
     if (p.tc) {
       const int h0 = p.Dd;
@@ -564,7 +579,8 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
     }
     // ---- L+A+B: frame + stop projection of step t, fed-back frame, prenet of step t+1 (row split) ----
     frame_phase(p, t, y, p.outp.K, Act2D{p.att_in[nxt], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc}, false, scratch);
-    phase_end();
+    if (p.tc && t + 1 < p.max_steps) phase_end(&p.tc_a, p.maps + nxt);
+    else phase_end();
     // ---- stop rule (every CTA evaluates the same data -> same decision) ----
     if (p.stop_mode != SAT_STOP_FIXED) {
       bool term = true, stopped = true;
@@ -587,6 +603,13 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
   }
   if (blockIdx.x == 0 && tid == 0) *p.n_steps = t;
   if (p.tc) {
+    if (tid == 0) {
+      // a stop decision can leave the prefetch for the next step in flight: let it land before the CTA exits
+      for (uint32_t c = 0; c < tcs.prefilled; ++c) {
+        const uint32_t n = tcs.n_chunks + c;
+        tc::mbar_wait(tcs.full + n % TC_STAGES, (n / TC_STAGES) & 1);
+      }
+    }
     tc::tc_fence_before();
     __syncthreads();
     if (tid < 32) tc::tmem_dealloc(tcs.tmem, 32);

@@ -43,6 +43,9 @@ struct TcLstmDesc {
   int st_off;         // byte offset of this layer's resident cell state inside the TC weight region
   int slots;          // resident (tile,row block) items per CTA
   int kchunks;        // ceil(K / 64)
+  int n_pre;          // leading chunks of `order` whose columns were produced at least two phases ago: their TMA
+                      // loads are issued while the CTA waits at the grid barrier in front of the phase
+  unsigned char order[48];  // chunk visiting order (a permutation of 0 .. kchunks-1), "old" columns first
 };
 
 // per-CTA pipeline state that persists across phases and decoder steps
@@ -55,6 +58,7 @@ struct TcState {
   uint32_t tmem;
   uint32_t n_chunks;   // chunks pushed through the ring so far (identical in every thread)
   uint32_t n_items;    // accumulator hand-overs so far
+  uint32_t prefilled;  // chunks of the next LSTM phase already requested by tc_prefill (thread 0 only)
   long long* prof;     // optional cycle counters (CTA 0): [0] producer loop, [1] wait for the accumulator, [2] cell update
 };
 
@@ -77,6 +81,22 @@ __device__ inline void tc_load_resident(const TcLstmDesc& d, int RB, const TcSta
   }
   float* state = (float*)(st.wimg + d.st_off);
   for (int i = threadIdx.x; i < d.slots * (TC_STATE_BYTES / 4); i += NT) state[i] = 0.f;
+}
+
+// thread 0, between arriving at and waiting on the grid barrier in front of an LSTM phase: request the first chunks
+// of the CTA's first item (columns that do not depend on the phase that is just finishing)
+__device__ inline void tc_prefill(const TcLstmDesc& d, const CUtensorMap* xmap, int RB, TcState& st) {
+  const int item = blockIdx.x;
+  if (item >= d.n_tiles * RB || d.n_pre == 0) return;
+  const int row0 = (item % RB) * TC_M;
+  tc::fence_proxy_async();
+  for (int c = 0; c < d.n_pre; ++c) {
+    const uint32_t n = st.n_chunks + c, s = n % TC_STAGES, use = n / TC_STAGES;
+    if (use > 0) tc::mbar_wait(st.empty + s, (use - 1) & 1);
+    tc::mbar_arrive_expect_tx(st.full + s, TC_STAGE_BYTES);
+    tc::tma_load_2d(st.ring + s * TC_STAGE_BYTES, xmap, st.full + s, d.order[c] * tc::CHUNK_K16, row0);
+  }
+  st.prefilled = d.n_pre;
 }
 
 struct TcLstmIO {
@@ -104,12 +124,14 @@ __device__ inline void lstm_phase_tc(const TcLstmDesc& d, const TcLstmIO& io, in
     long long t0 = 0;
     if (prof_on) t0 = clock64();
     if (tid == 0) {
-      // ---- TMA producer ----
-      for (int c = 0; c < d.kchunks; ++c) {
+      // ---- TMA producer (the first st.prefilled chunks of the first item are already in flight) ----
+      const int c0 = slot == 0 ? (int)st.prefilled : 0;
+      st.prefilled = 0;
+      for (int c = c0; c < d.kchunks; ++c) {
         const uint32_t n = st.n_chunks + c, s = n % TC_STAGES, use = n / TC_STAGES;
         if (use > 0) tc::mbar_wait(st.empty + s, (use - 1) & 1);
         tc::mbar_arrive_expect_tx(st.full + s, TC_STAGE_BYTES);
-        tc::tma_load_2d(st.ring + s * TC_STAGE_BYTES, io.xmap, st.full + s, c * tc::CHUNK_K16, row0);
+        tc::tma_load_2d(st.ring + s * TC_STAGE_BYTES, io.xmap, st.full + s, d.order[c] * tc::CHUNK_K16, row0);
       }
       if (prof_on) st.prof[0] += clock64() - t0;
     } else if (tid == 32) {
@@ -119,7 +141,7 @@ __device__ inline void lstm_phase_tc(const TcLstmDesc& d, const TcLstmIO& io, in
         const uint32_t n = st.n_chunks + c, s = n % TC_STAGES, use = n / TC_STAGES;
         tc::mbar_wait(st.full + s, use & 1);
         tc::tc_fence_after();
-        const uint32_t a0 = tc::smem_u32(st.ring + s * TC_STAGE_BYTES), b0 = tc::smem_u32(img + c * 2048);
+        const uint32_t a0 = tc::smem_u32(st.ring + s * TC_STAGE_BYTES), b0 = tc::smem_u32(img + d.order[c] * 2048);
 #pragma unroll
         for (int k16 = 0; k16 < tc::CHUNK_K16 / tc::UMMA_K16; ++k16)
           tc::mma_f16(st.tmem, tc::smem_desc_sw128(a0 + k16 * 32), tc::smem_desc_sw128(b0 + k16 * 32), idesc,
