@@ -1,5 +1,6 @@
 // common.cuh -- host-side plumbing shared by every translation unit of libsat.so.
 #pragma once
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <cstdint>
 #include <cstdio>
@@ -147,6 +148,28 @@ struct GemmArgs {
   int highway = 0;                       // 1: HighwayNet epilogue over interleaved (H_u, T_u) column pairs; R = layer input; writes N/2 columns
 };
 void gemm_launch(const GemmArgs& a, cudaStream_t st);
+
+// ---- tensor-core implicit-GEMM conv1d (conv_tc.cu) -----------------------------
+constexpr int CONV_TC_HALO = 8;  // zero rows on each side of every utterance in the haloed fp16 layout (taps <= 16)
+struct ConvTcLaunch {
+  const __half* xp = nullptr;  // haloed fp16 input [B][T + 2*HALO][ldxp]
+  int ldxp = 0, B = 0, T = 0, cin = 0, cout = 0, taps = 1, pad_left = 0;
+  const __half* wimg = nullptr;  // conv_tc_weight_image
+  const float* scale = nullptr;
+  const float* shift = nullptr;
+  int act = ACT_NONE;
+  __half* y16 = nullptr;  // haloed fp16 output (pointer already offset to the first output channel), row stride ld16
+  int ld16 = 0;
+  float* y32 = nullptr;   // dense fp32 output [B*T][ld32]
+  int ld32 = 0;
+  const float* res = nullptr;  // optional fp32 residual [B*T][ldr] (fp32 output only)
+  int ldr = 0;
+};
+bool conv_tc_supported(int cin, int cout);
+__half* conv_tc_weight_image(DevPool& pool, const float* w, int taps, int cin, int n);
+void conv_tc_pack(const float* x, int ldx, int B, int T, int C, __half* xp, int ldp, cudaStream_t st);
+void conv_tc_maxpool2(const __half* x, int B, int T, int C, __half* y, cudaStream_t st);
+void conv_tc_launch(const ConvTcLaunch& L, cudaStream_t st);
 
 // ---- multi-head self-attention (mha.cu) --------------------------------------
 // Device copy of one MultiHeadAttention (modules/self_attention.py:89-128) and, optionally, the

@@ -1,0 +1,228 @@
+// conv_tc.cu -- tensor-core implicit-GEMM conv1d for the dense contractions of the encoder (conv bank, proj1) and the
+// post-net: tcgen05.mma kind::f16 (fp16 operands, fp32 accumulation in TMEM), both operands fed by TMA.
+//
+// Activations live in a zero-haloed fp16 buffer XP[B][Tp][C], Tp = T + 2*HALO (flat rows R = B*Tp): the input window
+// of tap tau of a 128-row output tile is the same 128 x 64 box shifted by (tau - pad_left) rows, so 'SAME' padding and
+// the utterance boundaries need no gather -- the halo rows are zero and TMA zero-fills outside the buffer.
+// Weights are a K-major fp16 image Wimg[N][taps*Cin].  One CTA computes a 128 (rows) x 128 (channels) tile:
+//   thread 0   : TMA producer over taps x (Cin/64) chunks, 5-stage ring of {A 16 KB, B 16 KB}
+//   thread 32  : MMA issuer, 4 x (M=128, N=128, K=16) per chunk into a 128-column TMEM accumulator
+//   4 warps    : epilogue -- TMEM -> registers -> folded BatchNorm scale/shift -> activation -> fp16 (haloed layout,
+//                halo rows untouched) or fp32 (dense [B*T][ldc]) stores, 16 bytes per access.
+// Restates the Conv1d of tacotron2 (conv -> BN(inference) -> activation) used by
+// modules/module.py:77-110 (ZoneoutCBHG) and by PostNetV2.
+#include "common.cuh"
+#include "tc.cuh"
+
+namespace sat {
+namespace {
+
+constexpr int CT_STAGES = 5;
+constexpr int CT_STAGE_BYTES = 2 * 16384;
+constexpr int CT_THREADS = 128;
+
+struct ConvTcArgs {
+  int R, Tp, T, halo;       // flat rows, rows per utterance incl. halos, valid rows, halo size
+  int taps, pad_left, cin;  // cin % 64 == 0
+  const float* scale;       // [N] folded BN (null = 1)
+  const float* shift;       // [N] (null = 0)
+  int act;
+  __half* y16;              // haloed fp16 output [R][ld16] at channel offset (or null)
+  int ld16;
+  float* y32;               // dense fp32 output [B*T][ld32] (or null)
+  int ld32;
+  const float* res;         // optional fp32 residual [B*T][ldr] added before the store (fp32 output only)
+  int ldr;
+};
+
+__global__ void __launch_bounds__(CT_THREADS, 1)
+conv_tc_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant__ CUtensorMap wmap, const ConvTcArgs a) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* ring = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  __shared__ __align__(8) uint64_t bars[2 * CT_STAGES + 1];
+  __shared__ uint32_t tmem_slot;
+  uint64_t* full = bars;
+  uint64_t* empty = bars + CT_STAGES;
+  uint64_t* done = bars + 2 * CT_STAGES;
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int r0 = blockIdx.x * 128, n0 = blockIdx.y * 128;
+  const int cpc = a.cin / tc::CHUNK_K16, nchunks = a.taps * cpc;
+
+  if (tid == 0) {
+    for (int i = 0; i < 2 * CT_STAGES + 1; ++i) tc::mbar_init(bars + i, 1);
+    tc::fence_mbar_init();
+    tc::tma_prefetch_desc(&xmap);
+    tc::tma_prefetch_desc(&wmap);
+  }
+  if (warp == 0) tc::tmem_alloc(&tmem_slot, 128);
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem = tmem_slot;
+
+  if (tid == 0) {
+    for (int c = 0; c < nchunks; ++c) {
+      const int s = c % CT_STAGES, use = c / CT_STAGES;
+      if (use > 0) tc::mbar_wait(empty + s, (use - 1) & 1);
+      const int tau = c / cpc, c0 = (c - tau * cpc) * tc::CHUNK_K16;
+      tc::mbar_arrive_expect_tx(full + s, CT_STAGE_BYTES);
+      tc::tma_load_2d(ring + s * CT_STAGE_BYTES, &xmap, full + s, c0, r0 + tau - a.pad_left);
+      tc::tma_load_2d(ring + s * CT_STAGE_BYTES + 16384, &wmap, full + s, tau * a.cin + c0, n0);
+    }
+  } else if (tid == 32) {
+    const uint32_t idesc = tc::idesc_f16(128, 128);
+    for (int c = 0; c < nchunks; ++c) {
+      const int s = c % CT_STAGES, use = c / CT_STAGES;
+      tc::mbar_wait(full + s, use & 1);
+      tc::tc_fence_after();
+      const uint32_t a0 = tc::smem_u32(ring + s * CT_STAGE_BYTES), b0 = a0 + 16384;
+#pragma unroll
+      for (int k16 = 0; k16 < tc::CHUNK_K16 / tc::UMMA_K16; ++k16)
+        tc::mma_f16(tmem, tc::smem_desc_sw128(a0 + k16 * 32), tc::smem_desc_sw128(b0 + k16 * 32), idesc, (c | k16) != 0);
+      tc::mma_commit(empty + s);
+    }
+    tc::mma_commit(done);
+  }
+  __syncwarp();
+  tc::mbar_wait(done, 0);
+  tc::tc_fence_after();
+
+  // ---- epilogue: one flat row per thread ----
+  const int r = r0 + tid;
+  const int b = r / a.Tp, tt = r - b * a.Tp - a.halo;
+  const bool valid = r < a.R && tt >= 0 && tt < a.T;
+  const size_t drow = (size_t)b * a.T + tt;
+#pragma unroll 1
+  for (int cb = 0; cb < 128; cb += 16) {
+    float v[16];
+    tc::tmem_ld16(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)cb, v);
+    if (!valid) continue;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const int n = n0 + cb + i;
+      float x = v[i];
+      if (a.scale) x *= __ldg(a.scale + n);
+      if (a.shift) x += __ldg(a.shift + n);
+      if (a.act == ACT_RELU) x = fmaxf(x, 0.f);
+      else if (a.act == ACT_TANH) x = tanhf(x);
+      v[i] = x;
+    }
+    if (a.y16) {
+      __half2 h[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) h[i] = __halves2half2(tc::to_f16(v[2 * i]), tc::to_f16(v[2 * i + 1]));
+      uint4* dst = (uint4*)(a.y16 + (size_t)r * a.ld16 + n0 + cb);
+      dst[0] = *(const uint4*)&h[0];
+      dst[1] = *(const uint4*)&h[4];
+    }
+    if (a.y32) {
+      if (a.res) {
+        const float4* rp = (const float4*)(a.res + drow * a.ldr + n0 + cb);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float4 q = __ldg(rp + i);
+          v[4 * i] += q.x; v[4 * i + 1] += q.y; v[4 * i + 2] += q.z; v[4 * i + 3] += q.w;
+        }
+      }
+      float4* dst = (float4*)(a.y32 + drow * a.ld32 + n0 + cb);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) dst[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+    }
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tc::tmem_dealloc(tmem, 128);
+}
+
+// fp32 [B*T][C] (row stride ldx) -> interior of the haloed fp16 buffer [B][Tp][ldp] at channel offset 0
+__global__ void pack_f16_haloed_kernel(const float* __restrict__ x, int ldx, int B, int T, int C, int Tp, int halo,
+                                       __half* __restrict__ xp, int ldp) {
+  const size_t n = (size_t)B * T * (C / 4);
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const int c4 = (int)(i % (C / 4));
+    const size_t row = i / (C / 4);
+    const int b = (int)(row / T), t = (int)(row % T);
+    const float4 v = __ldg((const float4*)(x + row * ldx) + c4);
+    __half2* dst = (__half2*)(xp + ((size_t)b * Tp + halo + t) * ldp + 4 * c4);
+    dst[0] = __halves2half2(tc::to_f16(v.x), tc::to_f16(v.y));
+    dst[1] = __halves2half2(tc::to_f16(v.z), tc::to_f16(v.w));
+  }
+}
+
+// MaxPooling1D(pool 2, stride 1, 'same') over time on the haloed fp16 layout: y[t] = max(x[t], x[t+1]), y[T-1] = x[T-1]
+__global__ void maxpool2_f16_haloed_kernel(const __half* __restrict__ x, int B, int T, int C, int Tp, int halo,
+                                           __half* __restrict__ y) {
+  const size_t n = (size_t)B * T * (C / 8);
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const int c8 = (int)(i % (C / 8));
+    const size_t row = i / (C / 8);
+    const int b = (int)(row / T), t = (int)(row % T);
+    const size_t o = ((size_t)b * Tp + halo + t) * C + 8 * c8;
+    uint4 u = __ldg((const uint4*)(x + o));
+    if (t + 1 < T) {
+      const uint4 w = __ldg((const uint4*)(x + o + C));
+      __half2* p = (__half2*)&u;
+      const __half2* q = (const __half2*)&w;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) p[k] = __hmax2(p[k], q[k]);
+    }
+    *(uint4*)(y + o) = u;
+  }
+}
+
+}  // namespace
+
+// K-major fp16 image [N][taps*Cin] of a TF conv kernel [taps][Cin][N]
+__half* conv_tc_weight_image(DevPool& pool, const float* w, int taps, int cin, int n) {
+  std::vector<__half> img((size_t)n * taps * cin);
+  for (int t = 0; t < taps; ++t)
+    for (int c = 0; c < cin; ++c)
+      for (int o = 0; o < n; ++o) img[(size_t)o * taps * cin + (size_t)t * cin + c] = __float2half_rn(w[((size_t)t * cin + c) * n + o]);
+  std::vector<float> packed((img.size() + 1) / 2);
+  memcpy(packed.data(), img.data(), img.size() * sizeof(__half));
+  return (__half*)pool.upload(packed);
+}
+
+bool conv_tc_supported(int cin, int cout) { return cin % 64 == 0 && cout % 128 == 0; }
+
+void conv_tc_pack(const float* x, int ldx, int B, int T, int C, __half* xp, int ldp, cudaStream_t st) {
+  const int Tp = T + 2 * CONV_TC_HALO;
+  const size_t n = (size_t)B * T * (C / 4);
+  pack_f16_haloed_kernel<<<(unsigned)std::min<size_t>((n + 255) / 256, 148 * 16), 256, 0, st>>>(x, ldx, B, T, C, Tp, CONV_TC_HALO, xp, ldp);
+  count_launch();
+}
+
+void conv_tc_maxpool2(const __half* x, int B, int T, int C, __half* y, cudaStream_t st) {
+  const int Tp = T + 2 * CONV_TC_HALO;
+  const size_t n = (size_t)B * T * (C / 8);
+  maxpool2_f16_haloed_kernel<<<(unsigned)std::min<size_t>((n + 255) / 256, 148 * 16), 256, 0, st>>>(x, B, T, C, Tp, CONV_TC_HALO, y);
+  count_launch();
+}
+
+void conv_tc_launch(const ConvTcLaunch& L, cudaStream_t st) {
+  SAT_REQUIRE(conv_tc_supported(L.cin, L.cout), "tensor-core conv needs Cin %% 64 == 0 and Cout %% 128 == 0 (got %d, %d)", L.cin, L.cout);
+  SAT_REQUIRE(L.taps >= 1 && L.taps <= 2 * CONV_TC_HALO && L.pad_left <= CONV_TC_HALO && L.taps - 1 - L.pad_left <= CONV_TC_HALO,
+              "conv taps %d exceed the activation halo", L.taps);
+  const int Tp = L.T + 2 * CONV_TC_HALO;
+  const uint64_t R = (uint64_t)L.B * Tp;
+  CUtensorMap xmap, wmap;
+  make_tensor_map_2d_f16(&xmap, L.xp, R, (uint64_t)L.cin, (uint64_t)L.ldxp, 128);
+  make_tensor_map_2d_f16(&wmap, L.wimg, (uint64_t)L.cout, (uint64_t)L.taps * L.cin, (uint64_t)L.taps * L.cin, 128);
+  ConvTcArgs a;
+  a.R = (int)R; a.Tp = Tp; a.T = L.T; a.halo = CONV_TC_HALO;
+  a.taps = L.taps; a.pad_left = L.pad_left; a.cin = L.cin;
+  a.scale = L.scale; a.shift = L.shift; a.act = L.act;
+  a.y16 = L.y16; a.ld16 = L.ld16; a.y32 = L.y32; a.ld32 = L.ld32; a.res = L.res; a.ldr = L.ldr;
+  static bool attr_set = false;
+  const int smem = CT_STAGES * CT_STAGE_BYTES + 1024;
+  if (!attr_set) {
+    SAT_CUDA(cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    attr_set = true;
+  }
+  dim3 grid((unsigned)((R + 127) / 128), (unsigned)(L.cout / 128));
+  conv_tc_kernel<<<grid, CT_THREADS, smem, st>>>(xmap, wmap, a);
+  count_launch();
+  check_launch("conv_tc_kernel");
+}
+
+}  // namespace sat

@@ -14,6 +14,7 @@
 // The BiLSTM input projection is one time-batched GEMM; the recurrence runs in a kernel where each
 // CTA owns a few (row, direction) sequences for all T steps (rows are independent -> no grid sync).
 #include "common.cuh"
+#include <cstdlib>
 
 namespace sat {
 namespace {
@@ -88,6 +89,7 @@ __global__ void __launch_bounds__(LSTM_NT) bilstm_kernel(const float* __restrict
 }
 
 struct Conv {
+  __half* wimg = nullptr;  // K-major fp16 image for the tensor-core path (null when the shape is not supported)
   float* w = nullptr;      // [k][cin][cout]
   float* scale = nullptr;  // folded BN
   float* shift = nullptr;
@@ -98,6 +100,8 @@ Conv upload_conv_bn(DevPool& pool, const Blob& W, const std::string& P, int k, i
   Conv c;
   c.k = k; c.cin = cin; c.cout = cout;
   c.w = pool.upload(W.get(P + "/kernel", (int64_t)k * cin * cout), (size_t)k * cin * cout);
+  if (conv_tc_supported(cin, cout) && k <= 2 * CONV_TC_HALO)
+    c.wimg = conv_tc_weight_image(pool, W.get(P + "/kernel", (int64_t)k * cin * cout), k, cin, cout);
   const float* gamma = W.get(P + "/bn/gamma", cout);
   const float* beta = W.get(P + "/bn/beta", cout);
   const float* mean = W.get(P + "/bn/mean", cout);
@@ -146,6 +150,8 @@ struct sat_encoder {
   float *sap_w = nullptr, *sap_b = nullptr;
   std::vector<MhaDev> hops;
   int half = 0, cin = 0;
+  bool tc = false;  // conv bank + proj1 on the tensor cores (fp16 operands, fp32 accumulation)
+  Scratch ws16;     // haloed fp16 activations of that path
 };
 
 extern "C" int sat_encoder_create(const sat_hparams* hpp, const sat_tensor* weights, int32_t n_weights, sat_encoder** out) {
@@ -220,6 +226,9 @@ extern "C" int sat_encoder_create(const sat_hparams* hpp, const sat_tensor* weig
       h->lstm_bx = pool.upload(bx);
       h->lstm_wh = pool.upload(wh);
     }
+    h->tc = h->proj1.wimg != nullptr;
+    for (const Conv& c : h->bank) h->tc = h->tc && c.wimg != nullptr;
+    if (const char* e = getenv("SAT_ENC_TC")) h->tc = h->tc && atoi(e) != 0;
     if (hp.encoder_kind == SAT_ENC_SELF_ATTENTION_CBHG) {
       const int Ds = hp.self_attention_out_units;
       h->sap_w = pool.upload(W.get("encoder/sa_projection/kernel", (int64_t)hp.cbhg_out_units * Ds), (size_t)hp.cbhg_out_units * Ds);
@@ -274,16 +283,43 @@ static int encoder_forward_impl(sat_encoder* h, const int64_t* ids, const float*
       g1.W = h->pre_w[1]; g1.N = P1; g1.shift = h->pre_b[1]; g1.act = ACT_RELU; g1.C = ws + o_p1; g1.ldc = P1;
       gemm_launch(g1, st);
     }
-    // ---- conv bank -> concat buffer [rows][KW*Cb] ----
     const int ldb = KW * Cb;
-    for (int k = 1; k <= KW; ++k) {
-      const Conv& c = h->bank[k - 1];
-      conv_bn_act_launch(ws + o_p1, B, T, P1, c.w, c.scale, c.shift, k, P1, Cb, ACT_RELU, 0, nullptr, 0,
-                         ws + o_bank + (size_t)(k - 1) * Cb, ldb, st);
+    if (h->tc) {
+      // ---- conv bank, max-pool and proj1 on the tensor cores over zero-haloed fp16 activations (conv_tc.cu) ----
+      const int Tp = T + 2 * CONV_TC_HALO;
+      const size_t R = (size_t)B * Tp;
+      const size_t n_x = R * P1, n_bank = R * (size_t)ldb;
+      __half* x16 = h->ws16.get<__half>(n_x + 2 * n_bank + 64);
+      __half* bank16 = x16 + (n_x + 7) / 8 * 8;
+      __half* pool16 = bank16 + n_bank;
+      SAT_CUDA(cudaMemsetAsync(x16, 0, (n_x + 2 * n_bank + 64) * sizeof(__half), st));
+      conv_tc_pack(ws + o_p1, P1, B, T, P1, x16, P1, st);
+      for (int k = 1; k <= KW; ++k) {
+        const Conv& c = h->bank[k - 1];
+        ConvTcLaunch L;
+        L.xp = x16; L.ldxp = P1; L.B = B; L.T = T; L.cin = P1; L.cout = Cb; L.taps = k; L.pad_left = (k - 1) / 2;
+        L.wimg = c.wimg; L.scale = c.scale; L.shift = c.shift; L.act = ACT_RELU;
+        L.y16 = bank16 + (size_t)(k - 1) * Cb; L.ld16 = ldb;
+        conv_tc_launch(L, st);
+      }
+      conv_tc_maxpool2(bank16, B, T, ldb, pool16, st);
+      ConvTcLaunch L;
+      L.xp = pool16; L.ldxp = ldb; L.B = B; L.T = T; L.cin = ldb; L.cout = h->proj1.cout; L.taps = 3; L.pad_left = 1;
+      L.wimg = h->proj1.wimg; L.scale = h->proj1.scale; L.shift = h->proj1.shift; L.act = ACT_RELU;
+      L.y32 = ws + o_q1; L.ld32 = h->proj1.cout;
+      conv_tc_launch(L, st);
+    } else {
+      // ---- conv bank -> concat buffer [rows][KW*Cb] (fp32 SIMT form) ----
+      for (int k = 1; k <= KW; ++k) {
+        const Conv& c = h->bank[k - 1];
+        conv_bn_act_launch(ws + o_p1, B, T, P1, c.w, c.scale, c.shift, k, P1, Cb, ACT_RELU, 0, nullptr, 0,
+                           ws + o_bank + (size_t)(k - 1) * Cb, ldb, st);
+      }
+      // ---- maxpool (fused on load) + proj1 ----
+      conv_bn_act_launch(ws + o_bank, B, T, ldb, h->proj1.w, h->proj1.scale, h->proj1.shift, 3, ldb, h->proj1.cout, ACT_RELU,
+                         1, nullptr, 0, ws + o_q1, h->proj1.cout, st);
     }
-    // ---- maxpool (fused on load) + proj1, proj2 + residual ----
-    conv_bn_act_launch(ws + o_bank, B, T, ldb, h->proj1.w, h->proj1.scale, h->proj1.shift, 3, ldb, h->proj1.cout, ACT_RELU, 1,
-                       nullptr, 0, ws + o_q1, h->proj1.cout, st);
+    // ---- proj2 + residual ----
     conv_bn_act_launch(ws + o_q1, B, T, h->proj1.cout, h->proj2.w, h->proj2.scale, h->proj2.shift, 3, h->proj1.cout,
                        h->proj2.cout, ACT_NONE, 0, ws + o_p1, P1, ws + o_q2, h->proj2.cout, st);
     const float* hw_in = ws + o_q2;
