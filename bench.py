@@ -264,8 +264,11 @@ def run_ours(args, rank, world, local_rank):
                "sample_seconds": secs}
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic",
+            "dtype": "f32 (tcgen05 GEMMs: f16 operands, f32 accumulate)", "data": "synthetic",
             "config": {"workload": WORKLOAD, "frames_per_step_per_gpu": frames_per_step, "T_enc_padded": T,
+                       "precision": "state, attention, softmax, projections in fp32; LSTM gate GEMMs, encoder conv bank/"
+                                    "proj1 and prenet/projection weights at B>=64 use fp16 operands (11-bit significand, "
+                                    "as TF32) with fp32 accumulation; parity bar 1e-3 relative vs the fp64 oracle",
                        "l2": "256 MiB flush buffer written before every step (inside the timed region)",
                        "weights": "random-init seed 12345", "rtf": ms / args.steps * 1e-3 / (frames_per_step * world * 0.0125)},
             "clocks": clocks, "gpu_launches": launches,

@@ -100,6 +100,10 @@ int sat_encoder_forward(sat_encoder* h, const int64_t* ids, const int64_t* lengt
 /* same, for callers that did the embedding lookup themselves: embedded [B,T,embedding_dim] (device) */
 int sat_encoder_forward_embedded(sat_encoder* h, const float* embedded, const int64_t* lengths, int32_t B, int32_t T,
                                  float* lstm_out, float* sa_out, float* sa_probs, void* stream);
+/* 1 if this encoder runs its conv bank / max-pool / proj1 on the tensor cores (tcgen05 implicit-GEMM over fp16
+ * activations, fp32 accumulation; needs prenet/conv widths that are multiples of 64 / 128), 0 for the fp32 SIMT form.
+ * Environment SAT_ENC_TC=0 at create time forces the fp32 form. */
+int sat_encoder_uses_tensor_cores(sat_encoder* h, int32_t* used);
 void sat_encoder_destroy(sat_encoder* h);
 
 /* ---- decoder ---------------------------------------------------------- */
@@ -180,6 +184,9 @@ int sat_postnet_create(const sat_hparams* hp, const sat_tensor* weights, int32_t
 /* mel [B,T,M] -> mel_postnet [B,T,M] = mel + Dense(conv stack(mel)) */
 int sat_postnet_forward(sat_postnet* h, const float* mel, int32_t B, int32_t T, float* mel_postnet, void* stream);
 void sat_postnet_destroy(sat_postnet* h);
+/* 1 if the post-net convolutions run on the tensor cores (tcgen05 implicit-GEMM, fp16 operands, fp32 accumulation);
+ * SAT_POSTNET_TC=0 at create time forces the fp32 SIMT form */
+int sat_postnet_uses_tensor_cores(sat_postnet* h, int32_t* used);
 
 #ifdef __cplusplus
 }

@@ -245,6 +245,13 @@ extern "C" int sat_encoder_create(const sat_hparams* hpp, const sat_tensor* weig
 
 extern "C" void sat_encoder_destroy(sat_encoder* h) { delete h; }
 
+extern "C" int sat_encoder_uses_tensor_cores(sat_encoder* h, int32_t* used) {
+  return guarded([&] {
+    SAT_REQUIRE(h && used, "null argument");
+    *used = h->tc ? 1 : 0;
+  });
+}
+
 static int encoder_forward_impl(sat_encoder* h, const int64_t* ids, const float* embedded, const int64_t* lengths,
                                 int32_t B, int32_t T, float* lstm_out, float* sa_out, float* sa_probs, void* stream) {
   return guarded([&] {

@@ -123,6 +123,11 @@ class EncoderHandle:
             lib().sat_encoder_destroy(self._h)
             self._h = C.c_void_p()
 
+    def uses_tensor_cores(self):
+        used = C.c_int32()
+        check(lib().sat_encoder_uses_tensor_cores(self._h, C.byref(used)))
+        return bool(used.value)
+
     def forward(self, ids_or_embedded, lengths, want_probs=False, stream=None):
         hp = self.hp
         x = ids_or_embedded
@@ -165,6 +170,11 @@ class PostnetHandle:
         if getattr(self, "_h", None) and self._h.value:
             lib().sat_postnet_destroy(self._h)
             self._h = C.c_void_p()
+
+    def uses_tensor_cores(self):
+        used = C.c_int32()
+        check(lib().sat_postnet_uses_tensor_cores(self._h, C.byref(used)))
+        return bool(used.value)
 
     def forward(self, mel, stream=None):
         _need_cuda(mel)

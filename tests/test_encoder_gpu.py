@@ -52,6 +52,24 @@ def test_self_attention_cbhg_encoder(B, T):
         assert np.all(lo[b, lengths[b]:] == 0)
 
 
+@pytest.mark.parametrize("tc", ["1", "0"])
+def test_encoder_tensor_core_and_simt_conv_paths(tc, monkeypatch):
+    """The conv bank / max-pool / proj1 run as tcgen05 implicit GEMMs over fp16 activations by default and as fp32
+    SIMT GEMMs with SAT_ENC_TC=0; both must meet the 1e-3 bar against the float64 oracle at the real layer sizes."""
+    from sat_b200.engine import EncoderHandle
+    monkeypatch.setenv("SAT_ENC_TC", tc)
+    hp = small_hp("ljspeech_tacotron")
+    W = sat_b200.init_weights(hp, seed=5, stress=True)
+    ids, lengths = _enc_inputs(hp, 6, 83, seed=5)
+    ref = oenc.zoneout_encoder_v1(ids, lengths, _w64(W), hp)
+    h = EncoderHandle(hp, W)
+    assert h.uses_tensor_cores() == (tc == "1")
+    out = h.forward(_t(ids), _t(lengths))[0].cpu().numpy()
+    e = rel_err(out, ref)
+    print("encoder conv path tensor_cores=%s rel err %.3e" % (tc, e))
+    assert e <= TOL
+
+
 def test_zoneout_encoder_v1_and_embedded_input():
     import torch
     from sat_b200.engine import EncoderHandle
@@ -182,9 +200,12 @@ def test_multi_speaker_prenet_module():
     assert rel_err(out.cpu().numpy(), ref) <= TOL
 
 
-@pytest.mark.parametrize("B,T", [(1, 9), (3, 50)])
-def test_postnet_v2(B, T):
+@pytest.mark.parametrize("tc", ["1", "0"])
+@pytest.mark.parametrize("B,T", [(1, 9), (3, 50), (5, 131)])
+def test_postnet_v2(B, T, tc, monkeypatch):
+    """both conv forms: tcgen05 implicit GEMM over fp16 activations (default) and fp32 SIMT (SAT_POSTNET_TC=0)"""
     from sat_b200.modules import PostNetV2
+    monkeypatch.setenv("SAT_POSTNET_TC", tc)
     hp = small_hp("ljspeech_self_attention", use_postnet_v2=True)
     W = sat_b200.init_weights(hp, seed=7, stress=True)
     rng = np.random.default_rng(7)
