@@ -144,14 +144,6 @@ def run_reference(args, rank, world):
         secs.append(s)
     value = float(np.mean(vals))
     frames = B_PER_GPU * hp.max_iters * hp.outputs_per_step
-    # DRAM bytes of one launch of the dominant kernel from the committed `ncu --set full` capture of this workload
-    traffic, traffic_src = None, None
-    try:
-        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "ncu_traffic.json")) as f:
-            tj = json.load(f)["decoder_persistent_kernel"]
-        traffic, traffic_src = tj["dram_bytes_per_launch"], tj["source"]
-    except (OSError, KeyError, ValueError):
-        pass
     line = {"metric": METRIC, "value": value, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * frames / value,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -270,6 +262,14 @@ def run_ours(args, rank, world, local_rank):
         v, secs = cpu_sample(hp, W, ids_np, len_np, threads)
         cpu = {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": cpu_sample_text(),
                "sample_seconds": secs}
+    # DRAM bytes of one launch of the dominant kernel from the committed `ncu --set full` capture of this workload
+    traffic, traffic_src = None, None
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "ncu_traffic.json")) as f:
+            tj = json.load(f)["decoder_persistent_kernel"]
+        traffic, traffic_src = tj["dram_bytes_per_launch"], tj["source"]
+    except (OSError, KeyError, ValueError):
+        pass
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32 (tcgen05 GEMMs: f16 operands, f32 accumulate)", "data": "synthetic",
