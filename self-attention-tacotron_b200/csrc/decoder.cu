@@ -35,20 +35,25 @@ PackedDense pack_cols(DevPool& pool, const float* W, const float* bias, int K, i
   d.bias = pool.upload(bp);
   return d;
 }
+// row-major copies [K][Np] (fp32) and [K][Np8] (fp16) of the first N columns of W[K][Nsrc], zero-padded to Nout columns:
+// the operands of the row-split phases (row_dense)
+void add_row_major(DevPool& pool, PackedDense& d, const float* W, int K, int Nsrc, int N, int Nout) {
+  d.Np = (Nout + 3) / 4 * 4;
+  std::vector<float> rm((size_t)K * d.Np, 0.f);
+  for (int k = 0; k < K; ++k)
+    for (int n = 0; n < N; ++n) rm[(size_t)k * d.Np + n] = W[(size_t)k * Nsrc + n];
+  d.Wrm = pool.upload(rm);
+  d.Np8 = (Nout + 7) / 8 * 8;
+  std::vector<__half> rh((size_t)K * d.Np8 + 8, __float2half(0.f));
+  for (int k = 0; k < K; ++k)
+    for (int n = 0; n < N; ++n) rh[(size_t)k * d.Np8 + n] = __float2half_rn(W[(size_t)k * Nsrc + n]);
+  d.Wrm16 = pool.upload((const float*)rh.data(), (rh.size() + 1) / 2);
+}
 PackedDense pack_dense(DevPool& pool, const float* W, const float* bias, int K, int N) {
   std::vector<int> cm(N);
   for (int n = 0; n < N; ++n) cm[n] = n;
   PackedDense d = pack_cols(pool, W, bias, K, N, cm);
-  d.Np = (N + 3) / 4 * 4;
-  std::vector<float> rm((size_t)K * d.Np, 0.f);
-  for (int k = 0; k < K; ++k)
-    for (int n = 0; n < N; ++n) rm[(size_t)k * d.Np + n] = W[(size_t)k * N + n];
-  d.Wrm = pool.upload(rm);
-  d.Np8 = (N + 7) / 8 * 8;
-  std::vector<__half> rh((size_t)K * d.Np8 + 8, __float2half(0.f));
-  for (int k = 0; k < K; ++k)
-    for (int n = 0; n < N; ++n) rh[(size_t)k * d.Np8 + n] = __float2half_rn(W[(size_t)k * N + n]);
-  d.Wrm16 = pool.upload((const float*)rh.data(), (rh.size() + 1) / 2);
+  add_row_major(pool, d, W, K, N, N, N);
   return d;
 }
 // LSTM kernel [K][4*units] gate order i,j,f,o -> tiles of 2 units x 4 gates
@@ -198,6 +203,7 @@ extern "C" int sat_decoder_create(const sat_hparams* hpp, const sat_tensor* weig
         std::vector<int> cm(Up, -1);
         for (int u = 0; u < U; ++u) cm[u] = u;
         h->dq[i] = pack_cols(pool, W.get(P + "query_layer/kernel", (int64_t)A * U), nullptr, A, U, cm);
+        add_row_major(pool, h->dq[i], W.get(P + "query_layer/kernel", (int64_t)A * U), A, U, U, Up);
       }
       h->att_v[i] = padU(W.get(P + "attention_v", U), 1);
       std::vector<float> zeros(Up, 0.f);

@@ -69,9 +69,10 @@ __device__ __forceinline__ float block_max(float v, float* scratch) {
 
 // ---- grid-wide barrier -------------------------------------------------------
 // Monotonic arrival counter in global memory; barrier #n completes when the counter
-// reaches n * gridDim.x.  Same fence pattern as cooperative-groups grid.sync():
-// bar.sync, then one thread does fence + atomic + acquire-spin + fence, bar.sync.
-// Requires all CTAs co-resident (cooperative launch).
+// reaches n * gridDim.x: bar.sync, then one thread does red.release.gpu + ld.acquire.gpu spin, bar.sync
+// (release / acquire at gpu scope instead of the membar.gl pair of cooperative-groups grid.sync()).
+// Requires all CTAs co-resident (cooperative launch).  Measured on B200: 1.49 us per empty barrier; neither the
+// membar.gl -> release/acquire change nor spreading the arrivals over four counters moved that number.
 struct GridBarrier {
   unsigned* counter;
   unsigned gen;
@@ -86,14 +87,13 @@ struct GridBarrier {
     if (threadIdx.x == 0) {
       gen += 1;
       const unsigned target = gen * gridDim.x;
-      __threadfence();
-      atomicAdd(counter, 1u);
+      // release at gpu scope: cumulative over the CTA's writes ordered before it by the bar.sync above
+      asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(counter) : "memory");
       between();
       unsigned seen;
       do {
         asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(counter) : "memory");
       } while (seen < target);
-      __threadfence();
     }
     __syncthreads();
   }

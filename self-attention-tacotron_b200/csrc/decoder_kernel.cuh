@@ -2,8 +2,8 @@
 //
 // One cooperative launch runs ALL decoder steps.  Per step:
 //   C  attention ZoneoutLSTM                                     weight-stationary LSTM tiles
-//   D  query layers of the attention mechanisms                  column-split dense
-//   E  attention mechanisms: energies, softmax, alpha recursion, context   row-split
+//   D+E query layers of the attention mechanisms, then energies, softmax, alpha recursion, context
+//      -- all local to an utterance row                          row split, no barrier inside
 //   F  decoder ZoneoutLSTM 1                                     weight-stationary LSTM tiles
 //   G  decoder ZoneoutLSTM 2                                     weight-stationary LSTM tiles
 //   H-K decoder self-attention hops with a KV cache (transformer decoder only)
@@ -495,36 +495,70 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
                           p.att_in[nxt] + hoff, nullptr, 0, 0, p.zc, p.zh});
     }
     phase_end();
-    // ---- D: query layers ----
-    bool any_q = false;
-    for (int mi = 0; mi < p.n_mech; ++mi)
-      if (p.mech[mi].kind != SAT_ATT_TEACHER_FORCING) {
-        any_q = true;
-        dense_phase(p.dq[mi], p.tc ? p.qfm : p.l1_in[cur], ld, p.Bp, wres, scratch,
-                    DenseEpi{p.dq[mi].bias, p.dq[mi].N, ld, 0, Act2D{const_cast<float*>(p.mech[mi].pq), p.mech[mi].pq_su, p.mech[mi].pq_sb, 0}, nullptr, nullptr});
+    // ---- D+E: query layers and attention mechanisms (row split, no barrier in between) ----
+    // The processed query of a row is a row-local dense on the attention-LSTM output, so the CTA that owns the row's
+    // attention item computes it itself (two rows per pass share one stream of the query-layer weights from L2).
+    {
+      const float* qsrc = p.tc ? p.qfm : p.l1_in[cur];  // feature-major [A][ld]
+      const int n_items = p.B * p.n_mech;
+      for (int i0 = blockIdx.x; i0 < n_items; i0 += 2 * gridDim.x) {
+        const int i1 = i0 + gridDim.x;
+        const int nit = i1 < n_items ? 2 : 1;
+        const int items[2] = {i0, i1};
+        const int mi0 = i0 % p.n_mech;
+        // the items of one CTA share the mechanism whenever gridDim.x is a multiple of n_mech; otherwise one at a time
+        const bool pair = nit == 2 && (i1 % p.n_mech) == mi0;
+        for (int q0 = 0; q0 < nit; q0 += pair ? 2 : 1) {
+          const int nq = pair ? 2 : 1;
+          const int mi = items[q0] % p.n_mech;
+          if (p.mech[mi].kind == SAT_ATT_TEACHER_FORCING) continue;
+          const DenseDesc& dq = p.dq[mi];
+          float* xs = scratch;                 // [2][A]
+          float* outs = xs + al4(2 * p.A);     // [2][Np]
+          float* part = outs + 2 * dq.Np;      // [2 * NT * 8]
+          int rows[2];
+          for (int r = 0; r < nq; ++r) rows[r] = items[q0 + r] / p.n_mech;
+          for (int i = tid; i < nq * p.A; i += NT) {
+            const int r = i / p.A, k = i - r * p.A;
+            xs[r * p.A + k] = __ldcg(qsrc + (size_t)k * ld + rows[r]);
+          }
+          __syncthreads();
+          if (p.tc) {
+            if (nq == 2) row_dense<2, true>(dq, xs, p.A, part, outs, 0);
+            else row_dense<1, true>(dq, xs, p.A, part, outs, 0);
+          } else {
+            if (nq == 2) row_dense<2, false>(dq, xs, p.A, part, outs, 0);
+            else row_dense<1, false>(dq, xs, p.A, part, outs, 0);
+          }
+          const AttMech& mm = p.mech[mi];
+          for (int i = tid; i < nq * dq.N; i += NT) {
+            const int r = i / dq.N, n = i - r * dq.N;
+            const_cast<float*>(mm.pq)[(size_t)n * mm.pq_su + (size_t)rows[r] * mm.pq_sb] = outs[r * dq.Np + n];
+          }
+          __syncthreads();
+        }
+        for (int q = 0; q < nit; ++q) {
+          const int b = items[q] / p.n_mech, mi = items[q] % p.n_mech;
+          AttMech m = p.mech[mi];
+          const int coff = mi ? p.mech[0].Dv : 0;
+          if (p.tc) {
+            m.ctx_dst[0] = (__half*)p.att_in[nxt] + p.P1 + coff;
+            m.ctx_dst[1] = (__half*)p.l1_in[cur] + p.A + coff;
+            m.ctx_sd[0] = m.ctx_sd[1] = 1;
+            m.ctx_sb[0] = p.Ka_pad;
+            m.ctx_sb[1] = p.K1_pad;
+            m.ctx_f16 = 1;
+          } else {
+            m.ctx_f16 = 0;
+            m.ctx_dst[0] = p.att_in[nxt] + (size_t)(p.P1 + coff) * ld;
+            m.ctx_dst[1] = p.l1_in[cur] + (size_t)(p.A + coff) * ld;
+            m.ctx_sd[0] = m.ctx_sd[1] = ld;
+            m.ctx_sb[0] = m.ctx_sb[1] = 1;
+          }
+          m.prof = p.prof ? p.prof + 16 : nullptr;
+          attention_item(m, b, t, p.T, (int)p.lengths[b], scratch);
+        }
       }
-    if (any_q) phase_end();
-    // ---- E: attention mechanisms (row split) ----
-    for (int item = blockIdx.x; item < p.B * p.n_mech; item += gridDim.x) {
-      const int b = item / p.n_mech, mi = item % p.n_mech;
-      AttMech m = p.mech[mi];
-      const int coff = mi ? p.mech[0].Dv : 0;
-      if (p.tc) {
-        m.ctx_dst[0] = (__half*)p.att_in[nxt] + p.P1 + coff;
-        m.ctx_dst[1] = (__half*)p.l1_in[cur] + p.A + coff;
-        m.ctx_sd[0] = m.ctx_sd[1] = 1;
-        m.ctx_sb[0] = p.Ka_pad;
-        m.ctx_sb[1] = p.K1_pad;
-        m.ctx_f16 = 1;
-      } else {
-        m.ctx_f16 = 0;
-        m.ctx_dst[0] = p.att_in[nxt] + (size_t)(p.P1 + coff) * ld;
-        m.ctx_dst[1] = p.l1_in[cur] + (size_t)(p.A + coff) * ld;
-        m.ctx_sd[0] = m.ctx_sd[1] = ld;
-        m.ctx_sb[0] = m.ctx_sb[1] = 1;
-      }
-      m.prof = p.prof ? p.prof + 16 : nullptr;
-      attention_item(m, b, t, p.T, (int)p.lengths[b], scratch);
     }
     if (p.tc) phase_end(&p.tc_1, p.maps + 2 + cur);
     else phase_end();
