@@ -9,6 +9,8 @@
 // K/V/Q projections run as ONE fused [Din, 3D] GEMM; the attention kernel gives one warp per query
 // row (lanes split the keys for the scores, then (key group, 4 head dims) for the context).
 #include "common.cuh"
+#include "tc.cuh"
+#include <cstdlib>
 
 namespace sat {
 namespace {
@@ -107,6 +109,173 @@ __global__ void __launch_bounds__(MHA_WARPS * 32) mha_attn_kernel(const float* _
   }
 }
 
+
+// ---- tensor-core form (tcgen05 / TMEM) for short sequences and small heads: T <= 256, dh in {16, 32, 48, 64} ------
+// One CTA = one (batch row, head, 128-query tile).  Q (pre-scaled), K and V^T are converted to fp16 hi + lo pairs
+// into K-major 128-byte-swizzled shared memory; S = Q K^T (3 MMAs per K-step: lo*hi + hi*lo + hi*hi, i.e. fp32-grade
+// products) accumulates in TMEM columns [0, Tp); every thread owns one query row (= one TMEM lane), applies the
+// masks and the softmax straight from TMEM, writes the probabilities (optional) and the fp16 P operand; O = P V
+// (V as hi + lo) accumulates in TMEM columns [256, 256 + dh) and is written back as fp32.
+constexpr int MT_THREADS = 128;
+
+__global__ void __launch_bounds__(MT_THREADS, 1)
+mha_tc_kernel(const float* __restrict__ qkv, int T, int Tp, int D, int H, int causal, const long long* __restrict__ lengths,
+              float* __restrict__ ctx, float* __restrict__ probs, int head_major) {
+  extern __shared__ __align__(1024) uint8_t mt_smem[];
+  uint8_t* base = (uint8_t*)(((uintptr_t)mt_smem + 1023) & ~(uintptr_t)1023);
+  const int dh = D / H, nchunk = (Tp + 63) / 64;
+  uint8_t* Qh = base;
+  uint8_t* Ql = Qh + 16384;
+  uint8_t* Kh = Ql + 16384;
+  uint8_t* Kl = Kh + (size_t)256 * 128;
+  uint8_t* Vh = Kl + (size_t)256 * 128;              // nchunk x [dh rows][128 B]
+  uint8_t* Vl = Vh + (size_t)nchunk * dh * 128;
+  uint8_t* P = (uint8_t*)(((uintptr_t)(Vl + (size_t)nchunk * dh * 128) + 1023) & ~(uintptr_t)1023);  // nchunk x 16 KB
+  __shared__ __align__(8) uint64_t bars[2];
+  __shared__ uint32_t tmem_slot;
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int b = blockIdx.y / H, h = blockIdx.y % H, q0 = blockIdx.x * 128;
+  const size_t ld = 3 * (size_t)D;
+  const float* src = qkv + (size_t)b * T * ld + (size_t)h * dh;
+  const float scale = 1.f / sqrtf((float)dh);
+
+  if (tid == 0) {
+    tc::mbar_init(bars, 1);
+    tc::mbar_init(bars + 1, 1);
+    tc::fence_mbar_init();
+  }
+  if (warp == 0) tc::tmem_alloc(&tmem_slot, 512);
+  auto split_store = [](uint8_t* hi, uint8_t* lo, uint32_t off, float x) {
+    const __half xh = tc::to_f16(x);
+    *(__half*)(hi + off) = xh;
+    *(__half*)(lo + off) = tc::to_f16(x - __half2float(xh));
+  };
+  for (int i = tid; i < 128 * dh; i += MT_THREADS) {
+    const int r = i / dh, d = i - r * dh;
+    const float x = (q0 + r < T) ? __ldg(src + (size_t)(q0 + r) * ld + 2 * D + d) * scale : 0.f;
+    split_store(Qh, Ql, tc::sw128_offset16(r, d), x);
+  }
+  for (int i = tid; i < Tp * dh; i += MT_THREADS) {
+    const int j = i / dh, d = i - j * dh;
+    const bool ok = j < T;
+    split_store(Kh, Kl, tc::sw128_offset16(j, d), ok ? __ldg(src + (size_t)j * ld + d) : 0.f);
+    // V^T: row d, key j -> chunk j / 64
+    split_store(Vh, Vl, (uint32_t)((j >> 6) * dh * 128) + tc::sw128_offset16(d, j & 63), ok ? __ldg(src + (size_t)j * ld + D + d) : 0.f);
+  }
+  tc::fence_proxy_async();
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem = tmem_slot;
+
+  if (tid == 0) {
+    const uint32_t idesc = tc::idesc_f16(128, Tp);
+    bool first = true;
+    for (int ks = 0; ks < dh / 16; ++ks) {
+      const uint32_t o = ks * 32;
+      tc::mma_f16(tmem, tc::smem_desc_sw128(tc::smem_u32(Ql) + o), tc::smem_desc_sw128(tc::smem_u32(Kh) + o), idesc, !first);
+      first = false;
+      tc::mma_f16(tmem, tc::smem_desc_sw128(tc::smem_u32(Qh) + o), tc::smem_desc_sw128(tc::smem_u32(Kl) + o), idesc, 1);
+      tc::mma_f16(tmem, tc::smem_desc_sw128(tc::smem_u32(Qh) + o), tc::smem_desc_sw128(tc::smem_u32(Kh) + o), idesc, 1);
+    }
+    tc::mma_commit(bars);
+  }
+  __syncwarp();
+  tc::mbar_wait(bars, 0);
+  tc::tc_fence_after();
+
+  // ---- masks + softmax on this thread's query row (TMEM lane tid) ----
+  const int qi = q0 + tid;
+  const int len = lengths ? (int)lengths[b] : T;
+  const int nk = causal ? min(qi + 1, T) : T;
+  const int nvalid = (qi < len || !lengths) ? min(nk, len) : 0;  // keys j < nvalid take part
+  const uint32_t lane_addr = tmem + ((uint32_t)(warp * 32) << 16);
+  float mx = -INFINITY;
+  for (int c0 = 0; c0 < Tp; c0 += 16) {
+    float v[16];
+    tc::tmem_ld16(lane_addr + c0, v);
+#pragma unroll
+    for (int k = 0; k < 16; ++k)
+      if (c0 + k < nvalid) mx = fmaxf(mx, v[k]);
+  }
+  if (mx == -INFINITY) mx = 0.f;  // fully masked row: 0/0 = NaN like the reference
+  float sum = 0.f;
+  for (int c0 = 0; c0 < Tp; c0 += 16) {
+    float v[16];
+    tc::tmem_ld16(lane_addr + c0, v);
+#pragma unroll
+    for (int k = 0; k < 16; ++k)
+      if (c0 + k < nvalid) sum += expf(v[k] - mx);
+  }
+  const float inv = 1.f / sum;
+  float* pr = nullptr;
+  if (probs && qi < T)
+    pr = probs + ((head_major ? (size_t)h * (gridDim.y / H) + b : (size_t)b * H + h) * T + qi) * T;
+  for (int c0 = 0; c0 < Tp; c0 += 16) {
+    float v[16];
+    tc::tmem_ld16(lane_addr + c0, v);
+    __half2 ph[8];
+#pragma unroll
+    for (int k = 0; k < 16; k += 2) {
+      const float p0 = c0 + k < nvalid ? expf(v[k] - mx) * inv : (c0 + k < nk ? 0.f * inv : 0.f);
+      const float p1 = c0 + k + 1 < nvalid ? expf(v[k + 1] - mx) * inv : (c0 + k + 1 < nk ? 0.f * inv : 0.f);
+      v[k] = p0;
+      v[k + 1] = p1;
+      ph[k >> 1] = __halves2half2(tc::to_f16(p0), tc::to_f16(p1));
+    }
+    uint8_t* pc = P + (size_t)(c0 >> 6) * 16384;
+    *(uint4*)(pc + tc::sw128_offset16(tid, c0 & 63)) = *(const uint4*)&ph[0];
+    *(uint4*)(pc + tc::sw128_offset16(tid, (c0 & 63) + 8)) = *(const uint4*)&ph[4];
+    if (pr)
+#pragma unroll
+      for (int k = 0; k < 16; ++k)
+        if (c0 + k < T) pr[c0 + k] = v[k];
+  }
+  tc::fence_proxy_async();
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+
+  if (tid == 0) {
+    const uint32_t idesc = tc::idesc_f16(128, dh);
+    bool first = true;
+    for (int c = 0; c < nchunk; ++c)
+      for (int ks = 0; ks < 4 && c * 64 + ks * 16 < Tp; ++ks) {
+        const uint32_t pa = tc::smem_u32(P + (size_t)c * 16384) + ks * 32, vo = (uint32_t)(c * dh * 128 + ks * 32);
+        tc::mma_f16(tmem + 256, tc::smem_desc_sw128(pa), tc::smem_desc_sw128(tc::smem_u32(Vl) + vo), idesc, !first);
+        first = false;
+        tc::mma_f16(tmem + 256, tc::smem_desc_sw128(pa), tc::smem_desc_sw128(tc::smem_u32(Vh) + vo), idesc, 1);
+      }
+    tc::mma_commit(bars + 1);
+  }
+  __syncwarp();
+  tc::mbar_wait(bars + 1, 0);
+  tc::tc_fence_after();
+  for (int d0 = 0; d0 < dh; d0 += 16) {
+    float v[16];
+    tc::tmem_ld16(lane_addr + 256 + d0, v);
+    if (qi < T) {
+      float4* out = (float4*)(ctx + ((size_t)b * T + qi) * D + (size_t)h * dh + d0);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) out[k] = make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+    }
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tc::tmem_dealloc(tmem, 512);
+}
+
+size_t mha_tc_smem_bytes(int Tp, int dh) {
+  const size_t nchunk = (Tp + 63) / 64;
+  return 1024 + 2 * 16384 + 2 * 256 * 128 + 2 * nchunk * dh * 128 + 1024 + nchunk * 16384;
+}
+bool mha_tc_ok(int T, int D, int H) {
+  const int dh = D / H;
+  if (const char* e = getenv("SAT_MHA_TC"))
+    if (atoi(e) == 0) return false;
+  return T <= 256 && dh % 16 == 0 && dh <= 64 && D % 4 == 0 && mha_tc_smem_bytes((T + 15) & ~15, dh) <= 200 * 1024;
+}
+
 }  // namespace
 
 MhaDev mha_upload(DevPool& pool, const Blob& W, const std::string& P, const std::string& TP, int Din, int D, int H) {
@@ -142,6 +311,17 @@ static void attention_core(const MhaDev& m, const float* x, int B, int T, int ca
   g.W = m.Wqkv; g.N = 3 * m.D; g.shift = m.bqkv; g.C = qkv; g.ldc = 3 * m.D;
   gemm_launch(g, st);
   const int dh = m.D / m.H, Tpad = (T + 3) & ~3;
+  if (mha_tc_ok(T, m.D, m.H)) {
+    const int Tp = (T + 15) & ~15;
+    const size_t smem = mha_tc_smem_bytes(Tp, dh);
+    SAT_CUDA(cudaFuncSetAttribute(mha_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dim3 grid((unsigned)ceil_div(T, 128), (unsigned)(B * m.H));
+    mha_tc_kernel<<<grid, MT_THREADS, smem, st>>>(qkv, T, Tp, m.D, m.H, causal, (const long long*)pad_lengths, ctx, probs,
+                                                  head_major);
+    count_launch();
+    check_launch("mha_tc_kernel");
+    return;
+  }
   const size_t smem = (size_t)MHA_WARPS * (Tpad + dh) * sizeof(float);
   SAT_REQUIRE(smem <= 200 * 1024, "sequence too long for the SIMT attention kernel (T=%d)", T);
   SAT_CUDA(cudaFuncSetAttribute(mha_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

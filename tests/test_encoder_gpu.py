@@ -102,11 +102,14 @@ def test_encoder_two_hops_and_adjustment_free_dims():
         assert rel_err(probs[i].cpu().numpy(), a) <= TOL
 
 
+@pytest.mark.parametrize("tc", ["1", "0"])
 @pytest.mark.parametrize("D,H,T,causal", [(32, 2, 17, False), (32, 2, 40, True), (256, 2, 33, True), (24, 3, 9, False),
-                                           (12, 2, 7, True)])
-def test_self_attention_module(D, H, T, causal):
-    """modules/self_attention.py:131-144 through the SelfAttention mirror."""
+                                           (12, 2, 7, True), (32, 2, 150, False), (128, 2, 200, True), (96, 2, 256, False)])
+def test_self_attention_module(D, H, T, causal, tc, monkeypatch):
+    """modules/self_attention.py:131-144 through the SelfAttention mirror.  Head sizes 16..64 with T <= 256 take the
+    tcgen05 / TMEM kernel (SAT_MHA_TC=0 forces the SIMT kernel); the others always run the SIMT kernel."""
     from sat_b200.modules import SelfAttention
+    monkeypatch.setenv("SAT_MHA_TC", tc)
     rng = np.random.default_rng(D + T)
     W = {}
     for n in ("key", "value", "query", "output"):
