@@ -91,6 +91,40 @@ __global__ void spk_term_kernel(const float* spk, const float* Ws, const float* 
   out[(size_t)n * ld + b] = v / (1.f + fabsf(v));
 }
 
+// teacher-forced input frames of all steps, step-major: x[t][b][f] = 0 (<GO>) for t = 0, else the last n_feed frames
+// of target step min(t-1, S_target-1)   (modules/helpers.py:44-58)
+__global__ void teacher_inputs_kernel(const float* __restrict__ target, int B, int S, int S_target, int Mr, int Mnf,
+                                      float* __restrict__ x) {
+  const size_t n = (size_t)S * B * Mnf;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const int f = (int)(i % Mnf);
+    const size_t row = i / Mnf;
+    const int b = (int)(row % B), t = (int)(row / B);
+    x[i] = t == 0 ? 0.f : __ldg(target + ((size_t)b * S_target + min(t - 1, S_target - 1)) * Mr + (Mr - Mnf) + f);
+  }
+}
+// x[t][b][n] += spk_term[n][b]  (MultiSpeakerPreNet speaker term, feature-major source)
+__global__ void add_spk_rows_kernel(float* __restrict__ x, int rows, int B, int N, int ldx, const float* __restrict__ spk, int ld) {
+  const size_t n = (size_t)rows * N;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % N);
+    const size_t row = i / N;
+    x[row * ldx + c] += __ldg(spk + (size_t)c * ld + (int)(row % B));
+  }
+}
+// time-batched projection [B*S][ldy] -> mel [B][S][Mr], stop [B][S]
+__global__ void split_projection_kernel(const float* __restrict__ y, size_t rows, int ldy, int Mr, float* __restrict__ mel,
+                                        float* __restrict__ stop) {
+  const size_t n = rows * (size_t)(Mr + 1);
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % (Mr + 1));
+    const size_t row = i / (Mr + 1);
+    const float v = __ldg(y + row * ldy + c);
+    if (c == Mr) stop[row] = v;
+    else mel[row * Mr + c] = v;
+  }
+}
+
 // sample ids: argmax over M per r-slot (modules/helpers.py:49-52); first maximum wins like tf.argmax
 __global__ void argmax_kernel(const float* mel, long long rows, int M, int* ids) {
   const long long row = (long long)blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32;
@@ -119,6 +153,7 @@ struct sat_decoder {
   sat_hparams hp;
   DevPool pool;
   Scratch ws;
+  Scratch ws_tail;  // time-batched buffers of the teacher-forced form
   PackedDense pre0, msd, pre1, lstm_a, lstm_1, lstm_2, outp, dq[2];
   PackedDense sa_qkv[MAX_HOPS], sa_o[MAX_HOPS], sa_tr[MAX_HOPS];
   float* mem_layer[2] = {nullptr, nullptr};  // [Dm][Up]
@@ -541,6 +576,53 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
       p.hop[i].kcache = ws + o_kc[i]; p.hop[i].vcache = ws + o_vc[i];
     }
 
+    // ---- teacher-forced time-batched form: prenet of all steps before the loop, hops + projections after it ----
+    bool tail = io.feed_mode == SAT_FEED_TEACHER && io.stop_mode == SAT_STOP_FIXED;
+    if (const char* e = getenv("SAT_BATCHED_TAIL")) tail = tail && atoi(e) != 0;
+    auto dense_rows = [&](const PackedDense& d, const float* x, int ldx, size_t rows, int act, float* y) {
+      GemmArgs g;
+      g.X = x; g.Bn = 1; g.T = (int)rows; g.Cin = d.K; g.ldx = ldx;
+      g.W = d.Wrm; g.N = d.Np; g.shift = d.bias; g.act = act; g.C = y; g.ldc = d.Np;
+      gemm_launch(g, st);
+    };
+    const size_t rows_all = (size_t)B * S;
+    float *t_dec = nullptr, *t_y[2] = {nullptr, nullptr}, *t_mha = nullptr, *t_proj = nullptr;
+    if (tail) {
+      for (int i = 0; i < h->hops; ++i)
+        tail = tail && h->sa_qkv[i].Np == h->sa_qkv[i].N && h->sa_o[i].Np == h->sa_o[i].N && h->sa_tr[i].Np == h->sa_tr[i].N;
+    }
+    if (tail) {
+      size_t toff = 0;
+      auto ttake = [&](size_t n) { size_t o = toff; toff += (n + 63) / 64 * 64; return o; };
+      const size_t o_x = ttake(rows_all * p.Mnf), o_a = ttake(rows_all * h->pre0.Np), o_b = ttake(rows_all * h->pre0.Np);
+      const size_t o_p1 = ttake(rows_all * h->pre1.Np), o_dec = ttake(rows_all * Dd);
+      const size_t o_y0 = ttake(rows_all * Ds), o_y1 = ttake(rows_all * Ds);
+      MhaDev m0;
+      m0.D = Ds;
+      const size_t o_mha = ttake(h->hops ? mha_scratch_floats(m0, (int64_t)rows_all) : 0);
+      const size_t o_pr = ttake(rows_all * h->outp.Np);
+      float* tw = h->ws_tail.get<float>(toff);
+      teacher_inputs_kernel<<<(unsigned)std::min<size_t>((rows_all * p.Mnf + 255) / 256, 148 * 16), 256, 0, st>>>(
+          io.target, B, S, io.target_steps, p.Mr, p.Mnf, tw + o_x);
+      count_launch();
+      dense_rows(h->pre0, tw + o_x, p.Mnf, rows_all, ACT_RELU, tw + o_a);
+      const float* pin = tw + o_a;
+      if (p.ms) {
+        add_spk_rows_kernel<<<(unsigned)std::min<size_t>((rows_all * p.P0 + 255) / 256, 148 * 16), 256, 0, st>>>(
+            tw + o_a, (int)rows_all, B, p.P0, h->pre0.Np, p.spk_term, ld);
+        count_launch();
+        dense_rows(h->msd, tw + o_a, h->pre0.Np, rows_all, ACT_RELU, tw + o_b);
+        pin = tw + o_b;
+      }
+      dense_rows(h->pre1, pin, h->pre0.Np, rows_all, ACT_RELU, tw + o_p1);
+      p.batched_tail = 1;
+      p.p1_all = tw + o_p1;
+      p.p1_ld = h->pre1.Np;
+      t_dec = io.decoder_outputs ? io.decoder_outputs : tw + o_dec;
+      p.dec_out = t_dec;
+      t_y[0] = tw + o_y0; t_y[1] = tw + o_y1; t_mha = tw + o_mha; t_proj = tw + o_pr;
+    }
+
     if (use_tc) {
       float* bufs[6] = {p.att_in[0], p.att_in[1], p.l1_in[0], p.l1_in[1], p.l2_in[0], p.l2_in[1]};
       const int pads[6] = {p.Ka_pad, p.Ka_pad, p.K1_pad, p.K1_pad, p.K2_pad, p.K2_pad};
@@ -556,6 +638,22 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
     SAT_CUDA(cudaEventRecord(h->ev1, st));
     h->last_B = B; h->last_T = T; h->last_S = S;
     count_launch();
+    if (tail) {
+      // decoder self-attention hops as causal time-batched attention, then the frame + stop projection
+      const float* y = t_dec;
+      for (int i = 0; i < h->hops; ++i) {
+        MhaDev m;
+        m.Wqkv = h->sa_qkv[i].Wrm; m.bqkv = h->sa_qkv[i].bias; m.Wo = h->sa_o[i].Wrm; m.bo = h->sa_o[i].bias;
+        m.Wt = h->sa_tr[i].Wrm; m.bt = h->sa_tr[i].bias;
+        m.Din = Dd; m.D = Ds; m.H = hp.decoder_self_attention_num_heads;
+        sat_layer_forward(m, y, B, S, 1, nullptr, t_y[i & 1], nullptr, t_mha, st);
+        y = t_y[i & 1];
+      }
+      dense_rows(h->outp, y, h->outp.K, rows_all, ACT_NONE, t_proj);
+      split_projection_kernel<<<(unsigned)std::min<size_t>((rows_all * (p.Mr + 1) + 255) / 256, 148 * 16), 256, 0, st>>>(
+          t_proj, rows_all, h->outp.Np, p.Mr, io.mel, io.stop);
+      count_launch();
+    }
     if (io.sample_ids) {
       const long long rows = (long long)B * S * p.r;
       argmax_kernel<<<(unsigned)ceil_div64(rows, 8), 256, 0, st>>>(io.mel, rows, p.M, io.sample_ids);

@@ -47,6 +47,14 @@ struct DecParams {
   long long* prof;  // [N_PROF] accumulated SM cycles per phase (CTA 0), may be null
   // ---- tensor-core mode (B >= 64): LSTM inputs att_in / l1_in / l2_in are ROW-major fp16 [RB*128][K*_pad] ----
   int tc, RB, Ka_pad, K1_pad, K2_pad;
+  // ---- teacher-forced time-batched form (feed_mode teacher + fixed step count): everything that does not feed the
+  // recurrence leaves the loop.  The prenet of all (known) input frames is precomputed into p1_all[S][B][p1_ld]; the
+  // loop runs C, D+E, F, G only and records the LSTM2 outputs in dec_out; the decoder self-attention hops (as ONE
+  // causal batched attention per hop) and the frame / stop projections run afterwards as time-batched GEMMs --
+  // the structure of the reference's own training branch (modules/module.py:743-765).
+  int batched_tail;
+  const float* p1_all;
+  int p1_ld;
   int bench_barriers;       // diagnostic: time this many empty grid barriers before the loop (prof[30])
   int scratch_floats;       // phase scratch at the head of dynamic smem (>= SCRATCH_FLOATS; holds the TMA ring in tc mode)
   TcLstmDesc tc_a, tc_1, tc_2;
@@ -465,8 +473,17 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
     ++ph;
   };
 
+  // prenet outputs of step `step` (precomputed) -> prenet slot of an attention-LSTM input buffer
+  auto copy_prenet = [&](int step, Act2D dst) {
+    const float* src = p.p1_all + (size_t)step * p.B * p.p1_ld;
+    for (int i = blockIdx.x * NT + tid; i < p.B * p.P1; i += gridDim.x * NT) {
+      const int b = i / p.P1, n = i - b * p.P1;
+      dst.put(n, b, __ldg(src + (size_t)b * p.p1_ld + n));
+    }
+  };
   // prenet of the <GO> frame -> attention-LSTM input of step 0
-  frame_phase(p, 0, nullptr, 0, Act2D{p.att_in[0], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc}, true, scratch);
+  if (p.batched_tail) copy_prenet(0, Act2D{p.att_in[0], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc});
+  else frame_phase(p, 0, nullptr, 0, Act2D{p.att_in[0], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc}, true, scratch);
   if (p.tc) {
     tc::fence_proxy_async();
     bar.sync([&] { tc_prefill(p.tc_a, p.maps, p.RB, tcs); });
@@ -563,6 +580,8 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
     if (p.tc) phase_end(&p.tc_1, p.maps + 2 + cur);
     else phase_end();
     // ---- F: decoder LSTM 1 ----
+    if (p.batched_tail && t + 1 < p.max_steps)
+      copy_prenet(t + 1, Act2D{p.att_in[nxt], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc});
     if (p.tc) {
       const int h0 = p.A + p.Dctx;
       TcLstmIO io{p.maps + 2 + cur, Act2D{p.l2_in[cur], 1, p.K2_pad, 1}, Act2D{nullptr, 0, 0, 0},
@@ -593,28 +612,30 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
                           p.l2_in[nxt] + hoff, p.dec_out, p.max_steps * p.Dd, t * p.Dd, p.zc, p.zh});
     }
     phase_end();
-    // ---- H-K: decoder self-attention hops over the KV cache ----
-    const float* y = p.dout;
-    for (int hi = 0; hi < p.hops; ++hi) {
-      const SaHop& h = p.hop[hi];
-      dense_phase(h.qkv, y, ld, p.Bp, wres, scratch,
-                  QkvEpi{h.qkv.bias, p.Ds, p.Ds / p.heads, p.heads, p.Smax, t, ld, p.B, h.kcache, h.vcache, p.sa_q});
-      phase_end();
-      for (int item = blockIdx.x; item < p.B * p.heads; item += gridDim.x)
-        sa_item(p, h, item / p.heads, item % p.heads, t, scratch);
-      phase_end();
-      dense_phase(h.o, p.sa_ctx, ld, p.Bp, wres, scratch,
-                  DenseEpi{h.o.bias, h.o.N, ld, 0, Act2D{p.sa_a, ld, 1, 0}, nullptr, nullptr});
-      phase_end();
-      dense_phase(h.tr, p.sa_a, ld, p.Bp, wres, scratch,
-                  DenseEpi{h.tr.bias, h.tr.N, ld, 2, Act2D{p.sa_y[hi & 1], ld, 1, 0}, nullptr, y});
-      phase_end();
-      y = p.sa_y[hi & 1];
+    if (!p.batched_tail) {
+      // ---- H-K: decoder self-attention hops over the KV cache ----
+      const float* y = p.dout;
+      for (int hi = 0; hi < p.hops; ++hi) {
+        const SaHop& h = p.hop[hi];
+        dense_phase(h.qkv, y, ld, p.Bp, wres, scratch,
+                    QkvEpi{h.qkv.bias, p.Ds, p.Ds / p.heads, p.heads, p.Smax, t, ld, p.B, h.kcache, h.vcache, p.sa_q});
+        phase_end();
+        for (int item = blockIdx.x; item < p.B * p.heads; item += gridDim.x)
+          sa_item(p, h, item / p.heads, item % p.heads, t, scratch);
+        phase_end();
+        dense_phase(h.o, p.sa_ctx, ld, p.Bp, wres, scratch,
+                    DenseEpi{h.o.bias, h.o.N, ld, 0, Act2D{p.sa_a, ld, 1, 0}, nullptr, nullptr});
+        phase_end();
+        dense_phase(h.tr, p.sa_a, ld, p.Bp, wres, scratch,
+                    DenseEpi{h.tr.bias, h.tr.N, ld, 2, Act2D{p.sa_y[hi & 1], ld, 1, 0}, nullptr, y});
+        phase_end();
+        y = p.sa_y[hi & 1];
+      }
+      // ---- L+A+B: frame + stop projection of step t, fed-back frame, prenet of step t+1 (row split) ----
+      frame_phase(p, t, y, p.outp.K, Act2D{p.att_in[nxt], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc}, false, scratch);
+      if (p.tc && t + 1 < p.max_steps) phase_end(&p.tc_a, p.maps + nxt);
+      else phase_end();
     }
-    // ---- L+A+B: frame + stop projection of step t, fed-back frame, prenet of step t+1 (row split) ----
-    frame_phase(p, t, y, p.outp.K, Act2D{p.att_in[nxt], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc}, false, scratch);
-    if (p.tc && t + 1 < p.max_steps) phase_end(&p.tc_a, p.maps + nxt);
-    else phase_end();
     // ---- stop rule (every CTA evaluates the same data -> same decision) ----
     if (p.stop_mode != SAT_STOP_FIXED) {
       bool term = true, stopped = true;
