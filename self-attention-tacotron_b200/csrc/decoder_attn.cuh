@@ -631,10 +631,13 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
     if (lane == 0) s32[NW + warp] = sum;
     __syncthreads();
     sum = warp_sum(lane < NW ? s32[NW + lane] : 0.f);
+    ps = 6;
+    stamp();
+    const float inv_sum = 1.f / sum;
 #pragma unroll
     for (int i = 0; i < NJ; ++i) {
       const int j = tid + i * NT;
-      pr[i] = pr[i] / sum;
+      pr[i] = pr[i] * inv_sum;
       if (j < T) {
         e[j] = pr[i];
         m.st_align[(size_t)b * T + j] = m.cumulative ? pr[i] + aprev[HALO + j] : pr[i];
@@ -657,11 +660,12 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
       if (lane == 0) s32[2 * NW + warp] = s2;
       __syncthreads();
       s2 = warp_sum(lane < NW ? s32[2 * NW + lane] : 0.f);
+      const float inv_s2 = 1.f / s2;
 #pragma unroll
       for (int i = 0; i < NJ; ++i) {
         const int j = tid + i * NT;
         if (j < T) {
-          const float a = val[i] / s2;
+          const float a = val[i] * inv_s2;
           nal[j] = a;
           m.st_alpha[(size_t)b * T + j] = a;
         }
@@ -669,6 +673,8 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
       align = nal;
     }
     __syncthreads();
+    ps = 7;
+    stamp();
   }
   if (m.out_align)
     for (int j = tid; j < T; j += NT) m.out_align[((size_t)b * m.out_S + t) * T + j] = align[j];
