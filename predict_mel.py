@@ -1,11 +1,15 @@
 """CLI twin of /root/reference/predict_mel.py:1-15 over the CUDA hot path.
 
 Usage: predict_mel.py --hparam-json-file=<path> [--hparams=<k=v,...>] --output-dir=<path>
-                      [--weights=<npz>] [--sources=<npz>] [--batch-size=<n>]
+                      [--weights=<npz>] [--sources=<npz>] [--source-tfrecords=<glob>] [--target-tfrecords=<glob>]
+                      [--batch-size=<n>]
 
-Inputs are an .npz of utterances (keys ``<key>/source`` int64 ids, optional ``<key>/mel``) because the
-TFRecord reader is a "next" row.  Without --weights the model is random-initialised
-(seed 12345); without --sources a small synthetic list is synthesised."""
+Inputs: the reference's preprocessed source / target TFRecord files (--source-tfrecords / --target-tfrecords,
+preprocess/ljspeech.py:23-44; read without TensorFlow by sat_b200.tfrecord) or an .npz of utterances (keys
+``<key>/source`` int64 ids, optional ``<key>/mel``).  Outputs per utterance, like predict_mel.py:56-74: ``<key>.mfbsp``
+(raw '<f4' frames) and ``<key>.tfrecord`` (prediction record).  Without --weights the model is random-initialised
+(seed 12345); without any source a small synthetic list is synthesised."""
+import glob
 import argparse
 
 import numpy as np
@@ -21,6 +25,8 @@ def main():
     ap.add_argument("--output-dir", required=True)
     ap.add_argument("--weights")
     ap.add_argument("--sources")
+    ap.add_argument("--source-tfrecords")
+    ap.add_argument("--target-tfrecords")
     ap.add_argument("--batch-size", type=int, default=None)
     args = ap.parse_args()
     hp = sat_b200.HParams()
@@ -30,7 +36,11 @@ def main():
     print(sat_b200.hparams_debug_string(hp))
     W = dict(np.load(args.weights)) if args.weights else sat_b200.init_weights(hp)
     utts = []
-    if args.sources:
+    if args.source_tfrecords:
+        from sat_b200.predict_mel import load_utterances
+        utts = load_utterances(sorted(glob.glob(args.source_tfrecords)),
+                               sorted(glob.glob(args.target_tfrecords)) if args.target_tfrecords else None)
+    elif args.sources:
         z = np.load(args.sources)
         keys = sorted({k.split("/")[0] for k in z.files})
         for i, k in enumerate(keys):

@@ -2,14 +2,16 @@
 ``predict`` :36-74, raw little-endian float32 ``.mfbsp`` output :58-62) fed by the CUDA hot path.
 
 Differences from the reference: batched (the reference forces batch_size=1, :43-44), utterances are
-length-bucketed and sharded over the GPUs of one box (``sharding.py``), inputs arrive as arrays
-(the TFRecord reader is a "next" row), and no PNG plot is written (no plotting stack)."""
+length-bucketed and sharded over the GPUs of one box (``sharding.py``), inputs arrive as arrays or through
+``load_utterances`` (the reference's source / target TFRecord files, read by ``tfrecord.py`` without TensorFlow), and no
+PNG plot is written (no plotting stack).  Next to every ``.mfbsp`` a prediction TFRecord is written (:70-74)."""
 import os
 from collections import namedtuple
 
 import numpy as np
 import torch
 
+from . import tfrecord
 from .models import tacotron_model_factory
 from .sharding import make_buckets
 
@@ -104,4 +106,22 @@ def write_predicted_mel(v, hparams, output_dir):
     os.makedirs(output_dir, exist_ok=True)
     path = os.path.join(output_dir, f"{key}.{hparams.predicted_mel_extension}")
     np.ascontiguousarray(mel, dtype="<f4").tofile(path)
+    # predict_mel.py:70-74: the prediction record next to it (TFRecord, tf.train.Example; see tfrecord.py)
+    text = v.text.decode("utf-8") if isinstance(v.text, bytes) else str(v.text or "")
+    tfrecord.write_prediction_result(v.id, key, mel, v.ground_truth_mel, text, v.source,
+                                     os.path.join(output_dir, f"{key}.tfrecord"))
     return path
+
+
+def load_utterances(source_files, target_files=None):
+    """Source (and optional target) TFRecord files written by the reference's preprocessing
+    (preprocess/ljspeech.py:23-44) -> list[Utterance]; targets are matched to sources by key."""
+    targets = {}
+    for f in target_files or []:
+        for t in tfrecord.read_target_data(f):
+            targets[t.key] = t.mel
+    utts = []
+    for f in source_files:
+        for s in tfrecord.read_source_data(f):
+            utts.append(Utterance(s.id, s.key, s.source, text=s.text, mel=targets.get(s.key)))
+    return utts

@@ -98,3 +98,35 @@ def test_predict_mel_free_run_writes_mfbsp(tmp_path):
         assert v.alignment.shape == (lengths[row], n)
         raw = np.fromfile(tmp_path / f"utt{i}.mfbsp", dtype="<f4").reshape(-1, hp.num_mels)
         np.testing.assert_array_equal(raw, v.predicted_mel)
+        # the prediction record next to it (predict_mel.py:70-74), read back without TensorFlow
+        from sat_b200 import tfrecord
+        (p,) = tfrecord.read_prediction_result(str(tmp_path / f"utt{i}.tfrecord"))
+        assert (p.id, p.key, p.text, p.mel_width) == (i, f"utt{i}", "x", hp.num_mels)
+        np.testing.assert_array_equal(p.mel, v.predicted_mel)
+        np.testing.assert_array_equal(p.source, utts[i].source)
+
+
+def test_predict_mel_from_reference_tfrecords(tmp_path):
+    """drop-in data path: the reference's preprocessed source / target TFRecords -> load_utterances -> predict
+    (teacher-forced, needs the ground-truth mel of the target records) -> .mfbsp + prediction TFRecord."""
+    from sat_b200 import tfrecord
+    from sat_b200.predict_mel import predict, load_utterances
+    hp = small_hp("ljspeech_tacotron", max_iters=30)
+    W = sat_b200.init_weights(hp, seed=29)
+    rng = np.random.default_rng(29)
+    srcs, tgts = [], []
+    for i, (n, frames) in enumerate([(14, 22), (9, 16)]):
+        fs, ft = str(tmp_path / f"k{i}.source.tfrecord"), str(tmp_path / f"k{i}.target.tfrecord")
+        tfrecord.write_source_data(i, f"k{i}", rng.integers(1, 71, size=n), f"text {i}", fs)
+        tfrecord.write_target_data(i, f"k{i}", rng.normal(0, 1, size=(frames, hp.num_mels)).astype(np.float32), ft)
+        srcs.append(fs)
+        tgts.append(ft)
+    utts = load_utterances(srcs, tgts)
+    out_dir = tmp_path / "out"
+    res = predict(hp, W, utts, output_dir=str(out_dir), batch_size=4, mode="teacher_forced")
+    assert sorted(v.key for v in res) == ["k0", "k1"]
+    for v in res:
+        assert np.isfinite(v.predicted_mel).all() and v.predicted_mel.shape[0] == 22  # padded to the longest target
+        (p,) = tfrecord.read_prediction_result(str(out_dir / f"{v.key}.tfrecord"))
+        np.testing.assert_array_equal(p.mel, v.predicted_mel)
+        assert p.ground_truth_mel_length in (22, 16) and p.text.startswith("text ")
