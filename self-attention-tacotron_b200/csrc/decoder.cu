@@ -13,8 +13,11 @@ struct PackedDense {
   float* bias = nullptr;
   float* Wrm = nullptr;   // row-major [K][Np] copy (pack_dense only)
   void* Wrm16 = nullptr;  // row-major fp16 [K][Np8] copy
-  int K = 0, N = 0, n_tiles = 0, Np = 0, Np8 = 0;
-  DenseDesc desc() const { return DenseDesc{Wp, bias, K, N, n_tiles, -1, 0, Wrm, Np, Wrm16, Np8, 0, 0}; }
+  int K = 0, N = 0, n_tiles = 0, Np = 0, Np8 = 0, reps = 1;
+  size_t rep_stride = 0, rep_stride16 = 0;
+  DenseDesc desc() const {
+    return DenseDesc{Wp, bias, K, N, n_tiles, -1, 0, Wrm, Np, Wrm16, Np8, reps, rep_stride, rep_stride16, 0, 0};
+  }
 };
 
 // generic column-tile packing: column c of tile i comes from source column colmap[i*8+c] (or -1 = zero)
@@ -38,15 +41,22 @@ PackedDense pack_cols(DevPool& pool, const float* W, const float* bias, int K, i
 // row-major copies [K][Np] (fp32) and [K][Np8] (fp16) of the first N columns of W[K][Nsrc], zero-padded to Nout columns:
 // the operands of the row-split phases (row_dense)
 void add_row_major(DevPool& pool, PackedDense& d, const float* W, int K, int Nsrc, int N, int Nout) {
+  int reps = 1;  // replicas (see DenseDesc::reps); measured on B200: 1, 4 and 8 give the same phase times -> 1
+  if (const char* e = getenv("SAT_WEIGHT_REPLICAS")) reps = std::max(1, std::min(16, atoi(e)));
+  d.reps = reps;
   d.Np = (Nout + 3) / 4 * 4;
-  std::vector<float> rm((size_t)K * d.Np, 0.f);
-  for (int k = 0; k < K; ++k)
-    for (int n = 0; n < N; ++n) rm[(size_t)k * d.Np + n] = W[(size_t)k * Nsrc + n];
+  d.rep_stride = ((size_t)K * d.Np + 63) / 64 * 64 + 32;  // + 32 floats: successive replicas start on different lines
+  std::vector<float> rm(d.rep_stride * reps, 0.f);
+  for (int r = 0; r < reps; ++r)
+    for (int k = 0; k < K; ++k)
+      for (int n = 0; n < N; ++n) rm[r * d.rep_stride + (size_t)k * d.Np + n] = W[(size_t)k * Nsrc + n];
   d.Wrm = pool.upload(rm);
   d.Np8 = (Nout + 7) / 8 * 8;
-  std::vector<__half> rh((size_t)K * d.Np8 + 8, __float2half(0.f));
-  for (int k = 0; k < K; ++k)
-    for (int n = 0; n < N; ++n) rh[(size_t)k * d.Np8 + n] = __float2half_rn(W[(size_t)k * Nsrc + n]);
+  d.rep_stride16 = ((size_t)K * d.Np8 + 127) / 128 * 128 + 64;
+  std::vector<__half> rh(d.rep_stride16 * reps + 8, __float2half(0.f));
+  for (int r = 0; r < reps; ++r)
+    for (int k = 0; k < K; ++k)
+      for (int n = 0; n < N; ++n) rh[r * d.rep_stride16 + (size_t)k * d.Np8 + n] = __float2half_rn(W[(size_t)k * Nsrc + n]);
   d.Wrm16 = pool.upload((const float*)rh.data(), (rh.size() + 1) / 2);
 }
 PackedDense pack_dense(DevPool& pool, const float* W, const float* bias, int K, int N) {

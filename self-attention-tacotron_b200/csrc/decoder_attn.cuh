@@ -460,7 +460,7 @@ __device__ inline void attention_context_h8(const __half* __restrict__ vb, const
   float acc[8];
 #pragma unroll
   for (int c = 0; c < 8; ++c) acc[c] = 0.f;
-  constexpr int UN = 8;
+  constexpr int UN = 8;  // rows in flight per lane (16 measured no faster)
   const int stride = NW * G;
   for (int j0 = warp * G + g; j0 < len; j0 += UN * stride) {
     uint4 v[UN];

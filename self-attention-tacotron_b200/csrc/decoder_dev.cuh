@@ -32,6 +32,9 @@ struct DenseDesc {
   int Np;
   const void* Wrm16;  // the same in fp16 [K][Np8] (Np8 = N padded to 8), used in tensor-core mode
   int Np8;
+  int reps;           // both row-major copies exist `reps` times back to back (rep_stride / rep_stride16 elements apart):
+  size_t rep_stride, rep_stride16;  // CTAs read replica blockIdx % reps so that the broadcast read of a small weight
+                                    // set spreads over more L2 slices
   int rpg, R;         // rows per work item (32 / 64 / 128) and row groups = ceil(Bp / rpg): small layers split rows
                       // finer so that n_tiles * R work items cover the grid
 };

@@ -240,7 +240,9 @@ __device__ inline void row_dense(const DenseDesc& d, const float* xs, int xs_str
 #pragma unroll
       for (int c = 0; c < CW; ++c) acc[r][c] = 0.f;
     const int k0 = kp * kper, k1 = min(K, k0 + kper);
-    const uint4* w = (H ? (const uint4*)d.Wrm16 : (const uint4*)d.Wrm) + (size_t)k0 * Cn + cl;
+    const int rep = d.reps > 1 ? (int)(blockIdx.x % d.reps) : 0;
+    const uint4* w = (H ? (const uint4*)((const __half*)d.Wrm16 + rep * d.rep_stride16)
+                        : (const uint4*)(d.Wrm + rep * d.rep_stride)) + (size_t)k0 * Cn + cl;
     for (int k = k0; k < k1; k += 8, w += 8 * Cn) {
       uint4 wv[8];
 #pragma unroll
