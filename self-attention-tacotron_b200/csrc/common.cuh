@@ -162,13 +162,15 @@ struct ConvTcLaunch {
   int ld16 = 0;
   float* y32 = nullptr;   // dense fp32 output [B*T][ld32]
   int ld32 = 0;
-  const float* res = nullptr;  // optional fp32 residual [B*T][ldr] (fp32 output only)
+  const float* res = nullptr;  // optional fp32 residual [B*T][ldr] (joins before the stores; needs y32)
   int ldr = 0;
+  int highway = 0;  // HighwayNet epilogue over interleaved (H_u, T_u) columns: x = res, bias = shift, writes cout/2 columns
 };
 bool conv_tc_supported(int cin, int cout);
 __half* conv_tc_weight_image(DevPool& pool, const float* w, int taps, int cin, int n);
 void conv_tc_pack(const float* x, int ldx, int B, int T, int C, __half* xp, int ldp, cudaStream_t st);
 void conv_tc_maxpool2(const __half* x, int B, int T, int C, __half* y, cudaStream_t st);
+void conv_tc_zero_halo(__half* x, int B, int T, int C, cudaStream_t st);  // C % 8 == 0
 void conv_tc_launch(const ConvTcLaunch& L, cudaStream_t st);
 
 // ---- multi-head self-attention (mha.cu) --------------------------------------

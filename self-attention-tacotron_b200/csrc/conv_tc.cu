@@ -33,6 +33,7 @@ struct ConvTcArgs {
   int ld32;
   const float* res;         // optional fp32 residual [B*T][ldr] added before the store (fp32 output only)
   int ldr;
+  int highway;              // 1: HighwayNet epilogue over interleaved (H_u, T_u) column pairs, x = res; writes N/2 columns
 };
 
 __global__ void __launch_bounds__(CT_THREADS, 1)
@@ -97,6 +98,33 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant__
     float v[16];
     tc::tmem_ld16(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)cb, v);
     if (!valid) continue;
+    if (a.highway) {
+      // HighwayNet (tacotron2): y_u = relu(H_u) * sigmoid(T_u) + x_u * (1 - sigmoid(T_u)); 8 units here
+      const int u0 = (n0 + cb) >> 1;
+      const float4* xp = (const float4*)(a.res + drow * a.ldr + u0);
+      const float4 x0 = __ldg(xp), x1 = __ldg(xp + 1);
+      const float x[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+      float y[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int n = n0 + cb + 2 * k;
+        const float hh = fmaxf(v[2 * k] + __ldg(a.shift + n), 0.f);
+        const float tt = 1.f / (1.f + expf(-(v[2 * k + 1] + __ldg(a.shift + n + 1))));
+        y[k] = hh * tt + x[k] * (1.f - tt);
+      }
+      if (a.y16) {
+        __half2 h[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) h[k] = __halves2half2(tc::to_f16(y[2 * k]), tc::to_f16(y[2 * k + 1]));
+        *(uint4*)(a.y16 + (size_t)r * a.ld16 + u0) = *(const uint4*)&h[0];
+      }
+      if (a.y32) {
+        float4* dst = (float4*)(a.y32 + drow * a.ld32 + u0);
+        dst[0] = make_float4(y[0], y[1], y[2], y[3]);
+        dst[1] = make_float4(y[4], y[5], y[6], y[7]);
+      }
+      continue;
+    }
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
       const int n = n0 + cb + i;
@@ -107,6 +135,14 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant__
       else if (a.act == ACT_TANH) x = tanhf(x);
       v[i] = x;
     }
+    if (a.y32 && a.res) {  // residual joins before both stores (proj2 + input)
+      const float4* rp = (const float4*)(a.res + drow * a.ldr + n0 + cb);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float4 q = __ldg(rp + i);
+        v[4 * i] += q.x; v[4 * i + 1] += q.y; v[4 * i + 2] += q.z; v[4 * i + 3] += q.w;
+      }
+    }
     if (a.y16) {
       __half2 h[8];
 #pragma unroll
@@ -116,14 +152,6 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant__
       dst[1] = *(const uint4*)&h[4];
     }
     if (a.y32) {
-      if (a.res) {
-        const float4* rp = (const float4*)(a.res + drow * a.ldr + n0 + cb);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const float4 q = __ldg(rp + i);
-          v[4 * i] += q.x; v[4 * i + 1] += q.y; v[4 * i + 2] += q.z; v[4 * i + 3] += q.w;
-        }
-      }
       float4* dst = (float4*)(a.y32 + drow * a.ld32 + n0 + cb);
 #pragma unroll
       for (int i = 0; i < 4; ++i) dst[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
@@ -170,7 +198,26 @@ __global__ void maxpool2_f16_haloed_kernel(const __half* __restrict__ x, int B, 
   }
 }
 
+// zero the halo rows (HALO before and after every utterance) of a haloed fp16 buffer [B][Tp][C]
+__global__ void zero_halo_kernel(__half* __restrict__ x, int B, int T, int Tp, int halo, int C) {
+  const size_t per = (size_t)2 * halo * (C / 8), n = (size_t)B * per;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const int b = (int)(i / per);
+    const size_t q = i % per;
+    const int hr = (int)(q / (C / 8)), c8 = (int)(q % (C / 8));
+    const int row = hr < halo ? hr : T + hr;  // rows [0, halo) and [halo + T, Tp)
+    *(uint4*)(x + ((size_t)b * Tp + row) * C + 8 * c8) = make_uint4(0u, 0u, 0u, 0u);
+  }
+}
+
 }  // namespace
+
+void conv_tc_zero_halo(__half* x, int B, int T, int C, cudaStream_t st) {
+  const int Tp = T + 2 * CONV_TC_HALO;
+  const size_t n = (size_t)B * 2 * CONV_TC_HALO * (C / 8);
+  zero_halo_kernel<<<(unsigned)std::min<size_t>((n + 255) / 256, 148 * 8), 256, 0, st>>>(x, B, T, Tp, CONV_TC_HALO, C);
+  count_launch();
+}
 
 // K-major fp16 image [N][taps*Cin] of a TF conv kernel [taps][Cin][N]
 __half* conv_tc_weight_image(DevPool& pool, const float* w, int taps, int cin, int n) {
@@ -212,7 +259,8 @@ void conv_tc_launch(const ConvTcLaunch& L, cudaStream_t st) {
   a.R = (int)R; a.Tp = Tp; a.T = L.T; a.halo = CONV_TC_HALO;
   a.taps = L.taps; a.pad_left = L.pad_left; a.cin = L.cin;
   a.scale = L.scale; a.shift = L.shift; a.act = L.act;
-  a.y16 = L.y16; a.ld16 = L.ld16; a.y32 = L.y32; a.ld32 = L.ld32; a.res = L.res; a.ldr = L.ldr;
+  a.y16 = L.y16; a.ld16 = L.ld16; a.y32 = L.y32; a.ld32 = L.ld32; a.res = L.res; a.ldr = L.ldr; a.highway = L.highway;
+  SAT_REQUIRE(!L.highway || (L.res && L.shift), "highway epilogue needs the layer input (res) and the bias (shift)");
   static bool attr_set = false;
   const int smem = CT_STAGES * CT_STAGE_BYTES + 1024;
   if (!attr_set) {

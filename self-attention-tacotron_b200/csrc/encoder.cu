@@ -151,6 +151,10 @@ struct sat_encoder {
   std::vector<MhaDev> hops;
   int half = 0, cin = 0;
   bool tc = false;  // conv bank + proj1 on the tensor cores (fp16 operands, fp32 accumulation)
+  bool tc_full = false;  // ... and prenet layer 1, proj2, the highway layers and the BiLSTM input projection as well
+  __half* pre1_img = nullptr;
+  std::vector<__half*> hw_img;
+  __half* lstm_img = nullptr;
   Scratch ws16;     // haloed fp16 activations of that path
 };
 
@@ -205,6 +209,7 @@ extern "C" int sat_encoder_create(const sat_hparams* hpp, const sat_tensor* weig
       for (int u = 0; u < half; ++u) { b[2 * u] = bh[u]; b[2 * u + 1] = bt[u]; }
       h->hw_w.push_back(pool.upload(w));
       h->hw_b.push_back(pool.upload(b));
+      if (conv_tc_supported(half, 2 * half)) h->hw_img.push_back(conv_tc_weight_image(pool, w.data(), 1, half, 2 * half));
     }
     // BiLSTM: TF kernel [in + U][4U] gate blocks i,j,f,o -> input part [in][dir][u][g], recurrent part [dir][k][u][g]
     {
@@ -223,12 +228,23 @@ extern "C" int sat_encoder_create(const sat_hparams* hpp, const sat_tensor* weig
           }
       }
       h->lstm_wx = pool.upload(wx);
+      if (conv_tc_supported(in, 8 * U)) h->lstm_img = conv_tc_weight_image(pool, wx.data(), 1, in, 8 * U);
       h->lstm_bx = pool.upload(bx);
       h->lstm_wh = pool.upload(wh);
     }
     h->tc = h->proj1.wimg != nullptr;
     for (const Conv& c : h->bank) h->tc = h->tc && c.wimg != nullptr;
     if (const char* e = getenv("SAT_ENC_TC")) h->tc = h->tc && atoi(e) != 0;
+    {
+      const int P0 = hp.encoder_prenet_units[0], P1 = hp.encoder_prenet_units[1];
+      h->tc_full = h->tc && !h->adj_w && h->proj2.wimg && conv_tc_supported(P0, P1) && conv_tc_supported(half, 2 * half) &&
+                   conv_tc_supported(half, 8 * half) && hp.projection1_out_channels % 64 == 0 &&
+                   hp.projection2_out_channels == half;
+      if (const char* e = getenv("SAT_ENC_TC_FULL")) h->tc_full = h->tc_full && atoi(e) != 0;
+      if (h->tc_full) {
+        h->pre1_img = conv_tc_weight_image(pool, W.get("encoder/prenet/dense_1/kernel", (int64_t)P0 * P1), 1, P0, P1);
+      }
+    }
     if (hp.encoder_kind == SAT_ENC_SELF_ATTENTION_CBHG) {
       const int Ds = hp.self_attention_out_units;
       h->sap_w = pool.upload(W.get("encoder/sa_projection/kernel", (int64_t)hp.cbhg_out_units * Ds), (size_t)hp.cbhg_out_units * Ds);
@@ -285,22 +301,41 @@ static int encoder_forward_impl(sat_encoder* h, const int64_t* ids, const float*
       g.gather_ids = ids; g.gather_offset = 0;
       g.W = h->pre_w[0]; g.N = P0; g.shift = h->pre_b[0]; g.act = ACT_RELU; g.C = ws + o_p0; g.ldc = P0;
       gemm_launch(g, st);
-      GemmArgs g1;
-      g1.X = ws + o_p0; g1.Bn = 1; g1.T = (int)rows; g1.Cin = P0; g1.ldx = P0;
-      g1.W = h->pre_w[1]; g1.N = P1; g1.shift = h->pre_b[1]; g1.act = ACT_RELU; g1.C = ws + o_p1; g1.ldc = P1;
-      gemm_launch(g1, st);
+      if (!h->tc_full) {
+        GemmArgs g1;
+        g1.X = ws + o_p0; g1.Bn = 1; g1.T = (int)rows; g1.Cin = P0; g1.ldx = P0;
+        g1.W = h->pre_w[1]; g1.N = P1; g1.shift = h->pre_b[1]; g1.act = ACT_RELU; g1.C = ws + o_p1; g1.ldc = P1;
+        gemm_launch(g1, st);
+      }
     }
     const int ldb = KW * Cb;
-    if (h->tc) {
-      // ---- conv bank, max-pool and proj1 on the tensor cores over zero-haloed fp16 activations (conv_tc.cu) ----
+    const float* hw_in = nullptr;
+    if (h->tc_full) {
+      // ---- prenet layer 1 .. BiLSTM input projection, all tcgen05 implicit GEMMs over haloed fp16 activations ----
+      // fp32 copies are kept only where an fp32 residual is needed (prenet output, highway inputs).
       const int Tp = T + 2 * CONV_TC_HALO;
       const size_t R = (size_t)B * Tp;
-      const size_t n_x = R * P1, n_bank = R * (size_t)ldb;
-      __half* x16 = h->ws16.get<__half>(n_x + 2 * n_bank + 64);
-      __half* bank16 = x16 + (n_x + 7) / 8 * 8;
+      auto al8 = [](size_t n) { return (n + 7) / 8 * 8; };
+      const int Q1 = h->proj1.cout;
+      const size_t n_p0 = al8(R * P0), n_x = al8(R * P1), n_bank = al8(R * (size_t)ldb), n_q1 = al8(R * Q1), n_h = al8(R * half);
+      __half* p0_16 = h->ws16.get<__half>(n_p0 + n_x + 2 * n_bank + n_q1 + 2 * n_h + 64);
+      __half* x16 = p0_16 + n_p0;
+      __half* bank16 = x16 + n_x;
       __half* pool16 = bank16 + n_bank;
-      SAT_CUDA(cudaMemsetAsync(x16, 0, (n_x + 2 * n_bank + 64) * sizeof(__half), st));
-      conv_tc_pack(ws + o_p1, P1, B, T, P1, x16, P1, st);
+      __half* q1_16 = pool16 + n_bank;
+      __half* hw16[2] = {q1_16 + n_q1, q1_16 + n_q1 + n_h};
+      // only the inputs of multi-tap convolutions need zero halos
+      conv_tc_zero_halo(x16, B, T, P1, st);
+      conv_tc_zero_halo(pool16, B, T, ldb, st);
+      conv_tc_zero_halo(q1_16, B, T, Q1, st);
+      conv_tc_pack(ws + o_p0, P0, B, T, P0, p0_16, P0, st);
+      {
+        ConvTcLaunch L;  // prenet layer 1: relu(x W + b) -> fp16 (bank input) and fp32 (residual of proj2)
+        L.xp = p0_16; L.ldxp = P0; L.B = B; L.T = T; L.cin = P0; L.cout = P1; L.taps = 1; L.pad_left = 0;
+        L.wimg = h->pre1_img; L.shift = h->pre_b[1]; L.act = ACT_RELU;
+        L.y16 = x16; L.ld16 = P1; L.y32 = ws + o_p1; L.ld32 = P1;
+        conv_tc_launch(L, st);
+      }
       for (int k = 1; k <= KW; ++k) {
         const Conv& c = h->bank[k - 1];
         ConvTcLaunch L;
@@ -310,50 +345,105 @@ static int encoder_forward_impl(sat_encoder* h, const int64_t* ids, const float*
         conv_tc_launch(L, st);
       }
       conv_tc_maxpool2(bank16, B, T, ldb, pool16, st);
-      ConvTcLaunch L;
-      L.xp = pool16; L.ldxp = ldb; L.B = B; L.T = T; L.cin = ldb; L.cout = h->proj1.cout; L.taps = 3; L.pad_left = 1;
-      L.wimg = h->proj1.wimg; L.scale = h->proj1.scale; L.shift = h->proj1.shift; L.act = ACT_RELU;
-      L.y32 = ws + o_q1; L.ld32 = h->proj1.cout;
-      conv_tc_launch(L, st);
-    } else {
-      // ---- conv bank -> concat buffer [rows][KW*Cb] (fp32 SIMT form) ----
-      for (int k = 1; k <= KW; ++k) {
-        const Conv& c = h->bank[k - 1];
-        conv_bn_act_launch(ws + o_p1, B, T, P1, c.w, c.scale, c.shift, k, P1, Cb, ACT_RELU, 0, nullptr, 0,
-                           ws + o_bank + (size_t)(k - 1) * Cb, ldb, st);
+      {
+        ConvTcLaunch L;  // proj1
+        L.xp = pool16; L.ldxp = ldb; L.B = B; L.T = T; L.cin = ldb; L.cout = Q1; L.taps = 3; L.pad_left = 1;
+        L.wimg = h->proj1.wimg; L.scale = h->proj1.scale; L.shift = h->proj1.shift; L.act = ACT_RELU;
+        L.y16 = q1_16; L.ld16 = Q1;
+        conv_tc_launch(L, st);
       }
-      // ---- maxpool (fused on load) + proj1 ----
-      conv_bn_act_launch(ws + o_bank, B, T, ldb, h->proj1.w, h->proj1.scale, h->proj1.shift, 3, ldb, h->proj1.cout, ACT_RELU,
-                         1, nullptr, 0, ws + o_q1, h->proj1.cout, st);
-    }
-    // ---- proj2 + residual ----
-    conv_bn_act_launch(ws + o_q1, B, T, h->proj1.cout, h->proj2.w, h->proj2.scale, h->proj2.shift, 3, h->proj1.cout,
-                       h->proj2.cout, ACT_NONE, 0, ws + o_p1, P1, ws + o_q2, h->proj2.cout, st);
-    const float* hw_in = ws + o_q2;
-    float* ping = ws + o_ha;
-    float* pong = ws + o_hb;
-    if (h->adj_w) {
-      GemmArgs g;
-      g.X = hw_in; g.Bn = 1; g.T = (int)rows; g.Cin = h->proj2.cout; g.ldx = h->proj2.cout;
-      g.W = h->adj_w; g.N = half; g.shift = h->adj_b; g.C = ping; g.ldc = half;
-      gemm_launch(g, st);
-      hw_in = ping;
-      std::swap(ping, pong);
-    }
-    for (size_t i = 0; i < h->hw_w.size(); ++i) {
-      GemmArgs g;
-      g.X = hw_in; g.Bn = 1; g.T = (int)rows; g.Cin = half; g.ldx = half;
-      g.W = h->hw_w[i]; g.N = 2 * half; g.shift = h->hw_b[i]; g.highway = 1; g.R = hw_in; g.ldr = half; g.C = ping; g.ldc = half;
-      gemm_launch(g, st);
-      hw_in = ping;
-      std::swap(ping, pong);
+      {
+        ConvTcLaunch L;  // proj2 (linear) + prenet output
+        L.xp = q1_16; L.ldxp = Q1; L.B = B; L.T = T; L.cin = Q1; L.cout = h->proj2.cout; L.taps = 3; L.pad_left = 1;
+        L.wimg = h->proj2.wimg; L.scale = h->proj2.scale; L.shift = h->proj2.shift; L.act = ACT_NONE;
+        L.res = ws + o_p1; L.ldr = P1; L.y32 = ws + o_q2; L.ld32 = h->proj2.cout; L.y16 = hw16[0]; L.ld16 = half;
+        conv_tc_launch(L, st);
+      }
+      const float* x32 = ws + o_q2;
+      float* pp[2] = {ws + o_ha, ws + o_hb};
+      int cur16 = 0;
+      for (size_t i = 0; i < h->hw_w.size(); ++i) {
+        ConvTcLaunch L;  // highway layer: gate epilogue over interleaved (H_u, T_u) columns
+        L.xp = hw16[cur16]; L.ldxp = half; L.B = B; L.T = T; L.cin = half; L.cout = 2 * half; L.taps = 1; L.pad_left = 0;
+        L.wimg = h->hw_img[i]; L.shift = h->hw_b[i]; L.highway = 1; L.res = x32; L.ldr = half;
+        L.y32 = pp[i & 1]; L.ld32 = half; L.y16 = hw16[cur16 ^ 1]; L.ld16 = half;
+        conv_tc_launch(L, st);
+        x32 = pp[i & 1];
+        cur16 ^= 1;
+      }
+      {
+        ConvTcLaunch L;  // BiLSTM input projection (bias included), gate-interleaved [rows][2][U][4]
+        L.xp = hw16[cur16]; L.ldxp = half; L.B = B; L.T = T; L.cin = half; L.cout = 8 * half; L.taps = 1; L.pad_left = 0;
+        L.wimg = h->lstm_img; L.shift = h->lstm_bx; L.act = ACT_NONE; L.y32 = ws + o_xp; L.ld32 = 8 * half;
+        conv_tc_launch(L, st);
+      }
+    } else {
+      if (h->tc) {
+        // ---- conv bank, max-pool and proj1 on the tensor cores over zero-haloed fp16 activations (conv_tc.cu) ----
+        const int Tp = T + 2 * CONV_TC_HALO;
+        const size_t R = (size_t)B * Tp;
+        const size_t n_x = R * P1, n_bank = R * (size_t)ldb;
+        __half* x16 = h->ws16.get<__half>(n_x + 2 * n_bank + 64);
+        __half* bank16 = x16 + (n_x + 7) / 8 * 8;
+        __half* pool16 = bank16 + n_bank;
+        SAT_CUDA(cudaMemsetAsync(x16, 0, (n_x + 2 * n_bank + 64) * sizeof(__half), st));
+        conv_tc_pack(ws + o_p1, P1, B, T, P1, x16, P1, st);
+        for (int k = 1; k <= KW; ++k) {
+          const Conv& c = h->bank[k - 1];
+          ConvTcLaunch L;
+          L.xp = x16; L.ldxp = P1; L.B = B; L.T = T; L.cin = P1; L.cout = Cb; L.taps = k; L.pad_left = (k - 1) / 2;
+          L.wimg = c.wimg; L.scale = c.scale; L.shift = c.shift; L.act = ACT_RELU;
+          L.y16 = bank16 + (size_t)(k - 1) * Cb; L.ld16 = ldb;
+          conv_tc_launch(L, st);
+        }
+        conv_tc_maxpool2(bank16, B, T, ldb, pool16, st);
+        ConvTcLaunch L;
+        L.xp = pool16; L.ldxp = ldb; L.B = B; L.T = T; L.cin = ldb; L.cout = h->proj1.cout; L.taps = 3; L.pad_left = 1;
+        L.wimg = h->proj1.wimg; L.scale = h->proj1.scale; L.shift = h->proj1.shift; L.act = ACT_RELU;
+        L.y32 = ws + o_q1; L.ld32 = h->proj1.cout;
+        conv_tc_launch(L, st);
+      } else {
+        // ---- conv bank -> concat buffer [rows][KW*Cb] (fp32 SIMT form) ----
+        for (int k = 1; k <= KW; ++k) {
+          const Conv& c = h->bank[k - 1];
+          conv_bn_act_launch(ws + o_p1, B, T, P1, c.w, c.scale, c.shift, k, P1, Cb, ACT_RELU, 0, nullptr, 0,
+                             ws + o_bank + (size_t)(k - 1) * Cb, ldb, st);
+        }
+        // ---- maxpool (fused on load) + proj1 ----
+        conv_bn_act_launch(ws + o_bank, B, T, ldb, h->proj1.w, h->proj1.scale, h->proj1.shift, 3, ldb, h->proj1.cout, ACT_RELU,
+                           1, nullptr, 0, ws + o_q1, h->proj1.cout, st);
+      }
+      // ---- proj2 + residual ----
+      conv_bn_act_launch(ws + o_q1, B, T, h->proj1.cout, h->proj2.w, h->proj2.scale, h->proj2.shift, 3, h->proj1.cout,
+                         h->proj2.cout, ACT_NONE, 0, ws + o_p1, P1, ws + o_q2, h->proj2.cout, st);
+      hw_in = ws + o_q2;
+      float* ping = ws + o_ha;
+      float* pong = ws + o_hb;
+      if (h->adj_w) {
+        GemmArgs g;
+        g.X = hw_in; g.Bn = 1; g.T = (int)rows; g.Cin = h->proj2.cout; g.ldx = h->proj2.cout;
+        g.W = h->adj_w; g.N = half; g.shift = h->adj_b; g.C = ping; g.ldc = half;
+        gemm_launch(g, st);
+        hw_in = ping;
+        std::swap(ping, pong);
+      }
+      for (size_t i = 0; i < h->hw_w.size(); ++i) {
+        GemmArgs g;
+        g.X = hw_in; g.Bn = 1; g.T = (int)rows; g.Cin = half; g.ldx = half;
+        g.W = h->hw_w[i]; g.N = 2 * half; g.shift = h->hw_b[i]; g.highway = 1; g.R = hw_in; g.ldr = half; g.C = ping; g.ldc = half;
+        gemm_launch(g, st);
+        hw_in = ping;
+        std::swap(ping, pong);
+      }
     }
     // ---- BiLSTM: time-batched input projection, then the recurrence ----
     {
-      GemmArgs g;
-      g.X = hw_in; g.Bn = 1; g.T = (int)rows; g.Cin = half; g.ldx = half;
-      g.W = h->lstm_wx; g.N = 8 * half; g.shift = h->lstm_bx; g.C = ws + o_xp; g.ldc = 8 * half;
-      gemm_launch(g, st);
+      if (!h->tc_full) {
+        GemmArgs g;
+        g.X = hw_in; g.Bn = 1; g.T = (int)rows; g.Cin = half; g.ldx = half;
+        g.W = h->lstm_wx; g.N = 8 * half; g.shift = h->lstm_bx; g.C = ws + o_xp; g.ldc = 8 * half;
+        gemm_launch(g, st);
+      }
       SAT_CUDA(cudaMemsetAsync(lstm_out, 0, rows * 2 * half * sizeof(float), st));
       dim3 grid((unsigned)ceil_div(B, LSTM_ROWS), 2);
       bilstm_kernel<128><<<grid, LSTM_NT, 0, st>>>(ws + o_xp, h->lstm_wh, (const long long*)lengths, B, T,
