@@ -1,0 +1,181 @@
+"""Secondary measurements (not the driver's bench contract, which is bench.py on cfg 2): the other workloads of
+BASELINE.json / SURVEY.md 8d through the public API, one JSON line per config, on 1..N GPUs of one box.
+
+    python scripts/bench_configs.py [--gpus N] [--configs cfg1,cfg3,cfg4,cfg5] [--steps K] [--warmup W]
+
+  cfg1  dual-source self-attention Tacotron, teacher-forced, B=16, T_enc=150, 800 frames / utterance (per GPU)
+  cfg3  VCTK multi-speaker model (speaker embedding -> MultiSpeakerPreNet), 1024 utterances, T_enc ~ U[50,250],
+        T_dec = 5.33 T_enc, teacher-forced, length-bucketed (sat_b200.sharding.make_buckets) into batches of <= 128 and
+        sharded over the ranks: STRONG scaling (the 1024 utterances are split over N GPUs)
+  cfg4  cfg 1 model on long utterances (T_enc=400, 2000 frames), forced-alignment mode: teacher-forced pass producing
+        alignments, then the replay pass (teacher_forcing_forward / teacher_forcing_additive), B=16 per GPU
+  cfg5  VQ-code model (1025 one-hot classes, r=1, softmax feedback, max_iters=450), free run, 512 utterances sharded
+        over the ranks in batches of 64: STRONG scaling
+
+A "step" is one pass of the whole hot path (embedding -> encoder -> decoder [-> second pass]) over the rank's share;
+frames/s counts the frames actually emitted (true target lengths, not padding).  Inputs are resident in HBM, L2 is
+flushed (256 MiB write) before every step, timing is CUDA events, max over ranks."""
+import argparse
+import json
+import os
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import numpy as np  # noqa: E402
+
+
+def make_cfg(name, rank, world):
+    """-> (hparams, list of batches, description); a batch = dict(ids, lengths, target, speaker, frames, kwargs)."""
+    import sat_b200
+    from sat_b200.sharding import make_buckets
+    rng = np.random.default_rng(12345)
+
+    def batch(hp, lengths, t_dec=None, spk=None, **kw):
+        B, T = len(lengths), int(max(lengths))
+        ids = rng.integers(1, 71, size=(B, T)).astype(np.int64)
+        ids[np.arange(T)[None, :] >= np.asarray(lengths)[:, None]] = 0
+        d = dict(ids=ids, lengths=np.asarray(lengths, dtype=np.int64), target=None, speaker=spk, kwargs=kw)
+        if t_dec is not None:
+            S = int(max(t_dec))
+            d["target"] = rng.normal(0, 1, size=(B, S, hp.num_mels)).astype(np.float32)
+            d["frames"] = int(np.sum(t_dec))
+        return d
+
+    if name == "cfg1":
+        hp = sat_b200.config("ljspeech_self_attention")
+        return hp, [batch(hp, [150] * 16, [800] * 16, is_validation=True, teacher_forcing=True)], \
+            "teacher-forced, B=16/GPU, T_enc=150, 800 frames/utterance", "weak"
+    if name == "cfg4":
+        hp = sat_b200.config("ljspeech_self_attention")
+        hp.override(max_iters=1000, use_forced_alignment_mode=True)
+        return hp, [batch(hp, [400] * 16, [2000] * 16)], \
+            "forced-alignment mode (teacher-forced pass + alignment-replay pass), B=16/GPU, T_enc=400, 2000 frames/" \
+            "utterance (frames counted once)", "weak"
+    if name == "cfg3":
+        hp = sat_b200.config("vctk_self_attention")
+        n = 1024
+        lens = rng.integers(50, 251, size=n)
+        tdec = (np.round(5.33 * lens / hp.outputs_per_step).astype(np.int64) * hp.outputs_per_step)
+        hp.override(max_iters=int(tdec.max()) // hp.outputs_per_step)
+        spk = rng.integers(hp.speaker_embedding_offset, hp.speaker_embedding_offset + hp.num_speakers, size=n)
+        shards = make_buckets(lens, 128, world, bucket_width=50)[rank]
+        return hp, [batch(hp, lens[ix], tdec[ix], spk[ix].astype(np.int64), is_validation=True, teacher_forcing=True)
+                    for ix in map(np.asarray, shards)], \
+            "teacher-forced, 1024 utterances, T_enc~U[50,250], T_dec=5.33 T_enc, length buckets of <=128 sharded over " \
+            "the GPUs", "strong"
+    if name == "cfg5":
+        hp = sat_b200.config("codes_self_attention")
+        n = 512
+        lens = rng.integers(100, 201, size=n)
+        shards = make_buckets(lens, 64, world, bucket_width=50)[rank]
+        out = []
+        for ix in map(np.asarray, shards):
+            b = batch(hp, lens[ix])
+            b["frames"] = None  # free run: counted from the steps the stop rule actually allowed (n_steps)
+            out.append(b)
+        return hp, out, "free run (softmax feedback, argmax codes), 512 utterances, T_enc~U[100,200], max_iters=450, " \
+                        "batches of <=64 sharded over the GPUs", "strong"
+    raise ValueError(name)
+
+
+def run(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    import sat_b200
+    from sat_b200.models import tacotron_model_factory
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    for name in args.configs.split(","):
+        hp, batches, desc, scaling = make_cfg(name, rank, world)
+        W = sat_b200.init_weights(hp, seed=12345)
+        if name == "cfg5":
+            # random-init stop logits are arbitrary: bias the stop projection so that the reference's all-rows stop rule
+            # (modules/helpers.py:156-160) does not fire and every utterance runs max_iters steps (cfg 2 note)
+            W = dict(W)
+            W["decoder/stop_token_projection/bias"] = np.full_like(W["decoder/stop_token_projection/bias"], -8.0)
+        model = tacotron_model_factory(hp, W)
+        dbs = []
+        for b in batches:
+            dbs.append(dict(ids=torch.from_numpy(b["ids"]).to(dev), lengths=torch.from_numpy(b["lengths"]).to(dev),
+                            target=None if b["target"] is None else torch.from_numpy(b["target"]).to(dev),
+                            speaker=None if b["speaker"] is None else torch.from_numpy(b["speaker"]).to(dev),
+                            kwargs=b["kwargs"]))
+
+        def step():
+            flush.fill_(1)
+            outs = []
+            for d in dbs:
+                outs.append(model.predict(d["ids"], d["lengths"], target=d["target"], speaker_id=d["speaker"], **d["kwargs"]))
+            return outs
+
+        def barrier():
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize()
+
+        for _ in range(args.warmup):
+            outs = step()
+        barrier()
+        assert all(bool(torch.isfinite(o["mel"]).all()) for o in outs), "non-finite output"
+        frames, steps_run = 0, []
+        for b, o in zip(batches, outs):
+            n = int(o["n_steps"])
+            steps_run.append(n)
+            frames += b["frames"] if b.get("frames") is not None else len(b["lengths"]) * n * hp.outputs_per_step
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record()
+        for _ in range(args.steps):
+            step()
+        e1.record()
+        barrier()
+        t = torch.tensor([e0.elapsed_time(e1), float(frames)], dtype=torch.float64, device=dev)
+        if world > 1:
+            tm = t[:1].clone()
+            dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+            fs = t[1:].clone()
+            dist.all_reduce(fs, op=dist.ReduceOp.SUM)
+            t = torch.cat([tm, fs])
+        ms, total = float(t[0]) / args.steps, float(t[1])
+        if rank == 0:
+            print(json.dumps({"metric": "mel_frames_per_sec", "config": {"workload": f"{name}: {desc}"},
+                              "value": total / (ms * 1e-3), "unit": "frames/s", "n_gpus": world, "scaling": scaling,
+                              "ms_per_step": ms, "frames_per_step": total, "rtf": ms * 1e-3 / (total * 0.0125),
+                              "batches_rank0": [int(d["ids"].shape[0]) for d in dbs], "decoder_steps_rank0": steps_run,
+                              "steps": args.steps, "warmup": args.warmup, "data": "synthetic"}), flush=True)
+        del model, dbs
+        torch.cuda.empty_cache()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--configs", default="cfg1,cfg3,cfg4,cfg5")
+    args = ap.parse_args()
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world == 1 and args.gpus > 1:
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", str(29500 + os.getpid() % 1000)] + sys.argv
+        sys.exit(subprocess.call(cmd))
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    try:
+        run(args, rank, world, local_rank)
+    finally:
+        if world > 1:
+            import torch.distributed as dist
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

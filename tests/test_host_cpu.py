@@ -117,6 +117,27 @@ def test_buckets_partition_every_utterance_once(n, bs, world):
         assert max(loads) <= 1.25 * min(loads)
 
 
+def test_cost_model_buckets_never_cost_more_than_fixed_width():
+    """The DP cut minimises sum(longest * (c0 + c1 * size)) over contiguous cuts of the sorted share, so it is at
+    least as cheap as the fixed-width rule on the same share; with a flat step cost it merges down to the minimum
+    number of batches, with a purely per-utterance cost it isolates nothing longer than needed."""
+    from sat_b200.sharding import STEP_US0, STEP_US1
+    rng = np.random.default_rng(7)
+    lengths = rng.integers(50, 251, size=700)
+
+    def cost(per_rank):
+        return max(sum(int(lengths[b].max()) * (STEP_US0 + STEP_US1 * len(b)) for b in r) for r in per_rank)
+    for world in (1, 3, 8):
+        dp, fixed = make_buckets(lengths, 128, world), make_buckets(lengths, 128, world, cost_model=None)
+        assert cost(dp) <= cost(fixed) + 1e-6
+        assert sorted(i for r in dp for b in r for i in b) == list(range(700))
+    flat = make_buckets(lengths, 128, 1, cost_model=(1.0, 0.0))[0]
+    assert len(flat) == -(-700 // 128)
+    lens4 = np.array([10, 10, 10, 200])
+    per_utt = make_buckets(lens4, 4, 1, cost_model=(0.0, 1.0))[0]  # the long utterance must not drag the short ones
+    assert sum(int(lens4[b].max()) * len(b) for b in per_utt) == 230 and [3] in per_utt
+
+
 def test_two_rank_gloo_shard_and_gather(tmp_path):
     """world_size-2 gloo run of the host-side sharding + output gather (the only collective of the path)."""
     script = tmp_path / "w.py"
@@ -125,7 +146,8 @@ def test_two_rank_gloo_shard_and_gather(tmp_path):
         sys.path.insert(0, {ROOT!r})
         import numpy as np, torch.distributed as dist
         import sat_b200
-        from sat_b200.sharding import make_buckets, gather_results
+        import torch
+        from sat_b200.sharding import make_buckets, gather_results, gather_mels
         dist.init_process_group("gloo")
         rank, world = dist.get_rank(), dist.get_world_size()
         lengths = np.random.default_rng(0).integers(20, 90, size=41)
@@ -136,9 +158,20 @@ def test_two_rank_gloo_shard_and_gather(tmp_path):
             assert sorted(i for i, _ in allr) == list(range(41)), allr
             assert all(v == int(lengths[i]) * 2 for i, v in allr)
             print("GATHER_OK", len(allr))
+        # tensor gather of variable-length frames (all_reduce MAX + all_gather of the padded block)
+        ids = [i for b in mine for i in b]
+        mels = [torch.full((int(lengths[i]), 5), float(i)) for i in ids]
+        got = gather_mels(ids, mels, world, rank)
+        if rank == 0:
+            assert sorted(got) == list(range(41))
+            assert all(tuple(got[i].shape) == (int(lengths[i]), 5) and bool((got[i] == float(i)).all()) for i in got)
+            print("MELS_OK", len(got))
+        else:
+            assert got is None
         dist.destroy_process_group()
     """))
     out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
                           "--master-addr", "127.0.0.1", "--master-port", "29611", str(script)],
                          capture_output=True, text=True, timeout=240)
     assert "GATHER_OK 41" in out.stdout, out.stdout + out.stderr
+    assert "MELS_OK 41" in out.stdout, out.stdout + out.stderr
