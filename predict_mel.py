@@ -1,8 +1,12 @@
 """CLI twin of /root/reference/predict_mel.py:1-15 over the CUDA hot path.
 
 Usage: predict_mel.py --hparam-json-file=<path> [--hparams=<k=v,...>] --output-dir=<path>
-                      [--weights=<npz>] [--sources=<npz>] [--source-tfrecords=<glob>] [--target-tfrecords=<glob>]
-                      [--batch-size=<n>]
+                      [--checkpoint=<prefix> | --checkpoint-dir=<dir>] [--name-map=<json>] [--weights=<npz>]
+                      [--sources=<npz>] [--source-tfrecords=<glob>] [--target-tfrecords=<glob>] [--batch-size=<n>]
+
+Weights: ``--checkpoint`` (a TensorFlow V2 checkpoint prefix) or the latest checkpoint of ``--checkpoint-dir`` as in
+predict_mel.py:47-54, read without TensorFlow by sat_b200.checkpoint (``--name-map``: JSON {checkpoint variable:
+weight name} for variables the built-in rules do not recognise); or ``--weights``, an .npz weight blob.
 
 Inputs: the reference's preprocessed source / target TFRecord files (--source-tfrecords / --target-tfrecords,
 preprocess/ljspeech.py:23-44; read without TensorFlow by sat_b200.tfrecord) or an .npz of utterances (keys
@@ -24,6 +28,9 @@ def main():
     ap.add_argument("--hparams", default="")
     ap.add_argument("--output-dir", required=True)
     ap.add_argument("--weights")
+    ap.add_argument("--checkpoint")
+    ap.add_argument("--checkpoint-dir")
+    ap.add_argument("--name-map")
     ap.add_argument("--sources")
     ap.add_argument("--source-tfrecords")
     ap.add_argument("--target-tfrecords")
@@ -34,7 +41,16 @@ def main():
         hp.parse_json(args.hparam_json_file)
     hp.parse(args.hparams)
     print(sat_b200.hparams_debug_string(hp))
-    W = dict(np.load(args.weights)) if args.weights else sat_b200.init_weights(hp)
+    if args.checkpoint or args.checkpoint_dir:
+        import json
+        from sat_b200 import checkpoint
+        prefix = args.checkpoint or checkpoint.latest_checkpoint(args.checkpoint_dir)
+        if prefix is None:
+            raise SystemExit(f"no checkpoint found in {args.checkpoint_dir}")
+        name_map = json.load(open(args.name_map)) if args.name_map else None
+        W = checkpoint.import_weights(hp, prefix, name_map=name_map)
+    else:
+        W = dict(np.load(args.weights)) if args.weights else sat_b200.init_weights(hp)
     utts = []
     if args.source_tfrecords:
         from sat_b200.predict_mel import load_utterances

@@ -7,4 +7,4 @@ library or a CUDA device is missing.
 """
 from .hparams import HParams, config, hparams_debug_string  # noqa: F401
 from .weights import init_weights, weight_shapes, decoder_param_count  # noqa: F401
-from . import modules, models, sharding, predict_mel  # noqa: F401,E402
+from . import modules, models, sharding, predict_mel, checkpoint  # noqa: F401,E402
