@@ -30,7 +30,7 @@ using namespace dec;
 
 __global__ void __launch_bounds__(NT) attention_step_kernel(AttMech m, int B, int T, const long long* lengths) {
   extern __shared__ __align__(16) float sm[];
-  for (int b = blockIdx.x; b < B; b += gridDim.x) attention_item(m, b, 0, T, (int)lengths[b], sm);
+  for (int b = blockIdx.x; b < B; b += gridDim.x) attention_item<NT>(m, b, 0, T, (int)lengths[b], sm);
 }
 
 __global__ void embedding_kernel(const float* table, long long rows, int dim, long long offset, const long long* ids,
@@ -165,6 +165,7 @@ extern "C" int sat_attention_step(const sat_tensor* weights, int32_t n_weights, 
     m.st_alpha = state_alpha; m.st_u = state_u;
     m.out_align = alignments; m.out_S = 1;
     m.ctx_dst[0] = context; m.ctx_dst[1] = nullptr; m.ctx_sd[0] = 1; m.ctx_sb[0] = Dv;
+    m.TS = dec::MAX_T; m.FB = 8 * dec::MAX_T;
     const size_t smem = dec::ATT_SMEM_FLOATS * sizeof(float);
     SAT_CUDA(cudaFuncSetAttribute(attention_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attention_step_kernel<<<B < 148 ? B : 148, dec::NT, smem, st>>>(m, B, T, (const long long*)lengths);

@@ -483,6 +483,13 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
       }
     }
     if (!use_tc) smem_bytes = smem_floats * sizeof(float);
+    // ---- attention row plan: per-position arrays sized by this batch's T; two concurrent rows per CTA when they fit ----
+    int att_TS = (T + 15) / 16 * 16, att_FB = 8 * att_TS;
+    for (int i = 0; i < h->n_mech; ++i) att_FB = std::max(att_FB, NW * hp.memory_dim[i]);
+    if (att_smem_floats(att_TS, att_FB) > (int)ATT_SMEM_FLOATS) { att_TS = MAX_T; att_FB = 8 * MAX_T; }
+    p.att_row_floats = (att_smem_floats(att_TS, att_FB) + 31) / 32 * 32;
+    p.att_pair = (att_TS < MAX_T && 2 * p.att_row_floats <= p.scratch_floats && B * h->n_mech > h->grid) ? 1 : 0;
+    if (const char* e = getenv("SAT_ATT_PAIR")) p.att_pair = p.att_pair && atoi(e) != 0;
 
     // ---- workspace carve-up (floats) ----
     size_t off = 0;
@@ -562,6 +569,7 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
       m.pq = ws + o_pq[i]; m.pq_su = 1; m.pq_sb = m.Up;  // row-major [b][Up]: one 16-byte load per lane
       m.st_align = ws + o_sal[i]; m.st_alpha = ws + o_sap[i]; m.st_u = ws + o_su[i];
       m.out_align = io.alignments[i]; m.out_S = S;
+      m.TS = att_TS; m.FB = att_FB;
       p.dq[i] = h->dq[i].desc();
       plan_rows(p.dq[i], false);
       if (kind == SAT_ATT_TEACHER_FORCING) {

@@ -55,7 +55,24 @@ struct AttMech {
   void* ctx_dst[2];     // context element (d, b) written at ctx_dst[i][d * ctx_sd[i] + b * ctx_sb[i]]; may be null
   int ctx_sd[2], ctx_sb[2];
   int ctx_f16;          // 1: the context destinations are fp16 buffers feeding tensor-core GEMMs, 0: fp32
+  // shared-memory plan of the row phase: TS = capacity of the per-position arrays (>= T, multiple of 16; MAX_T for the
+  // stand-alone entry point), FB = floats of the location-feature / context-partial buffer (>= 8 TS and >= 16 Dv)
+  int TS, FB;
 };
+
+// floats of shared memory one attention row needs for a given plan
+__host__ __device__ inline int att_smem_floats(int TS, int FB) {
+  return 5 * TS + 2 * HALO + FB + NT + MAX_DV + 64 + (TS < MAX_T ? 8 * TS : 0);
+}
+
+// A row is processed either by the whole CTA (GT = NT, CTA barrier) or, when the CTA owns two rows of the phase, by
+// one half of it (GT = NT / 2, named barrier 1 + half): the two rows then run concurrently, each stage of one hiding
+// the barrier / L2 latencies of the other, instead of back to back.
+template <int GT>
+__device__ __forceinline__ void group_sync(int gid) {
+  if (GT == NT) __syncthreads();
+  else asm volatile("bar.sync %0, %1;" ::"r"(gid + 1), "n"(GT) : "memory");
+}
 
 // exp2 / reciprocal on the MUFU pipe
 __device__ __forceinline__ float ex2_approx(float x) {
@@ -300,11 +317,12 @@ __device__ __forceinline__ float quad_recip_dot(float y0, float y1, float y2, fl
   return fmaf(nab, cd, ncd * ab) * rcp_approx(ab * cd);
 }
 
-template <int NUG>
-__device__ void attention_energies_mma(const AttMech& m, int b, int T, int len, const float* fbuf, float* epart, int Tpad) {
+template <int NUG, int GT>
+__device__ void attention_energies_mma(const AttMech& m, int b, int T, int len, const float* fbuf, float* epart, int Tpad,
+                                       int gtid) {
   constexpr float C2 = 2.8853900817779268f;  // 2 * log2(e)
-  constexpr int NRG = NW / NUG;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  constexpr int NRG = (GT / 32) / NUG;
+  const int lane = gtid & 31, warp = gtid >> 5;
   const int g = lane >> 2, t = lane & 3;
   const int ug = warp % NUG, rg = warp / NUG;
   const int ubase = 32 * ug;
@@ -452,9 +470,11 @@ __device__ void attention_context_vec(const float* __restrict__ vb, const float*
 
 // The same over an fp16 copy of the values (tensor-core mode: the context is rounded to fp16 on its way into the
 // LSTM inputs anyway, and this phase is bound by the L2 -> SM bytes): a lane owns 8 halves, Dv / 8 lanes per row.
+template <int GT>
 __device__ inline void attention_context_h8(const __half* __restrict__ vb, const float* align, int len, int Dv, float* part,
-                                            float* ctx_out /* smem [Dv] */) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+                                            float* ctx_out /* smem [Dv] */, int gtid, int gid) {
+  constexpr int NW = GT / 32;  // warps of the group (shadows the CTA-wide constant)
+  const int lane = gtid & 31, warp = gtid >> 5;
   const int lpr = Dv >> 3, G = 32 / lpr;
   const int c0 = lane % lpr, g = lane / lpr;
   float acc[8];
@@ -491,28 +511,40 @@ __device__ inline void attention_context_h8(const __half* __restrict__ vb, const
     dst[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
     dst[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
   }
-  __syncthreads();
-  for (int d = threadIdx.x; d < Dv; d += NT) {
+  group_sync<GT>(gid);
+  for (int d = gtid; d < Dv; d += GT) {
     float s = 0.f;
 #pragma unroll
     for (int w = 0; w < NW; ++w) s += part[w * Dv + d];
     ctx_out[d] = s;
   }
-  __syncthreads();
+  group_sync<GT>(gid);
 }
 
-// One (row, mechanism) item.  `sm` = ATT_SMEM_FLOATS floats of shared memory.  t = decoder step.
-__device__ inline void attention_item(const AttMech& m, int b, int t, int T, int len, float* sm) {
-  float* e = sm;                         // [MAX_T] energies -> softmax probs a
-  float* aprev = e + MAX_T;              // [MAX_T + 2*HALO]
-  float* alpha = aprev + MAX_T + 2 * HALO;  // [MAX_T]
-  float* fbuf = alpha + MAX_T;           // [MAX_T * 8] location features; later the context partials [NW * Dv]
-  float* nal = fbuf + 8 * MAX_T;         // [MAX_T] normalised forward variable
-  float* e2 = nal + MAX_T;               // [MAX_T] partial energies of units [128,256)
-  float* part = e2 + MAX_T;              // [NT] context partials of the scalar path
+// One (row, mechanism) item, processed by a group of GT threads (GT = NT: the whole CTA, gid 0; GT = NT / 2: half
+// gid of the CTA, only for the tensor-core energy form + fp16 context, no transition agent -- see att_row_pairable).
+// `sm` = att_smem_floats(m.TS, m.FB) floats of shared memory owned by the group.  t = decoder step.
+__device__ __forceinline__ bool att_row_pairable(const AttMech& m) {
+  const int C8 = m.Dv >> 3;
+  return (m.kind == SAT_ATT_FORWARD || m.kind == SAT_ATT_LOCATION_SENSITIVE) && m.F <= 7 && (m.Up == 128 || m.Up == 256) &&
+         m.TS < MAX_T && !m.agent && m.values16 && (m.Dv & 7) == 0 && (C8 & (C8 - 1)) == 0 && C8 <= 32;
+}
+
+template <int GT>
+__device__ inline void attention_item(const AttMech& m, int b, int t, int T, int len, float* sm, int gid = 0) {
+  constexpr int GW = GT / 32;
+  const int TS = m.TS;
+  float* e = sm;                         // [TS] energies -> softmax probs a
+  float* aprev = e + TS;                 // [TS + 2*HALO]
+  float* alpha = aprev + TS + 2 * HALO;  // [TS]
+  float* fbuf = alpha + TS;              // [FB] location features [TS * 8]; later the context partials [GW * Dv]
+  float* nal = fbuf + m.FB;              // [TS] normalised forward variable
+  float* e2 = nal + TS;                  // [TS] partial energies of units [128,256)
+  float* part = e2 + TS;                 // [NT] context partials of the scalar path
   float* ctxs = part + NT;               // [MAX_DV] context of this row
-  float* s32 = ctxs + MAX_DV;            // [32] block-reduce scratch
-  const int tid = threadIdx.x;
+  float* s32 = ctxs + MAX_DV;            // [64] block-reduce scratch
+  float* epart_own = s32 + 64;           // [8 * TS] per-unit-group partial energies (TS < MAX_T only)
+  const int tid = threadIdx.x - gid * GT;
   const bool loc = (m.kind == SAT_ATT_FORWARD || m.kind == SAT_ATT_LOCATION_SENSITIVE);
   const bool fwd = (m.kind == SAT_ATT_FORWARD);
   float* align = e;  // the alignments handed to the context / history
@@ -520,7 +552,7 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
   float u_prev = 0.f;
   long long tp = 0;
   int ps = 0;
-  const bool profiling = m.prof && blockIdx.x == 0 && tid == 0;
+  const bool profiling = m.prof && blockIdx.x == 0 && threadIdx.x == 0;
   if (profiling) tp = clock64();
   auto stamp = [&]() {
     if (profiling) {
@@ -534,28 +566,28 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
   if (m.kind == SAT_ATT_TEACHER_FORCING) {
     // index = prev_index + 1 = t ; alignments = teacher_alignments[:, index]
     const int ti = min(t, m.teacher_S - 1);
-    for (int j = tid; j < T; j += NT) e[j] = __ldg(m.teacher + ((size_t)b * m.teacher_S + ti) * T + j);
-    __syncthreads();
+    for (int j = tid; j < T; j += GT) e[j] = __ldg(m.teacher + ((size_t)b * m.teacher_S + ti) * T + j);
+    group_sync<GT>(gid);
   } else {
-    for (int j = tid; j < T + 2 * HALO; j += NT) {
+    for (int j = tid; j < T + 2 * HALO; j += GT) {
       const int jj = j - HALO;
       aprev[j] = (loc && jj >= 0 && jj < T) ? __ldcg(m.st_align + (size_t)b * T + jj) : 0.f;
     }
     if (fwd) {
-      for (int j = tid; j < T; j += NT) alpha[j] = __ldcg(m.st_alpha + (size_t)b * T + j);
+      for (int j = tid; j < T; j += GT) alpha[j] = __ldcg(m.st_alpha + (size_t)b * T + j);
       u_prev = __ldcg(m.st_u + b);
     }
-    __syncthreads();
+    group_sync<GT>(gid);
     stamp();
     if (loc && m.F <= 8) {
       // location features f[j][c] = b_c + sum_k w[k][c] a[j - pad + k]: a thread owns filter c = tid & 7 and four
       // consecutive positions, sliding a 4-wide register window over the taps (1 weight + 1 alignment LDS per tap)
       float* wsm = part;  // [Kc * 8] taps, zero-filled for c >= F
-      for (int i = tid; i < m.Kc * 8; i += NT) wsm[i] = (i & 7) < m.F ? __ldg(m.conv_w + (i >> 3) * m.F + (i & 7)) : 0.f;
-      __syncthreads();
+      for (int i = tid; i < m.Kc * 8; i += GT) wsm[i] = (i & 7) < m.F ? __ldg(m.conv_w + (i >> 3) * m.F + (i & 7)) : 0.f;
+      group_sync<GT>(gid);
       const int c = tid & 7;
       const float cb = c < m.F ? __ldg(m.conv_b + c) : (c == m.F ? 1.f : 0.f);  // slot F = 1: carries pq + b in the MMA form
-      for (int j0 = 4 * (tid >> 3); j0 < T; j0 += 4 * (NT / 8)) {
+      for (int j0 = 4 * (tid >> 3); j0 < T; j0 += 4 * (GT / 8)) {
         const float* a = aprev + HALO + j0 - m.pad_left;
         float f0 = cb, f1 = cb, f2 = cb, f3 = cb;
         float x0 = a[0], x1 = a[1], x2 = a[2];
@@ -574,37 +606,39 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
         if (j0 + 2 < T) fbuf[(j0 + 2) * 8 + c] = f2;
         if (j0 + 3 < T) fbuf[(j0 + 3) * 8 + c] = f3;
       }
-      __syncthreads();
+      group_sync<GT>(gid);
     }
     stamp();
     const int Tpad = (T + 15) & ~15;
     const int nug = m.Up >> 5;
-    // partial energies per 32-unit group live in the (dead) nal .. ctxs region: 3 * MAX_T floats
-    const bool use_mma = loc && m.F <= 7 && (m.Up == 128 || m.Up == 256) && nug * Tpad <= 3 * MAX_T;
-    float* epart = nal;
+    // partial energies per 32-unit group: own region, or (TS == MAX_T) the dead nal .. ctxs region of 3 * MAX_T floats
+    const bool use_mma = loc && m.F <= 7 && (m.Up == 128 || m.Up == 256) && (TS < MAX_T || nug * Tpad <= 3 * MAX_T);
+    float* epart = TS < MAX_T ? epart_own : nal;
     if (use_mma) {
-      if (m.Up == 256) attention_energies_mma<8>(m, b, T, len, fbuf, epart, Tpad);
-      else attention_energies_mma<4>(m, b, T, len, fbuf, epart, Tpad);
-    } else if (m.Up >= 128 && (!loc || m.F <= 8)) {
-      if (!loc) attention_energies_w32<0>(m, b, T, len, fbuf, e, e2);
-      else if (m.F <= 4) attention_energies_w32<4>(m, b, T, len, fbuf, e, e2);
-      else if (m.F == 5) attention_energies_w32<5>(m, b, T, len, fbuf, e, e2);
-      else attention_energies_w32<8>(m, b, T, len, fbuf, e, e2);
-    } else if (!loc) attention_energies<0>(m, b, T, len, aprev, fbuf, e, e2);
-    else if (m.F <= 4) attention_energies<4>(m, b, T, len, aprev, fbuf, e, e2);
-    else if (m.F == 5) attention_energies<5>(m, b, T, len, aprev, fbuf, e, e2);
-    else if (m.F <= 8) attention_energies<8>(m, b, T, len, aprev, fbuf, e, e2);
-    else attention_energies<-1>(m, b, T, len, aprev, fbuf, e, e2);
-    __syncthreads();
+      if (m.Up == 256) attention_energies_mma<8, GT>(m, b, T, len, fbuf, epart, Tpad, tid);
+      else attention_energies_mma<4, GT>(m, b, T, len, fbuf, epart, Tpad, tid);
+    } else if (GT == NT) {
+      if (m.Up >= 128 && (!loc || m.F <= 8)) {
+        if (!loc) attention_energies_w32<0>(m, b, T, len, fbuf, e, e2);
+        else if (m.F <= 4) attention_energies_w32<4>(m, b, T, len, fbuf, e, e2);
+        else if (m.F == 5) attention_energies_w32<5>(m, b, T, len, fbuf, e, e2);
+        else attention_energies_w32<8>(m, b, T, len, fbuf, e, e2);
+      } else if (!loc) attention_energies<0>(m, b, T, len, aprev, fbuf, e, e2);
+      else if (m.F <= 4) attention_energies<4>(m, b, T, len, aprev, fbuf, e, e2);
+      else if (m.F == 5) attention_energies<5>(m, b, T, len, aprev, fbuf, e, e2);
+      else if (m.F <= 8) attention_energies<8>(m, b, T, len, aprev, fbuf, e, e2);
+      else attention_energies<-1>(m, b, T, len, aprev, fbuf, e, e2);
+    }
+    group_sync<GT>(gid);
     stamp();
     // masked softmax (TF: softmax(where(j < len, score, -inf))), the forward-variable recursion and the state update
-    // with every element in registers (T <= 2 * NT) and one CTA barrier per reduction
-    constexpr int NJ = MAX_T / NT;
+    // with every element in registers (T <= NJ * GT) and one group barrier per reduction
+    constexpr int NJ = MAX_T / NT * (NT / GT);
     float x[NJ], pr[NJ];
     float mx = -INFINITY;
 #pragma unroll
     for (int i = 0; i < NJ; ++i) {
-      const int j = tid + i * NT;
+      const int j = tid + i * GT;
       x[i] = -INFINITY;
       if (j < len) {
         if (use_mma) {
@@ -619,24 +653,24 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
     }
     mx = warp_max(mx);
     if (lane == 0) s32[warp] = mx;
-    __syncthreads();
-    mx = warp_max(lane < NW ? s32[lane] : -INFINITY);
+    group_sync<GT>(gid);
+    mx = warp_max(lane < GW ? s32[lane] : -INFINITY);
     float sum = 0.f;
 #pragma unroll
     for (int i = 0; i < NJ; ++i) {
-      pr[i] = (tid + i * NT < len) ? expf(x[i] - mx) : 0.f;
+      pr[i] = (tid + i * GT < len) ? expf(x[i] - mx) : 0.f;
       sum += pr[i];
     }
     sum = warp_sum(sum);
     if (lane == 0) s32[NW + warp] = sum;
-    __syncthreads();
-    sum = warp_sum(lane < NW ? s32[NW + lane] : 0.f);
+    group_sync<GT>(gid);
+    sum = warp_sum(lane < GW ? s32[NW + lane] : 0.f);
     ps = 6;
     stamp();
     const float inv_sum = 1.f / sum;
 #pragma unroll
     for (int i = 0; i < NJ; ++i) {
-      const int j = tid + i * NT;
+      const int j = tid + i * GT;
       pr[i] = pr[i] * inv_sum;
       if (j < T) {
         e[j] = pr[i];
@@ -648,7 +682,7 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
       float val[NJ], s2 = 0.f;
 #pragma unroll
       for (int i = 0; i < NJ; ++i) {
-        const int j = tid + i * NT;
+        const int j = tid + i * GT;
         val[i] = 0.f;
         if (j < T) {
           const float sh = j > 0 ? alpha[j - 1] : 0.f;
@@ -658,12 +692,12 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
       }
       s2 = warp_sum(s2);
       if (lane == 0) s32[2 * NW + warp] = s2;
-      __syncthreads();
-      s2 = warp_sum(lane < NW ? s32[2 * NW + lane] : 0.f);
+      group_sync<GT>(gid);
+      s2 = warp_sum(lane < GW ? s32[2 * NW + lane] : 0.f);
       const float inv_s2 = 1.f / s2;
 #pragma unroll
       for (int i = 0; i < NJ; ++i) {
-        const int j = tid + i * NT;
+        const int j = tid + i * GT;
         if (j < T) {
           const float a = val[i] * inv_s2;
           nal[j] = a;
@@ -672,12 +706,12 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
       }
       align = nal;
     }
-    __syncthreads();
+    group_sync<GT>(gid);
     ps = 7;
     stamp();
   }
   if (m.out_align)
-    for (int j = tid; j < T; j += NT) m.out_align[((size_t)b * m.out_S + t) * T + j] = align[j];
+    for (int j = tid; j < T; j += GT) m.out_align[((size_t)b * m.out_S + t) * T + j] = align[j];
   ps = 3;
   stamp();
 
@@ -687,31 +721,33 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
   const bool vec = (Dv & 3) == 0 && (Cq & (Cq - 1)) == 0 && Cq <= 128 && ((((size_t)vb) & 15) == 0);
   const int C8 = Dv >> 3;
   if (m.values16 && (Dv & 7) == 0 && (C8 & (C8 - 1)) == 0 && C8 <= 32) {
-    attention_context_h8(m.values16 + (size_t)b * T * Dv, align, len, Dv, fbuf, ctxs);
-  } else if (vec) {
-    float* cpart = fbuf;  // location features are dead by now
-    if (Cq <= 32) attention_context_vec<1>(vb, align, len, Dv, cpart, ctxs);
-    else if (Cq == 64) attention_context_vec<2>(vb, align, len, Dv, cpart, ctxs);
-    else attention_context_vec<4>(vb, align, len, Dv, cpart, ctxs);
-  } else {
-    const int G = max(1, NT / Dv);
-    const int d = tid % Dv, grp = tid / Dv;
-    float c = 0.f;
-    if (grp < G && tid < G * Dv) {
+    attention_context_h8<GT>(m.values16 + (size_t)b * T * Dv, align, len, Dv, fbuf, ctxs, tid, gid);
+  } else if (GT == NT) {
+    if (vec) {
+      float* cpart = fbuf;  // location features are dead by now
+      if (Cq <= 32) attention_context_vec<1>(vb, align, len, Dv, cpart, ctxs);
+      else if (Cq == 64) attention_context_vec<2>(vb, align, len, Dv, cpart, ctxs);
+      else attention_context_vec<4>(vb, align, len, Dv, cpart, ctxs);
+    } else {
+      const int G = max(1, NT / Dv);
+      const int d = tid % Dv, grp = tid / Dv;
+      float c = 0.f;
+      if (grp < G && tid < G * Dv) {
 #pragma unroll 4
-      for (int j = grp; j < len; j += G) c = fmaf(align[j], __ldg(vb + (size_t)j * Dv + d), c);
+        for (int j = grp; j < len; j += G) c = fmaf(align[j], __ldg(vb + (size_t)j * Dv + d), c);
+      }
+      part[tid] = c;
+      __syncthreads();
+      if (tid < Dv) {
+        float ctx = 0.f;
+        for (int g = 0; g < G; ++g) ctx += part[g * Dv + tid];
+        ctxs[tid] = ctx;
+      }
+      __syncthreads();
     }
-    part[tid] = c;
-    __syncthreads();
-    if (tid < Dv) {
-      float ctx = 0.f;
-      for (int g = 0; g < G; ++g) ctx += part[g * Dv + tid];
-      ctxs[tid] = ctx;
-    }
-    __syncthreads();
   }
   stamp();
-  for (int d = tid; d < Dv; d += NT) {
+  for (int d = tid; d < Dv; d += GT) {
     const float ctx = ctxs[d];
 #pragma unroll
     for (int i = 0; i < 2; ++i)
@@ -721,7 +757,7 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
         else ((float*)m.ctx_dst[i])[o] = ctx;
       }
   }
-  if (fwd && m.agent) {
+  if (GT == NT && fwd && m.agent) {
     // u = sigmoid([context, processed_query] . Wt + bt)   forward_attention.py:111-114
     float z = 0.f;
     for (int d = tid; d < Dv; d += NT) z = fmaf(ctxs[d], __ldg(m.Wt + d), z);
@@ -730,7 +766,7 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
     z = block_sum(z, s32);
     if (tid == 0) m.st_u[b] = sigmoidf_(z + m.bt);
   }
-  __syncthreads();
+  group_sync<GT>(gid);
   stamp();
 }
 

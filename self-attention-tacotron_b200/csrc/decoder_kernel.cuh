@@ -60,6 +60,8 @@ struct DecParams {
   TcLstmDesc tc_a, tc_1, tc_2;
   const CUtensorMap* maps;  // [6]: att_in[0,1], l1_in[0,1], l2_in[0,1]
   float* qfm;               // feature-major copy of the attention-LSTM output (query) for the SIMT query layers
+  int att_pair;             // 1: a CTA that owns two rows of the attention phase runs them concurrently, one per half
+  int att_row_floats;       // shared-memory floats of one attention row (second row of a pair starts there)
 };
 
 struct DenseEpi {
@@ -556,9 +558,9 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
           }
           __syncthreads();
         }
-        for (int q = 0; q < nit; ++q) {
-          const int b = items[q] / p.n_mech, mi = items[q] % p.n_mech;
-          AttMech m = p.mech[mi];
+        auto setup = [&](int item, AttMech& m) {
+          const int mi = item % p.n_mech;
+          m = p.mech[mi];
           const int coff = mi ? p.mech[0].Dv : 0;
           if (p.tc) {
             m.ctx_dst[0] = (__half*)p.att_in[nxt] + p.P1 + coff;
@@ -575,7 +577,22 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
             m.ctx_sb[0] = m.ctx_sb[1] = 1;
           }
           m.prof = p.prof ? p.prof + 16 : nullptr;
-          attention_item(m, b, t, p.T, (int)p.lengths[b], scratch);
+        };
+        if (p.att_pair && pair && att_row_pairable(p.mech[mi0])) {
+          // two rows of the same mechanism: one per half of the CTA, concurrently (named barriers 1 / 2)
+          const int gid = tid / (NT / 2);
+          AttMech m;
+          setup(items[gid], m);
+          const int b = items[gid] / p.n_mech;
+          attention_item<NT / 2>(m, b, t, p.T, (int)p.lengths[b], scratch + gid * p.att_row_floats, gid);
+          __syncthreads();  // both halves are done with the scratch
+        } else {
+          for (int q = 0; q < nit; ++q) {
+            AttMech m;
+            setup(items[q], m);
+            const int b = items[q] / p.n_mech;
+            attention_item<NT>(m, b, t, p.T, (int)p.lengths[b], scratch);
+          }
         }
       }
     }
