@@ -107,6 +107,27 @@ def test_tensor_core_gate_gemms_full_dims(name, B, T, S):
     print("tensor-core path rel err", name, B, errs)
 
 
+@pytest.mark.parametrize("name,B,T", [("ljspeech_tacotron", 256, 53), ("ljspeech_tacotron", 149, 200),
+                                      ("ljspeech_self_attention", 128, 77)])
+def test_attention_rows_paired_and_sequential(name, B, T, monkeypatch):
+    """More attention items than CTAs: a CTA runs its two rows concurrently, one per half (named barriers,
+    per-batch shared-memory plan); SAT_ATT_PAIR=0 runs them back to back on the whole CTA.  Both forms meet the
+    oracle bar on ragged lengths, a T that is not a multiple of 16 and an odd number of second rows."""
+    hp = small_hp(name)
+    W = sat_b200.init_weights(hp, seed=5, stress=True)
+    S = 5
+    mems, lengths, target, _ = decoder_inputs(hp, B, T, S, seed=5)
+    ref = oracle_decoder(hp, W, mems, lengths, target=target, is_validation=True, teacher_forcing=True)
+    outs = []
+    for pair in ("1", "0"):
+        monkeypatch.setenv("SAT_ATT_PAIR", pair)
+        got = run_cuda(hp, W, mems, lengths, target=target, feed_mode=0, stop_mode=0, max_steps=S)
+        assert got["tensor_cores"]
+        check_close(got, ref)
+        outs.append(got)
+    assert rel_err(outs[0]["alignments"][0], outs[1]["alignments"][0]) <= 1e-4
+
+
 def test_small_batch_uses_fp32_simt():
     hp = small_hp("ljspeech_tacotron", **SMALL)
     W = sat_b200.init_weights(hp, seed=1)
