@@ -221,7 +221,8 @@ mha_tc_kernel(const float* __restrict__ qkv, int T, int Tp, int D, int H, int ca
       const float p1 = c0 + k + 1 < nvalid ? expf(v[k + 1] - mx) * inv : (c0 + k + 1 < nk ? 0.f * inv : 0.f);
       v[k] = p0;
       v[k + 1] = p1;
-      ph[k >> 1] = __halves2half2(tc::to_f16(p0), tc::to_f16(p1));
+      // fully masked row: NaN probabilities (reference: 0/0), zero P operand, NaN context row written at the end
+      ph[k >> 1] = __halves2half2(tc::to_f16(c0 + k < nvalid ? p0 : 0.f), tc::to_f16(c0 + k + 1 < nvalid ? p1 : 0.f));
     }
     uint8_t* pc = P + (size_t)(c0 >> 6) * 16384;
     *(uint4*)(pc + tc::sw128_offset16(tid, c0 & 63)) = *(const uint4*)&ph[0];
@@ -254,6 +255,9 @@ mha_tc_kernel(const float* __restrict__ qkv, int T, int Tp, int D, int H, int ca
   for (int d0 = 0; d0 < dh; d0 += 16) {
     float v[16];
     tc::tmem_ld16(lane_addr + 256 + d0, v);
+    if (nvalid == 0)
+#pragma unroll
+      for (int k = 0; k < 16; ++k) v[k] = __int_as_float(0x7fc00000);
     if (qi < T) {
       float4* out = (float4*)(ctx + ((size_t)b * T + qi) * D + (size_t)h * dh + d0);
 #pragma unroll
@@ -263,6 +267,216 @@ mha_tc_kernel(const float* __restrict__ qkv, int T, int Tp, int D, int H, int ca
   tc::tc_fence_before();
   __syncthreads();
   if (warp == 0) tc::tmem_dealloc(tmem, 512);
+}
+
+// ---- tensor-core form for long sequences and wide heads (decoder self-attention of the teacher-forced form:
+// S up to max_iters, dh = 128): any T, dh a multiple of 16 up to 128.  One CTA = one (batch row, head, 128-query tile),
+// one thread = one query row = one TMEM lane.  The keys are visited in chunks of 64, twice (the probabilities are an
+// output of the layer, so they must be normalised when they are written):
+//   pass 1  S = Q K_c^T (hi/lo fp16 split, 3 MMAs per K-step) -> running row maximum and sum (online softmax);
+//   pass 2  S again, p = exp(s - max) / sum: written to `probs` (optional), stored as the fp16 A operand, and
+//           O += P V_c (V as hi + lo) accumulates in TMEM without any rescaling.
+// With the subsequent mask only the chunks up to the tile's last query are visited.
+constexpr int MF_THREADS = 128;
+constexpr int MF_KEYS = 64;
+
+__global__ void __launch_bounds__(MF_THREADS, 1)
+mha_flash_tc_kernel(const float* __restrict__ qkv, int T, int D, int H, int causal, const long long* __restrict__ lengths,
+                    float* __restrict__ ctx, float* __restrict__ probs, int head_major) {
+  extern __shared__ __align__(1024) uint8_t mf_smem[];
+  uint8_t* base = (uint8_t*)(((uintptr_t)mf_smem + 1023) & ~(uintptr_t)1023);
+  const int dh = D / H, nkc = (dh + 63) / 64;  // 64-wide chunks of the head dimension
+  uint8_t* Qh = base;                          // nkc x [128 rows][128 B]
+  uint8_t* Ql = Qh + (size_t)nkc * 16384;
+  uint8_t* Kh = Ql + (size_t)nkc * 16384;      // nkc x [64 keys][128 B]
+  uint8_t* Kl = Kh + (size_t)nkc * 8192;
+  uint8_t* Vh = Kl + (size_t)nkc * 8192;       // V^T: [dh rows][64 keys] (16 KB reserved)
+  uint8_t* Vl = Vh + 16384;
+  uint8_t* P = Vl + 16384;                     // [128 rows][64 keys]
+  __shared__ __align__(8) uint64_t bars[2];
+  __shared__ uint32_t tmem_slot;
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int b = blockIdx.y / H, h = blockIdx.y % H, q0 = blockIdx.x * 128;
+  const size_t ld = 3 * (size_t)D;
+  const float* src = qkv + (size_t)b * T * ld + (size_t)h * dh;
+  const float scale = 1.f / sqrtf((float)dh);
+
+  if (tid == 0) {
+    tc::mbar_init(bars, 1);
+    tc::mbar_init(bars + 1, 1);
+    tc::fence_mbar_init();
+  }
+  if (warp == 0) tc::tmem_alloc(&tmem_slot, 256);
+  auto split_store = [](uint8_t* hi, uint8_t* lo, uint32_t off, float x) {
+    const __half xh = tc::to_f16(x);
+    *(__half*)(hi + off) = xh;
+    *(__half*)(lo + off) = tc::to_f16(x - __half2float(xh));
+  };
+  for (int i = tid; i < 128 * dh; i += MF_THREADS) {
+    const int r = i / dh, d = i - r * dh;
+    const float x = (q0 + r < T) ? __ldg(src + (size_t)(q0 + r) * ld + 2 * D + d) * scale : 0.f;
+    split_store(Qh, Ql, (uint32_t)((d >> 6) * 16384) + tc::sw128_offset16(r, d & 63), x);
+  }
+  tc::fence_proxy_async();
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem = tmem_slot, tmem_o = tmem + 64;
+  const uint32_t lane_addr = tmem + ((uint32_t)(warp * 32) << 16);
+
+  const int qi = q0 + tid;
+  const int len = lengths ? (int)lengths[b] : T;
+  const int nk = causal ? min(qi + 1, T) : T;
+  const int nvalid = (qi < len || !lengths) ? min(nk, len) : 0;  // keys j < nvalid take part
+  const int kmax = causal ? min(q0 + 128, T) : T;                // keys any row of this tile can see
+  const int nchunks = (kmax + MF_KEYS - 1) / MF_KEYS;
+  uint32_t ph0 = 0, ph1 = 0;
+
+  auto load_keys = [&](int c, bool with_values) {
+    for (int i = tid; i < MF_KEYS * dh; i += MF_THREADS) {
+      const int j = i / dh, d = i - j * dh, kj = c * MF_KEYS + j;
+      const bool ok = kj < T;
+      split_store(Kh, Kl, (uint32_t)((d >> 6) * 8192) + tc::sw128_offset16(j, d & 63), ok ? __ldg(src + (size_t)kj * ld + d) : 0.f);
+      if (with_values) split_store(Vh, Vl, tc::sw128_offset16(d, j), ok ? __ldg(src + (size_t)kj * ld + D + d) : 0.f);
+    }
+    tc::fence_proxy_async();
+    tc::tc_fence_before();
+    __syncthreads();
+    tc::tc_fence_after();
+  };
+  auto scores = [&]() {  // S[128 x 64] = Q K_c^T into TMEM columns [0, 64)
+    if (tid == 0) {
+      const uint32_t idesc = tc::idesc_f16(128, MF_KEYS);
+      bool first = true;
+      for (int ks = 0; ks < dh / 16; ++ks) {
+        const uint32_t qo = (uint32_t)((ks >> 2) * 16384 + (ks & 3) * 32), ko = (uint32_t)((ks >> 2) * 8192 + (ks & 3) * 32);
+        tc::mma_f16(tmem, tc::smem_desc_sw128(tc::smem_u32(Ql) + qo), tc::smem_desc_sw128(tc::smem_u32(Kh) + ko), idesc, !first);
+        first = false;
+        tc::mma_f16(tmem, tc::smem_desc_sw128(tc::smem_u32(Qh) + qo), tc::smem_desc_sw128(tc::smem_u32(Kl) + ko), idesc, 1);
+        tc::mma_f16(tmem, tc::smem_desc_sw128(tc::smem_u32(Qh) + qo), tc::smem_desc_sw128(tc::smem_u32(Kh) + ko), idesc, 1);
+      }
+      tc::mma_commit(bars);
+    }
+    __syncwarp();
+    tc::mbar_wait(bars, ph0);
+    ph0 ^= 1;
+    tc::tc_fence_after();
+  };
+
+  // ---- pass 1: running maximum and sum of this thread's row ----
+  float mx = -INFINITY, sum = 0.f;
+  for (int c = 0; c < nchunks; ++c) {
+    load_keys(c, false);
+    scores();
+    const int k0 = c * MF_KEYS;
+    float cm = -INFINITY;
+    float v[MF_KEYS];
+#pragma unroll
+    for (int c0 = 0; c0 < MF_KEYS; c0 += 16) tc::tmem_ld16(lane_addr + c0, v + c0);
+#pragma unroll
+    for (int k = 0; k < MF_KEYS; ++k)
+      if (k0 + k < nvalid) cm = fmaxf(cm, v[k]);
+    if (cm > -INFINITY) {
+      const float mn = fmaxf(mx, cm);
+      float part = 0.f;
+#pragma unroll
+      for (int k = 0; k < MF_KEYS; ++k)
+        if (k0 + k < nvalid) part += expf(v[k] - mn);
+      sum = sum * expf(mx - mn) + part;  // expf(-inf) = 0 for the first valid chunk
+      mx = mn;
+    }
+    tc::tc_fence_before();  // this thread's TMEM reads precede the next chunk's MMAs (ordered by the barrier in load_keys)
+  }
+  if (mx == -INFINITY) mx = 0.f;  // fully masked row: 0/0 = NaN like the reference
+  const float inv = 1.f / sum;
+  float* pr = nullptr;
+  if (probs && qi < T)
+    pr = probs + ((head_major ? (size_t)h * (gridDim.y / H) + b : (size_t)b * H + h) * T + qi) * T;
+  const bool vec4 = (T & 3) == 0;
+
+  // ---- pass 2: normalised probabilities and O += P V ----
+  for (int c = 0; c < nchunks; ++c) {
+    load_keys(c, true);
+    scores();
+    const int k0 = c * MF_KEYS;
+#pragma unroll
+    for (int c0 = 0; c0 < MF_KEYS; c0 += 16) {
+      float v[16];
+      tc::tmem_ld16(lane_addr + c0, v);
+      __half2 ph[8];
+#pragma unroll
+      for (int k = 0; k < 16; k += 2) {
+        const int j = k0 + c0 + k;
+        const float p0 = j < nvalid ? expf(v[k] - mx) * inv : (j < nk ? 0.f * inv : 0.f);
+        const float p1 = j + 1 < nvalid ? expf(v[k + 1] - mx) * inv : (j + 1 < nk ? 0.f * inv : 0.f);
+        v[k] = p0;
+        v[k + 1] = p1;
+        // a fully masked row is NaN in the reference (0/0): its probabilities are written as such, its P operand is
+        // zero and its context row is set to NaN at the end (fp16 conversion would turn the NaN into a finite value)
+        ph[k >> 1] = __halves2half2(tc::to_f16(j < nvalid ? p0 : 0.f), tc::to_f16(j + 1 < nvalid ? p1 : 0.f));
+      }
+      *(uint4*)(P + tc::sw128_offset16(tid, c0)) = *(const uint4*)&ph[0];
+      *(uint4*)(P + tc::sw128_offset16(tid, c0 + 8)) = *(const uint4*)&ph[4];
+      if (pr) {
+        if (vec4) {
+#pragma unroll
+          for (int k = 0; k < 16; k += 4)
+            if (k0 + c0 + k < T) *(float4*)(pr + k0 + c0 + k) = make_float4(v[k], v[k + 1], v[k + 2], v[k + 3]);
+        } else {
+#pragma unroll
+          for (int k = 0; k < 16; ++k)
+            if (k0 + c0 + k < T) pr[k0 + c0 + k] = v[k];
+        }
+      }
+    }
+    tc::fence_proxy_async();
+    tc::tc_fence_before();
+    __syncthreads();
+    tc::tc_fence_after();
+    if (tid == 0) {
+      const uint32_t idesc = tc::idesc_f16(128, dh);
+      for (int ks = 0; ks < MF_KEYS / 16; ++ks) {
+        const uint32_t pa = tc::smem_u32(P) + ks * 32, vo = (uint32_t)(ks * 32);
+        tc::mma_f16(tmem_o, tc::smem_desc_sw128(pa), tc::smem_desc_sw128(tc::smem_u32(Vl) + vo), idesc, (c > 0 || ks > 0) ? 1 : 0);
+        tc::mma_f16(tmem_o, tc::smem_desc_sw128(pa), tc::smem_desc_sw128(tc::smem_u32(Vh) + vo), idesc, 1);
+      }
+      tc::mma_commit(bars + 1);
+    }
+    __syncwarp();
+    tc::mbar_wait(bars + 1, ph1);  // P, V (and K) may be overwritten by the next chunk
+    ph1 ^= 1;
+    tc::tc_fence_after();
+  }
+  // causal tiles never look past kmax: the probabilities of the remaining keys are zero
+  if (pr)
+    for (int j = nchunks * MF_KEYS; j < T; ++j) pr[j] = 0.f;
+  const uint32_t lane_o = tmem_o + ((uint32_t)(warp * 32) << 16);
+  for (int d0 = 0; d0 < dh; d0 += 16) {
+    float v[16];
+    tc::tmem_ld16(lane_o + d0, v);
+    if (nvalid == 0)
+#pragma unroll
+      for (int k = 0; k < 16; ++k) v[k] = __int_as_float(0x7fc00000);
+    if (qi < T) {
+      float4* out = (float4*)(ctx + ((size_t)b * T + qi) * D + (size_t)h * dh + d0);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) out[k] = make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+    }
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tc::tmem_dealloc(tmem, 256);
+}
+
+size_t mha_flash_smem_bytes(int dh) {
+  const size_t nkc = (dh + 63) / 64;
+  return 1024 + 2 * nkc * 16384 + 2 * nkc * 8192 + 2 * 16384 + 16384;
+}
+bool mha_flash_ok(int T, int D, int H) {
+  const int dh = D / H;
+  if (const char* e = getenv("SAT_MHA_TC"))
+    if (atoi(e) == 0) return false;
+  return T >= 1 && dh % 16 == 0 && dh <= 128 && D % 4 == 0;
 }
 
 size_t mha_tc_smem_bytes(int Tp, int dh) {
@@ -320,6 +534,16 @@ static void attention_core(const MhaDev& m, const float* x, int B, int T, int ca
                                                   head_major);
     count_launch();
     check_launch("mha_tc_kernel");
+    return;
+  }
+  if (mha_flash_ok(T, m.D, m.H)) {
+    const size_t smem = mha_flash_smem_bytes(dh);
+    SAT_CUDA(cudaFuncSetAttribute(mha_flash_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dim3 grid((unsigned)ceil_div(T, 128), (unsigned)(B * m.H));
+    mha_flash_tc_kernel<<<grid, MF_THREADS, smem, st>>>(qkv, T, m.D, m.H, causal, (const long long*)pad_lengths, ctx, probs,
+                                                        head_major);
+    count_launch();
+    check_launch("mha_flash_tc_kernel");
     return;
   }
   const size_t smem = (size_t)MHA_WARPS * (Tpad + dh) * sizeof(float);

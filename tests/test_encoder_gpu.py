@@ -104,10 +104,12 @@ def test_encoder_two_hops_and_adjustment_free_dims():
 
 @pytest.mark.parametrize("tc", ["1", "0"])
 @pytest.mark.parametrize("D,H,T,causal", [(32, 2, 17, False), (32, 2, 40, True), (256, 2, 33, True), (24, 3, 9, False),
-                                           (12, 2, 7, True), (32, 2, 150, False), (128, 2, 200, True), (96, 2, 256, False)])
+                                           (12, 2, 7, True), (32, 2, 150, False), (128, 2, 200, True), (96, 2, 256, False),
+                                           (256, 2, 400, True), (256, 2, 130, False), (64, 2, 300, True), (192, 2, 257, False)])
 def test_self_attention_module(D, H, T, causal, tc, monkeypatch):
     """modules/self_attention.py:131-144 through the SelfAttention mirror.  Head sizes 16..64 with T <= 256 take the
-    tcgen05 / TMEM kernel (SAT_MHA_TC=0 forces the SIMT kernel); the others always run the SIMT kernel."""
+    single-tile tcgen05 / TMEM kernel, longer sequences and heads up to 128 (the decoder's self-attention) the
+    two-pass flash-style tcgen05 kernel (SAT_MHA_TC=0 forces the SIMT kernel); other head sizes run the SIMT kernel."""
     from sat_b200.modules import SelfAttention
     monkeypatch.setenv("SAT_MHA_TC", tc)
     rng = np.random.default_rng(D + T)
@@ -127,18 +129,18 @@ def test_self_attention_module(D, H, T, causal, tc, monkeypatch):
         assert rel_err(aligns[i].cpu().numpy(), ref_p[:, i]) <= TOL
 
 
-def test_self_attention_padding_mask():
+@pytest.mark.parametrize("D,H,T", [(16, 2, 11), (32, 2, 300), (256, 2, 70)])
+def test_self_attention_padding_mask(D, H, T):
     """use_padding_mask=True (:67-78): rows/columns past the length are -inf; fully masked rows are NaN in the
-    reference, so only the valid block is compared."""
+    reference, so only the valid block is compared.  (SIMT, and both tensor-core kernels.)"""
     from sat_b200.modules import SelfAttention
     rng = np.random.default_rng(5)
-    D, H, T = 16, 2, 11
     W = {}
     for n in ("key", "value", "query", "output"):
         W[f"sa/{n}/kernel"] = rng.normal(0, 0.3, size=(D, D)).astype(np.float32)
         W[f"sa/{n}/bias"] = rng.normal(0, 0.1, size=(D,)).astype(np.float32)
     x = rng.normal(0, 1, size=(2, T, D)).astype(np.float32)
-    lengths = np.array([11, 6], dtype=np.int64)
+    lengths = np.array([T, T // 2 + 1], dtype=np.int64)
     w64 = {n: (W[f"sa/{n}/kernel"].astype(np.float64), W[f"sa/{n}/bias"].astype(np.float64))
            for n in ("key", "value", "query", "output")}
     with np.errstate(invalid="ignore"):
