@@ -20,58 +20,72 @@ namespace sat {
 namespace {
 
 constexpr int LSTM_NT = 512;
-constexpr int LSTM_ROWS = 4;  // sequences per CTA
 
 __device__ __forceinline__ float sigm(float x) { return 1.f / (1.f + expf(-x)); }
 
 // xproj [B][T][2][U][4] (bias included); Wh [2][U(k)][U][4]; out [B][T][2U] (fw | bw), zero past the length.
-// grid = (ceil(B / LSTM_ROWS), 2).  Thread (u, kpart): partial gate sums of unit u over k in its quarter.
-template <int U>
-__global__ void __launch_bounds__(LSTM_NT) bilstm_kernel(const float* __restrict__ xproj, const float* __restrict__ Wh,
-                                                         const long long* __restrict__ lengths, int B, int T,
-                                                         float zc, float zh, float* __restrict__ out) {
+// grid = (ceil(B / ROWS), 2).  Thread (u, kpart): partial gate sums of unit u over k in its quarter.
+// The recurrent weights of the direction (U x U x 4 fp32 = 256 KB at U = 128 -- the whole register file, or more
+// than the shared memory of an SM) stay ON the SM for all T steps, split between the two: every thread keeps the
+// float4 gate weights of half of its k values in registers (16 x 4 = 64 registers) and the other half in shared
+// memory (W_s[kk][thread], 128 KB, conflict-free 16-byte reads), so a step reads nothing from L2 but the input
+// projection of its position.  ROWS = sequences per CTA (1 / 2 / 4: small batches spread over more SMs).
+template <int U, int ROWS>
+__global__ void __launch_bounds__(LSTM_NT, 1) bilstm_kernel(const float* __restrict__ xproj, const float* __restrict__ Wh,
+                                                            const long long* __restrict__ lengths, int B, int T,
+                                                            float zc, float zh, float* __restrict__ out) {
   constexpr int KP = LSTM_NT / U;  // k partitions
   constexpr int KQ = U / KP;       // k values per partition
-  __shared__ __align__(16) float h_s[LSTM_ROWS][U];
-  __shared__ __align__(16) float part[KP][LSTM_ROWS][U][4];
+  constexpr int KR = KQ / 2;       // ... of which in registers; the rest in shared memory
+  extern __shared__ __align__(16) float lstm_smem[];
+  float4* W_s = (float4*)lstm_smem;                                     // [KQ - KR][LSTM_NT]
+  float (*part)[ROWS][U][4] = (float (*)[ROWS][U][4])(lstm_smem + (size_t)(KQ - KR) * LSTM_NT * 4);  // [KP]
+  float (*h_s)[U] = (float (*)[U])(lstm_smem + (size_t)(KQ - KR) * LSTM_NT * 4 + (size_t)KP * ROWS * U * 4);  // [ROWS]
   const int tid = threadIdx.x, u = tid % U, kp = tid / U;
-  const int dir = blockIdx.y, b0 = blockIdx.x * LSTM_ROWS;
+  const int dir = blockIdx.y, b0 = blockIdx.x * ROWS;
   const float4* W4 = (const float4*)(Wh + (size_t)dir * U * U * 4);
+  float4 w_reg[KR];
+#pragma unroll
+  for (int kk = 0; kk < KR; ++kk) w_reg[kk] = __ldg(W4 + (size_t)(kp * KQ + kk) * U + u);
+#pragma unroll
+  for (int kk = KR; kk < KQ; ++kk) W_s[(size_t)(kk - KR) * LSTM_NT + tid] = __ldg(W4 + (size_t)(kp * KQ + kk) * U + u);
   int maxlen = 0;
 #pragma unroll
-  for (int r = 0; r < LSTM_ROWS; ++r)
+  for (int r = 0; r < ROWS; ++r)
     maxlen = max(maxlen, (b0 + r < B) ? min((int)lengths[b0 + r], T) : 0);
-  for (int i = tid; i < LSTM_ROWS * U; i += LSTM_NT) (&h_s[0][0])[i] = 0.f;
+  for (int i = tid; i < ROWS * U; i += LSTM_NT) (&h_s[0][0])[i] = 0.f;
   // the thread that finalises (row r, unit u) keeps that cell's c and zoned h in registers
   float c_reg = 0.f, h_reg = 0.f;
-  const int fr = kp;  // finalising thread of row r has kp == r (needs KP >= LSTM_ROWS)
-  static_assert(KP >= LSTM_ROWS, "one finalising k-partition per row");
-  const int my_len = (fr < LSTM_ROWS && b0 + fr < B) ? min((int)lengths[b0 + fr], T) : 0;
+  const int fr = kp;  // finalising thread of row r has kp == r (needs KP >= ROWS)
+  static_assert(KP >= ROWS, "one finalising k-partition per row");
+  const int my_len = (fr < ROWS && b0 + fr < B) ? min((int)lengths[b0 + fr], T) : 0;
   __syncthreads();
   for (int s = 0; s < maxlen; ++s) {
-    float acc[LSTM_ROWS][4];
+    // the input projection of this step's position does not depend on the recurrence: request it first
+    float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+    const int pos = dir == 0 ? s : my_len - 1 - s;  // backward direction walks the row reversed by its own length
+    if (s < my_len) g = __ldg((const float4*)(xproj + ((((size_t)(b0 + fr) * T + pos) * 2 + dir) * U + u) * 4));
+    float acc[ROWS][4];
 #pragma unroll
-    for (int r = 0; r < LSTM_ROWS; ++r)
+    for (int r = 0; r < ROWS; ++r)
 #pragma unroll
-      for (int g = 0; g < 4; ++g) acc[r][g] = 0.f;
-#pragma unroll 4
+      for (int q = 0; q < 4; ++q) acc[r][q] = 0.f;
+#pragma unroll
     for (int kk = 0; kk < KQ; ++kk) {
       const int k = kp * KQ + kk;
-      const float4 w = __ldg(W4 + (size_t)k * U + u);
+      const float4 w = kk < KR ? w_reg[kk < KR ? kk : 0] : W_s[(size_t)(kk < KR ? 0 : kk - KR) * LSTM_NT + tid];
 #pragma unroll
-      for (int r = 0; r < LSTM_ROWS; ++r) {
+      for (int r = 0; r < ROWS; ++r) {
         const float hv = h_s[r][k];
         acc[r][0] = fmaf(hv, w.x, acc[r][0]); acc[r][1] = fmaf(hv, w.y, acc[r][1]);
         acc[r][2] = fmaf(hv, w.z, acc[r][2]); acc[r][3] = fmaf(hv, w.w, acc[r][3]);
       }
     }
 #pragma unroll
-    for (int r = 0; r < LSTM_ROWS; ++r) *(float4*)part[kp][r][u] = make_float4(acc[r][0], acc[r][1], acc[r][2], acc[r][3]);
+    for (int r = 0; r < ROWS; ++r) *(float4*)part[kp][r][u] = make_float4(acc[r][0], acc[r][1], acc[r][2], acc[r][3]);
     __syncthreads();
     if (s < my_len) {
       const int r = fr, b = b0 + r;
-      const int pos = dir == 0 ? s : my_len - 1 - s;  // backward direction walks the row reversed by its own length
-      float4 g = __ldg((const float4*)(xproj + ((((size_t)b * T + pos) * 2 + dir) * U + u) * 4));
 #pragma unroll
       for (int q = 0; q < KP; ++q) {
         const float4 pp = *(const float4*)part[q][r][u];
@@ -86,6 +100,16 @@ __global__ void __launch_bounds__(LSTM_NT) bilstm_kernel(const float* __restrict
     }
     __syncthreads();
   }
+}
+
+template <int U, int ROWS>
+void bilstm_launch(const float* xproj, const float* Wh, const long long* lengths, int B, int T, float zc, float zh, float* out,
+                   cudaStream_t st) {
+  constexpr int KP = LSTM_NT / U, KQ = U / KP, KR = KQ / 2;
+  const size_t smem = ((size_t)(KQ - KR) * LSTM_NT * 4 + (size_t)KP * ROWS * U * 4 + (size_t)ROWS * U) * sizeof(float);
+  SAT_CUDA(cudaFuncSetAttribute(bilstm_kernel<U, ROWS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  dim3 grid((unsigned)ceil_div(B, ROWS), 2);
+  bilstm_kernel<U, ROWS><<<grid, LSTM_NT, smem, st>>>(xproj, Wh, lengths, B, T, zc, zh, out);
 }
 
 struct Conv {
@@ -149,7 +173,7 @@ struct sat_encoder {
   float *lstm_wx = nullptr, *lstm_bx = nullptr, *lstm_wh = nullptr;
   float *sap_w = nullptr, *sap_b = nullptr;
   std::vector<MhaDev> hops;
-  int half = 0, cin = 0;
+  int half = 0, cin = 0, sm_count = 148;
   bool tc = false;  // conv bank + proj1 on the tensor cores (fp16 operands, fp32 accumulation)
   bool tc_full = false;  // ... and prenet layer 1, proj2, the highway layers and the BiLSTM input projection as well
   __half* pre1_img = nullptr;
@@ -167,6 +191,11 @@ extern "C" int sat_encoder_create(const sat_hparams* hpp, const sat_tensor* weig
     auto* h = new sat_encoder();
     std::unique_ptr<sat_encoder> guard(h);
     h->hp = hp;
+    {
+      int dev = 0;
+      SAT_CUDA(cudaGetDevice(&dev));
+      SAT_CUDA(cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, dev));
+    }
     DevPool& pool = h->pool;
     const int E = hp.embedding_dim;
     SAT_REQUIRE(hp.encoder_prenet_units[0] > 0 && hp.encoder_prenet_units[1] > 0, "encoder prenet needs two layers");
@@ -445,9 +474,11 @@ static int encoder_forward_impl(sat_encoder* h, const int64_t* ids, const float*
         gemm_launch(g, st);
       }
       SAT_CUDA(cudaMemsetAsync(lstm_out, 0, rows * 2 * half * sizeof(float), st));
-      dim3 grid((unsigned)ceil_div(B, LSTM_ROWS), 2);
-      bilstm_kernel<128><<<grid, LSTM_NT, 0, st>>>(ws + o_xp, h->lstm_wh, (const long long*)lengths, B, T,
-                                                   hp.zoneout_factor_cell, hp.zoneout_factor_output, lstm_out);
+      // sequences per CTA: as few as still fit one wave of the SMs (2 directions x ceil(B / rows) CTAs)
+      const float zc = hp.zoneout_factor_cell, zh = hp.zoneout_factor_output;
+      if (2 * B <= h->sm_count) bilstm_launch<128, 1>(ws + o_xp, h->lstm_wh, (const long long*)lengths, B, T, zc, zh, lstm_out, st);
+      else if (B <= h->sm_count) bilstm_launch<128, 2>(ws + o_xp, h->lstm_wh, (const long long*)lengths, B, T, zc, zh, lstm_out, st);
+      else bilstm_launch<128, 4>(ws + o_xp, h->lstm_wh, (const long long*)lengths, B, T, zc, zh, lstm_out, st);
       count_launch();
       check_launch("bilstm_kernel");
     }
