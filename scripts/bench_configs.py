@@ -9,6 +9,10 @@ BASELINE.json / SURVEY.md 8d through the public API, one JSON line per config, o
         sharded over the ranks: STRONG scaling (the 1024 utterances are split over N GPUs)
   cfg4  cfg 1 model on long utterances (T_enc=400, 2000 frames), forced-alignment mode: teacher-forced pass producing
         alignments, then the replay pass (teacher_forcing_forward / teacher_forcing_additive), B=16 per GPU
+  cfg2p cfg 2 (baseline Tacotron, free run, B=256/GPU) with the PER-ROW stop rule: the stop-projection bias is shifted (the
+        stop logit does not feed back, so one probe run predicts every row's stop step for any shift) until the median
+        row stops near step 300; the run ends when the last row has stopped, frames = frames up to each row's own stop
+        step; the predicted stop steps must equal the kernel's
   cfg5  VQ-code model (1025 one-hot classes, r=1, softmax feedback, max_iters=450), free run, 512 utterances sharded
         over the ranks in batches of 64: STRONG scaling
 
@@ -47,6 +51,12 @@ def make_cfg(name, rank, world):
         hp = sat_b200.config("ljspeech_self_attention")
         return hp, [batch(hp, [150] * 16, [800] * 16, is_validation=True, teacher_forcing=True)], \
             "teacher-forced, B=16/GPU, T_enc=150, 800 frames/utterance", "weak"
+    if name == "cfg2p":
+        hp = sat_b200.config("ljspeech_tacotron")
+        lens = rng.integers(100, 201, size=256)
+        b = batch(hp, lens)
+        b["frames"] = None
+        return hp, [b], "baseline Tacotron, free run, per-row stop rule, B=256/GPU, T_enc~U[100,200], max_iters=500", "weak"
     if name == "cfg4":
         hp = sat_b200.config("ljspeech_self_attention")
         hp.override(max_iters=1000, use_forced_alignment_mode=True)
@@ -97,6 +107,27 @@ def run(args, rank, world, local_rank):
             W = dict(W)
             W["decoder/stop_token_projection/bias"] = np.full_like(W["decoder/stop_token_projection/bias"], -8.0)
         model = tacotron_model_factory(hp, W)
+        extra = {}
+        if name == "cfg2p":
+            # probe: never-stopping run -> stop logits [B, S]; pick the bias shift whose median first crossing is ~300
+            Wp = dict(W)
+            Wp["decoder/stop_token_projection/bias"] = np.full_like(W["decoder/stop_token_projection/bias"], -30.0)
+            b0 = batches[0]
+            o = tacotron_model_factory(hp, Wp).predict(torch.from_numpy(b0["ids"]).to(dev), torch.from_numpy(b0["lengths"]).to(dev))
+            logit = o["stop_token"].float().cpu().numpy().reshape(len(b0["lengths"]), -1) + 30.0
+            S = logit.shape[1]
+
+            def stops(bias):
+                hit = (logit + bias > 0) & (np.arange(S)[None, :] > 10)   # sigmoid(x) > 0.5 and time > 10 (helpers.py:156-160)
+                return np.where(hit.any(1), hit.argmax(1), -1)
+            cands = np.quantile(-logit[:, 11:], np.linspace(0.0, 0.2, 81))   # logit = kernel . h (bias removed)
+            bias = float(min(cands, key=lambda c: abs(np.median(np.where(stops(c) < 0, S, stops(c))) - 300)))
+            W = dict(W)
+            W["decoder/stop_token_projection/bias"] = np.full_like(W["decoder/stop_token_projection/bias"], bias)
+            predicted = stops(np.float32(bias))
+            model = tacotron_model_factory(hp, W)
+            model.decoder.stop_mode = "per_row"
+            extra = {"stop_bias": float(W["decoder/stop_token_projection/bias"][0]), "predicted": predicted}
         dbs = []
         for b in batches:
             dbs.append(dict(ids=torch.from_numpy(b["ids"]).to(dev), lengths=torch.from_numpy(b["lengths"]).to(dev),
@@ -125,7 +156,15 @@ def run(args, rank, world, local_rank):
         for b, o in zip(batches, outs):
             n = int(o["n_steps"])
             steps_run.append(n)
-            frames += b["frames"] if b.get("frames") is not None else len(b["lengths"]) * n * hp.outputs_per_step
+            if name == "cfg2p":
+                ss = o["stop_steps"].cpu().numpy()
+                assert np.array_equal(ss, extra["predicted"]), "per-row stop steps differ from the probe's prediction"
+                per_row = np.where(ss < 0, n, ss + 1)
+                frames += int(per_row.sum()) * hp.outputs_per_step
+                extra["histogram"] = {"min": int(per_row.min()), "p25": int(np.quantile(per_row, .25)), "median": int(np.median(per_row)),
+                                      "p75": int(np.quantile(per_row, .75)), "max": int(per_row.max()), "never_stopped": int((ss < 0).sum())}
+            else:
+                frames += b["frames"] if b.get("frames") is not None else len(b["lengths"]) * n * hp.outputs_per_step
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier()
         e0.record()
@@ -146,7 +185,9 @@ def run(args, rank, world, local_rank):
                               "value": total / (ms * 1e-3), "unit": "frames/s", "n_gpus": world, "scaling": scaling,
                               "ms_per_step": ms, "frames_per_step": total, "rtf": ms * 1e-3 / (total * 0.0125),
                               "batches_rank0": [int(d["ids"].shape[0]) for d in dbs], "decoder_steps_rank0": steps_run,
-                              "steps": args.steps, "warmup": args.warmup, "data": "synthetic"}), flush=True)
+                              "steps": args.steps, "warmup": args.warmup, "data": "synthetic",
+                              **({"stop_bias": extra["stop_bias"], "stop_step_histogram": extra["histogram"]} if extra else {})}),
+                  flush=True)
         del model, dbs
         torch.cuda.empty_cache()
 
@@ -156,7 +197,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--configs", default="cfg1,cfg3,cfg4,cfg5")
+    ap.add_argument("--configs", default="cfg1,cfg2p,cfg3,cfg4,cfg5")
     args = ap.parse_args()
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
