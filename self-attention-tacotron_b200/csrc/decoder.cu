@@ -165,6 +165,8 @@ struct sat_decoder {
   Scratch ws;
   Scratch ws_tail;  // time-batched buffers of the teacher-forced form
   PackedDense pre0, msd, pre1, lstm_a, lstm_1, lstm_2, outp, dq[2];
+  PackedDense outp_f;  // outp + prenet layer 0 folded onto the fed-back frame (self feed): [d_out][Mr + 1 + P0]
+  bool has_outp_f = false;
   PackedDense sa_qkv[MAX_HOPS], sa_o[MAX_HOPS], sa_tr[MAX_HOPS];
   float* mem_layer[2] = {nullptr, nullptr};  // [Dm][Up]
   float *att_v[2], *att_ba[2], *conv_w[2], *conv_b[2], *Wl[2], *Wt[2];
@@ -305,6 +307,36 @@ extern "C" int sat_decoder_create(const sat_hparams* hpp, const sat_tensor* weig
       for (int n = 0; n < h->Mr; ++n) b[n] = bo[n];
       b[h->Mr] = bs[0];
       h->outp = pack_dense(pool, w.data(), b.data(), d_out, N);
+      // Self feed: the next input frame is the last n_feed_frame frames of this projection, and prenet layer 0 is a
+      // dense layer on it -- two GEMVs in sequence on the critical path of every step.  Their composition is one
+      // linear map of the decoder output: column Mr + 1 + j = sum_f W_out[:, f0 + f] W_pre0[f][j] (bias likewise),
+      // formed here in double precision; the relu is applied when the columns are read.  (modules/module.py:599-617,
+      // helpers: feed slice [:, -M * n_feed_frame:]; PreNet layer 0 / MultiSpeakerPreNet dense0.)
+      const char* p0name = hp.multi_speaker_prenet ? "prenet/ms/dense0" : "prenet/dense_0";
+      const float* kp = W.get(D + p0name + "/kernel", (int64_t)h->Mnf * h->P0);
+      const float* bp = W.get(D + p0name + "/bias", h->P0);
+      const int f0 = h->Mr - h->Mnf, NF = N + h->P0;
+      std::vector<float> wf((size_t)d_out * NF), bf(NF);
+      std::vector<double> acc(h->P0);
+      for (int k = 0; k < d_out; ++k) {
+        for (int n = 0; n < N; ++n) wf[(size_t)k * NF + n] = w[(size_t)k * N + n];
+        std::fill(acc.begin(), acc.end(), 0.0);
+        for (int f = 0; f < h->Mnf; ++f) {
+          const double a = ko[(size_t)k * h->Mr + f0 + f];
+          for (int j = 0; j < h->P0; ++j) acc[j] += a * (double)kp[(size_t)f * h->P0 + j];
+        }
+        for (int j = 0; j < h->P0; ++j) wf[(size_t)k * NF + N + j] = (float)acc[j];
+      }
+      for (int n = 0; n < N; ++n) bf[n] = b[n];
+      for (int j = 0; j < h->P0; ++j) {
+        double a = bp[j];
+        for (int f = 0; f < h->Mnf; ++f) a += (double)bo[f0 + f] * (double)kp[(size_t)f * h->P0 + j];
+        bf[N + j] = (float)a;
+      }
+      if (NF <= 4 * NT && (size_t)d_out * NF <= (size_t)1 << 22) {
+        h->outp_f = pack_dense(pool, wf.data(), bf.data(), d_out, NF);
+        h->has_outp_f = true;
+      }
     }
     // launch geometry
     int dev = 0;
@@ -387,6 +419,14 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
     p.S_target = io.target_steps; p.Smax = S;
     p.zc = hp.zoneout_factor_cell; p.zh = hp.zoneout_factor_output;
     p.pre0 = h->pre0.desc(); p.pre1 = h->pre1.desc(); p.outp = h->outp.desc();
+    {
+      bool fuse = h->has_outp_f && io.feed_mode == SAT_FEED_SELF;
+      if (const char* e = getenv("SAT_FUSE_PRENET0")) fuse = fuse && atoi(e) != 0;
+      if (fuse) {
+        p.outp = h->outp_f.desc();
+        p.fused_prenet0 = 1;
+      }
+    }
     if (p.ms) p.msd = h->msd.desc();
     p.lstm_a = h->lstm_a.desc(); p.lstm_1 = h->lstm_1.desc(); p.lstm_2 = h->lstm_2.desc();
 

@@ -60,6 +60,8 @@ struct DecParams {
   TcLstmDesc tc_a, tc_1, tc_2;
   const CUtensorMap* maps;  // [6]: att_in[0,1], l1_in[0,1], l2_in[0,1]
   float* qfm;               // feature-major copy of the attention-LSTM output (query) for the SIMT query layers
+  int fused_prenet0;        // 1: `outp` carries P0 extra columns = prenet layer 0 applied to the fed-back frame, folded
+                            //    into the projection (self feed only): column Mr + 1 + j = sum_f W_out[:, f0 + f] W_pre0[f][j]
   int att_pair;             // 1: a CTA that owns two rows of the attention phase runs them concurrently, one per half
   int att_row_floats;       // shared-memory floats of one attention row (second row of a pair starts there)
 };
@@ -338,7 +340,13 @@ __device__ inline void frame_item(const DecParams& p, const int* b, int t, const
       else p.mel[((size_t)b[r] * p.max_steps + t) * p.Mr + n] = v;
     }
     const int f0 = p.Mr - p.Mnf;
-    if (p.feed_mode == SAT_FEED_TEACHER) {
+    if (p.fused_prenet0) {
+      // self feed with prenet layer 0 folded into the projection: its pre-activations are columns Mr + 1 .. of `os`
+      for (int i = tid; i < RR * p.P0; i += NT) {
+        const int r = i / p.P0, n = i - r * p.P0;
+        p0s[r * P0p + n] = fmaxf(os[r * Npo + p.Mr + 1 + n], 0.f);
+      }
+    } else if (p.feed_mode == SAT_FEED_TEACHER) {
       const int ts = min(t, p.S_target - 1);
       for (int i = tid; i < RR * p.Mnf; i += NT) {
         const int r = i / p.Mnf, f = i - r * p.Mnf;
@@ -370,7 +378,7 @@ __device__ inline void frame_item(const DecParams& p, const int* b, int t, const
   __syncthreads();
   ps = 34;
   stamp();
-  row_dense<RR, H>(p.pre0, fr, p.Mnf, part, p0s, 1);
+  if (prologue || !p.fused_prenet0) row_dense<RR, H>(p.pre0, fr, p.Mnf, part, p0s, 1);
   stamp();
   const float* pin = p0s;
   if (p.ms) {
