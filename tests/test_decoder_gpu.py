@@ -128,6 +128,18 @@ def test_attention_rows_paired_and_sequential(name, B, T, monkeypatch):
     assert rel_err(outs[0]["alignments"][0], outs[1]["alignments"][0]) <= 1e-4
 
 
+def test_long_memory_rows_fall_back_to_sequential_rows():
+    """T_enc = 600: two rows' attention arrays no longer fit the phase scratch together, so a CTA with two rows runs
+    them back to back (per-batch shared-memory plan, whole CTA per row); T_enc = 1000 uses the full-size plan."""
+    hp = small_hp("ljspeech_tacotron")
+    W = sat_b200.init_weights(hp, seed=9, stress=True)
+    for B, T in ((150, 600), (66, 1000)):
+        mems, lengths, target, _ = decoder_inputs(hp, B, T, 3, seed=9)
+        ref = oracle_decoder(hp, W, mems, lengths, target=target, is_validation=True, teacher_forcing=True)
+        got = run_cuda(hp, W, mems, lengths, target=target, feed_mode=0, stop_mode=0, max_steps=3)
+        check_close(got, ref)
+
+
 def test_small_batch_uses_fp32_simt():
     hp = small_hp("ljspeech_tacotron", **SMALL)
     W = sat_b200.init_weights(hp, seed=1)
