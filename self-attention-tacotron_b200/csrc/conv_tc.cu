@@ -17,7 +17,7 @@
 namespace sat {
 namespace {
 
-constexpr int CT_STAGES = 5;
+constexpr int CT_STAGES = 3;  // 3 x 32 KB: two CTAs per SM, so that one tile's epilogue overlaps the other's main loop
 constexpr int CT_STAGE_BYTES = 2 * 16384;
 constexpr int CT_THREADS = 128;
 
@@ -36,7 +36,7 @@ struct ConvTcArgs {
   int highway;              // 1: HighwayNet epilogue over interleaved (H_u, T_u) column pairs, x = res; writes N/2 columns
 };
 
-__global__ void __launch_bounds__(CT_THREADS, 1)
+__global__ void __launch_bounds__(CT_THREADS, 2)
 conv_tc_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant__ CUtensorMap wmap, const ConvTcArgs a) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* ring = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
