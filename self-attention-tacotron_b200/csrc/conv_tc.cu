@@ -17,7 +17,7 @@
 namespace sat {
 namespace {
 
-constexpr int CT_STAGES = 3;  // 3 x 32 KB: two CTAs per SM, so that one tile's epilogue overlaps the other's main loop
+constexpr int CT_STAGES = 2;  // 2 x 32 KB: three CTAs per SM -- the tiles are latency-bound (TMA fill, epilogue), measured 2.48 (5 stages, 1 CTA) -> 2.14 (3, 2) -> 1.84 ms (2, 3) per encoder forward at B=256
 constexpr int CT_STAGE_BYTES = 2 * 16384;
 constexpr int CT_THREADS = 128;
 
@@ -36,7 +36,7 @@ struct ConvTcArgs {
   int highway;              // 1: HighwayNet epilogue over interleaved (H_u, T_u) column pairs, x = res; writes N/2 columns
 };
 
-__global__ void __launch_bounds__(CT_THREADS, 2)
+__global__ void __launch_bounds__(CT_THREADS, 3)
 conv_tc_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant__ CUtensorMap wmap, const ConvTcArgs a) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* ring = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
