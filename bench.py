@@ -12,9 +12,13 @@ rule, batch 256 per GPU, T_enc ~ U[100,200], max_iters=500.  With random-init we
 Prints ONE JSON line (rank 0).  `value` = frames/s with inputs resident in HBM; `e2e` = the same through the
 public API (sat_b200.models.SynthesisModel.predict) with pinned HOST buffers in and out (the read-back of one step
 overlaps the compute of the next on a copy stream); `roofline` = the
-persistent decoder kernel against the measured HBM peak; `cpu_baseline` = the torch-CPU port of the oracle on a
-bounded sample.  `--impl reference` times that CPU port alone (TensorFlow 1.x, the reference's own runtime, is
-not installable here -- see BASELINE.md).
+persistent decoder kernel against the measured HBM peak; `cpu_baseline` = the torch-CPU port of the oracle timed on
+one FULL workload step (all 500 decoder steps, nothing extrapolated); `parity` = the benched workload checked
+against the fp64 oracle outside the timed region (oracle/parity.py; every 4th row of the batch -- rows are
+independent); `teacher_forced` = cfg 1 (BASELINE.json's metric names both modes); `postnet` = PostNetV2 on
+[256,1000,80]; `sharded` = cfg 3's 1024 utterances length-bucketed over the N ranks with the NCCL gather of the
+frames inside the timed region.  `--impl reference` times the CPU port alone (TensorFlow 1.x, the reference's own
+runtime, is not installable here -- see BASELINE.md).
 """
 import argparse
 import json
@@ -93,14 +97,12 @@ class ClockSampler:
 # ---------------------------------------------------------------------------------------------------------
 # CPU baseline: the torch-CPU port of the oracle (oracle/torch_cpu.py), the one place bench.py runs oracle/ code
 # ---------------------------------------------------------------------------------------------------------
-CPU_SAMPLE_STEPS = 50
 _cpu_warm = False
 
 
 def cpu_sample(hp, W, ids, lengths, threads):
-    """One bounded sample of the workload on the host cores: the whole encoder for the full batch plus the first
-    CPU_SAMPLE_STEPS of the 500 decoder steps; the decoder part is scaled to 500 steps (cfg 2 has no KV cache, so
-    every step costs the same).  -> (frames/s of the whole workload, seconds spent)."""
+    """One FULL workload step on the host cores: the whole encoder and all `max_iters` decoder steps of the full
+    batch (nothing scaled or extrapolated).  -> (frames/s, seconds spent)."""
     import torch
     from oracle import torch_cpu
     global _cpu_warm
@@ -114,17 +116,15 @@ def cpu_sample(hp, W, ids, lengths, threads):
             _cpu_warm = True
         t0 = time.perf_counter()
         src = torch_cpu.encoder(ids, lengths, Wt, hp)
-        t1 = time.perf_counter()
-        torch_cpu.decoder_free_run(src, lengths, Wt, hp, CPU_SAMPLE_STEPS)
-        t2 = time.perf_counter()
-    est = (t1 - t0) + (t2 - t1) * S / CPU_SAMPLE_STEPS
+        torch_cpu.decoder_free_run(src, lengths, Wt, hp, S)
+        secs = time.perf_counter() - t0
     frames = ids.shape[0] * S * hp.outputs_per_step
-    return frames / est, t2 - t0
+    return frames / secs, secs
 
 
 def cpu_sample_text():
-    return (f"full batch (B={B_PER_GPU}): whole encoder + first {CPU_SAMPLE_STEPS} of 500 decoder steps, decoder time "
-            f"scaled x{500 // CPU_SAMPLE_STEPS}; torch-CPU fp32 port of the oracle (TF 1.x reference not installable)")
+    return (f"one full workload step: B={B_PER_GPU}, whole encoder + all 500 decoder steps (256 000 frames), measured, "
+            f"not extrapolated; torch-CPU fp32 port of the oracle (TF 1.x reference not installable)")
 
 
 def run_reference(args, rank, world):
@@ -138,21 +138,207 @@ def run_reference(args, rank, world):
     threads = os.cpu_count() or 1
     for _ in range(min(args.warmup, 1)):
         cpu_sample(hp, W, ids, lengths, threads)
-    vals, secs = [], []
+    secs, t_start = [], time.perf_counter()
     for _ in range(args.steps):
-        v, s = cpu_sample(hp, W, ids, lengths, threads)
-        vals.append(v)
-        secs.append(s)
-    value = float(np.mean(vals))
+        secs.append(cpu_sample(hp, W, ids, lengths, threads)[1])
+        if time.perf_counter() - t_start + secs[-1] > 420.0:  # keep the whole run within a few minutes; `steps` says
+            break                                              # how many full passes were actually timed
     frames = B_PER_GPU * hp.max_iters * hp.outputs_per_step
+    value = float(frames * len(secs) / np.sum(secs))
     line = {"metric": METRIC, "value": value, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * frames / value,
+            "steps": len(secs), "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * float(np.mean(secs)),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "note": "ms_per_step = estimated CPU time of one full workload step"},
+            "config": {"workload": WORKLOAD, "note": "every step is one full workload pass (256 x 500 decoder steps) on "
+                                                     "the host cores; ms_per_step is measured"},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": cpu_sample_text()},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "sample_seconds": float(np.mean(secs))}
     print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# secondary records of the same JSON line (all through the public API; timing = CUDA events, max over ranks)
+# ---------------------------------------------------------------------------------------------------------
+def _timed(fn, steps, warmup, dev, world, barrier):
+    """-> ms per call of fn (max over ranks), after `warmup` untimed calls"""
+    import torch
+    import torch.distributed as dist
+    for _ in range(warmup):
+        fn()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    barrier()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item()) / steps
+
+
+def parity_record(hp, W, ids_np, len_np, out):
+    """The benched workload against the fp64 oracle, OUTSIDE the timed region: rows 0, 4, 8, ... of the batch the
+    GPU just decoded (rows are independent, so the oracle can run a subset of them; oracle/parity.py)."""
+    from oracle import parity
+    rows = np.arange(0, ids_np.shape[0], 4)
+    t0 = time.perf_counter()
+    W64 = {k: v.astype(np.float64) for k, v in W.items()}
+    ref = parity.synthesize_rows_parallel(ids_np[rows], len_np[rows], W64, hp, mode="free_run", stop_mode="never",
+                                          max_iters=hp.max_iters)
+    n = int(out["n_steps"].item())
+    got = {"n_steps": n, "stop_steps": out["stop_steps"].cpu().numpy()[rows],
+           "mel": out["mel"].cpu().numpy()[rows], "stop": out["stop"].cpu().numpy()[rows],
+           "alignment": out["alignments"][0].cpu().numpy()[rows]}
+    rep = parity.free_run_report(got, ref, "never", hp.outputs_per_step, hp.max_iters)
+    # the all_rows rule over the checked rows must not fire either (frames/step would be wrong)
+    rep["all_rows_rule_fires_in_oracle"] = bool(parity.stop_rule(ref["stop"], "all_rows", hp.max_iters)[0] < hp.max_iters)
+    rep["oracle"] = "fp64 NumPy restatement (oracle/), parity unpinned at the TF boundary"
+    rep["checked_rows"] = f"{len(rows)} of {ids_np.shape[0]} (every 4th)"
+    rep["oracle_seconds"] = time.perf_counter() - t0
+    return rep
+
+
+def teacher_forced_record(args, dev, world, barrier, flush):
+    """cfg 1 (BASELINE.json configs[0]): dual-source self-attention Tacotron, teacher-forced, B=16/GPU, T_enc=150,
+    800 frames per utterance -- the '>= 1e6 teacher-forced mel frames/s' target of north_star."""
+    import torch
+    import sat_b200
+    from sat_b200.models import tacotron_model_factory
+    hp = sat_b200.config("ljspeech_self_attention")
+    W = sat_b200.init_weights(hp, seed=SEED)
+    B, T, S = 16, 150, 400
+    rng = np.random.default_rng(SEED)
+    ids_np = rng.integers(1, 71, size=(B, T)).astype(np.int64)
+    len_np = np.full(B, T, dtype=np.int64)
+    tgt_np = rng.normal(0, 1, size=(B, S * hp.outputs_per_step, hp.num_mels)).astype(np.float32)
+    model = tacotron_model_factory(hp, W)
+    ids, lengths, target = (torch.from_numpy(a).to(dev) for a in (ids_np, len_np, tgt_np))
+    frames = B * S * hp.outputs_per_step
+    steps = max(5, args.steps)
+
+    def step():
+        flush.fill_(1)
+        return model.predict(ids, lengths, target=target, is_validation=True, teacher_forcing=True)
+
+    ms = _timed(step, steps, 3, dev, world, barrier)
+    (dec, _), = model.decoder._handles.values()
+    kms = []
+    for _ in range(3):
+        step()
+        kms.append(dec.kernel_ms())
+    k_ms = float(np.mean(kms))
+    bytes_step = dec.step_bytes(B, T, S // 2)
+    peak, peak_src = peaks()
+    achieved = bytes_step * S / (k_ms * 1e-3) / 1e9
+    ids_h, len_h, tgt_h = (torch.from_numpy(a).pin_memory() for a in (ids_np, len_np, tgt_np))
+    mel_h = torch.empty((B, S * hp.outputs_per_step, hp.num_mels), dtype=torch.float32).pin_memory()
+
+    def e2e_step():
+        flush.fill_(1)
+        o = model.predict(ids_h.to(dev, non_blocking=True), len_h.to(dev, non_blocking=True),
+                          target=tgt_h.to(dev, non_blocking=True), is_validation=True, teacher_forcing=True)
+        mel_h.copy_(o["mel"], non_blocking=True)
+
+    ms_e2e = _timed(e2e_step, steps, 2, dev, world, barrier)
+    return {"workload": "cfg1: LJSpeech self-attention Tacotron, teacher-forced, B=16/GPU, T_enc=150, 800 frames/utterance",
+            "metric": "mel_frames_per_sec_teacher_forced", "unit": UNIT, "value": world * frames / (ms * 1e-3),
+            "ms_per_step": ms, "steps": steps, "target": 1e6, "scaling": "weak",
+            "e2e": {"value": world * frames / (ms_e2e * 1e-3), "unit": UNIT,
+                    "h2d_bytes_per_step": int(ids_np.nbytes + len_np.nbytes + tgt_np.nbytes),
+                    "d2h_bytes_per_step": int(mel_h.numel() * 4)},
+            "roofline": {"kernel": "decoder_persistent_kernel", "bound": "hbm", "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src, "traffic": None,
+                         "bytes_per_decoder_step": bytes_step, "decoder_steps_per_launch": S, "kernel_ms": k_ms,
+                         "kernel_share_of_step": k_ms / ms}}
+
+
+def postnet_record(args, dev, world, barrier, flush):
+    """PostNetV2 on the frames one bench step emits: [256, 1000, 80]."""
+    import torch
+    import sat_b200
+    from sat_b200.engine import PostnetHandle
+    hp = sat_b200.config("ljspeech_tacotron")
+    hp.override(use_postnet_v2=True)
+    W = sat_b200.init_weights(hp, seed=SEED)
+    post = PostnetHandle(hp, W)
+    B, Tf, M = 256, 1000, hp.num_mels
+    mel = torch.randn((B, Tf, M), device=dev, dtype=torch.float32)
+    C, k, n = hp.postnet_v2_out_channels, hp.postnet_v2_kernel_size, hp.num_postnet_v2_layers
+    flops_frame = 2.0 * (k * M * C + (n - 1) * k * C * C + C * M)
+
+    def step():
+        flush.fill_(1)
+        post.forward(mel)
+
+    ms = _timed(step, max(5, args.steps), 3, dev, world, barrier)
+    ms_flush = _timed(lambda: flush.fill_(1), 5, 1, dev, world, barrier)
+    ms_net = max(ms - ms_flush, 1e-6)
+    tflops = flops_frame * B * Tf / (ms_net * 1e-3) / 1e12
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    peak, src = 1400.0, "fallback (B200_PROFILING.md, sustained)"
+    if os.path.exists(path):
+        with open(path) as f:
+            peak, src = float(json.load(f)["bf16_tflops_sustained"]), "measured bf16_tflops_sustained (MEASURED_PEAKS.json)"
+    return {"workload": f"PostNetV2 {n} x conv1d(k={k}, {C} ch) + Dense({M}) on [{B},{Tf},{M}]", "ms": ms_net,
+            "flops_per_frame": flops_frame, "tflops": tflops, "peak_tflops": peak, "frac": tflops / peak,
+            "peak_source": src, "tensor_cores": post.uses_tensor_cores(),
+            "frames_per_sec": world * B * Tf / (ms_net * 1e-3)}
+
+
+def sharded_record(args, rank, world, dev, barrier, flush):
+    """cfg 3 the way north_star describes multi-GPU inference: 1024 utterances, length-bucketed
+    (sharding.make_buckets), dealt to the N ranks, decoded with no collective, then the variable-length frames
+    gathered on rank 0 (sharding.gather_mels, NCCL) -- ALL inside the timed region.  Strong scaling."""
+    import torch
+    import sat_b200
+    from sat_b200.models import tacotron_model_factory
+    from sat_b200.sharding import make_buckets, gather_mels
+    hp = sat_b200.config("vctk_self_attention")
+    rng = np.random.default_rng(SEED)
+    n = 1024
+    lens = rng.integers(50, 251, size=n)
+    r = hp.outputs_per_step
+    tdec = np.round(5.33 * lens / r).astype(np.int64) * r
+    hp.override(max_iters=int(tdec.max()) // r)
+    spk = rng.integers(hp.speaker_embedding_offset, hp.speaker_embedding_offset + hp.num_speakers, size=n).astype(np.int64)
+    W = sat_b200.init_weights(hp, seed=SEED)
+    model = tacotron_model_factory(hp, W)
+    batches = []
+    for ix in map(np.asarray, make_buckets(lens, 128, world, bucket_width=50)[rank]):
+        L, Td = lens[ix], tdec[ix]
+        T, S = int(L.max()), int(Td.max())
+        ids = rng.integers(1, 71, size=(len(ix), T)).astype(np.int64)
+        ids[np.arange(T)[None, :] >= L[:, None]] = 0
+        tgt = rng.normal(0, 1, size=(len(ix), S, hp.num_mels)).astype(np.float32)
+        batches.append(dict(ix=ix, td=Td, ids=torch.from_numpy(ids).to(dev), lengths=torch.from_numpy(L.astype(np.int64)).to(dev),
+                            target=torch.from_numpy(tgt).to(dev), spk=torch.from_numpy(spk[ix]).to(dev)))
+    got = {}
+
+    def step():
+        flush.fill_(1)
+        uid, mels = [], []
+        for b in batches:
+            o = model.predict(b["ids"], b["lengths"], target=b["target"], speaker_id=b["spk"], is_validation=True,
+                              teacher_forcing=True)
+            for i, u in enumerate(b["ix"]):
+                uid.append(int(u))
+                mels.append(o["mel"][i, :int(b["td"][i])])
+        got["all"] = gather_mels(uid, mels, world, rank, device=dev)
+
+    steps = max(2, min(args.steps, 3))
+    ms = _timed(step, steps, 1, dev, world, barrier)
+    if rank == 0:
+        assert len(got["all"]) == n and all(got["all"][i].shape[0] == int(tdec[i]) for i in (0, n // 2, n - 1))
+    frames = int(tdec.sum())
+    return {"workload": "cfg3: VCTK multi-speaker self-attention Tacotron, 1024 utterances, T_enc~U[50,250], T_dec=5.33 T_enc, "
+                        "teacher-forced, length buckets of <=128 dealt to the ranks, frames gathered on rank 0 inside "
+                        "the timed region", "metric": "mel_frames_per_sec_teacher_forced", "unit": UNIT,
+            "value": frames / (ms * 1e-3), "ms_per_step": ms, "steps": steps, "scaling": "strong", "frames_per_step": frames,
+            "batches_rank0": [int(len(b["ix"])) for b in batches], "gathered_bytes": frames * hp.num_mels * 4,
+            "collective": "none on the compute path; all_reduce(MAX) + 2 all_gather (NCCL) for the result gather"
+            if world > 1 else "single rank: no collective"}
 
 
 # ---------------------------------------------------------------------------------------------------------
@@ -269,8 +455,14 @@ def run_ours(args, rank, world, local_rank):
     e2e_value = world * frames_per_step * k2 / (float(t.item()) * 1e-3)
     assert bool(np.isfinite(mel_hs[0].numpy()[:, -1]).all()) and bool(np.isfinite(mel_hs[1].numpy()[:, -1]).all())
 
+    tf_rec = teacher_forced_record(args, dev, world, barrier, flush) if not args.no_extras else None
+    post_rec = postnet_record(args, dev, world, barrier, flush) if not args.no_extras else None
+    shard_rec = sharded_record(args, rank, world, dev, barrier, flush) if not args.no_extras else None
     if rank != 0:
         return
+    par = None
+    if world == 1 and not args.no_parity:
+        par = parity_record(hp, W, ids_np, len_np, out)
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
@@ -304,7 +496,7 @@ def run_ours(args, rank, world, local_rank):
                          "peak_source": peak_src,
                          "bytes_per_decoder_step": bytes_step, "decoder_steps_per_launch": S, "kernel_ms": k_ms,
                          "kernel_share_of_step": k_ms / (ms / args.steps)},
-            "cpu_baseline": cpu}
+            "cpu_baseline": cpu, "parity": par, "teacher_forced": tf_rec, "postnet": post_rec, "sharded": shard_rec}
     print(json.dumps(line), flush=True)
 
 
@@ -315,6 +507,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the oracle check of the benched workload")
+    ap.add_argument("--no-extras", action="store_true", help="skip the teacher_forced / postnet / sharded records")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))

@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define SAT_ABI_VERSION 1
+#define SAT_ABI_VERSION 2
 
 enum { SAT_OK = 0, SAT_EINVAL = -1, SAT_ECUDA = -2, SAT_EMISSING = -3, SAT_EUNSUPPORTED = -4, SAT_ENOMEM = -5 };
 
@@ -127,6 +127,9 @@ typedef struct {
   float* decoder_outputs;       /* [B,max_steps,decoder_out_units] pre-projection cell outputs or NULL */
   int32_t* stop_steps;          /* [B] first step meeting the stop rule (-1 if none) */
   int32_t* n_steps;             /* [1] steps actually run */
+  /* decoder self-attention probabilities per hop, [B,heads,max_steps,max_steps] (row t = step t, causal; zero above
+   * the diagonal) or NULL: what models/models.py:110-111,143-144 reads from decoder_state.alignments ("alignment3/4") */
+  float* self_attention_probs[2];
 } sat_decoder_io;
 
 int sat_decoder_create(const sat_hparams* hp, const sat_tensor* weights, int32_t n_weights, sat_decoder** out);

@@ -44,7 +44,8 @@ class SatDecoderIO(C.Structure):
                 ("teacher_alignments", C.c_void_p * 2), ("forced_alignment", C.c_int32),
                 ("feed_mode", C.c_int32), ("stop_mode", C.c_int32), ("max_steps", C.c_int32), ("min_iters", C.c_int32),
                 ("mel", C.c_void_p), ("stop", C.c_void_p), ("alignments", C.c_void_p * 2), ("sample_ids", C.c_void_p),
-                ("decoder_outputs", C.c_void_p), ("stop_steps", C.c_void_p), ("n_steps", C.c_void_p)]
+                ("decoder_outputs", C.c_void_p), ("stop_steps", C.c_void_p), ("n_steps", C.c_void_p),
+                ("self_attention_probs", C.c_void_p * 2)]
 
 
 _lib = None

@@ -632,6 +632,7 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
       p.hop[i].qkv = h->sa_qkv[i].desc(); p.hop[i].o = h->sa_o[i].desc(); p.hop[i].tr = h->sa_tr[i].desc();
       plan_rows(p.hop[i].qkv, false); plan_rows(p.hop[i].o, false); plan_rows(p.hop[i].tr, false);
       p.hop[i].kcache = ws + o_kc[i]; p.hop[i].vcache = ws + o_vc[i];
+      p.hop[i].probs = io.self_attention_probs[i];
     }
 
     // ---- teacher-forced time-batched form: prenet of all steps before the loop, hops + projections after it ----
@@ -704,7 +705,7 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
         m.Wqkv = h->sa_qkv[i].Wrm; m.bqkv = h->sa_qkv[i].bias; m.Wo = h->sa_o[i].Wrm; m.bo = h->sa_o[i].bias;
         m.Wt = h->sa_tr[i].Wrm; m.bt = h->sa_tr[i].bias;
         m.Din = Dd; m.D = Ds; m.H = hp.decoder_self_attention_num_heads;
-        sat_layer_forward(m, y, B, S, 1, nullptr, t_y[i & 1], nullptr, t_mha, st);
+        sat_layer_forward(m, y, B, S, 1, nullptr, t_y[i & 1], io.self_attention_probs[i], t_mha, st);
         y = t_y[i & 1];
       }
       dense_rows(h->outp, y, h->outp.K, rows_all, ACT_NONE, t_proj);

@@ -25,6 +25,7 @@ struct SaHop {
   DenseDesc qkv, o, tr;
   float* kcache;  // [B][H][Smax][dh]
   float* vcache;
+  float* probs;   // [B][H][Smax][Smax] attention probabilities (row t written at step t) or null
 };
 
 struct DecParams {
@@ -203,6 +204,10 @@ __device__ inline void sa_item(const DecParams& p, const SaHop& h, int b, int hd
   sum = block_sum(sum, s32);
   const float inv = 1.f / sum;
   __syncthreads();
+  if (h.probs) {
+    float* pr = h.probs + (((size_t)b * p.heads + hd) * p.Smax + t) * p.Smax;
+    for (int j = tid; j < p.Smax; j += NT) pr[j] = j < n ? sc[j] * inv : 0.f;
+  }
   if (vec && ((((size_t)vb) & 15) == 0)) {
     attention_context_vec<1>(vb, sc, n, dh, part, ctxs);
     for (int d = tid; d < dh; d += NT) p.sa_ctx[(size_t)(hd * dh + d) * p.ld + b] = ctxs[d] * inv;

@@ -34,7 +34,8 @@ class DecoderHandle:
 
     def run(self, memories, lengths, *, target=None, teacher_alignments=None, speaker_embed=None,
             feed_mode, stop_mode, max_steps, forced_alignment=False, min_iters=10,
-            want_alignments=True, want_sample_ids=False, want_decoder_outputs=False, stream=None):
+            want_alignments=True, want_sample_ids=False, want_decoder_outputs=False,
+            want_self_attention_probs=False, stream=None):
         hp = self.hp
         if not isinstance(memories, (tuple, list)):
             memories = (memories,)
@@ -82,8 +83,14 @@ class DecoderHandle:
         io.sample_ids = ids.data_ptr() if ids is not None else 0
         io.decoder_outputs = dout.data_ptr() if dout is not None else 0
         io.stop_steps, io.n_steps = stop_steps.data_ptr(), n_steps.data_ptr()
+        sa_probs = []
+        if want_self_attention_probs and hp.decoder == "DualSourceTransformerDecoder":
+            sa_probs = [torch.empty((B, hp.decoder_self_attention_num_heads, S, S), device=dev, dtype=torch.float32)
+                        for _ in range(hp.decoder_self_attention_num_hop)]
+        io.self_attention_probs = (C.c_void_p * 2)(*[a.data_ptr() for a in sa_probs] + [0] * (2 - len(sa_probs)))
         check(lib().sat_decoder_run(self._h, C.byref(io), stream_ptr(stream)))
         return {"mel": mel, "stop": stop, "alignments": aligns, "sample_ids": ids, "decoder_outputs": dout,
+                "self_attention_probs": sa_probs,
                 "stop_steps": stop_steps, "n_steps": n_steps, "_keep": (memories, lengths, target, tas, speaker_embed)}
 
     def step_bytes(self, B, T, avg_cache_len=0):

@@ -76,10 +76,11 @@ class SynthesisModel:
                                  params.postnet_v2_out_channels, False, weights=weights) if params.use_postnet_v2 else None
 
     def predict(self, source, source_length, target=None, speaker_id=None, is_validation=False,
-                teacher_forcing=False, want_encoder_alignments=False):
+                teacher_forcing=False, want_encoder_alignments=False, want_decoder_self_attention_alignments=False):
         """source int64 ids [B,T_enc] (device), source_length [B]; target [B,T_dec,M] for validation /
         forced alignment.  Returns a dict of device tensors."""
         p = self.params
+        self.decoder.want_self_attention_alignments = want_decoder_self_attention_alignments
         if self.dual:
             lstm_out, sa_out, enc_align = self.encoder(source, input_lengths=source_length,
                                                        want_alignments=want_encoder_alignments)
@@ -125,6 +126,12 @@ class SynthesisModel:
         # alignments arranged (B, T_memory, T_query) like models/models.py:104-115
         for i, a in enumerate(state.alignment_history):
             out["alignment" if i == 0 else f"alignment{i + 1}"] = a.transpose(1, 2)
+        # decoder self-attention alignments -> alignment3/4, encoder self-attention -> alignment5..7, each
+        # (B, T_key, T_query) like models/models.py:105,110-111,265-269
+        for i, a in enumerate(state.alignments[:2]):
+            out[f"alignment{3 + i}"] = a.transpose(1, 2)
+        for i, a in enumerate(enc_align[:3]):
+            out[f"alignment{5 + i}"] = a.transpose(1, 2)
         if len(res) == 4:
             out["predicted_samples"] = res[2]
         if self.postnet is not None:

@@ -156,9 +156,11 @@ class PostNetV2:
 
 # ---- decoders ---------------------------------------------------------------------------------
 
-class AttentionHistoryState(namedtuple("AttentionHistoryState", ["alignment_history", "stop_steps", "n_steps"])):
-    """What the hot path reads out of the reference's final decoder state (models/models.py:107-115):
-    per-mechanism alignment history, here already stacked as [B, S, T_enc]."""
+class AttentionHistoryState(namedtuple("AttentionHistoryState", ["alignment_history", "stop_steps", "n_steps",
+                                                                 "alignments"])):
+    """What the hot path reads out of the reference's final decoder state (models/models.py:107-115,143-144):
+    per-mechanism alignment history, here already stacked as [B, S, T_enc], and ``alignments`` = the decoder
+    self-attention probabilities per hop and head, each [B, S, S] (``decoder_state.alignments`` of the reference)."""
 
 
 class _DecoderBase:
@@ -168,16 +170,23 @@ class _DecoderBase:
     def __init__(self, prenet_out_units=(256, 128), drop_rate=0.5, attention_out_units=256, decoder_version="v1",
                  decoder_out_units=256, num_mels=80, outputs_per_step=2, max_iters=200, n_feed_frame=1,
                  zoneout_factor_cell=0.0, zoneout_factor_output=0.0, lstm_impl=None, trainable=True, name=None,
-                 dtype=None, weights=None, **kwargs):
+                 dtype=None, weights=None, attention_rnn_out_units=None, **kwargs):
         if weights is None:
             raise ValueError(f"{type(self).__name__} needs weights=")
+        # the dual-source decoders of the reference call this width attention_rnn_out_units (modules/module.py:1054,1458)
+        if attention_rnn_out_units is not None:
+            attention_out_units = attention_rnn_out_units
+        extra = kwargs.pop("_extra", {})
+        if kwargs:
+            raise TypeError(f"{type(self).__name__}() got unexpected keyword arguments {sorted(kwargs)}")
         self._base = dict(decoder=self.kind, decoder_prenet_out_units=tuple(prenet_out_units),
                           attention_out_units=attention_out_units, decoder_version=decoder_version,
                           decoder_out_units=decoder_out_units, num_mels=num_mels, outputs_per_step=outputs_per_step,
                           max_iters=max_iters, n_feed_frame=n_feed_frame, zoneout_factor_cell=zoneout_factor_cell,
                           zoneout_factor_output=zoneout_factor_output)
-        self._base.update(kwargs.pop("_extra", {}))
+        self._base.update(extra)
         self.weights = weights
+        self.want_self_attention_alignments = False  # [B,H,S,S] per hop: only on request
         self.max_iters = max_iters
         self.outputs_per_step = outputs_per_step
         self._handles = {}
@@ -230,7 +239,8 @@ class _DecoderBase:
         if any(m.kind.startswith("teacher_forcing") for m in mechs) and not forced:
             raise ValueError("teacher-forcing attention must be selected for every source or for none")
         r = hp.outputs_per_step
-        kw = dict(speaker_embed=speaker_embed, forced_alignment=forced, want_sample_ids=True)
+        kw = dict(speaker_embed=speaker_embed, forced_alignment=forced, want_sample_ids=True,
+                  want_self_attention_probs=self.want_self_attention_alignments)
         if forced:
             kw["teacher_alignments"] = [m.teacher_alignments for m in mechs]
         if is_validation:
@@ -247,7 +257,8 @@ class _DecoderBase:
         n = int(out["n_steps"].item())  # the one host sync of a run: how many steps the stop rule allowed
         mel = out["mel"][:, :n * r]
         stop_token = out["stop"][:, :n, None]
-        state = AttentionHistoryState([a[:, :n] for a in out["alignments"]], out["stop_steps"], n)
+        sa = [p[:, hd, :n, :n] for p in out["self_attention_probs"] for hd in range(p.shape[1])]
+        state = AttentionHistoryState([a[:, :n] for a in out["alignments"]], out["stop_steps"], n, sa)
         return mel, stop_token, out["sample_ids"][:, :n], state
 
 

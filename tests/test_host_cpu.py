@@ -28,7 +28,7 @@ def test_library_exports_every_declared_symbol():
     missing = [n for n in sorted(names) if not hasattr(lib, n)]
     assert not missing, f"declared in sat.h but not exported: {missing}"
     lib.sat_abi_version.restype = ctypes.c_int
-    assert lib.sat_abi_version() == 1
+    assert lib.sat_abi_version() == 2
 
 
 def test_hparams_struct_matches_header_field_order():
