@@ -45,8 +45,15 @@ def _merge(parts, sizes):
 
 def _worker(conn, fn, kwargs):
     try:
-        os.environ["OMP_NUM_THREADS"] = "1"
+        # one BLAS / OpenMP thread per worker: the parallelism is over rows, and N workers x N BLAS threads thrash
+        # (setting OMP_NUM_THREADS here would be too late -- numpy is already loaded in the forked child)
+        try:
+            from threadpoolctl import threadpool_limits
+            limit = threadpool_limits(limits=1)
+        except ImportError:  # pragma: no cover
+            limit = None
         conn.send(("ok", _shrink(fn(**kwargs))))
+        del limit
     except BaseException as e:  # noqa: BLE001 -- reported to the parent
         import traceback
         conn.send(("err", f"{e!r}\n{traceback.format_exc()}"))
@@ -57,7 +64,11 @@ def _worker(conn, fn, kwargs):
 def run_rows_parallel(fn, row_kwargs, shared_kwargs, B, nproc=None, drop=("sa_probs_steps", "sources")):
     """fn(**row_kwargs[rows], **shared_kwargs) over contiguous row chunks in forked processes; results merged on
     axis 0.  row_kwargs: {name: array with leading axis B (or None)}."""
-    nproc = max(1, min(nproc or (os.cpu_count() or 1), B))
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except AttributeError:  # pragma: no cover
+        cores = os.cpu_count() or 1
+    nproc = max(1, min(nproc or cores, B))
     bounds = np.linspace(0, B, nproc + 1).astype(int)
     chunks = [(int(a), int(b)) for a, b in zip(bounds[:-1], bounds[1:]) if b > a]
     ctx = mp.get_context("fork")

@@ -36,8 +36,8 @@ def synthesize(ids, lengths, W, hp, *, target=None, speaker_ids=None, mode="free
     speaker_embed = None
     if getattr(hp, "use_speaker_embedding", False) and speaker_ids is not None:
         speaker_embed = embedding(W["speaker_embedding"], speaker_ids, hp.speaker_embedding_offset)
-        if not hp.speaker_embedd_to_prenet:
-            speaker_embed = None
+        if getattr(hp, "speaker_embedding_projection_out_dim", -1) > -1:  # models/models.py:73-75
+            speaker_embed = nn.relu(nn.dense(speaker_embed, *kb(W, "speaker_embedding_projection")))
     if hp.encoder == "SelfAttentionCBHGEncoder":
         lstm_out, sa_out, enc_align = self_attention_cbhg_encoder(ids, lengths, W, hp)
         sources = (lstm_out, sa_out)
@@ -46,6 +46,11 @@ def synthesize(ids, lengths, W, hp, *, target=None, speaker_ids=None, mode="free
         enc_align = []
     else:
         raise ValueError(f"Unknown encoder: {hp.encoder}")
+    if speaker_embed is not None and getattr(hp, "speaker_embedd_to_decoder", False):  # models/models.py:78-83
+        tile = lambda s: np.concatenate([s, np.repeat(speaker_embed[:, None, :], s.shape[1], axis=1)], axis=-1)  # noqa: E731
+        sources = tuple(tile(s) for s in sources) if isinstance(sources, tuple) else tile(sources)
+    if speaker_embed is not None and not hp.speaker_embedd_to_prenet:
+        speaker_embed = None
     kw = dict(speaker_embed=speaker_embed, stop_mode=stop_mode, max_iters=max_iters, sa_form=sa_form)
     if mode == "teacher_forced":
         res = decoder_run(sources, lengths, W, hp, hp.decoder, target=target, is_validation=True,

@@ -1,8 +1,14 @@
 """CLI twin of /root/reference/predict_mel.py:1-15 over the CUDA hot path.
 
-Usage: predict_mel.py --hparam-json-file=<path> [--hparams=<k=v,...>] --output-dir=<path>
-                      [--checkpoint=<prefix> | --checkpoint-dir=<dir>] [--name-map=<json>] [--weights=<npz>]
-                      [--sources=<npz>] [--source-tfrecords=<glob>] [--target-tfrecords=<glob>] [--batch-size=<n>]
+Usage (the reference's own options, predict_mel.py:4-14, so its Slurm scripts run unchanged):
+    predict_mel.py --source-data-root=<dir> --target-data-root=<dir> --selected-list-dir=<dir>
+                   [--selected-list-filename=<name>] --checkpoint-dir=<dir> [--checkpoint=<path>]
+                   --hparam-json-file=<path> [--hparams=<k=v,...>] --output-dir=<path>
+  -> synthesises <source-data-root>/<key>.<source_file_extension> for every key of <selected-list-dir>/<test.csv>
+     (predict_mel.py:84-119); ground truth from <target-data-root>/<key>.<target_file_extension> when present.
+Additional options of this implementation:
+    [--name-map=<json>] [--weights=<npz>] [--sources=<npz>] [--source-tfrecords=<glob>] [--target-tfrecords=<glob>]
+    [--batch-size=<n>] [--mode=free_run|validation|teacher_forced]
 
 Weights: ``--checkpoint`` (a TensorFlow V2 checkpoint prefix) or the latest checkpoint of ``--checkpoint-dir`` as in
 predict_mel.py:47-54, read without TensorFlow by sat_b200.checkpoint (``--name-map``: JSON {checkpoint variable:
@@ -35,6 +41,11 @@ def main():
     ap.add_argument("--source-tfrecords")
     ap.add_argument("--target-tfrecords")
     ap.add_argument("--batch-size", type=int, default=None)
+    ap.add_argument("--source-data-root")
+    ap.add_argument("--target-data-root")
+    ap.add_argument("--selected-list-dir")
+    ap.add_argument("--selected-list-filename", default="test.csv")
+    ap.add_argument("--mode", default="free_run", choices=["free_run", "validation", "teacher_forced"])
     args = ap.parse_args()
     hp = sat_b200.HParams()
     if args.hparam_json_file:
@@ -52,10 +63,19 @@ def main():
     else:
         W = dict(np.load(args.weights)) if args.weights else sat_b200.init_weights(hp)
     utts = []
-    if args.source_tfrecords:
+    if args.source_data_root:
+        # predict_mel.py:104-112: key list -> <root>/<key>.<extension> files
+        from sat_b200.predict_mel import load_utterances, selected_files
+        if not args.selected_list_dir:
+            raise SystemExit("--source-data-root needs --selected-list-dir (directory holding test.csv)")
+        src, tgt = selected_files(hp, args.source_data_root, args.target_data_root, args.selected_list_dir,
+                                  args.selected_list_filename)
+        print(f"A selected list file to use: {args.selected_list_dir}/{args.selected_list_filename} ({len(src)} keys)")
+        utts = load_utterances(src, tgt, hp)
+    elif args.source_tfrecords:
         from sat_b200.predict_mel import load_utterances
         utts = load_utterances(sorted(glob.glob(args.source_tfrecords)),
-                               sorted(glob.glob(args.target_tfrecords)) if args.target_tfrecords else None)
+                               sorted(glob.glob(args.target_tfrecords)) if args.target_tfrecords else None, hp)
     elif args.sources:
         z = np.load(args.sources)
         keys = sorted({k.split("/")[0] for k in z.files})
@@ -64,7 +84,7 @@ def main():
     else:
         rng = np.random.default_rng(12345)
         utts = [Utterance(i, f"synthetic_{i:04d}", rng.integers(1, 71, size=int(rng.integers(20, 60)))) for i in range(4)]
-    res = predict(hp, W, utts, output_dir=args.output_dir, batch_size=args.batch_size)
+    res = predict(hp, W, utts, output_dir=args.output_dir, batch_size=args.batch_size, mode=args.mode)
     for v in res:
         print(v.key, v.predicted_mel.shape)
 

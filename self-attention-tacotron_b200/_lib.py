@@ -88,8 +88,9 @@ def tensor_list(weights):
 
 
 def _mem_dims(hp):
-    extra = hp.speaker_embedding_dim if getattr(hp, "speaker_embedd_to_decoder", False) else 0
-    return [hp.cbhg_out_units + extra, hp.self_attention_out_units + extra]
+    from .weights import _mem_dims as md
+    d = md(hp)
+    return d if len(d) == 2 else d + [0]
 
 
 def make_hparams(hp):
@@ -99,8 +100,10 @@ def make_hparams(hp):
               "num_highway", "self_attention_out_units", "self_attention_num_heads", "self_attention_num_hop",
               "attention_out_units", "decoder_out_units", "attention_kernel", "attention_filters",
               "decoder_self_attention_out_units", "decoder_self_attention_num_heads",
-              "decoder_self_attention_num_hop", "speaker_embedding_dim", "max_iters"):
+              "decoder_self_attention_num_hop", "max_iters"):
         setattr(s, n, int(getattr(hp, n)))
+    from .weights import speaker_dim
+    s.speaker_embedding_dim = int(speaker_dim(hp))
     if hp.encoder not in SAT_ENC:
         raise ValueError(f"Unknown encoder: {hp.encoder}")
     if hp.decoder not in SAT_DEC:

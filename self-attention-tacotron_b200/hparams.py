@@ -4,9 +4,11 @@ Same key names and default values as the reference's global
 ``tf.contrib.training.HParams`` object (/root/reference/hparams.py:11-225), and
 the same two override entry points the reference CLIs use
 (``parse_json(file)`` then ``parse("k=v,...")``; train.py:110-115,
-predict_mel.py:95-100) -- without TensorFlow.  Only keys that the synthesis
-path reads are listed; unknown keys in a JSON file are kept (so the example
-JSONs load unchanged) but nothing on the path looks at them.
+predict_mel.py:95-100) -- without TensorFlow.  ``_DEFAULTS`` holds the keys
+the synthesis path reads; ``_INERT`` carries every other key of the reference
+(training schedule, preprocessing, dataset pipeline, vocoder-parameter
+decoders) with its default so that any reference command line or JSON parses
+here exactly as it does there -- nothing on the path looks at those values.
 """
 import ast
 import copy
@@ -59,16 +61,55 @@ _DEFAULTS = dict(
 )
 
 
+# keys of hparams.py:11-225 that the synthesis path never reads (kept for config compatibility)
+_INERT = dict(
+    # audio analysis / feature statistics
+    num_mgcs=60, num_freq=2049, sample_rate=48000, frame_length_ms=50.0, ref_level_db=20,
+    average_mel_level_db=(0.0,), stddev_mel_level_db=(0.0,), min_mel_level_db=(0.0,),
+    mgc_dim=60, mgc_alpha=0.77, mgc_gamma=0.0, mgc_fft_len=4096,
+    num_lf0s=256, f0_max=529.0, f0_min=66.0, lf0_loss_factor=0.5,
+    trim_top_db=30, trim_frame_length=1024, trim_hop_length=256, num_silent_frames=0,
+    # dataset / text front end
+    dataset="codes.dataset.DatasetSource", source="phone", source_file_extension="source.tfrecord",
+    target_file_extension="target.tfrecord", phoneme="flite",
+    flite_binary_path="/home/s1738075/taco_modified/self_attention_tacotron/flite",
+    phoneset_path="/home/s1738075/taco_modified/self_attention_tacotron/extensions/phoneset/uscmu_phoneset.json",
+    embedding_file="",
+    # accent-type encoders, EncoderV2, CBHG post-net, self-attention encoder variants (not on the hot path)
+    use_accent_type=False, accent_type_embedding_dim=32, num_accent_type=129, accent_type_offset=0x3100,
+    accent_type_unknown=0x3180, accent_type_prenet_out_units=(32, 16), encoder_prenet_out_units_if_accent=(224, 112),
+    encoder_v2_num_conv_layers=3, encoder_v2_kernel_size=5, encoder_v2_out_units=512, encoder_v2_drop_rate=0.5,
+    self_attention_encoder_out_units=32,
+    post_net_cbhg_out_units=256, post_net_conv_channels=128, post_net_max_filter_width=8,
+    post_net_projection1_out_channels=256, post_net_projection2_out_channels=80, post_net_num_highway=4,
+    # optimiser / schedule / losses
+    initial_learning_rate=0.002, decay_learning_rate=True, learning_rate_step_factor=1,
+    adam_beta1=0.9, adam_beta2=0.999, adam_eps=1e-8, use_l2_regularization=False, l2_regularization_weight=1e-7,
+    code_loss_type="l1",
+    # estimator run configuration
+    save_summary_steps=50, save_checkpoints_steps=50, keep_checkpoint_max=20000, keep_checkpoint_every_n_hours=1,
+    log_step_count_steps=1, alignment_save_steps=50, save_training_time_metrics=False,
+    num_evaluation_steps=5, keep_eval_results_max_epoch=10, eval_start_delay_secs=120, eval_throttle_secs=600,
+    record_profile=False, profile_steps=50, logfile="log.txt",
+    warm_start=False, ckpt_to_initialize_from="", vars_to_warm_start=(".*",),
+    # tf.data input pipeline
+    interleave_cycle_length_cpu_factor=1.0, interleave_cycle_length_min=4, interleave_cycle_length_max=16,
+    interleave_buffer_output_elements=200, interleave_prefetch_input_elements=200, prefetch_buffer_size=4,
+    use_cache=False, cache_file_name="", suffle_buffer_size=64,
+)
+
+
 class HParams:
-    """Attribute bag with the reference's names (hparams.py:11-225)."""
+    """Attribute bag with the reference's names and defaults (hparams.py:11-225): all of its keys."""
 
     def __init__(self, **overrides):
+        self.__dict__.update(copy.deepcopy(_INERT))
         self.__dict__.update(copy.deepcopy(_DEFAULTS))
         self.override(**overrides)
 
     def override(self, **kw):
         for k, v in kw.items():
-            if isinstance(v, list) and isinstance(_DEFAULTS.get(k), tuple):
+            if isinstance(v, list) and isinstance(_DEFAULTS.get(k, _INERT.get(k)), tuple):
                 v = tuple(v)
             setattr(self, k, v)
         return self
@@ -99,7 +140,8 @@ class HParams:
             elif isinstance(cur, (int, float)):
                 val = type(cur)(ast.literal_eval(raw))
             elif isinstance(cur, (tuple, list)):
-                val = tuple(ast.literal_eval(raw))
+                val = ast.literal_eval(raw)
+                val = tuple(val) if isinstance(val, (tuple, list)) else (val,)
             else:
                 val = raw
             setattr(self, name, val)

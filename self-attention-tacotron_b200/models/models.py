@@ -94,8 +94,17 @@ class SynthesisModel:
             if p.speaker_for_synthesis > -1:
                 ids = torch.full_like(speaker_id, p.speaker_for_synthesis)
             spk = self.speaker_embedding(ids)
+            if p.speaker_embedding_projection_out_dim > -1:
+                # models/models.py:73-75: resize the speaker embedding with a relu Dense
+                from .. import engine
+                spk = engine.dense_forward(spk, self.weights["speaker_embedding_projection/kernel"],
+                                           self.weights["speaker_embedding_projection/bias"], "relu")
             if p.speaker_embedd_to_decoder:
-                raise NotImplementedError("speaker_embedd_to_decoder (tile+concat onto encoder outputs)")
+                # models/models.py:78-83: tile over time, concatenate onto the encoder outputs (tensor plumbing only)
+                tiled = spk[:, None, :].expand(-1, sources[0].shape[1], -1) if self.dual else \
+                    spk[:, None, :].expand(-1, sources.shape[1], -1)
+                sources = tuple(torch.cat((s_, tiled), dim=-1) for s_ in sources) if self.dual else \
+                    torch.cat((sources, tiled), dim=-1)
         spk_prenet = spk if p.speaker_embedd_to_prenet else None
         forced = p.use_forced_alignment_mode
         kw = dict(speaker_embed=spk_prenet, is_training=False, is_validation=is_validation or forced,

@@ -9,6 +9,7 @@ from collections import namedtuple
 import torch
 
 from .. import engine, _lib
+from . import rnn_wrappers, helpers
 from ..hparams import HParams
 
 
@@ -226,6 +227,17 @@ class _DecoderBase:
             self._handles[key] = (engine.DecoderHandle(hp, self.weights), hp)
         return self._handles[key]
 
+    def _cell_stack(self, mechs):
+        """The RNNCell wrapper stack of the reference for this decoder (modules/rnn_wrappers.py), as a declarative
+        description: rnn_wrappers.compose() maps it to the persistent-kernel form that implements it."""
+        cell = "DecoderRNNV2"
+        if self.kind == "DualSourceTransformerDecoder":
+            cell = rnn_wrappers.TransformerWrapper(rnn_wrappers.RNNStateHistoryWrapper(cell, self.max_iters),
+                                                   self._base.get("decoder_self_attention_num_hop", 1),
+                                                   mechs[0].memory_sequence_length)
+        return rnn_wrappers.OutputAndStopTokenTransparentWrapper(cell, self._base["num_mels"] * self.outputs_per_step,
+                                                                 "out_projection", "stop_token_projection")
+
     def _trained_kind(self, i):
         p = f"decoder/attention{i}"
         if p + "/location_conv/kernel" in self.weights:
@@ -243,17 +255,24 @@ class _DecoderBase:
                   want_self_attention_probs=self.want_self_attention_alignments)
         if forced:
             kw["teacher_alignments"] = [m.teacher_alignments for m in mechs]
+        # the cell composition the reference would build (modules/module.py:767-775 / :599-600) selects the kernel form
+        assert rnn_wrappers.compose(self._cell_stack(mechs)) in (None, self.kind)
+        # the seq2seq Helper the reference would construct (modules/module.py:604-617, 728-741) carries the feed and
+        # stop rule of the run
+        B = mechs[0].memory.shape[0]
         if is_validation:
             if target is None:
                 raise ValueError("validation mode needs target")
-            S = min(target.shape[1] // r, self.max_iters)
-            feed = _lib.FEED_TEACHER if teacher_forcing else (_lib.FEED_SELF_SOFTMAX if softmax_feed else _lib.FEED_SELF)
-            out = h.run([m.memory for m in mechs], mechs[0].memory_sequence_length, target=target, feed_mode=feed,
-                        stop_mode=_lib.STOP_FIXED, max_steps=S, **kw)
+            cls = helpers.OneHotValidationHelper if softmax_feed else helpers.ValidationHelper
+            helper = cls(target, B, hp.num_mels, r, n_feed_frame=hp.n_feed_frame, teacher_forcing=teacher_forcing)
+            out = h.run([m.memory for m in mechs], mechs[0].memory_sequence_length, target=target,
+                        feed_mode=helper.feed_mode, stop_mode=helper.stop_mode,
+                        max_steps=min(helper.num_steps, self.max_iters), **kw)
         else:
-            stop = _lib.STOP_ALL_ROWS if self.stop_mode == "all_rows" else _lib.STOP_PER_ROW
-            out = h.run([m.memory for m in mechs], mechs[0].memory_sequence_length, feed_mode=_lib.FEED_SELF,
-                        stop_mode=stop, max_steps=self.max_iters, **kw)
+            helper = helpers.StopTokenBasedInferenceHelper(B, hp.num_mels, r, n_feed_frame=hp.n_feed_frame)
+            stop = helper.stop_mode if self.stop_mode == "all_rows" else _lib.STOP_PER_ROW
+            out = h.run([m.memory for m in mechs], mechs[0].memory_sequence_length, feed_mode=helper.feed_mode,
+                        stop_mode=stop, max_steps=self.max_iters, min_iters=helper.min_iters, **kw)
         n = int(out["n_steps"].item())  # the one host sync of a run: how many steps the stop rule allowed
         mel = out["mel"][:, :n * r]
         stop_token = out["stop"][:, :n, None]

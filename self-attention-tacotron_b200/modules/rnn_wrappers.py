@@ -48,10 +48,12 @@ class OutputAndStopTokenTransparentWrapper(TransparentRNNCellLike):
 
 
 def compose(cell):
-    """-> 'DualSourceTransformerDecoder' | 'DualSourceDecoder' kernel composition for a wrapper stack."""
+    """Wrapper stack -> the persistent-kernel form that implements it: 'DualSourceTransformerDecoder' (KV-cached
+    self-attention hops inside the step) or None for the plain projection-wrapped cell (ExtendedDecoder /
+    DualSourceDecoder differ in their attention mechanisms, not in the cell stack); anything else raises."""
     names = cell.layers()
     if names[:3] == ["OutputAndStopTokenTransparentWrapper", "TransformerWrapper", "RNNStateHistoryWrapper"]:
         return "DualSourceTransformerDecoder"
-    if names[:1] == ["OutputAndStopTokenTransparentWrapper"]:
-        return "DualSourceDecoder"
+    if names == ["OutputAndStopTokenTransparentWrapper", "str"]:
+        return None  # plain DecoderRNNV2 under the projection wrapper: ExtendedDecoder / DualSourceDecoder
     raise ValueError(f"unsupported decoder cell composition: {names}")

@@ -51,7 +51,15 @@ def _pad_batch(utts, hp, device):
         target = torch.from_numpy(tgt).pin_memory().to(device, non_blocking=True)
     spk = None
     if hp.use_speaker_embedding:
-        spk = torch.tensor([int(u.speaker_id) for u in utts], dtype=torch.int64).to(device)
+        if hp.speaker_for_synthesis > -1:
+            sid = [int(hp.speaker_for_synthesis)] * B
+        elif any(u.speaker_id is None for u in utts):
+            missing = [u.key for u in utts if u.speaker_id is None][:3]
+            raise ValueError(f"use_speaker_embedding is set but utterances {missing} carry no speaker_id "
+                             "(VCTK / codes source records have one: datasets/vctk/dataset.py:70)")
+        else:
+            sid = [int(u.speaker_id) for u in utts]
+        spk = torch.tensor(sid, dtype=torch.int64).to(device)
     return (torch.from_numpy(ids).pin_memory().to(device, non_blocking=True),
             torch.from_numpy(lengths).pin_memory().to(device, non_blocking=True), target, spk)
 
@@ -108,20 +116,44 @@ def write_predicted_mel(v, hparams, output_dir):
     np.ascontiguousarray(mel, dtype="<f4").tofile(path)
     # predict_mel.py:70-74: the prediction record next to it (TFRecord, tf.train.Example; see tfrecord.py)
     text = v.text.decode("utf-8") if isinstance(v.text, bytes) else str(v.text or "")
-    tfrecord.write_prediction_result(v.id, key, mel, v.ground_truth_mel, text, v.source,
+    alignments = [a for a in (v.alignment, v.alignment2, v.alignment3, v.alignment4, v.alignment5, v.alignment6)
+                  if a is not None]
+    tfrecord.write_prediction_result(v.id, key, alignments, mel, v.ground_truth_mel, text, v.source, v.accent_type,
                                      os.path.join(output_dir, f"{key}.tfrecord"))
     return path
 
 
-def load_utterances(source_files, target_files=None):
+def load_utterances(source_files, target_files=None, hparams=None):
     """Source (and optional target) TFRecord files written by the reference's preprocessing
-    (preprocess/ljspeech.py:23-44) -> list[Utterance]; targets are matched to sources by key."""
+    (preprocess/ljspeech.py:23-44; VCTK / codes form datasets/codes/dataset.py:66-96) -> list[Utterance]; targets are
+    matched to sources by key.  With ``hparams.source == 'phone'`` the phone sequence of a VCTK / codes record is
+    the model input (datasets/codes/dataset.py:147-149); the record's speaker_id travels with the utterance."""
     targets = {}
     for f in target_files or []:
+        if not os.path.exists(f):
+            continue
         for t in tfrecord.read_target_data(f):
             targets[t.key] = t.mel
     utts = []
     for f in source_files:
         for s in tfrecord.read_source_data(f):
-            utts.append(Utterance(s.id, s.key, s.source, text=s.text, mel=targets.get(s.key)))
+            ids, text = s.source, s.text
+            if hparams is not None and getattr(hparams, "source", None) == "phone" and s.phone is not None:
+                ids, text = s.phone, s.phone_txt
+            utts.append(Utterance(s.id, s.key, ids, text=text, mel=targets.get(s.key), speaker_id=s.speaker_id))
     return utts
+
+
+def load_key_list(filename, in_dir):
+    """predict_mel.py:77-81: one utterance key per line."""
+    with open(os.path.join(in_dir, filename), mode="r", encoding="utf-8") as f:
+        return [line.rstrip("\n") for line in f if line.rstrip("\n")]
+
+
+def selected_files(hparams, source_data_root, target_data_root, selected_list_dir, selected_list_filename="test.csv"):
+    """predict_mel.py:106-112: <root>/<key>.<source_file_extension> / <key>.<target_file_extension> for every key of
+    the selected list."""
+    keys = load_key_list(selected_list_filename or "test.csv", selected_list_dir)
+    src = [os.path.join(source_data_root, f"{k}.{hparams.source_file_extension}") for k in keys]
+    tgt = [os.path.join(target_data_root, f"{k}.{hparams.target_file_extension}") for k in keys] if target_data_root else []
+    return src, tgt

@@ -143,15 +143,16 @@ def _fields(buf):
         yield field, wt, v
 
 
-def encode_example(features: dict) -> bytes:
-    """features: name -> list/tuple of bytes | of ints | of floats (numpy arrays of int / float dtype work too)."""
+def encode_example(features: dict, bytes_features=()) -> bytes:
+    """features: name -> list/tuple of bytes | of ints | of floats (numpy arrays of int / float dtype work too);
+    names in `bytes_features` are BytesList features even when their list is empty."""
     entries = b""
     for name in sorted(features):
         v = features[name]
         if isinstance(v, (bytes, str)):
             raise TypeError(f"feature {name!r} must be a list (reference: assert isinstance(value, Iterable))")
         v = list(v)
-        if v and isinstance(v[0], bytes):
+        if (v and isinstance(v[0], bytes)) or (not v and name in bytes_features):
             feat = _ld(1, b"".join(_ld(1, x) for x in v))
         elif v and isinstance(v[0], (float, np.floating)):
             feat = _ld(2, _ld(1, struct.pack(f"<{len(v)}f", *v)))
@@ -202,30 +203,60 @@ def decode_example(buf: bytes) -> dict:
 
 # ---- the reference's record schemas -----------------------------------------------------------------------------------
 
-SourceData = namedtuple("SourceData", ["id", "key", "source", "source_length", "text"])
+class SourceData(namedtuple("SourceData", ["id", "key", "source", "source_length", "text", "speaker_id", "age", "gender",
+                                           "phone", "phone_length", "phone_txt"])):
+    """LJSpeech source records carry the first five fields (datasets/ljspeech/dataset.py:52-72); the VCTK / codes
+    records add speaker_id, age, gender and the phone sequence (datasets/codes/dataset.py:66-96,
+    datasets/vctk/dataset.py:64-77).  Absent features read as None."""
+
+    def __new__(cls, id, key, source, source_length, text, speaker_id=None, age=None, gender=None, phone=None,
+                phone_length=None, phone_txt=None):
+        return super().__new__(cls, id, key, source, source_length, text, speaker_id, age, gender, phone, phone_length,
+                               phone_txt)
+
+
 TargetData = namedtuple("TargetData", ["id", "key", "mel", "mel_width", "target_length"])
+# utils/tfrecord.py:20-22
+CodeData = namedtuple("CodeData", ["id", "key", "lang", "codes", "codes_length", "codes_width"])
+# utils/tfrecord.py:30-32 (+ the alignments the writer family stores, :176)
 PredictionResult = namedtuple("PredictionResult", ["id", "key", "mel", "mel_length", "mel_width", "ground_truth_mel",
-                                                   "ground_truth_mel_length", "text", "source", "source_length"])
+                                                   "ground_truth_mel_length", "text", "source", "source_length",
+                                                   "alignment"])
+CodePredictionResult = namedtuple("CodePredictionResult", ["id", "key", "codes", "codes_length", "codes_width",
+                                                           "ground_truth_codes", "ground_truth_codes_length", "text",
+                                                           "source", "source_length"])
 
 
-def write_source_data(id_, key, source, text, filename):
-    """preprocess/ljspeech.py:35-44"""
+def write_source_data(id_, key, source, text, filename, speaker_id=None, age=None, gender=None, phone=None,
+                      phone_txt=None):
+    """preprocess/ljspeech.py:35-44; with speaker_id / age / gender / phone the VCTK / codes form
+    (datasets/codes/dataset.py:66-79)."""
     source = np.asarray(source, dtype=np.int64)
-    write_records(filename, [encode_example({
-        "id": [int(id_)], "key": [key.encode("utf-8")], "source": [source.tobytes()],
-        "source_length": [len(source)], "text": [text.encode("utf-8")]})])
+    feats = {"id": [int(id_)], "key": [key.encode("utf-8")], "source": [source.tobytes()],
+             "source_length": [len(source)], "text": [text.encode("utf-8")]}
+    if speaker_id is not None:
+        feats.update(speaker_id=[int(speaker_id)], age=[int(age or 0)], gender=[int(gender or 0)])
+    if phone is not None:
+        phone = np.asarray(phone, dtype=np.int64)
+        feats.update(phone=[phone.tobytes()], phone_length=[len(phone)], phone_txt=[(phone_txt or "").encode("utf-8")])
+    write_records(filename, [encode_example(feats)])
 
 
 def read_source_data(filename):
-    """datasets/ljspeech/dataset.py:52-72 -> list of SourceData (source as int64 ndarray)."""
+    """datasets/ljspeech/dataset.py:52-72 / datasets/codes/dataset.py:66-96 -> list of SourceData (ids as int64)."""
     out = []
     for rec in read_records(filename):
         e = decode_example(rec)
         src = np.frombuffer(e["source"][0], dtype="<i8").copy()
         if len(src) != e["source_length"][0]:
             raise ValueError(f"{filename}: source_length {e['source_length'][0]} != {len(src)} ids")
+        one = lambda k: e[k][0] if e.get(k) else None  # noqa: E731
+        phone = np.frombuffer(e["phone"][0], dtype="<i8").copy() if e.get("phone") else None
+        if phone is not None and len(phone) != one("phone_length"):
+            raise ValueError(f"{filename}: phone_length {one('phone_length')} != {len(phone)} ids")
         out.append(SourceData(e["id"][0], e["key"][0].decode("utf-8"), src, e["source_length"][0],
-                              e["text"][0].decode("utf-8")))
+                              e["text"][0].decode("utf-8"), one("speaker_id"), one("age"), one("gender"), phone,
+                              one("phone_length"), e["phone_txt"][0].decode("utf-8") if e.get("phone_txt") else None))
     return out
 
 
@@ -247,26 +278,89 @@ def read_target_data(filename):
     return out
 
 
-def write_prediction_result(id_, key, mel, ground_truth_mel, text, source, filename):
-    """The mel twin of utils/tfrecord.py write_prediction_result (same field naming scheme, mel instead of codes)."""
+def write_code_data(id_, key, lang, codes, filename):
+    """Target record of the code models, the schema utils/tfrecord.py:62-113 parses: ``codes`` = raw float32
+    [codes_length, codes_width] (one-hot rows), ``lang`` bytes."""
+    codes = np.ascontiguousarray(codes, dtype="<f4")
+    write_records(filename, [encode_example({
+        "id": [int(id_)], "key": [key.encode("utf-8")], "lang": [lang.encode("utf-8")], "codes": [codes.tobytes()],
+        "codes_length": [codes.shape[0]], "codes_width": [codes.shape[1]]})])
+
+
+def read_code_data(filename):
+    """utils/tfrecord.py:62-113 (parse_preprocessed_code_data + decode_preprocessed_code_data)."""
+    out = []
+    for rec in read_records(filename):
+        e = decode_example(rec)
+        n, w = e["codes_length"][0], e["codes_width"][0]
+        codes = np.frombuffer(e["codes"][0], dtype="<f4")
+        if codes.size != n * w:
+            raise ValueError(f"{filename}: codes has {codes.size} values, expected {n} x {w}")
+        out.append(CodeData(e["id"][0], e["key"][0].decode("utf-8"), e["lang"][0].decode("utf-8"),
+                            codes.reshape(n, w).copy(), n, w))
+    return out
+
+
+def write_prediction_result(id_, key, alignments, mel, ground_truth_mel, text, source, accent_type, filename):
+    """predict_mel.py:72-74 calls write_prediction_result(id, key, alignments, mel, ground_truth_mel, text, source,
+    accent_type, path); the record is the one utils/tfrecord.py:183-195 (parse_prediction_result) declares: mel
+    / mel_length / mel_width, ground truth, ``alignment`` (bytes list, one raw float32 array per alignment like
+    :176), text, source."""
     mel = np.ascontiguousarray(mel, dtype="<f4")
     gt = np.ascontiguousarray(ground_truth_mel if ground_truth_mel is not None else np.zeros((0, mel.shape[1])), dtype="<f4")
     source = np.asarray(source, dtype=np.int64)
-    write_records(filename, [encode_example({
+    feats = {
         "id": [int(id_)], "key": [key.encode("utf-8")], "mel": [mel.tobytes()], "mel_length": [mel.shape[0]],
         "mel_width": [mel.shape[1]], "ground_truth_mel": [gt.tobytes()], "ground_truth_mel_length": [gt.shape[0]],
-        "text": [text.encode("utf-8")], "source": [source.tobytes()], "source_length": [len(source)]})])
+        "alignment": [np.ascontiguousarray(a, dtype="<f4").tobytes() for a in (alignments or []) if a is not None],
+        "text": [text.encode("utf-8")], "source": [source.tobytes()], "source_length": [len(source)]}
+    if accent_type is not None:
+        feats["accent_type"] = [np.asarray(accent_type).tobytes()]
+    write_records(filename, [encode_example(feats, bytes_features=("alignment",))])
 
 
 def read_prediction_result(filename):
+    """utils/tfrecord.py:183-215; ``alignment`` -> list of float32 arrays [source_length, -1] (memory x steps)."""
     out = []
     for rec in read_records(filename):
         e = decode_example(rec)
         w = e["mel_width"][0]
+        n_src = e["source_length"][0]
+        aligns = []
+        for a in e.get("alignment", []):
+            a = np.frombuffer(a, dtype="<f4").copy()
+            aligns.append(a.reshape(n_src, -1) if n_src and a.size % n_src == 0 else a)
         out.append(PredictionResult(
             e["id"][0], e["key"][0].decode("utf-8"),
             np.frombuffer(e["mel"][0], dtype="<f4").reshape(e["mel_length"][0], w).copy(), e["mel_length"][0], w,
             np.frombuffer(e["ground_truth_mel"][0], dtype="<f4").reshape(e["ground_truth_mel_length"][0], w).copy(),
             e["ground_truth_mel_length"][0], e["text"][0].decode("utf-8"),
+            np.frombuffer(e["source"][0], dtype="<i8").copy(), n_src, aligns))
+    return out
+
+
+def write_code_prediction_result(id_, key, alignments, codes, ground_truth_codes, text, source, accent_type, filename):
+    """utils/tfrecord.py:144-157 (the live writer of this fork, called by predict_code.py): the alignments and
+    accent_type arguments are accepted and, as in the reference, not stored."""
+    codes = np.ascontiguousarray(codes, dtype="<f4")
+    gt = np.ascontiguousarray(ground_truth_codes if ground_truth_codes is not None else np.zeros((0, codes.shape[1])),
+                              dtype="<f4")
+    source = np.asarray(source, dtype=np.int64)
+    write_records(filename, [encode_example({
+        "id": [int(id_)], "key": [key.encode("utf-8")], "codes": [codes.tobytes()], "codes_length": [codes.shape[0]],
+        "codes_width": [codes.shape[1]], "ground_truth_codes": [gt.tobytes()], "ground_truth_codes_length": [gt.shape[0]],
+        "text": [text.encode("utf-8")], "source": [source.tobytes()], "source_length": [len(source)]})])
+
+
+def read_code_prediction_result(filename):
+    out = []
+    for rec in read_records(filename):
+        e = decode_example(rec)
+        w = e["codes_width"][0]
+        out.append(CodePredictionResult(
+            e["id"][0], e["key"][0].decode("utf-8"),
+            np.frombuffer(e["codes"][0], dtype="<f4").reshape(e["codes_length"][0], w).copy(), e["codes_length"][0], w,
+            np.frombuffer(e["ground_truth_codes"][0], dtype="<f4").reshape(e["ground_truth_codes_length"][0], w).copy(),
+            e["ground_truth_codes_length"][0], e["text"][0].decode("utf-8"),
             np.frombuffer(e["source"][0], dtype="<i8").copy(), e["source_length"][0]))
     return out

@@ -12,8 +12,18 @@ tests exercise every term.
 import numpy as np
 
 
+def speaker_dim(hp):
+    """width of the speaker vector the decoder sees: the embedding, or its relu projection when
+    speaker_embedding_projection_out_dim > -1 (models/models.py:73-75)"""
+    p = getattr(hp, "speaker_embedding_projection_out_dim", -1)
+    return p if p > -1 else hp.speaker_embedding_dim
+
+
 def _mem_dims(hp):
-    extra = hp.speaker_embedding_dim if getattr(hp, "speaker_embedd_to_decoder", False) else 0
+    # speaker_embedd_to_decoder: the speaker vector is tiled over time and concatenated onto both encoder outputs
+    # (models/models.py:78-83), so the attention memories (and contexts) widen by its width
+    use = getattr(hp, "use_speaker_embedding", False) and getattr(hp, "speaker_embedd_to_decoder", False)
+    extra = speaker_dim(hp) if use else 0
     if hp.decoder == "ExtendedDecoder":
         return [hp.cbhg_out_units + extra]
     return [hp.cbhg_out_units + extra, hp.self_attention_out_units + extra]
@@ -73,13 +83,15 @@ def weight_shapes(hp):
             mha(f"encoder/sa_{i}", hp.self_attention_out_units, hp.self_attention_out_units)
     if hp.use_speaker_embedding:
         s["speaker_embedding"] = ((hp.num_speakers, hp.speaker_embedding_dim), "table")
+        if hp.speaker_embedding_projection_out_dim > -1:
+            dense("speaker_embedding_projection", hp.speaker_embedding_dim, hp.speaker_embedding_projection_out_dim)
 
     # ---- decoder (modules/module.py:562-623, 1017-1152, 1499-1562) ----
     M, r, nf = hp.num_mels, hp.outputs_per_step, hp.n_feed_frame
     pu = hp.decoder_prenet_out_units
     if hp.use_speaker_embedding and hp.speaker_embedd_to_prenet:
         dense("decoder/prenet/ms/dense0", M * nf, pu[0])
-        dense("decoder/prenet/ms/speaker_projection", hp.speaker_embedding_dim, pu[0])
+        dense("decoder/prenet/ms/speaker_projection", speaker_dim(hp), pu[0])
         dense("decoder/prenet/ms/dense", pu[0], pu[0])
         dense("decoder/prenet/dense_1", pu[0], pu[1])
     else:

@@ -114,7 +114,15 @@ def test_cfg1_teacher_forced_full_size():
     assert len(ref["encoder_alignments"]) == hp.self_attention_num_heads * hp.self_attention_num_hop
     for k, e in errs.items():
         assert e <= TOL, f"{k}: {e:.3e}"
-    np.testing.assert_array_equal(out["predicted_samples"].cpu().numpy(), ref["sample_ids"])
+    # sample ids = argmax over the 80 mel bins per frame (modules/helpers.py:49-52): identical wherever the oracle's
+    # top-1 / top-2 gap exceeds the floating-point tolerance of the values being compared
+    vals = ref["mel"].reshape(B, S, hp.outputs_per_step, hp.num_mels).astype(np.float64)
+    part = np.partition(vals, -2, axis=-1)
+    gap = (part[..., -1] - part[..., -2]) / float(np.max(np.abs(vals)))
+    mism = out["predicted_samples"].cpu().numpy() != ref["sample_ids"]
+    print("[cfg1] sample ids:", int(mism.size), "mismatches", int(mism.sum()), "decidable", int((mism & (gap > TOL)).sum()),
+          "largest gap at a mismatch", float(gap[mism].max()) if mism.any() else 0.0)
+    assert int((mism & (gap > TOL)).sum()) == 0
 
 
 def test_cfg4_forced_alignment_long_utterances():

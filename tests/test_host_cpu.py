@@ -65,6 +65,21 @@ def test_hparams_json_and_overrides():
         sat_b200.config("nope")
 
 
+def test_hparams_carry_every_reference_key_with_its_default():
+    """hparams.py:11-225: the full key set and defaults (golden listing made by tests/golden/make_hparams_golden.py
+    from the reference file); a reference command line that touches training-only keys must parse here too."""
+    import json
+    ref = json.load(open(os.path.join(ROOT, "tests", "golden", "reference_hparams_defaults.json")))
+    ours = sat_b200.HParams().values()
+    assert set(ours) == set(ref) and len(ref) == 150
+    norm = lambda v: list(v) if isinstance(v, (list, tuple)) else v  # noqa: E731
+    assert {k for k in ref if norm(ours[k]) != ref[k]} == set()
+    hp = sat_b200.HParams()
+    hp.parse("batch_size=1,learning_rate_step_factor=4,vars_to_warm_start=['a','b'],use_cache=true,logfile=x.txt")
+    assert (hp.batch_size, hp.learning_rate_step_factor, hp.vars_to_warm_start, hp.use_cache, hp.logfile) == \
+        (1, 4, ("a", "b"), True, "x.txt")
+
+
 def test_decoder_parameter_counts_match_survey():
     """decoder parameters cfg1/3/4 = 2 584 216, cfg2 = 2 197 080, cfg5 = 3 048 441."""
     assert sat_b200.decoder_param_count(sat_b200.config("ljspeech_self_attention")) == 2584216

@@ -55,6 +55,26 @@ def test_teacher_forced_end_to_end(cfg, extra):
         assert rel_err(out["mel_postnet"].cpu().numpy(), ref["mel_postnet"]) <= TOL
 
 
+@pytest.mark.parametrize("to_prenet", [True, False])
+def test_speaker_embedding_to_decoder_and_projection(to_prenet):
+    """models/models.py:73-83: relu projection of the speaker embedding (speaker_embedding_projection_out_dim > -1)
+    and speaker_embedd_to_decoder (tile over time + concat onto both encoder outputs)."""
+    from sat_b200.models import tacotron_model_factory
+    hp = small_hp("vctk_self_attention", speaker_embedd_to_decoder=True, speaker_embedding_projection_out_dim=24,
+                  speaker_embedd_to_prenet=to_prenet)
+    W = sat_b200.init_weights(hp, seed=31, stress=True)
+    assert W["speaker_embedding_projection/kernel"].shape == (16, 24)
+    assert W["decoder/attention1/memory_layer/kernel"].shape[0] == hp.cbhg_out_units + 24
+    ids, lengths, target = _inputs(hp, 3, 29, 11, seed=31)
+    spk = np.array([226, 230, 300], dtype=np.int64)
+    ref = synthesize(ids, lengths, _w64(W), hp, target=target.astype(np.float64), speaker_ids=spk, mode="teacher_forced")
+    out = tacotron_model_factory(hp, W).predict(_t(ids), _t(lengths), target=_t(target), speaker_id=_t(spk),
+                                                is_validation=True, teacher_forcing=True)
+    assert rel_err(out["mel"].cpu().numpy(), ref["mel"]) <= TOL
+    assert rel_err(out["alignment"].cpu().numpy(), ref["alignments"][0].transpose(0, 2, 1)) <= TOL
+    assert rel_err(out["alignment2"].cpu().numpy(), ref["alignments"][1].transpose(0, 2, 1)) <= TOL
+
+
 def test_forced_alignment_mode_end_to_end():
     from sat_b200.models import tacotron_model_factory
     hp = small_hp("ljspeech_self_attention", use_forced_alignment_mode=True)

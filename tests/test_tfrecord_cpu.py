@@ -71,11 +71,20 @@ def test_reference_schemas_round_trip(tmp_path):
     np.testing.assert_array_equal(s.source, src)
     assert (t.id, t.key, t.mel_width, t.target_length) == (7, "LJ001-0007", 80, 123)
     np.testing.assert_array_equal(t.mel, mel)
-    tfr.write_prediction_result(7, "LJ001-0007", mel[:50], mel, s.text, src, pp)
+    al = rng.random(size=(37, 25)).astype(np.float32)
+    tfr.write_prediction_result(7, "LJ001-0007", [al], mel[:50], mel, s.text, src, None, pp)
     (p,) = tfr.read_prediction_result(pp)
     assert p.mel_length == 50 and p.ground_truth_mel_length == 123 and p.source_length == 37
     np.testing.assert_array_equal(p.mel, mel[:50])
     np.testing.assert_array_equal(p.ground_truth_mel, mel)
+    assert len(p.alignment) == 1
+    np.testing.assert_array_equal(p.alignment[0], al)
+    # every feature utils/tfrecord.py:183-195 (parse_prediction_result) declares as a required FixedLenFeature is
+    # present, each with exactly one value (one alignment: the single-source mel models predict_mel.py serves)
+    e = tfr.decode_example(next(tfr.read_records(pp)))
+    required = {"id", "key", "mel", "mel_length", "mel_width", "ground_truth_mel", "ground_truth_mel_length",
+                "alignment", "text", "source", "source_length"}
+    assert required <= set(e) and all(len(e[k]) == 1 for k in required)
     # the field set of the source record is exactly what datasets/ljspeech/dataset.py:52-60 parses
     assert set(tfr.decode_example(next(tfr.read_records(ps)))) == {"id", "key", "source", "source_length", "text"}
 
@@ -94,3 +103,69 @@ def test_load_utterances_matches_sources_and_targets(tmp_path):
     utts = load_utterances(files_s, files_t)
     assert [u.key for u in utts] == ["a", "b", "c"] and [len(u.source) for u in utts] == [10, 11, 12]
     assert utts[0].mel.shape == (20, 80) and utts[1].mel is None and utts[2].mel.shape == (22, 80)
+
+
+def test_code_record_known_answer_and_round_trips(tmp_path):
+    """Code target / prediction records (utils/tfrecord.py:62-113,144-157).  The serialized Example of a 1 x 2 code
+    record is derived by hand from example.proto / feature.proto: map entries in key order, BytesList = field 1,
+    Int64List = field 3 (packed)."""
+    codes = np.array([[0.0, 1.0]], dtype="<f4")
+
+    def entry(name, feat):
+        body = bytes([0x0A, len(name)]) + name + bytes([0x12, len(feat)]) + feat
+        return bytes([0x0A, len(body)]) + body
+
+    def blist(b):
+        inner = bytes([0x0A, len(b)]) + b
+        return bytes([0x0A, len(inner)]) + inner
+
+    def ilist(v):
+        return bytes([0x1A, 0x03, 0x0A, 0x01, v])
+
+    feats = (entry(b"codes", blist(codes.tobytes())) + entry(b"codes_length", ilist(1)) + entry(b"codes_width", ilist(2)) +
+             entry(b"id", ilist(5)) + entry(b"key", blist(b"k")) + entry(b"lang", blist(b"en")))
+    golden = bytes([0x0A, len(feats)]) + feats
+    path = os.path.join(tmp_path, "c.tfrecord")
+    tfr.write_code_data(5, "k", "en", codes, path)
+    assert next(tfr.read_records(path)) == golden
+    (c,) = tfr.read_code_data(path)
+    assert (c.id, c.key, c.lang, c.codes_length, c.codes_width) == (5, "k", "en", 1, 2)
+    np.testing.assert_array_equal(c.codes, codes)
+    # prediction record of the code models: exactly the ten features of utils/tfrecord.py:146-155
+    rng = np.random.default_rng(3)
+    pred = np.eye(6, dtype=np.float32)[rng.integers(0, 6, size=9)]
+    gt = np.eye(6, dtype=np.float32)[rng.integers(0, 6, size=11)]
+    src = rng.integers(1, 71, size=13).astype(np.int64)
+    pp = os.path.join(tmp_path, "p.tfrecord")
+    tfr.write_code_prediction_result(3, "utt", [np.zeros((13, 9), np.float32)], pred, gt, "txt", src, None, pp)
+    assert set(tfr.decode_example(next(tfr.read_records(pp)))) == {
+        "id", "key", "codes", "codes_length", "codes_width", "ground_truth_codes", "ground_truth_codes_length", "text",
+        "source", "source_length"}
+    (r,) = tfr.read_code_prediction_result(pp)
+    assert (r.id, r.key, r.codes_length, r.codes_width, r.ground_truth_codes_length, r.text) == (3, "utt", 9, 6, 11, "txt")
+    np.testing.assert_array_equal(r.codes, pred)
+    np.testing.assert_array_equal(r.ground_truth_codes, gt)
+    np.testing.assert_array_equal(r.source, src)
+
+
+def test_vctk_source_record_speaker_and_phone(tmp_path):
+    """VCTK / codes source records (datasets/codes/dataset.py:66-96): speaker_id, age, gender, phone sequence; with
+    hparams.source == 'phone' the phone ids are the model input (:147-149)."""
+    import sat_b200
+    from sat_b200.predict_mel import load_utterances, selected_files
+    rng = np.random.default_rng(4)
+    hp = sat_b200.config("vctk_self_attention")
+    root = str(tmp_path)
+    keys = ["p225_001", "p226_002"]
+    for i, k in enumerate(keys):
+        tfr.write_source_data(i, k, rng.integers(1, 71, size=12 + i), "hello", os.path.join(root, f"{k}.{hp.source_file_extension}"),
+                              speaker_id=225 + i, age=23, gender=1, phone=rng.integers(1, 60, size=7 + i), phone_txt="HH AH")
+    open(os.path.join(root, "test.csv"), "w").write("\n".join(keys) + "\n")
+    src, tgt = selected_files(hp, root, root, root, "test.csv")
+    assert [os.path.basename(f) for f in src] == [f"{k}.source.tfrecord" for k in keys] and len(tgt) == 2
+    (s0,) = tfr.read_source_data(src[0])
+    assert (s0.speaker_id, s0.age, s0.gender, s0.phone_length, s0.phone_txt) == (225, 23, 1, 7, "HH AH")
+    utts = load_utterances(src, tgt, hp)   # hp.source == 'phone' by default: the phone ids feed the model
+    assert [len(u.source) for u in utts] == [7, 8] and [u.speaker_id for u in utts] == [225, 226]
+    hp.override(source="char")
+    assert [len(u.source) for u in load_utterances(src, tgt, hp)] == [12, 13]
