@@ -144,6 +144,20 @@ void sat_decoder_destroy(sat_decoder* h);
 int sat_mha_forward(const sat_tensor* weights, int32_t n_weights, const char* prefix,
                     const float* x, int32_t B, int32_t T, int32_t Din, int32_t D, int32_t H,
                     int32_t causal, const int64_t* lengths, float* out, float* probs, void* stream);
+/* Allocation-free variant of sat_mha_forward.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  It calls no cudaMalloc / cudaFree / allocating library routine and does not synchronise the stream.
+ * Weights are DEVICE pointers supplied by the caller: wqkv [Din, 3*D] with the column blocks key | value | query,
+ * bqkv [3*D], wo [D, D], bo [D]; x [B,T,Din] -> out [B,T,D]; probs [B,H,T,T] or NULL; lengths != NULL enables the
+ * padding mask.  The qkv / context scratch (B*T*4*D floats) lives in one file-scope device array of
+ * SAT_MHA_NOALLOC_MAX_FLOATS floats (8 MiB, held by every GPU that loads the library until exit); larger problems are
+ * rejected with SAT_EINVAL.  All calls share that array: the region a call uses is cleared first, and calls that
+ * overlap on the GPU (other streams / threads) race -- serialise them. */
+#define SAT_MHA_NOALLOC_MAX_FLOATS (2 * 1024 * 1024)
+int sat_mha_forward_noalloc(const float* wqkv, const float* bqkv, const float* wo, const float* bo,
+                            const float* x, int32_t B, int32_t T, int32_t Din, int32_t D, int32_t H,
+                            int32_t causal, const int64_t* lengths, float* out, float* probs, void* stream);
+int64_t sat_mha_noalloc_max_floats(void);
 /* SelfAttentionTransformer: prefix/mha/... and prefix/transform/... ; out = x + tanh(Dense(mha(x))) */
 int sat_sat_forward(const sat_tensor* weights, int32_t n_weights, const char* prefix,
                     const float* x, int32_t B, int32_t T, int32_t D, int32_t H, int32_t causal,

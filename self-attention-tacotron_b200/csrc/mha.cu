@@ -614,3 +614,56 @@ extern "C" int sat_sat_forward(const sat_tensor* weights, int32_t n_weights, con
     SAT_CUDA(cudaStreamSynchronize(st));
   });
 }
+
+// ---- allocation-free variant of sat_mha_forward (no counterpart in the reference) ----
+// For callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it): the
+// qkv / context scratch of the attention lives in a file-scope device array of fixed size, so the entry point calls no
+// cudaMalloc / cudaFree / allocating library routine.  Every GPU that loads libsat.so holds the array (8 MiB) until
+// the process exits.  All calls share it and it keeps the last call's contents: the region a call uses is cleared
+// first, and calls that overlap on the GPU (different streams, or different host threads) race.
+static __device__ __align__(256) float g_mha_noalloc_scratch[SAT_MHA_NOALLOC_MAX_FLOATS];
+
+namespace {
+constexpr int NOALLOC_MAX_DEVICES = 64;
+float* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {nullptr};
+
+// device address of the scratch array on the CURRENT device, resolved once per device.  In host code the symbol name
+// is only a stand-in for the array, never a device address: it must go through cudaGetSymbolAddress.
+float* noalloc_scratch_ptr() {
+  int dev = 0;
+  SAT_CUDA(cudaGetDevice(&dev));
+  SAT_REQUIRE(dev >= 0 && dev < NOALLOC_MAX_DEVICES, "device index %d out of range", dev);
+  if (!g_noalloc_ptr[dev]) {
+    float* p = nullptr;
+    SAT_CUDA(cudaGetSymbolAddress((void**)&p, g_mha_noalloc_scratch));
+    SAT_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a null scratch address");
+    g_noalloc_ptr[dev] = p;
+  }
+  return g_noalloc_ptr[dev];
+}
+}  // namespace
+
+extern "C" int64_t sat_mha_noalloc_max_floats(void) { return (int64_t)SAT_MHA_NOALLOC_MAX_FLOATS; }
+
+extern "C" int sat_mha_forward_noalloc(const float* wqkv, const float* bqkv, const float* wo, const float* bo,
+                                       const float* x, int32_t B, int32_t T, int32_t Din, int32_t D, int32_t H,
+                                       int32_t causal, const int64_t* lengths, float* out, float* probs, void* stream) {
+  return guarded([&] {
+    SAT_REQUIRE(wqkv && bqkv && wo && bo && x && out && B >= 1 && T >= 1 && Din >= 1 && D >= 1, "bad argument");
+    SAT_REQUIRE(H >= 1 && D % H == 0, "model_dim %d is not a multiple of num_heads %d", D, H);
+    const int64_t need = (int64_t)B * T * 4 * D;  // qkv [B*T, 3D] + context [B*T, D]
+    SAT_REQUIRE(need <= (int64_t)SAT_MHA_NOALLOC_MAX_FLOATS,
+                "sat_mha_forward_noalloc: B*T*4*D = %lld floats of scratch exceed the fixed maximum of %lld "
+                "(SAT_MHA_NOALLOC_MAX_FLOATS); use sat_mha_forward for larger problems",
+                (long long)need, (long long)SAT_MHA_NOALLOC_MAX_FLOATS);
+    cudaStream_t st = (cudaStream_t)stream;
+    float* scratch = noalloc_scratch_ptr();
+    // the array keeps the previous call's contents: start this call's region from zero
+    SAT_CUDA(cudaMemsetAsync(scratch, 0, (size_t)need * sizeof(float), st));
+    MhaDev m;
+    m.Wqkv = const_cast<float*>(wqkv); m.bqkv = const_cast<float*>(bqkv);
+    m.Wo = const_cast<float*>(wo); m.bo = const_cast<float*>(bo);
+    m.Din = Din; m.D = D; m.H = H;
+    mha_forward(m, x, B, T, causal, lengths, out, probs, scratch, st);
+  });
+}
