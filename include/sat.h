@@ -191,6 +191,10 @@ int sat_decoder_kernel_ms(sat_decoder* h, float* ms);
 /* 1 if the last sat_decoder_run computed the LSTM gate GEMMs on the tensor cores (tcgen05, fp16 operands, fp32
  * accumulation; batch >= 64), 0 if it used the fp32 SIMT form */
 int sat_decoder_used_tensor_cores(sat_decoder* h, int32_t* used);
+/* thread-block cluster size of the last sat_decoder_run: 4 or 2 when every attention row (one
+ * ForwardAttention.__call__, modules/forward_attention.py:88-122) was split over a cluster of CTAs (small batches:
+ * B * mechanisms * size <= SM count, fp32 form), 1 when each row ran on one CTA */
+int sat_decoder_cluster_size(sat_decoder* h, int32_t* size);
 
 /* diagnostic: one-CTA self-test of the tcgen05 / TMA / TMEM building blocks (csrc/tc.cuh):
  * D[128,16] = A[128,K] . Wt[16,K]^T in TF32 with fp32 accumulation; all pointers device, K % 32 == 0, K <= 1024 */

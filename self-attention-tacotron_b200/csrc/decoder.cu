@@ -169,6 +169,8 @@ struct sat_decoder {
   bool has_outp_f = false;
   PackedDense sa_qkv[MAX_HOPS], sa_o[MAX_HOPS], sa_tr[MAX_HOPS];
   float* mem_layer[2] = {nullptr, nullptr};  // [Dm][Up]
+  float* dq_cl[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};  // [mech][0: cluster of 2, 1: cluster of 4]: query-layer
+                                                                  // weights as contiguous column slices [cl][A][Up / cl]
   float *att_v[2], *att_ba[2], *conv_w[2], *conv_b[2], *Wl[2], *Wt[2];
   float bt[2] = {0.f, 0.f};
   float *ms_Ws = nullptr, *ms_bs = nullptr;
@@ -180,7 +182,7 @@ struct sat_decoder {
   size_t max_dyn_smem = 0;
   CUtensorMap hmaps[6];
   CUtensorMap* dmaps = nullptr;  // device copy, 64-byte aligned
-  int last_tc = 0;
+  int last_tc = 0, last_cl = 1;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;  // bracket the persistent launch of the last run
   int last_B = 0, last_T = 0, last_S = 0;
   ~sat_decoder() {
@@ -251,6 +253,18 @@ extern "C" int sat_decoder_create(const sat_hparams* hpp, const sat_tensor* weig
         for (int u = 0; u < U; ++u) cm[u] = u;
         h->dq[i] = pack_cols(pool, W.get(P + "query_layer/kernel", (int64_t)A * U), nullptr, A, U, cm);
         add_row_major(pool, h->dq[i], W.get(P + "query_layer/kernel", (int64_t)A * U), A, U, U, Up);
+        // column slices for the cluster-split rows of the small-batch form (decoder_kernel.cuh, DecParams::cl)
+        const float* wq = W.get(P + "query_layer/kernel", (int64_t)A * U);
+        for (int ci = 0; ci < 2; ++ci) {
+          const int cl = 2 << ci, sw = Up / cl;
+          if (Up % (32 * cl)) continue;
+          std::vector<float> sl((size_t)A * Up, 0.f);
+          for (int r = 0; r < cl; ++r)
+            for (int k = 0; k < A; ++k)
+              for (int n = 0; n < sw; ++n)
+                if (r * sw + n < U) sl[((size_t)r * A + k) * sw + n] = wq[(size_t)k * U + r * sw + n];
+          h->dq_cl[i][ci] = pool.upload(sl);
+        }
       }
       h->att_v[i] = padU(W.get(P + "attention_v", U), 1);
       std::vector<float> zeros(Up, 0.f);
@@ -436,7 +450,6 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
     if (const char* e = getenv("SAT_TC")) use_tc = atoi(e) != 0;
     use_tc = use_tc && (A % 4 == 0) && (Dd % 4 == 0);
     const int RB = ceil_div(Bp, TC_M);
-    size_t smem_floats = SCRATCH_FLOATS;
     size_t smem_bytes = 0;
     if (use_tc) {
       TcLstmDesc* td[3] = {&p.tc_a, &p.tc_1, &p.tc_2};
@@ -512,17 +525,22 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
     for (DenseDesc* d : lst) plan_rows(*d, true);
     plan_rows(p.pre0, false); plan_rows(p.pre1, false); plan_rows(p.outp, false);
     if (p.ms) plan_rows(p.msd, false);
-    for (DenseDesc* d : lst) {
-      if (use_tc) break;
-      const int slots = ceil_div(d->n_tiles * d->R, h->grid);
-      const size_t need = (size_t)slots * d->K * TILE_N;
-      if ((smem_floats + need) * sizeof(float) <= h->max_dyn_smem) {
-        d->smem_off = (int)(smem_floats - SCRATCH_FLOATS);
-        d->slots = slots;
-        smem_floats += need;
+    auto plan_simt = [&](int grid) {  // resident LSTM tiles of the SIMT form for a launch of `grid` CTAs -> bytes
+      size_t fl = SCRATCH_FLOATS;
+      for (DenseDesc* d : lst) {
+        d->smem_off = -1;
+        d->slots = 0;
+        const int slots = ceil_div(d->n_tiles * d->R, grid);
+        const size_t need = (size_t)slots * d->K * TILE_N;
+        if ((fl + need) * sizeof(float) <= h->max_dyn_smem) {
+          d->smem_off = (int)(fl - SCRATCH_FLOATS);
+          d->slots = slots;
+          fl += need;
+        }
       }
-    }
-    if (!use_tc) smem_bytes = smem_floats * sizeof(float);
+      return fl * sizeof(float);
+    };
+    if (!use_tc) smem_bytes = plan_simt(h->grid);
     // ---- attention row plan: per-position arrays sized by this batch's T; two concurrent rows per CTA when they fit ----
     int att_TS = (T + 15) / 16 * 16, att_FB = 8 * att_TS;
     for (int i = 0; i < h->n_mech; ++i) att_FB = std::max(att_FB, NW * hp.memory_dim[i]);
@@ -530,6 +548,61 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
     p.att_row_floats = (att_smem_floats(att_TS, att_FB) + 31) / 32 * 32;
     p.att_pair = (att_TS < MAX_T && 2 * p.att_row_floats <= p.scratch_floats && B * h->n_mech > h->grid) ? 1 : 0;
     if (const char* e = getenv("SAT_ATT_PAIR")) p.att_pair = p.att_pair && atoi(e) != 0;
+    // ---- cluster-split attention rows: small batches leave most SMs idle in the row-split phase, so a cluster of 4
+    // (or 2) CTAs shares each (row, mechanism) item (DecParams::cl).  fp32 SIMT form only. ----
+    int grid_run = h->grid;
+    p.cl = 1;
+    if (!use_tc) {
+      int want = 4;
+      if (const char* e = getenv("SAT_CLUSTER")) want = atoi(e);
+      for (int cl = want; cl >= 2 && p.cl == 1; cl >>= 1) {
+        if (cl != 2 && cl != 4) continue;
+        const int ci = cl == 4 ? 1 : 0;
+        bool any = false;
+        int split[2] = {0, 0};
+        for (int i = 0; i < h->n_mech; ++i) {
+          int kind = hp.attention_kind[i];
+          if (io.forced_alignment) kind = SAT_ATT_TEACHER_FORCING;
+          const int Dv = hp.memory_dim[i], win = Dv / cl, F = hp.attention_filters, Up = h->Up[i];
+          const bool ctx_ok = Dv % cl == 0 && win % 4 == 0 && ((win / 4) & (win / 4 - 1)) == 0 && win / 4 <= 32 &&
+                              io.memory[i] && (((uintptr_t)io.memory[i]) & 15) == 0;
+          const bool loc = kind == SAT_ATT_FORWARD || kind == SAT_ATT_LOCATION_SENSITIVE;
+          const bool mma_ok = loc && F <= 7 && (Up == 128 || Up == 256) && att_TS < MAX_T && (Up / 32) % cl == 0 &&
+                              !h->Wt[i] && h->dq_cl[i][ci];
+          split[i] = ctx_ok && (kind == SAT_ATT_TEACHER_FORCING || mma_ok);
+          any = any || split[i];
+        }
+        int maxNp = 0;
+        for (int i = 0; i < h->n_mech; ++i) maxNp = std::max(maxNp, h->dq[i].Np);
+        const int att_off = (al4(A) + maxNp + 4 * NT + 31) / 32 * 32;
+        if (!any || att_off + p.att_row_floats > (int)SCRATCH_FLOATS) continue;
+        int grid_c = h->grid / cl * cl;
+        for (int pass = 0; pass < 2 && grid_c >= B * h->n_mech * cl; ++pass) {
+          const size_t bytes = plan_simt(grid_c);
+          cudaLaunchConfig_t cfg = {};
+          cfg.gridDim = dim3(grid_c); cfg.blockDim = dim3(NT); cfg.dynamicSmemBytes = bytes; cfg.stream = st;
+          cudaLaunchAttribute at[1];
+          at[0].id = cudaLaunchAttributeClusterDimension;
+          at[0].val.clusterDim.x = cl; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+          cfg.attrs = at; cfg.numAttrs = 1;
+          int n_cl = 0;
+          if (cudaOccupancyMaxActiveClusters(&n_cl, (const void*)decoder_persistent_kernel, &cfg) != cudaSuccess) {
+            cudaGetLastError();
+            break;
+          }
+          if (n_cl * cl >= grid_c) {
+            p.cl = cl; grid_run = grid_c; smem_bytes = bytes; p.cl_att_off = att_off;
+            for (int i = 0; i < h->n_mech; ++i) {
+              p.cl_split[i] = split[i]; p.cl_wq[i] = h->dq_cl[i][ci]; p.cl_sw[i] = h->Up[i] / cl;
+            }
+            break;
+          }
+          grid_c = n_cl * cl;  // fewer clusters fit than CTAs / cl: shrink the grid and re-plan once
+        }
+      }
+      if (p.cl == 1) smem_bytes = plan_simt(h->grid);
+    }
+    h->last_cl = p.cl;
 
     // ---- workspace carve-up (floats) ----
     size_t off = 0;
@@ -692,8 +765,17 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
     }
     void* args[] = {&p};
     SAT_CUDA(cudaEventRecord(h->ev0, st));
-    SAT_CUDA(cudaLaunchCooperativeKernel((const void*)decoder_persistent_kernel, dim3(h->grid), dim3(NT), args,
-                                         smem_bytes, st));
+    {
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3(grid_run); cfg.blockDim = dim3(NT); cfg.dynamicSmemBytes = smem_bytes; cfg.stream = st;
+      cudaLaunchAttribute at[2];
+      at[0].id = cudaLaunchAttributeCooperative;
+      at[0].val.cooperative = 1;
+      at[1].id = cudaLaunchAttributeClusterDimension;
+      at[1].val.clusterDim.x = p.cl; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
+      cfg.attrs = at; cfg.numAttrs = p.cl > 1 ? 2 : 1;
+      SAT_CUDA(cudaLaunchKernelExC(&cfg, (const void*)decoder_persistent_kernel, args));
+    }
     SAT_CUDA(cudaEventRecord(h->ev1, st));
     h->last_B = B; h->last_T = T; h->last_S = S;
     count_launch();
@@ -738,6 +820,13 @@ extern "C" int sat_decoder_used_tensor_cores(sat_decoder* h, int32_t* used) {
   return guarded([&] {
     SAT_REQUIRE(h && used, "null argument");
     *used = h->last_tc;
+  });
+}
+
+extern "C" int sat_decoder_cluster_size(sat_decoder* h, int32_t* size) {
+  return guarded([&] {
+    SAT_REQUIRE(h && size, "null argument");
+    *size = h->last_cl;
   });
 }
 

@@ -74,6 +74,34 @@ __device__ __forceinline__ void group_sync(int gid) {
   else asm volatile("bar.sync %0, %1;" ::"r"(gid + 1), "n"(GT) : "memory");
 }
 
+// ---- thread-block cluster helpers (cluster-split attention rows of the small-batch form) ----------------------------
+// A row's attention is split over the CS CTAs of a cluster: each CTA owns Up / CS attention units (its slice of the
+// query layer and of the energies) and Dv / CS columns of the context; the per-unit-group partial energies are
+// all-gathered through distributed shared memory (every CTA stores its partials into the same offset of every CTA's
+// shared memory), one cluster barrier, then each CTA runs the (cheap) softmax / alpha recursion redundantly.
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t cluster_nctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r));
+  return r;
+}
+// all threads of all CTAs of the cluster; release / acquire: shared-memory stores (local and remote) before it are
+// visible after it
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// store v at the address of `local` in the shared memory of CTA `rank` of the cluster
+__device__ __forceinline__ void st_cluster_f32(float* local, uint32_t rank, float v) {
+  uint32_t ra;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"((uint32_t)__cvta_generic_to_shared(local)), "r"(rank));
+  asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(ra), "f"(v) : "memory");
+}
+
 // exp2 / reciprocal on the MUFU pipe
 __device__ __forceinline__ float ex2_approx(float x) {
   float y;
@@ -319,12 +347,12 @@ __device__ __forceinline__ float quad_recip_dot(float y0, float y1, float y2, fl
 
 template <int NUG, int GT>
 __device__ void attention_energies_mma(const AttMech& m, int b, int T, int len, const float* fbuf, float* epart, int Tpad,
-                                       int gtid) {
+                                       int gtid, int ug_off = 0, int csize = 1) {
   constexpr float C2 = 2.8853900817779268f;  // 2 * log2(e)
   constexpr int NRG = (GT / 32) / NUG;
   const int lane = gtid & 31, warp = gtid >> 5;
   const int g = lane >> 2, t = lane & 3;
-  const int ug = warp % NUG, rg = warp / NUG;
+  const int ug = warp % NUG + ug_off, rg = warp / NUG;  // ug_off: first unit group of this CTA (cluster-split rows)
   const int ubase = 32 * ug;
   // first key block in flight before anything else (rows past the end are clamped to the last valid row)
   const float* kb = m.keys + (size_t)b * T * m.Up + ubase + 2 * t;
@@ -407,7 +435,12 @@ __device__ void attention_energies_mma(const AttMech& m, int b, int T, int len, 
     s += __shfl_xor_sync(0xffffffffu, odd ? r0 : r1, 1);
     s += __shfl_xor_sync(0xffffffffu, s, 2);
     const int j = 16 * jb + g + (odd ? 8 : 0);
-    if (t < 2 && j < len) epart[ug * Tpad + j] = s;
+    if (t < 2 && j < len) {
+      float* dst = epart + ug * Tpad + j;
+      if (csize == 1) *dst = s;
+      else
+        for (int cr = 0; cr < csize; ++cr) st_cluster_f32(dst, (uint32_t)cr, s);  // all-gather over the cluster
+    }
   }
 }
 
@@ -416,12 +449,13 @@ __device__ void attention_energies_mma(const AttMech& m, int b, int T, int len, 
 // Cq = 64 / 128: CH = 2 / 4).  part = NW * Dv floats of shared memory.
 template <int CH>
 __device__ void attention_context_vec(const float* __restrict__ vb, const float* align, int len, int Dv,
-                                      float* part, float* ctx_out /* smem [Dv] */) {
+                                      float* part, float* ctx_out /* smem [Dv] */, int rstride = 0 /* 0: Dv */) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int Cq = Dv >> 2;
   const int lpr = CH > 1 ? 32 : Cq;      // lanes per memory row
   const int G = 32 / lpr;                // memory rows per warp pass
   const int c0 = lane % lpr, g = lane / lpr;
+  const size_t rs = rstride ? rstride : Dv;  // floats between memory rows (a column window of a wider memory)
   float4 acc[CH];
 #pragma unroll
   for (int c = 0; c < CH; ++c) acc[c] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -437,7 +471,7 @@ __device__ void attention_context_vec(const float* __restrict__ vb, const float*
       a[s] = ok ? align[j] : 0.f;
 #pragma unroll
       for (int c = 0; c < CH; ++c)
-        v[s][c] = ok ? __ldg((const float4*)(vb + (size_t)j * Dv) + c0 + 32 * c) : make_float4(0.f, 0.f, 0.f, 0.f);
+        v[s][c] = ok ? __ldg((const float4*)(vb + (size_t)j * rs) + c0 + 32 * c) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
 #pragma unroll
     for (int s = 0; s < UN; ++s)
@@ -530,8 +564,11 @@ __device__ __forceinline__ bool att_row_pairable(const AttMech& m) {
          m.TS < MAX_T && !m.agent && m.values16 && (m.Dv & 7) == 0 && (C8 & (C8 - 1)) == 0 && C8 <= 32;
 }
 
+// crank / csize: rank of this CTA in, and size of, the cluster that shares the row (csize = 1: the row is not split;
+// csize > 1 needs GT == NT, the tensor-core energy form (use_mma below) and no transition agent -- the host checks).
 template <int GT>
-__device__ inline void attention_item(const AttMech& m, int b, int t, int T, int len, float* sm, int gid = 0) {
+__device__ inline void attention_item(const AttMech& m, int b, int t, int T, int len, float* sm, int gid = 0,
+                                      int crank = 0, int csize = 1) {
   constexpr int GW = GT / 32;
   const int TS = m.TS;
   float* e = sm;                         // [TS] energies -> softmax probs a
@@ -614,7 +651,15 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
     // partial energies per 32-unit group: own region, or (TS == MAX_T) the dead nal .. ctxs region of 3 * MAX_T floats
     const bool use_mma = loc && m.F <= 7 && (m.Up == 128 || m.Up == 256) && (TS < MAX_T || nug * Tpad <= 3 * MAX_T);
     float* epart = TS < MAX_T ? epart_own : nal;
-    if (use_mma) {
+    if (use_mma && csize > 1) {
+      if constexpr (GT == NT) {
+        // cluster-split row: this CTA evaluates nug / csize unit groups and stores its partials into every CTA
+        const int nl = nug / csize;
+        if (nl == 4) attention_energies_mma<4, GT>(m, b, T, len, fbuf, epart, Tpad, tid, 4 * crank, csize);
+        else if (nl == 2) attention_energies_mma<2, GT>(m, b, T, len, fbuf, epart, Tpad, tid, 2 * crank, csize);
+        else attention_energies_mma<1, GT>(m, b, T, len, fbuf, epart, Tpad, tid, crank, csize);
+      }
+    } else if (use_mma) {
       if (m.Up == 256) attention_energies_mma<8, GT>(m, b, T, len, fbuf, epart, Tpad, tid);
       else attention_energies_mma<4, GT>(m, b, T, len, fbuf, epart, Tpad, tid);
     } else if (GT == NT) {
@@ -629,7 +674,8 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
       else if (m.F <= 8) attention_energies<8>(m, b, T, len, aprev, fbuf, e, e2);
       else attention_energies<-1>(m, b, T, len, aprev, fbuf, e, e2);
     }
-    group_sync<GT>(gid);
+    if (csize > 1) cluster_sync_all();  // the partial energies of the other CTAs have landed
+    else group_sync<GT>(gid);
     stamp();
     // masked softmax (TF: softmax(where(j < len, score, -inf))), the forward-variable recursion and the state update
     // with every element in registers (T <= NJ * GT) and one group barrier per reduction
@@ -674,7 +720,7 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
       pr[i] = pr[i] * inv_sum;
       if (j < T) {
         e[j] = pr[i];
-        m.st_align[(size_t)b * T + j] = m.cumulative ? pr[i] + aprev[HALO + j] : pr[i];
+        if (crank == 0) m.st_align[(size_t)b * T + j] = m.cumulative ? pr[i] + aprev[HALO + j] : pr[i];
       }
     }
     if (fwd) {
@@ -701,7 +747,7 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
         if (j < T) {
           const float a = val[i] * inv_s2;
           nal[j] = a;
-          m.st_alpha[(size_t)b * T + j] = a;
+          if (crank == 0) m.st_alpha[(size_t)b * T + j] = a;
         }
       }
       align = nal;
@@ -710,7 +756,7 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
     ps = 7;
     stamp();
   }
-  if (m.out_align)
+  if (m.out_align && crank == 0)
     for (int j = tid; j < T; j += GT) m.out_align[((size_t)b * m.out_S + t) * T + j] = align[j];
   ps = 3;
   stamp();
@@ -720,6 +766,27 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
   const float* vb = m.values + (size_t)b * T * Dv;
   const bool vec = (Dv & 3) == 0 && (Cq & (Cq - 1)) == 0 && Cq <= 128 && ((((size_t)vb) & 15) == 0);
   const int C8 = Dv >> 3;
+  if (csize > 1) {
+    if constexpr (GT == NT) {
+      // cluster-split row: this CTA reduces its window of Dv / csize context columns over all memory rows
+      const int win = Dv / csize, w0 = crank * win;
+      attention_context_vec<1>(vb + w0, align, len, win, fbuf, ctxs, Dv);
+      stamp();
+      for (int d = tid; d < win; d += GT) {
+        const float ctx = ctxs[d];
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+          if (m.ctx_dst[i]) {
+            const size_t o = (size_t)(w0 + d) * m.ctx_sd[i] + (size_t)b * m.ctx_sb[i];
+            if (m.ctx_f16) ((__half*)m.ctx_dst[i])[o] = tc::to_f16(ctx);
+            else ((float*)m.ctx_dst[i])[o] = ctx;
+          }
+      }
+      group_sync<GT>(gid);
+      stamp();
+    }
+    return;
+  }
   if (m.values16 && (Dv & 7) == 0 && (C8 & (C8 - 1)) == 0 && C8 <= 32) {
     attention_context_h8<GT>(m.values16 + (size_t)b * T * Dv, align, len, Dv, fbuf, ctxs, tid, gid);
   } else if (GT == NT) {

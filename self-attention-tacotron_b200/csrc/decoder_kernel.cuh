@@ -65,6 +65,15 @@ struct DecParams {
                             //    into the projection (self feed only): column Mr + 1 + j = sum_f W_out[:, f0 + f] W_pre0[f][j]
   int att_pair;             // 1: a CTA that owns two rows of the attention phase runs them concurrently, one per half
   int att_row_floats;       // shared-memory floats of one attention row (second row of a pair starts there)
+  // ---- cluster-split attention rows (small batches: B * n_mech * cl <= grid; launched with cluster dimension cl) ----
+  // The cl CTAs of a cluster share one (row, mechanism) item: each computes Up / cl columns of the query layer, the
+  // energies of those units (partials all-gathered through distributed shared memory) and Dv / cl context columns.
+  int cl;                   // cluster size of the launch (1: rows are not split)
+  int cl_split[2];          // mechanism i is split over the cluster (else rank 0 takes the whole item)
+  const float* cl_wq[2];    // query-layer weights as cl contiguous column slices [cl][A][cl_sw] (fp32)
+  int cl_sw[2];             // columns per slice = Up / cl
+  int cl_att_off;           // float offset of the attention row's shared memory (behind the query-layer arrays, which a
+                            // slower CTA of the cluster may still be using when remote partial energies arrive)
 };
 
 struct DenseEpi {
@@ -532,7 +541,48 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
     // ---- D+E: query layers and attention mechanisms (row split, no barrier in between) ----
     // The processed query of a row is a row-local dense on the attention-LSTM output, so the CTA that owns the row's
     // attention item computes it itself (two rows per pass share one stream of the query-layer weights from L2).
-    {
+    if (p.cl > 1) {
+      // cluster-split form (fp32 SIMT mode only): item = cluster index, every CTA of the cluster works on it
+      const float* qsrc = p.l1_in[cur];  // feature-major [A][ld]
+      const int n_items = p.B * p.n_mech, ncl = gridDim.x / p.cl, crank = (int)cluster_ctarank();
+      for (int item = blockIdx.x / p.cl; item < n_items; item += ncl) {
+        const int mi = item % p.n_mech, b = item / p.n_mech;
+        const bool split = p.cl_split[mi] != 0;
+        AttMech m = p.mech[mi];
+        const int coff = mi ? p.mech[0].Dv : 0;
+        m.ctx_f16 = 0;
+        m.ctx_dst[0] = p.att_in[nxt] + (size_t)(p.P1 + coff) * ld;
+        m.ctx_dst[1] = p.l1_in[cur] + (size_t)(p.A + coff) * ld;
+        m.ctx_sd[0] = m.ctx_sd[1] = ld;
+        m.ctx_sb[0] = m.ctx_sb[1] = 1;
+        m.prof = p.prof ? p.prof + 16 : nullptr;
+        if (split || crank == 0) {
+          if (m.kind != SAT_ATT_TEACHER_FORCING) {
+            DenseDesc dq = p.dq[mi];
+            int c0 = 0;
+            if (split) {
+              dq.Wrm = p.cl_wq[mi] + (size_t)crank * dq.K * p.cl_sw[mi];
+              dq.Np = dq.N = p.cl_sw[mi];
+              dq.reps = 1;
+              c0 = crank * p.cl_sw[mi];
+            }
+            float* xs = scratch;            // [A]
+            float* outs = xs + al4(p.A);    // [Np]
+            float* part = outs + dq.Np;     // [kparts * Np] <= [NT * 4]
+            for (int k = tid; k < p.A; k += NT) xs[k] = __ldcg(qsrc + (size_t)k * ld + b);
+            __syncthreads();
+            row_dense<1, false>(dq, xs, p.A, part, outs, 0);
+            for (int n = tid; n < dq.N; n += NT)
+              const_cast<float*>(m.pq)[(size_t)(c0 + n) * m.pq_su + (size_t)b * m.pq_sb] = outs[n];
+            __syncthreads();
+          }
+          attention_item<NT>(m, b, t, p.T, (int)p.lengths[b], scratch + p.cl_att_off, 0, split ? crank : 0,
+                             split ? p.cl : 1);
+        }
+        // the next item's remote partial energies must not land while a CTA of the cluster still reads this item's
+        if (item + ncl < n_items) cluster_sync_all();
+      }
+    } else {
       const float* qsrc = p.tc ? p.qfm : p.l1_in[cur];  // feature-major [A][ld]
       const int n_items = p.B * p.n_mech;
       for (int i0 = blockIdx.x; i0 < n_items; i0 += 2 * gridDim.x) {

@@ -106,6 +106,11 @@ class DecoderHandle:
         check(lib().sat_decoder_used_tensor_cores(self._h, C.byref(used)))
         return bool(used.value)
 
+    def cluster_size(self):
+        size = C.c_int32()
+        check(lib().sat_decoder_cluster_size(self._h, C.byref(size)))
+        return int(size.value)
+
     def profile(self, reset=True):
         out = (C.c_int64 * 48)()
         check(lib().sat_decoder_profile(self._h, out, int(reset)))

@@ -33,7 +33,7 @@ def run_cuda(hp, W, mems, lengths, **kw):
     out = h.run([t(m) for m in mems], t(lengths), **kw)
     torch.cuda.synchronize()
     n = int(out["n_steps"].item())
-    res = {"n_steps": n, "tensor_cores": h.used_tensor_cores(), "stop_steps": out["stop_steps"].cpu().numpy(),
+    res = {"n_steps": n, "tensor_cores": h.used_tensor_cores(), "cluster": h.cluster_size(), "stop_steps": out["stop_steps"].cpu().numpy(),
            "mel": out["mel"].cpu().numpy()[:, :n * hp.outputs_per_step],
            "stop": out["stop"].cpu().numpy()[:, :n, None],
            "alignments": [a.cpu().numpy()[:, :n] for a in out["alignments"] if a is not None]}
@@ -79,6 +79,42 @@ def test_extended_decoder_full_dims_teacher_forced():
     ref = oracle_decoder(hp, W, mems, lengths, target=target, is_validation=True, teacher_forcing=True)
     got = run_cuda(hp, W, mems, lengths, target=target, feed_mode=0, stop_mode=0, max_steps=40)
     check_close(got, ref)
+
+
+@pytest.mark.parametrize("name,B,T,S,mode", [("ljspeech_self_attention", 16, 150, 24, "teacher"),
+                                             ("ljspeech_self_attention", 5, 77, 16, "teacher"),
+                                             ("ljspeech_tacotron", 16, 200, 30, "free"),
+                                             ("ljspeech_tacotron", 33, 61, 12, "free"),
+                                             ("ljspeech_self_attention", 9, 100, 10, "replay")])
+def test_cluster_split_attention_rows(name, B, T, S, mode, monkeypatch):
+    """Small batches: every (row, mechanism) attention item is split over a thread-block cluster (query-layer columns,
+    attention units of the energies, context columns; partial energies exchanged through distributed shared memory).
+    Same bar as the one-CTA-per-row form, which SAT_CLUSTER=0 selects and which must agree to fp32 rounding."""
+    hp = small_hp(name)
+    W = sat_b200.init_weights(hp, seed=21, stress=True)
+    mems, lengths, target, _ = decoder_inputs(hp, B, T, S, seed=21)
+    kw = dict(max_steps=S)
+    if mode == "free":
+        kw.update(feed_mode=1, stop_mode=0)
+        ref = oracle_decoder(hp, W, mems, lengths, max_iters=S, stop_mode="never")
+    elif mode == "teacher":
+        kw.update(target=target, feed_mode=0, stop_mode=0)
+        ref = oracle_decoder(hp, W, mems, lengths, target=target, is_validation=True, teacher_forcing=True)
+    else:  # forced-alignment replay (models/models.py:118-134): the alignments are given, only the context is split
+        p1 = oracle_decoder(hp, W, mems, lengths, target=target, is_validation=True, teacher_forcing=True)
+        ta = [a.astype(np.float32) for a in p1["alignments"]]
+        ref = oracle_decoder(hp, W, mems, lengths, target=target, is_validation=True, teacher_forcing=False,
+                             teacher_alignments=ta, forced_alignment=True)
+        kw.update(target=target, teacher_alignments=ta, forced_alignment=True, feed_mode=2, stop_mode=0)
+    got = run_cuda(hp, W, mems, lengths, **kw)
+    assert got["cluster"] in (2, 4) and not got["tensor_cores"]
+    check_close(got, ref)
+    monkeypatch.setenv("SAT_CLUSTER", "0")
+    one = run_cuda(hp, W, mems, lengths, **kw)
+    assert one["cluster"] == 1
+    for k in ("mel", "stop"):
+        assert rel_err(got[k], one[k]) <= 2e-5, k
+    print("cluster", got["cluster"], name, B, T, {k: rel_err(got[k], ref[k]) for k in ("mel", "stop")})
 
 
 @pytest.mark.parametrize("B", [130, 256])
