@@ -165,7 +165,13 @@ struct ConvTcLaunch {
   const float* res = nullptr;  // optional fp32 residual [B*T][ldr] (joins before the stores; needs y32)
   int ldr = 0;
   int highway = 0;  // HighwayNet epilogue over interleaved (H_u, T_u) columns: x = res, bias = shift, writes cout/2 columns
+  // conv-bank form: ONE launch computes the convolutions of widths 1 .. bank (128 channels each, 'SAME' padding) of the
+  // same input.  wimg = conv_tc_bank_image: [bank * 128][bank * cin], tap slot s of every width = input offset
+  // s - (bank - 1) / 2; column tile w computes width w + 1 over its own tap slots only.  cout = bank * 128;
+  // scale / shift / y16 cover all widths (channel offset 128 * w); taps / pad_left are ignored.
+  int bank = 0;
 };
+__half* conv_tc_bank_image(DevPool& pool, const std::vector<const float*>& w, int cin);  // w[k-1] = [k][cin][128]
 bool conv_tc_supported(int cin, int cout);
 __half* conv_tc_weight_image(DevPool& pool, const float* w, int taps, int cin, int n);
 void conv_tc_pack(const float* x, int ldx, int B, int T, int C, __half* xp, int ldp, cudaStream_t st);

@@ -34,6 +34,7 @@ struct ConvTcArgs {
   const float* res;         // optional fp32 residual [B*T][ldr] added before the store (fp32 output only)
   int ldr;
   int highway;              // 1: HighwayNet epilogue over interleaved (H_u, T_u) column pairs, x = res; writes N/2 columns
+  int bank;                 // > 0: conv-bank form (ConvTcLaunch::bank): grid = (widths, row tiles), widest first
 };
 
 __global__ void __launch_bounds__(CT_THREADS, 3)
@@ -46,8 +47,14 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant__
   uint64_t* empty = bars + CT_STAGES;
   uint64_t* done = bars + 2 * CT_STAGES;
   const int tid = threadIdx.x, warp = tid >> 5;
-  const int r0 = blockIdx.x * 128, n0 = blockIdx.y * 128;
-  const int cpc = a.cin / tc::CHUNK_K16, nchunks = a.taps * cpc;
+  // conv-bank form: blockIdx.x walks the widths (widest first, so the long tiles of a row block start first and the
+  // 16 CTAs that read the same input rows run together), blockIdx.y the row tiles
+  const int width = a.bank ? a.bank - (int)blockIdx.x : 0;
+  const int r0 = (a.bank ? blockIdx.y : blockIdx.x) * 128, n0 = (a.bank ? width - 1 : (int)blockIdx.y) * 128;
+  const int taps = a.bank ? width : a.taps;
+  const int pad_left = a.bank ? (a.bank - 1) / 2 : a.pad_left;          // input offset of tap slot 0
+  const int tap0 = a.bank ? (a.bank - 1) / 2 - (width - 1) / 2 : 0;      // first tap slot of this width
+  const int cpc = a.cin / tc::CHUNK_K16, nchunks = taps * cpc;
 
   if (tid == 0) {
     for (int i = 0; i < 2 * CT_STAGES + 1; ++i) tc::mbar_init(bars + i, 1);
@@ -65,9 +72,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant__
     for (int c = 0; c < nchunks; ++c) {
       const int s = c % CT_STAGES, use = c / CT_STAGES;
       if (use > 0) tc::mbar_wait(empty + s, (use - 1) & 1);
-      const int tau = c / cpc, c0 = (c - tau * cpc) * tc::CHUNK_K16;
+      const int tl = c / cpc, c0 = (c - tl * cpc) * tc::CHUNK_K16, tau = tap0 + tl;
       tc::mbar_arrive_expect_tx(full + s, CT_STAGE_BYTES);
-      tc::tma_load_2d(ring + s * CT_STAGE_BYTES, &xmap, full + s, c0, r0 + tau - a.pad_left);
+      tc::tma_load_2d(ring + s * CT_STAGE_BYTES, &xmap, full + s, c0, r0 + tau - pad_left);
       tc::tma_load_2d(ring + s * CT_STAGE_BYTES + 16384, &wmap, full + s, tau * a.cin + c0, n0);
     }
   } else if (tid == 32) {
@@ -230,6 +237,23 @@ __half* conv_tc_weight_image(DevPool& pool, const float* w, int taps, int cin, i
   return (__half*)pool.upload(packed);
 }
 
+// conv-bank image (ConvTcLaunch::bank): rows = 128 channels of width 1, then of width 2, ...; columns = tap slots x cin,
+// slot s = input offset s - (KW - 1) / 2; a width's unused slots stay zero (and are never read)
+__half* conv_tc_bank_image(DevPool& pool, const std::vector<const float*>& w, int cin) {
+  const int KW = (int)w.size(), n = 128, PL = (KW - 1) / 2;
+  std::vector<__half> img((size_t)KW * n * KW * cin, __float2half_rn(0.f));
+  for (int k = 1; k <= KW; ++k)
+    for (int t = 0; t < k; ++t) {
+      const int slot = PL - (k - 1) / 2 + t;
+      for (int c = 0; c < cin; ++c)
+        for (int o = 0; o < n; ++o)
+          img[((size_t)(k - 1) * n + o) * KW * cin + (size_t)slot * cin + c] = __float2half_rn(w[k - 1][((size_t)t * cin + c) * n + o]);
+    }
+  std::vector<float> packed((img.size() + 1) / 2);
+  memcpy(packed.data(), img.data(), img.size() * sizeof(__half));
+  return (__half*)pool.upload(packed);
+}
+
 bool conv_tc_supported(int cin, int cout) { return cin % 64 == 0 && cout % 128 == 0; }
 
 void conv_tc_pack(const float* x, int ldx, int B, int T, int C, __half* xp, int ldp, cudaStream_t st) {
@@ -248,18 +272,21 @@ void conv_tc_maxpool2(const __half* x, int B, int T, int C, __half* y, cudaStrea
 
 void conv_tc_launch(const ConvTcLaunch& L, cudaStream_t st) {
   SAT_REQUIRE(conv_tc_supported(L.cin, L.cout), "tensor-core conv needs Cin %% 64 == 0 and Cout %% 128 == 0 (got %d, %d)", L.cin, L.cout);
-  SAT_REQUIRE(L.taps >= 1 && L.taps <= 2 * CONV_TC_HALO && L.pad_left <= CONV_TC_HALO && L.taps - 1 - L.pad_left <= CONV_TC_HALO,
-              "conv taps %d exceed the activation halo", L.taps);
+  const int taps_total = L.bank ? L.bank : L.taps, pad_left = L.bank ? (L.bank - 1) / 2 : L.pad_left;
+  SAT_REQUIRE(taps_total >= 1 && taps_total <= 2 * CONV_TC_HALO && pad_left <= CONV_TC_HALO && taps_total - 1 - pad_left <= CONV_TC_HALO,
+              "conv taps %d exceed the activation halo", taps_total);
+  SAT_REQUIRE(!L.bank || (L.cout == L.bank * 128 && !L.highway && !L.y32), "conv-bank form: cout = widths * 128, fp16 output");
   const int Tp = L.T + 2 * CONV_TC_HALO;
   const uint64_t R = (uint64_t)L.B * Tp;
   CUtensorMap xmap, wmap;
   make_tensor_map_2d_f16(&xmap, L.xp, R, (uint64_t)L.cin, (uint64_t)L.ldxp, 128);
-  make_tensor_map_2d_f16(&wmap, L.wimg, (uint64_t)L.cout, (uint64_t)L.taps * L.cin, (uint64_t)L.taps * L.cin, 128);
+  make_tensor_map_2d_f16(&wmap, L.wimg, (uint64_t)L.cout, (uint64_t)taps_total * L.cin, (uint64_t)taps_total * L.cin, 128);
   ConvTcArgs a;
   a.R = (int)R; a.Tp = Tp; a.T = L.T; a.halo = CONV_TC_HALO;
   a.taps = L.taps; a.pad_left = L.pad_left; a.cin = L.cin;
   a.scale = L.scale; a.shift = L.shift; a.act = L.act;
   a.y16 = L.y16; a.ld16 = L.ld16; a.y32 = L.y32; a.ld32 = L.ld32; a.res = L.res; a.ldr = L.ldr; a.highway = L.highway;
+  a.bank = L.bank;
   SAT_REQUIRE(!L.highway || (L.res && L.shift), "highway epilogue needs the layer input (res) and the bias (shift)");
   static bool attr_set = false;
   const int smem = CT_STAGES * CT_STAGE_BYTES + 1024;
@@ -268,6 +295,7 @@ void conv_tc_launch(const ConvTcLaunch& L, cudaStream_t st) {
     attr_set = true;
   }
   dim3 grid((unsigned)((R + 127) / 128), (unsigned)(L.cout / 128));
+  if (L.bank) grid = dim3((unsigned)L.bank, (unsigned)((R + 127) / 128));
   conv_tc_kernel<<<grid, CT_THREADS, smem, st>>>(xmap, wmap, a);
   count_launch();
   check_launch("conv_tc_kernel");

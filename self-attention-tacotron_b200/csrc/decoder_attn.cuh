@@ -102,17 +102,6 @@ __device__ __forceinline__ void st_cluster_f32(float* local, uint32_t rank, floa
   asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(ra), "f"(v) : "memory");
 }
 
-// exp2 / reciprocal on the MUFU pipe
-__device__ __forceinline__ float ex2_approx(float x) {
-  float y;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-__device__ __forceinline__ float rcp_approx(float x) {
-  float y;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
 
 // Energies of one row.  v . tanh(x) = sum(v) - 2 sum_u v_u / (exp(2 x_u) + 1); the constant sum(v) is the same
 // for every j of the row and cancels in the softmax, so the kernel evaluates
@@ -566,9 +555,27 @@ __device__ __forceinline__ bool att_row_pairable(const AttMech& m) {
 
 // crank / csize: rank of this CTA in, and size of, the cluster that shares the row (csize = 1: the row is not split;
 // csize > 1 needs GT == NT, the tensor-core energy form (use_mma below) and no transition agent -- the host checks).
+// previous alignments (zero-haloed) and forward variable of row b -> the row's shared memory (no barrier): lets a
+// caller put these loads in flight together with other loads of its own (attention_item with preloaded = true)
+template <int GT>
+__device__ __forceinline__ void attention_load_state(const AttMech& m, int b, int T, float* sm, int gid = 0) {
+  if (m.kind == SAT_ATT_TEACHER_FORCING) return;
+  const int TS = m.TS;
+  float* aprev = sm + TS;
+  float* alpha = aprev + TS + 2 * HALO;
+  const int tid = threadIdx.x - gid * GT;
+  const bool loc = (m.kind == SAT_ATT_FORWARD || m.kind == SAT_ATT_LOCATION_SENSITIVE);
+  for (int j = tid; j < T + 2 * HALO; j += GT) {
+    const int jj = j - HALO;
+    aprev[j] = (loc && jj >= 0 && jj < T) ? __ldcg(m.st_align + (size_t)b * T + jj) : 0.f;
+  }
+  if (m.kind == SAT_ATT_FORWARD)
+    for (int j = tid; j < T; j += GT) alpha[j] = __ldcg(m.st_alpha + (size_t)b * T + j);
+}
+
 template <int GT>
 __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int len, float* sm, int gid = 0,
-                                      int crank = 0, int csize = 1) {
+                                      int crank = 0, int csize = 1, bool preloaded = false) {
   constexpr int GW = GT / 32;
   const int TS = m.TS;
   float* e = sm;                         // [TS] energies -> softmax probs a
@@ -606,15 +613,11 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
     for (int j = tid; j < T; j += GT) e[j] = __ldg(m.teacher + ((size_t)b * m.teacher_S + ti) * T + j);
     group_sync<GT>(gid);
   } else {
-    for (int j = tid; j < T + 2 * HALO; j += GT) {
-      const int jj = j - HALO;
-      aprev[j] = (loc && jj >= 0 && jj < T) ? __ldcg(m.st_align + (size_t)b * T + jj) : 0.f;
+    if (fwd) u_prev = __ldcg(m.st_u + b);
+    if (!preloaded) {
+      attention_load_state<GT>(m, b, T, sm, gid);
+      group_sync<GT>(gid);
     }
-    if (fwd) {
-      for (int j = tid; j < T; j += GT) alpha[j] = __ldcg(m.st_alpha + (size_t)b * T + j);
-      u_prev = __ldcg(m.st_u + b);
-    }
-    group_sync<GT>(gid);
     stamp();
     if (loc && m.F <= 8) {
       // location features f[j][c] = b_c + sum_k w[k][c] a[j - pad + k]: a thread owns filter c = tid & 7 and four

@@ -42,6 +42,25 @@ struct DenseDesc {
 // ---- small math helpers (accurate versions: parity first) ------------------
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + expf(-x)); }
 
+// exp2 / reciprocal on the MUFU pipe
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+// Gate non-linearities of the LSTM cell updates: 1 / (1 + 2^(-x log2 e)) and 1 - 2 / (2^(2 x log2 e) + 1) on the MUFU
+// pipe (abs error ~2e-7, saturate cleanly at +-inf) -- a fifth of the instructions of expf / tanhf / IEEE division on
+// the critical path behind every gate GEMM.  Decisions (stop rule) keep the accurate sigmoidf_.
+__device__ __forceinline__ float sigmoid_fast(float x) { return rcp_approx(1.f + ex2_approx(-1.4426950408889634f * x)); }
+__device__ __forceinline__ float tanh_fast(float x) {
+  return fmaf(-2.f, rcp_approx(ex2_approx(2.8853900817779268f * x) + 1.f), 1.f);
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -135,17 +154,28 @@ __device__ void dense_phase(const DenseDesc& d, const float* X, int ld, int Bp, 
     if (q < nq) {
       const float* xp = X + r0 + 4 * q;
       const int kstride = NW * ksub;
-#pragma unroll 4
-      for (int k = warp * ksub + ks; k < d.K; k += kstride) {
-        const float4 x = __ldcg((const float4*)(xp + (size_t)k * ld));
-        const float4 w0 = *(const float4*)(W + k * TILE_N);
-        const float4 w1 = *(const float4*)(W + k * TILE_N + 4);
-        const float xv[4] = {x.x, x.y, x.z, x.w};
-        const float wv[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+      // batches of PF activation loads in flight (one L2 round trip per batch; K = 672 at 16 rows is one batch)
+      constexpr int PF = 8;
+      for (int kb = warp * ksub + ks; kb < d.K; kb += PF * kstride) {
+        float4 xq[PF];
 #pragma unroll
-        for (int i = 0; i < 4; ++i)
+        for (int s = 0; s < PF; ++s) {
+          const int k = kb + s * kstride;
+          xq[s] = k < d.K ? __ldcg((const float4*)(xp + (size_t)k * ld)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
 #pragma unroll
-          for (int c = 0; c < TILE_N; ++c) acc[i][c] = fmaf(xv[i], wv[c], acc[i][c]);
+        for (int s = 0; s < PF; ++s) {
+          const int k = kb + s * kstride;
+          if (k >= d.K) break;
+          const float4 w0 = *(const float4*)(W + k * TILE_N);
+          const float4 w1 = *(const float4*)(W + k * TILE_N + 4);
+          const float xv[4] = {xq[s].x, xq[s].y, xq[s].z, xq[s].w};
+          const float wv[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int c = 0; c < TILE_N; ++c) acc[i][c] = fmaf(xv[i], wv[c], acc[i][c]);
+        }
       }
     }
     // reduce over the k-sub lanes of the warp

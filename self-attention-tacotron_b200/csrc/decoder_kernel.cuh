@@ -106,8 +106,8 @@ struct LstmEpi {
     const float gi = g[0] + __ldg(bb + 0), gj = g[1] + __ldg(bb + 1), gf = g[2] + __ldg(bb + 2), go = g[3] + __ldg(bb + 3);
     const size_t idx = (size_t)u * ld + b;
     const float cp = c[idx], hp = __ldcg(hprev + idx);
-    const float cn = sigmoidf_(gf + 1.0f) * cp + sigmoidf_(gi) * tanhf(gj);
-    const float hn = sigmoidf_(go) * tanhf(cn);
+    const float cn = sigmoid_fast(gf + 1.0f) * cp + sigmoid_fast(gi) * tanh_fast(gj);
+    const float hn = sigmoid_fast(go) * tanh_fast(cn);
     c[idx] = cn - zc * (cn - cp);
     hz[idx] = hn - zh * (hn - hp);
     out[idx] = hn;
@@ -557,6 +557,8 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
         m.ctx_sb[0] = m.ctx_sb[1] = 1;
         m.prof = p.prof ? p.prof + 16 : nullptr;
         if (split || crank == 0) {
+          // the row's attention state goes in flight together with the query-layer input
+          attention_load_state<NT>(m, b, p.T, scratch + p.cl_att_off);
           if (m.kind != SAT_ATT_TEACHER_FORCING) {
             DenseDesc dq = p.dq[mi];
             int c0 = 0;
@@ -575,9 +577,11 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
             for (int n = tid; n < dq.N; n += NT)
               const_cast<float*>(m.pq)[(size_t)(c0 + n) * m.pq_su + (size_t)b * m.pq_sb] = outs[n];
             __syncthreads();
+          } else {
+            __syncthreads();
           }
           attention_item<NT>(m, b, t, p.T, (int)p.lengths[b], scratch + p.cl_att_off, 0, split ? crank : 0,
-                             split ? p.cl : 1);
+                             split ? p.cl : 1, true);
         }
         // the next item's remote partial energies must not land while a CTA of the cluster still reads this item's
         if (item + ncl < n_items) cluster_sync_all();

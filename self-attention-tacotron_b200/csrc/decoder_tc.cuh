@@ -169,8 +169,8 @@ __device__ inline void lstm_phase_tc(const TcLstmDesc& d, const TcLstmIO& io, in
       const float4 bb = __ldg((const float4*)(d.bias + (size_t)(2 * tile + (ul >> 1)) * TILE_N + (ul & 1) * 4));
       const float gi = g[0] + bb.x, gj = g[1] + bb.y, gf = g[2] + bb.z, go = g[3] + bb.w;
       const float cp = *cs, hp = *hs;
-      const float cn = sigmoidf_(gf + 1.0f) * cp + sigmoidf_(gi) * tanhf(gj);
-      const float hn = sigmoidf_(go) * tanhf(cn);
+      const float cn = sigmoid_fast(gf + 1.0f) * cp + sigmoid_fast(gi) * tanh_fast(gj);
+      const float hn = sigmoid_fast(go) * tanh_fast(cn);
       if (b < Bp) {
         *cs = cn - zc * (cn - cp);
         // the recurrent input of the next step is the fp16 value; the blend uses the same rounded value

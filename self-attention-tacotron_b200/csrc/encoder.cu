@@ -177,6 +177,8 @@ struct sat_encoder {
   bool tc = false;  // conv bank + proj1 on the tensor cores (fp16 operands, fp32 accumulation)
   bool tc_full = false;  // ... and prenet layer 1, proj2, the highway layers and the BiLSTM input projection as well
   __half* pre1_img = nullptr;
+  __half* bank_img = nullptr;  // all widths in one image (conv_tc_bank_image): the bank is ONE launch
+  float *bank_scale = nullptr, *bank_shift = nullptr;
   std::vector<__half*> hw_img;
   __half* lstm_img = nullptr;
   Scratch ws16;     // haloed fp16 activations of that path
@@ -263,6 +265,25 @@ extern "C" int sat_encoder_create(const sat_hparams* hpp, const sat_tensor* weig
     }
     h->tc = h->proj1.wimg != nullptr;
     for (const Conv& c : h->bank) h->tc = h->tc && c.wimg != nullptr;
+    if (h->tc && hp.conv_channels == 128 && hp.max_filter_width <= 2 * CONV_TC_HALO) {
+      std::vector<const float*> ws;
+      std::vector<float> sc, sh;
+      for (int k = 1; k <= hp.max_filter_width; ++k) {
+        const std::string P = C + "conv1d_K" + std::to_string(k);
+        ws.push_back(W.get(P + "/kernel", (int64_t)k * d * 128));
+        const float *gamma = W.get(P + "/bn/gamma", 128), *beta = W.get(P + "/bn/beta", 128);
+        const float *mean = W.get(P + "/bn/mean", 128), *var = W.get(P + "/bn/var", 128);
+        for (int i = 0; i < 128; ++i) {
+          const float s = gamma[i] / sqrtf(var[i] + 1e-3f);
+          sc.push_back(s);
+          sh.push_back(beta[i] - mean[i] * s);
+        }
+      }
+      h->bank_img = conv_tc_bank_image(pool, ws, d);
+      h->bank_scale = pool.upload(sc);
+      h->bank_shift = pool.upload(sh);
+      if (const char* e = getenv("SAT_ENC_BANK_FUSED")) if (atoi(e) == 0) h->bank_img = nullptr;
+    }
     if (const char* e = getenv("SAT_ENC_TC")) h->tc = h->tc && atoi(e) != 0;
     {
       const int P0 = hp.encoder_prenet_units[0], P1 = hp.encoder_prenet_units[1];
@@ -365,13 +386,21 @@ static int encoder_forward_impl(sat_encoder* h, const int64_t* ids, const float*
         L.y16 = x16; L.ld16 = P1; L.y32 = ws + o_p1; L.ld32 = P1;
         conv_tc_launch(L, st);
       }
-      for (int k = 1; k <= KW; ++k) {
-        const Conv& c = h->bank[k - 1];
-        ConvTcLaunch L;
-        L.xp = x16; L.ldxp = P1; L.B = B; L.T = T; L.cin = P1; L.cout = Cb; L.taps = k; L.pad_left = (k - 1) / 2;
-        L.wimg = c.wimg; L.scale = c.scale; L.shift = c.shift; L.act = ACT_RELU;
-        L.y16 = bank16 + (size_t)(k - 1) * Cb; L.ld16 = ldb;
+      if (h->bank_img) {
+        ConvTcLaunch L;  // all widths of the bank in one launch
+        L.xp = x16; L.ldxp = P1; L.B = B; L.T = T; L.cin = P1; L.cout = KW * Cb; L.bank = KW;
+        L.wimg = h->bank_img; L.scale = h->bank_scale; L.shift = h->bank_shift; L.act = ACT_RELU;
+        L.y16 = bank16; L.ld16 = ldb;
         conv_tc_launch(L, st);
+      } else {
+        for (int k = 1; k <= KW; ++k) {
+          const Conv& c = h->bank[k - 1];
+          ConvTcLaunch L;
+          L.xp = x16; L.ldxp = P1; L.B = B; L.T = T; L.cin = P1; L.cout = Cb; L.taps = k; L.pad_left = (k - 1) / 2;
+          L.wimg = c.wimg; L.scale = c.scale; L.shift = c.shift; L.act = ACT_RELU;
+          L.y16 = bank16 + (size_t)(k - 1) * Cb; L.ld16 = ldb;
+          conv_tc_launch(L, st);
+        }
       }
       conv_tc_maxpool2(bank16, B, T, ldb, pool16, st);
       {
@@ -417,13 +446,21 @@ static int encoder_forward_impl(sat_encoder* h, const int64_t* ids, const float*
         __half* pool16 = bank16 + n_bank;
         SAT_CUDA(cudaMemsetAsync(x16, 0, (n_x + 2 * n_bank + 64) * sizeof(__half), st));
         conv_tc_pack(ws + o_p1, P1, B, T, P1, x16, P1, st);
-        for (int k = 1; k <= KW; ++k) {
-          const Conv& c = h->bank[k - 1];
-          ConvTcLaunch L;
-          L.xp = x16; L.ldxp = P1; L.B = B; L.T = T; L.cin = P1; L.cout = Cb; L.taps = k; L.pad_left = (k - 1) / 2;
-          L.wimg = c.wimg; L.scale = c.scale; L.shift = c.shift; L.act = ACT_RELU;
-          L.y16 = bank16 + (size_t)(k - 1) * Cb; L.ld16 = ldb;
+        if (h->bank_img) {
+          ConvTcLaunch L;  // all widths of the bank in one launch
+          L.xp = x16; L.ldxp = P1; L.B = B; L.T = T; L.cin = P1; L.cout = KW * Cb; L.bank = KW;
+          L.wimg = h->bank_img; L.scale = h->bank_scale; L.shift = h->bank_shift; L.act = ACT_RELU;
+          L.y16 = bank16; L.ld16 = ldb;
           conv_tc_launch(L, st);
+        } else {
+          for (int k = 1; k <= KW; ++k) {
+            const Conv& c = h->bank[k - 1];
+            ConvTcLaunch L;
+            L.xp = x16; L.ldxp = P1; L.B = B; L.T = T; L.cin = P1; L.cout = Cb; L.taps = k; L.pad_left = (k - 1) / 2;
+            L.wimg = c.wimg; L.scale = c.scale; L.shift = c.shift; L.act = ACT_RELU;
+            L.y16 = bank16 + (size_t)(k - 1) * Cb; L.ld16 = ldb;
+            conv_tc_launch(L, st);
+          }
         }
         conv_tc_maxpool2(bank16, B, T, ldb, pool16, st);
         ConvTcLaunch L;
