@@ -180,7 +180,7 @@ struct sat_decoder {
   unsigned* barrier = nullptr;
   long long* prof = nullptr;
   size_t max_dyn_smem = 0;
-  CUtensorMap hmaps[6];
+  CUtensorMap hmaps[9];
   CUtensorMap* dmaps = nullptr;  // device copy, 64-byte aligned
   int last_tc = 0, last_cl = 1;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;  // bracket the persistent launch of the last run
@@ -364,7 +364,7 @@ extern "C" int sat_decoder_create(const sat_hparams* hpp, const sat_tensor* weig
     h->grid = h->sm_count;
     h->barrier = pool.alloc<unsigned>(1);
     h->prof = pool.alloc<long long>(N_PROF);
-    h->dmaps = (CUtensorMap*)(((uintptr_t)pool.alloc<uint8_t>(6 * sizeof(CUtensorMap) + 64) + 63) & ~(uintptr_t)63);
+    h->dmaps = (CUtensorMap*)(((uintptr_t)pool.alloc<uint8_t>(9 * sizeof(CUtensorMap) + 64) + 63) & ~(uintptr_t)63);
     SAT_CUDA(cudaEventCreate(&h->ev0));
     SAT_CUDA(cudaEventCreate(&h->ev1));
     guard.release();
@@ -493,9 +493,46 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
         td[i]->st_off = off;
         off += td[i]->slots * TC_STATE_BYTES;
       }
+      // ---- the row-local dense layers as tensor-core tile phases (dense_phase_tc): query layers always, frame / stop
+      // projection + prenet when prenet layer 0 is folded into the projection (self feed, no speaker term, no hops) ----
+      // Measured on B200 (cfg 2, B=256, profiles/README.md round 2): parity green, but every TMA-fed tile phase costs
+      // ~6 us (grid barrier + two TMA round trips + epilogue) -- Q 6.1 us against 5.5 us inside the attention rows,
+      // P + R 22 us against the 11.8 us row-split frame phase; step 59.4 -> 72.4 us.  Off unless SAT_TC_DENSE=1.
+      bool dense_tc = false;
+      if (const char* e = getenv("SAT_TC_DENSE")) dense_tc = use_tc && atoi(e) != 0;
+      auto plan_dense = [&](TcDense& d, int K, int terms) {  // one resident slot per CTA, or not at all
+        d.K = K; d.kc = ceil_div(K, tc::CHUNK_K16); d.terms = terms;
+        d.n_tiles = d.nt[0] + d.nt[1];
+        d.slots = 1; d.img_off = off;
+        if (d.n_tiles * RB > h->grid) return false;
+        off += (terms == 3 ? 2 : 1) * d.kc * 2048;
+        return true;
+      };
+      if (dense_tc && !io.forced_alignment) {
+        bool ok = true;
+        for (int i = 0; i < h->n_mech; ++i) {
+          ok = ok && h->Up[i] % TC_N == 0 && h->dq[i].Wrm;
+          p.tq.W[i] = h->dq[i].Wrm; p.tq.ldw[i] = h->dq[i].Np; p.tq.nt[i] = h->Up[i] / TC_N; p.tq.ncol[i] = h->Up[i];
+        }
+        const int off0 = off;
+        if (ok && plan_dense(p.tq, A, 2)) p.tc_q = 1;
+        else off = off0;
+      }
+      if (dense_tc && p.fused_prenet0 && !p.ms && h->hops == 0) {
+        const int off0 = off;
+        p.tp.W[0] = p.outp.Wrm; p.tp.ldw[0] = p.outp.Np; p.tp.ncol[0] = p.Mr + 1 + p.P0;
+        p.tp.nt[0] = ceil_div(p.tp.ncol[0], TC_N); p.tp.bias = p.outp.bias;
+        p.tr.W[0] = p.pre1.Wrm; p.tr.ldw[0] = p.pre1.Np; p.tr.ncol[0] = p.P1;
+        p.tr.nt[0] = ceil_div(p.P1, TC_N); p.tr.bias = p.pre1.bias;
+        if (plan_dense(p.tp, p.outp.K, 3) && plan_dense(p.tr, p.P0, 2)) p.tc_frame = 1;
+        else off = off0;
+      }
       p.scratch_floats = std::max((int)SCRATCH_FLOATS, (int)TC_SCRATCH_FLOATS);
       smem_bytes = p.scratch_floats * sizeof(float) + 1024 + (size_t)off;
-      if (smem_bytes > h->max_dyn_smem) use_tc = false;  // resident images do not fit: SIMT form
+      if (smem_bytes > h->max_dyn_smem) {  // resident images do not fit: SIMT form
+        use_tc = false;
+        p.tc_q = p.tc_frame = 0;
+      }
     }
     {
       const int need = frame_smem_floats(p.outp.K, p.outp.Np, p.Mnf, p.pre0.Np, p.pre1.Np);
@@ -506,6 +543,7 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
     }
     if (const char* e = getenv("SAT_BENCH_BARRIERS")) p.bench_barriers = atoi(e);
     p.tc = use_tc ? 1 : 0;
+    if (!use_tc) p.tc_q = p.tc_frame = 0;
     if (!use_tc) p.scratch_floats = SCRATCH_FLOATS;
     p.RB = RB;
     p.Ka_pad = ceil_div(Ka, tc::CHUNK_K16) * tc::CHUNK_K16;
@@ -616,6 +654,10 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
     const size_t o_l10 = take(n_l1), o_l11 = take(n_l1);
     const size_t o_l20 = take(n_l2), o_l21 = take(n_l2);
     const size_t o_qfm = take((size_t)A * ld);
+    // fp16 hi + lo activation pairs of the tensor-core dense phases (zeroed per run: padding rows / columns stay zero)
+    p.qx_ld = 2 * p.tq.kc * tc::CHUNK_K16; p.px_ld = 2 * p.tp.kc * tc::CHUNK_K16; p.rx_ld = 2 * p.tr.kc * tc::CHUNK_K16;
+    const size_t o_qx = take(p.tc_q ? rows_tc * p.qx_ld / 2 : 0), o_px = take(p.tc_frame ? rows_tc * p.px_ld / 2 : 0);
+    const size_t o_rx = take(p.tc_frame ? rows_tc * p.rx_ld / 2 : 0);
     const size_t o_ca = take((size_t)A * ld), o_c1 = take((size_t)Dd * ld), o_c2 = take((size_t)Dd * ld);
     const size_t o_dout = take((size_t)Dd * ld);
     const size_t o_saq = take((size_t)Ds * ld), o_sactx = take((size_t)Ds * ld), o_saa = take((size_t)Ds * ld);
@@ -648,6 +690,7 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
     p.l1_in[0] = ws + o_l10; p.l1_in[1] = ws + o_l11;
     p.l2_in[0] = ws + o_l20; p.l2_in[1] = ws + o_l21;
     p.qfm = ws + o_qfm;
+    p.qx = (__half*)(ws + o_qx); p.px = (__half*)(ws + o_px); p.rx = (__half*)(ws + o_rx);
     p.c_a = ws + o_ca; p.c_1 = ws + o_c1; p.c_2 = ws + o_c2; p.dout = ws + o_dout;
     p.sa_q = ws + o_saq; p.sa_ctx = ws + o_sactx; p.sa_a = ws + o_saa; p.sa_y[0] = ws + o_say0; p.sa_y[1] = ws + o_say1;
     p.target = io.target; p.lengths = (const long long*)io.memory_lengths;
@@ -760,6 +803,11 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
       const int pads[6] = {p.Ka_pad, p.Ka_pad, p.K1_pad, p.K1_pad, p.K2_pad, p.K2_pad};
       for (int i = 0; i < 6; ++i)
         make_tensor_map_2d_f16(&h->hmaps[i], bufs[i], rows_tc, (uint64_t)pads[i], (uint64_t)pads[i], TC_M);
+      if (p.tc_q) make_tensor_map_2d_f16(&h->hmaps[6], p.qx, rows_tc, (uint64_t)p.qx_ld, (uint64_t)p.qx_ld, TC_M);
+      if (p.tc_frame) {
+        make_tensor_map_2d_f16(&h->hmaps[7], p.px, rows_tc, (uint64_t)p.px_ld, (uint64_t)p.px_ld, TC_M);
+        make_tensor_map_2d_f16(&h->hmaps[8], p.rx, rows_tc, (uint64_t)p.rx_ld, (uint64_t)p.rx_ld, TC_M);
+      }
       SAT_CUDA(cudaMemcpyAsync(h->dmaps, h->hmaps, sizeof(h->hmaps), cudaMemcpyHostToDevice, st));
       p.maps = h->dmaps;
     }

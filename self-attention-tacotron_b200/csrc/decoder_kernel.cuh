@@ -59,7 +59,7 @@ struct DecParams {
   int bench_barriers;       // diagnostic: time this many empty grid barriers before the loop (prof[30])
   int scratch_floats;       // phase scratch at the head of dynamic smem (>= SCRATCH_FLOATS; holds the TMA ring in tc mode)
   TcLstmDesc tc_a, tc_1, tc_2;
-  const CUtensorMap* maps;  // [6]: att_in[0,1], l1_in[0,1], l2_in[0,1]
+  const CUtensorMap* maps;  // [9]: att_in[0,1], l1_in[0,1], l2_in[0,1], qx, px, rx
   float* qfm;               // feature-major copy of the attention-LSTM output (query) for the SIMT query layers
   int fused_prenet0;        // 1: `outp` carries P0 extra columns = prenet layer 0 applied to the fed-back frame, folded
                             //    into the projection (self feed only): column Mr + 1 + j = sum_f W_out[:, f0 + f] W_pre0[f][j]
@@ -68,6 +68,13 @@ struct DecParams {
   // ---- cluster-split attention rows (small batches: B * n_mech * cl <= grid; launched with cluster dimension cl) ----
   // The cl CTAs of a cluster share one (row, mechanism) item: each computes Up / cl columns of the query layer, the
   // energies of those units (partials all-gathered through distributed shared memory) and Dv / cl context columns.
+  // ---- tensor-core mode: the row-local dense layers as tile phases of their own (dense_phase_tc) instead of per-row
+  // GEMVs that make every CTA stream the whole weight matrix from L2 ----
+  int tc_q;                 // query layers of all mechanisms: phase Q between the attention LSTM and the attention rows
+  int tc_frame;             // frame / stop projection (+ folded prenet layer 0) and prenet layer 1: phases P and R
+  TcDense tq, tp, tr;
+  __half *qx, *px, *rx;     // fp16 hi + lo pairs [RB * 128][ld]: attention-LSTM output, LSTM2 output, prenet layer-0 output
+  int qx_ld, px_ld, rx_ld;
   int cl;                   // cluster size of the launch (1: rows are not split)
   int cl_split[2];          // mechanism i is split over the cluster (else rank 0 takes the whole item)
   const float* cl_wq[2];    // query-layer weights as cl contiguous column slices [cl][A][cl_sw] (fp32)
@@ -132,6 +139,54 @@ struct QkvEpi {
       const int hd = d / dh, dd = d % dh;
       float* dst = (which == 0 ? kc : vc) + (((size_t)b * H + hd) * Smax + t) * dh + dd;
       *(float4*)dst = make_float4(v[0], v[1], v[2], v[3]);
+    }
+  }
+};
+
+// epilogues of the tensor-core dense phases (dense_phase_tc): one utterance row x four columns per call
+struct QueryTcEpi {  // processed queries of up to two mechanisms, row-major [b][Up]
+  float* pq[2];
+  int Up[2], nt0, B;
+  __device__ __forceinline__ void operator()(int b, int tile, int ul, const float* g) const {
+    if (b >= B) return;
+    const int grp = tile < nt0 ? 0 : 1, n = (tile - (grp ? nt0 : 0)) * TC_N + ul * 4;
+    *(float4*)(pq[grp] + (size_t)b * Up[grp] + n) = make_float4(g[0], g[1], g[2], g[3]);
+  }
+};
+struct FrameTcEpi {  // frame + stop projection with prenet layer 0 folded in (self feed): [mel (Mr) | stop | relu -> p0]
+  const float* bias;
+  int Mr, P0, N, B, t, max_steps;
+  float *mel, *stop;
+  __half* rx;
+  int rx_ld, rx_lo;
+  __device__ __forceinline__ void operator()(int b, int tile, int ul, const float* g) const {
+    if (b >= B) return;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const int n = tile * TC_N + ul * 4 + c;
+      if (n >= N) continue;
+      const float v = g[c] + __ldg(bias + n);
+      if (n < Mr) mel[((size_t)b * max_steps + t) * Mr + n] = v;
+      else if (n == Mr) stop[(size_t)b * max_steps + t] = v;
+      else {
+        const float r = fmaxf(v, 0.f);
+        const __half hh = tc::to_f16(r);
+        rx[(size_t)b * rx_ld + (n - Mr - 1)] = hh;
+        rx[(size_t)b * rx_ld + rx_lo + (n - Mr - 1)] = tc::to_f16(r - __half2float(hh));
+      }
+    }
+  }
+};
+struct PrenetTcEpi {  // prenet layer 1 -> the attention-LSTM input of the next step
+  const float* bias;
+  int N, B;
+  Act2D dst;
+  __device__ __forceinline__ void operator()(int b, int tile, int ul, const float* g) const {
+    if (b >= B) return;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const int n = tile * TC_N + ul * 4 + c;
+      if (n < N) dst.put(n, b, fmaxf(g[c] + __ldg(bias + n), 0.f));
     }
   }
 };
@@ -461,6 +516,11 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
     tc_load_resident(p.tc_a, p.RB, tcs);
     tc_load_resident(p.tc_1, p.RB, tcs);
     tc_load_resident(p.tc_2, p.RB, tcs);
+    if (p.tc_q) tc_load_dense_resident(p.tq, p.RB, tcs);
+    if (p.tc_frame) {
+      tc_load_dense_resident(p.tp, p.RB, tcs);
+      tc_load_dense_resident(p.tr, p.RB, tcs);
+    }
     tc::fence_proxy_async();
     tc::tc_fence_before();
     __syncthreads();
@@ -526,8 +586,9 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
     if (p.tc) {
       // fp16 row-major buffers: att_in = [prenet | context | zoned h], l1_in = [h_a | context | zoned h1]
       const int h0 = p.P1 + p.Dctx;
-      TcLstmIO io{p.maps + cur, Act2D{p.l1_in[cur], 1, p.K1_pad, 1}, Act2D{p.qfm, ld, 1, 0},
-                  Act2D{(__half*)p.att_in[nxt] + h0, 1, p.Ka_pad, 1}, nullptr, 0, 0};
+      TcLstmIO io{p.maps + cur, Act2D{p.l1_in[cur], 1, p.K1_pad, 1}, Act2D{p.tc_q ? nullptr : p.qfm, ld, 1, 0},
+                  Act2D{(__half*)p.att_in[nxt] + h0, 1, p.Ka_pad, 1}, nullptr, 0, 0,
+                  p.tc_q ? p.qx : nullptr, p.qx_ld, p.qx_ld / 2};
       tc::fence_proxy_async();
       __syncthreads();
       lstm_phase_tc(p.tc_a, io, p.B, p.Bp, p.RB, p.zc, p.zh, tcs);
@@ -538,6 +599,15 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
                           p.att_in[nxt] + hoff, nullptr, 0, 0, p.zc, p.zh});
     }
     phase_end();
+    // ---- Q: query layers of all mechanisms as tensor-core tiles ----
+    if (p.tc_q) {
+      tc::fence_proxy_async();
+      __syncthreads();
+      dense_phase_tc(p.tq, p.maps + 6, p.RB, tcs,
+                     QueryTcEpi{{const_cast<float*>(p.mech[0].pq), const_cast<float*>(p.mech[1].pq)},
+                                {p.mech[0].Up, p.mech[1].Up}, p.tq.nt[0], p.B});
+      phase_end();
+    }
     // ---- D+E: query layers and attention mechanisms (row split, no barrier in between) ----
     // The processed query of a row is a row-local dense on the attention-LSTM output, so the CTA that owns the row's
     // attention item computes it itself (two rows per pass share one stream of the query-layer weights from L2).
@@ -596,7 +666,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
         const int mi0 = i0 % p.n_mech;
         // the items of one CTA share the mechanism whenever gridDim.x is a multiple of n_mech; otherwise one at a time
         const bool pair = nit == 2 && (i1 % p.n_mech) == mi0;
-        for (int q0 = 0; q0 < nit; q0 += pair ? 2 : 1) {
+        for (int q0 = 0; q0 < nit && !p.tc_q; q0 += pair ? 2 : 1) {
           const int nq = pair ? 2 : 1;
           const int mi = items[q0] % p.n_mech;
           if (p.mech[mi].kind == SAT_ATT_TEACHER_FORCING) continue;
@@ -671,7 +741,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
     if (p.tc) {
       const int h0 = p.A + p.Dctx;
       TcLstmIO io{p.maps + 2 + cur, Act2D{p.l2_in[cur], 1, p.K2_pad, 1}, Act2D{nullptr, 0, 0, 0},
-                  Act2D{(__half*)p.l1_in[nxt] + h0, 1, p.K1_pad, 1}, nullptr, 0, 0};
+                  Act2D{(__half*)p.l1_in[nxt] + h0, 1, p.K1_pad, 1}, nullptr, 0, 0, nullptr, 0, 0};
       tc::fence_proxy_async();
       __syncthreads();
       lstm_phase_tc(p.tc_1, io, p.B, p.Bp, p.RB, p.zc, p.zh, tcs);
@@ -686,8 +756,9 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
     // ---- G: decoder LSTM 2 ----
     if (p.tc) {
       const int h0 = p.Dd;
-      TcLstmIO io{p.maps + 4 + cur, Act2D{p.dout, ld, 1, 0}, Act2D{nullptr, 0, 0, 0},
-                  Act2D{(__half*)p.l2_in[nxt] + h0, 1, p.K2_pad, 1}, p.dec_out, p.max_steps * p.Dd, t * p.Dd};
+      TcLstmIO io{p.maps + 4 + cur, Act2D{p.tc_frame ? nullptr : p.dout, ld, 1, 0}, Act2D{nullptr, 0, 0, 0},
+                  Act2D{(__half*)p.l2_in[nxt] + h0, 1, p.K2_pad, 1}, p.dec_out, p.max_steps * p.Dd, t * p.Dd,
+                  p.tc_frame ? p.px : nullptr, p.px_ld, p.px_ld / 2};
       tc::fence_proxy_async();
       __syncthreads();
       lstm_phase_tc(p.tc_2, io, p.B, p.Bp, p.RB, p.zc, p.zh, tcs);
@@ -717,8 +788,22 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
         phase_end();
         y = p.sa_y[hi & 1];
       }
-      // ---- L+A+B: frame + stop projection of step t, fed-back frame, prenet of step t+1 (row split) ----
-      frame_phase(p, t, y, p.outp.K, Act2D{p.att_in[nxt], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc}, false, scratch);
+      if (p.tc_frame) {
+        // ---- P: frame + stop projection of step t with prenet layer 0 folded in; R: prenet layer 1 of step t+1 ----
+        tc::fence_proxy_async();
+        __syncthreads();
+        dense_phase_tc(p.tp, p.maps + 7, p.RB, tcs,
+                       FrameTcEpi{p.outp.bias, p.Mr, p.P0, p.Mr + 1 + p.P0, p.B, t, p.max_steps, p.mel, p.stop, p.rx,
+                                  p.rx_ld, p.rx_ld / 2});
+        phase_end();
+        tc::fence_proxy_async();
+        __syncthreads();
+        dense_phase_tc(p.tr, p.maps + 8, p.RB, tcs,
+                       PrenetTcEpi{p.pre1.bias, p.P1, p.B, Act2D{p.att_in[nxt], 1, p.Ka_pad, 1}});
+      } else {
+        // ---- L+A+B: frame + stop projection of step t, fed-back frame, prenet of step t+1 (row split) ----
+        frame_phase(p, t, y, p.outp.K, Act2D{p.att_in[nxt], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc}, false, scratch);
+      }
       if (p.tc && t + 1 < p.max_steps) phase_end(&p.tc_a, p.maps + nxt);
       else phase_end();
     }

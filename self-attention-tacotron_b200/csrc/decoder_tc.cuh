@@ -101,11 +101,99 @@ __device__ inline void tc_prefill(const TcLstmDesc& d, const CUtensorMap* xmap, 
 
 struct TcLstmIO {
   const CUtensorMap* xmap;  // activations of this step: row-major fp16 [rows][Kpad]
-  Act2D out0, out1;         // un-zoned cell output (written; out1.p may be null)
+  Act2D out0, out1;         // un-zoned cell output (written; either .p may be null)
   Act2D hz;                 // zoned h for the next step (written)
   float* rm_out;            // optional row-major fp32 copy of the output: rm_out[b * rm_stride + rm_off + u]
   int rm_stride, rm_off;
+  __half* hl;               // optional fp16 hi + lo copy of the output (the input of a dense_phase_tc layer):
+  int hl_stride, hl_lo;     // hl[b * hl_stride + u] = f16(h), hl[b * hl_stride + hl_lo + u] = f16(h - f16(h))
 };
+
+// ---- a dense layer of the step on the tensor cores (B >= 64): query layers, frame / stop projection, prenet -------
+// y[rows, N] = x[rows, K] W[K, N] as tiles of 16 columns x 128 rows, the CTA's W^T slice resident in shared memory
+// (K-major SW128 fp16 image, built once from the fp32 row-major weights).  fp32-grade accuracy from fp16 operands:
+// the activations arrive as an fp16 pair x = xh + xl ([rows][2 * kc * 64]: hi columns, then lo columns) and the GEMM
+// runs the terms xh Wh + xl Wh (+ xh Wl when terms = 3, Wl = f16(W - Wh)) as one K loop of terms * kc chunks.
+struct TcDense {
+  const float* W[2];   // up to two column groups (the query layers of two mechanisms): fp32 row-major [K][ldw]
+  int ldw[2], nt[2];   // row stride and 16-column tiles of each group
+  int ncol[2];         // valid columns of each group (columns beyond read as zero)
+  const float* bias;   // [n_tiles * 16] or null
+  int K, kc;           // kc = ceil(K / 64)
+  int n_tiles, terms;
+  int img_off, slots;  // resident images: slots x terms' weight chunks (kc for Wh, + kc for Wl) x 2 KB
+};
+
+__device__ inline void tc_load_dense_resident(const TcDense& d, int RB, const TcState& st) {
+  if (d.slots == 0) return;
+  const int n_items = d.n_tiles * RB, wch = (d.terms == 3 ? 2 : 1) * d.kc;
+  int slot = 0;
+  for (int item = blockIdx.x; item < n_items && slot < d.slots; item += gridDim.x, ++slot) {
+    const int tile = item / RB;
+    const int grp = tile < d.nt[0] ? 0 : 1, lt = tile - (grp ? d.nt[0] : 0);
+    uint8_t* img = st.wimg + d.img_off + (size_t)slot * wch * 2048;
+    for (int i = threadIdx.x; i < d.kc * tc::CHUNK_K16 * TC_N; i += NT) {
+      const int n = i & (TC_N - 1), k = i >> 4;
+      float w = 0.f;
+      if (k < d.K && lt * TC_N + n < d.ncol[grp]) w = __ldg(d.W[grp] + (size_t)k * d.ldw[grp] + lt * TC_N + n);
+      const __half hi = tc::to_f16(w);
+      const uint32_t o = (k / tc::CHUNK_K16) * 2048 + tc::sw128_offset16(n, k % tc::CHUNK_K16);
+      *(__half*)(img + o) = hi;
+      if (d.terms == 3) *(__half*)(img + d.kc * 2048 + o) = tc::to_f16(w - __half2float(hi));
+    }
+  }
+}
+
+// Every thread of the CTA calls it.  epi(row b, tile, ul, g[4]) receives the pre-bias sums of columns
+// tile * 16 + ul * 4 .. + 3 of utterance row b (one call per thread and item).
+template <class Epi>
+__device__ inline void dense_phase_tc(const TcDense& d, const CUtensorMap* xmap, int RB, TcState& st, Epi epi) {
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int n_items = d.n_tiles * RB, wch = (d.terms == 3 ? 2 : 1) * d.kc, nch = d.terms * d.kc;
+  int slot = 0;
+  for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++slot) {
+    const int tile = item / RB, row0 = (item % RB) * TC_M;
+    const uint8_t* img = st.wimg + d.img_off + (size_t)slot * wch * 2048;
+    if (tid == 0) {
+      for (int c = 0; c < nch; ++c) {
+        const uint32_t n = st.n_chunks + c, s = n % TC_STAGES, use = n / TC_STAGES;
+        if (use > 0) tc::mbar_wait(st.empty + s, (use - 1) & 1);
+        const int term = c / d.kc, cc = c - term * d.kc;
+        tc::mbar_arrive_expect_tx(st.full + s, TC_STAGE_BYTES);
+        tc::tma_load_2d(st.ring + s * TC_STAGE_BYTES, xmap, st.full + s, ((term == 1 ? d.kc : 0) + cc) * tc::CHUNK_K16, row0);
+      }
+    } else if (tid == 32) {
+      const uint32_t idesc = tc::idesc_f16(TC_M, TC_N);
+      for (int c = 0; c < nch; ++c) {
+        const uint32_t n = st.n_chunks + c, s = n % TC_STAGES, use = n / TC_STAGES;
+        tc::mbar_wait(st.full + s, use & 1);
+        tc::tc_fence_after();
+        const int term = c / d.kc, cc = c - term * d.kc;
+        const uint32_t a0 = tc::smem_u32(st.ring + s * TC_STAGE_BYTES);
+        const uint32_t b0 = tc::smem_u32(img + ((term == 2 ? d.kc : 0) + cc) * 2048);
+#pragma unroll
+        for (int k16 = 0; k16 < tc::CHUNK_K16 / tc::UMMA_K16; ++k16)
+          tc::mma_f16(st.tmem, tc::smem_desc_sw128(a0 + k16 * 32), tc::smem_desc_sw128(b0 + k16 * 32), idesc,
+                      (c | k16) != 0);
+        tc::mma_commit(st.empty + s);
+      }
+      tc::mma_commit(st.done);
+    }
+    __syncwarp();
+    tc::mbar_wait(st.done, st.n_items & 1);
+    tc::tc_fence_after();
+    {
+      const int q = warp & 3, ul = warp >> 2;
+      float g[4];
+      tc::tmem_ld4(st.tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(ul * 4), g);
+      epi(row0 + q * 32 + lane, tile, ul, g);
+    }
+    tc::tc_fence_before();
+    st.n_chunks += nch;
+    st.n_items += 1;
+    __syncthreads();  // TMEM accumulator and ring hand-over to the next item / phase
+  }
+}
 
 // One ZoneoutLSTM phase on the tensor cores.  Every thread of the CTA calls it.
 // Roles: thread 0 issues the TMA loads, thread 32 the MMAs; once the accumulator is complete all 16 warps run the
@@ -177,8 +265,13 @@ __device__ inline void lstm_phase_tc(const TcLstmDesc& d, const TcLstmIO& io, in
         const __half hzh = tc::to_f16(hn - zh * (hn - hp));
         *hs = __half2float(hzh);
         ((__half*)io.hz.p)[(size_t)u * io.hz.sd + (size_t)b * io.hz.sb] = hzh;
-        io.out0.put(u, b, hn);
+        if (io.out0.p) io.out0.put(u, b, hn);
         if (io.out1.p) io.out1.put(u, b, hn);
+        if (io.hl) {
+          const __half hh = tc::to_f16(hn);
+          io.hl[(size_t)b * io.hl_stride + u] = hh;
+          io.hl[(size_t)b * io.hl_stride + io.hl_lo + u] = tc::to_f16(hn - __half2float(hh));
+        }
         if (io.rm_out && b < B) io.rm_out[(size_t)b * io.rm_stride + io.rm_off + u] = hn;
       }
     }

@@ -50,8 +50,10 @@ void make_tensor_map_2d_f16(CUtensorMap* map, const void* base, uint64_t rows, u
 namespace {
 constexpr int ST_STAGES = 2;
 
+// M = 128: D row i = TMEM lane i.  M = 64 (SAT_SELFTEST_M=64; A rows 64..127 are not read): the raw dump of all 128
+// lanes shows where the 64 accumulator rows live (rows 16 q .. 16 q + 15 in lanes 32 q .. 32 q + 15).
 __global__ void __launch_bounds__(128) tc_selftest_kernel(const CUtensorMap* __restrict__ mapA, const float* __restrict__ Wt,
-                                                          int K, float* __restrict__ D) {
+                                                          int K, float* __restrict__ D, int M) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const int nchunks = K / tc::CHUNK_K;
@@ -89,11 +91,11 @@ __global__ void __launch_bounds__(128) tc_selftest_kernel(const CUtensorMap* __r
       const int s = c % ST_STAGES;
       const uint32_t use = c / ST_STAGES;
       if (use > 0) tc::mbar_wait(empty + s, (use - 1) & 1);
-      tc::mbar_arrive_expect_tx(full + s, 16384);
+      tc::mbar_arrive_expect_tx(full + s, M * 128);
       tc::tma_load_2d(a_ring + s * 16384, mapA, full + s, c * tc::CHUNK_K, 0);
     }
   } else if (tid == 32) {
-    const uint32_t idesc = tc::idesc_tf32(128, 16);
+    const uint32_t idesc = tc::idesc_tf32(M, 16);
     for (int c = 0; c < nchunks; ++c) {
       const int s = c % ST_STAGES;
       tc::mbar_wait(full + s, (c / ST_STAGES) & 1);
@@ -128,14 +130,16 @@ extern "C" int sat_tc_selftest(const float* A, const float* Wt, int32_t K, float
     SAT_REQUIRE(A && Wt && D && K >= 32 && K % 32 == 0 && K <= 1024, "bad argument");
     cudaStream_t st = (cudaStream_t)stream;
     CUtensorMap hmap;
-    make_tensor_map_2d(&hmap, A, 128, (uint64_t)K, (uint64_t)K, 128);
+    int M = 128;
+    if (const char* e = getenv("SAT_SELFTEST_M")) M = atoi(e) == 64 ? 64 : 128;
+    make_tensor_map_2d(&hmap, A, 128, (uint64_t)K, (uint64_t)K, (uint32_t)M);
     DevPool pool;
     CUtensorMap* dmap = (CUtensorMap*)pool.alloc<uint8_t>(sizeof(CUtensorMap) + 64);
     dmap = (CUtensorMap*)(((uintptr_t)dmap + 63) & ~(uintptr_t)63);
     SAT_CUDA(cudaMemcpyAsync(dmap, &hmap, sizeof(hmap), cudaMemcpyHostToDevice, st));
     const size_t smem = 1024 + ST_STAGES * 16384 + (size_t)(K / 32) * 2048 + 256;
     SAT_CUDA(cudaFuncSetAttribute(tc_selftest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    tc_selftest_kernel<<<1, 128, smem, st>>>(dmap, Wt, K, D);
+    tc_selftest_kernel<<<1, 128, smem, st>>>(dmap, Wt, K, D, M);
     count_launch();
     check_launch("tc_selftest_kernel");
     SAT_CUDA(cudaStreamSynchronize(st));

@@ -143,6 +143,26 @@ def test_tensor_core_gate_gemms_full_dims(name, B, T, S):
     print("tensor-core path rel err", name, B, errs)
 
 
+@pytest.mark.parametrize("name,B,T,S,mode", [("ljspeech_tacotron", 200, 61, 14, "free"),
+                                             ("ljspeech_self_attention", 96, 41, 10, "teacher")])
+def test_tensor_core_dense_phases_switch(name, B, T, S, mode, monkeypatch):
+    """SAT_TC_DENSE=1 (an experiment switch, off by default: slower on B200, see profiles/README.md) runs the query
+    layers -- and, for the self-feeding baseline decoder, the frame / stop projection with the folded prenet layer 0
+    and prenet layer 1 -- as tcgen05 tile phases with fp16 hi + lo operand pairs; same bar."""
+    monkeypatch.setenv("SAT_TC_DENSE", "1")
+    hp = small_hp(name)
+    W = sat_b200.init_weights(hp, seed=13, stress=True)
+    mems, lengths, target, _ = decoder_inputs(hp, B, T, S, seed=13)
+    if mode == "free":
+        ref = oracle_decoder(hp, W, mems, lengths, max_iters=S, stop_mode="never")
+        got = run_cuda(hp, W, mems, lengths, feed_mode=1, stop_mode=0, max_steps=S)
+    else:
+        ref = oracle_decoder(hp, W, mems, lengths, target=target, is_validation=True, teacher_forcing=True)
+        got = run_cuda(hp, W, mems, lengths, target=target, feed_mode=0, stop_mode=0, max_steps=S)
+    assert got["tensor_cores"]
+    check_close(got, ref)
+
+
 @pytest.mark.parametrize("name,B,T", [("ljspeech_tacotron", 256, 53), ("ljspeech_tacotron", 149, 200),
                                       ("ljspeech_self_attention", 128, 77)])
 def test_attention_rows_paired_and_sequential(name, B, T, monkeypatch):
