@@ -104,6 +104,16 @@ int sat_encoder_forward_embedded(sat_encoder* h, const float* embedded, const in
  * activations, fp32 accumulation; needs prenet/conv widths that are multiples of 64 / 128), 0 for the fp32 SIMT form.
  * Environment SAT_ENC_TC=0 at create time forces the fp32 form. */
 int sat_encoder_uses_tensor_cores(sat_encoder* h, int32_t* used);
+/* Padded frames of a batch.  0 (default) = the reference's batched graph: padding (the embedding of id 0) flows through
+ * the conv bank / projections and the encoder self-attention unmasked (modules/module.py:77-110, 425-438; no
+ * sequence-length masking anywhere but the BiLSTM).  1 = every utterance is computed as if it were alone in the batch,
+ * i.e. what the reference's predict produces with its forced batch_size=1 (predict_mel.py:43-44): frames past an
+ * utterance's length read as zeros in every multi-tap convolution and are masked as keys of the self-attention. */
+int sat_encoder_set_mask_padding(sat_encoder* h, int32_t on);
+/* Synchronises `stream`, then returns SAT_EINVAL if any forward issued so far met a symbol id outside [0, num_symbols)
+ * (tacotron2 Embedding asserts the range, models/models.py:28; here such an id embeds as zeros and sets a sticky flag,
+ * which the next sat_encoder_forward also reports once the offending forward has finished). */
+int sat_encoder_check(sat_encoder* h, void* stream);
 void sat_encoder_destroy(sat_encoder* h);
 
 /* ---- decoder ---------------------------------------------------------- */

@@ -144,6 +144,8 @@ struct GemmArgs {
   const int64_t* row_lengths = nullptr;  // optional [Bn]: rows with t >= length read as zero input (values mask)
   const int64_t* gather_ids = nullptr;   // optional [Bn*T] int64: X row index = ids - gather_offset (embedding lookup); T-shift disabled
   int64_t gather_offset = 0;
+  int64_t gather_rows = 0;               // rows of the gathered table: an id outside [offset, offset + rows) reads as a zero
+  int* err_flag = nullptr;               // row and sets *err_flag = 1 (device int, sticky) instead of reading out of bounds
   int maxpool2 = 0;                      // 1: input element = max(X[t], X[t+1]) (MaxPooling1D k2 s1 SAME) fused on load
   int highway = 0;                       // 1: HighwayNet epilogue over interleaved (H_u, T_u) column pairs; R = layer input; writes N/2 columns
 };
@@ -170,6 +172,9 @@ struct ConvTcLaunch {
   // s - (bank - 1) / 2; column tile w computes width w + 1 over its own tap slots only.  cout = bank * 128;
   // scale / shift / y16 cover all widths (channel offset 128 * w); taps / pad_left are ignored.
   int bank = 0;
+  // optional [B] int64 utterance lengths: output rows t >= length are written as ZEROS (both outputs), so that a
+  // following multi-tap convolution sees what it would see for the un-padded utterance ('SAME' zero padding)
+  const int64_t* lengths = nullptr;
 };
 __half* conv_tc_bank_image(DevPool& pool, const std::vector<const float*>& w, int cin);  // w[k-1] = [k][cin][128]
 bool conv_tc_supported(int cin, int cout);

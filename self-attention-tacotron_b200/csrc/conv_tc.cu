@@ -35,6 +35,7 @@ struct ConvTcArgs {
   int ldr;
   int highway;              // 1: HighwayNet epilogue over interleaved (H_u, T_u) column pairs, x = res; writes N/2 columns
   int bank;                 // > 0: conv-bank form (ConvTcLaunch::bank): grid = (widths, row tiles), widest first
+  const long long* lengths; // optional [B]: rows t >= lengths[b] are stored as zeros
 };
 
 __global__ void __launch_bounds__(CT_THREADS, 3)
@@ -99,6 +100,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant__
   const int r = r0 + tid;
   const int b = r / a.Tp, tt = r - b * a.Tp - a.halo;
   const bool valid = r < a.R && tt >= 0 && tt < a.T;
+  const bool dead = valid && a.lengths && tt >= (int)a.lengths[b];  // padded frame of a shorter utterance
   const size_t drow = (size_t)b * a.T + tt;
 #pragma unroll 1
   for (int cb = 0; cb < 128; cb += 16) {
@@ -117,7 +119,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant__
         const int n = n0 + cb + 2 * k;
         const float hh = fmaxf(v[2 * k] + __ldg(a.shift + n), 0.f);
         const float tt = 1.f / (1.f + expf(-(v[2 * k + 1] + __ldg(a.shift + n + 1))));
-        y[k] = hh * tt + x[k] * (1.f - tt);
+        y[k] = dead ? 0.f : hh * tt + x[k] * (1.f - tt);
       }
       if (a.y16) {
         __half2 h[4];
@@ -149,6 +151,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant__
         const float4 q = __ldg(rp + i);
         v[4 * i] += q.x; v[4 * i + 1] += q.y; v[4 * i + 2] += q.z; v[4 * i + 3] += q.w;
       }
+    }
+    if (dead) {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) v[i] = 0.f;
     }
     if (a.y16) {
       __half2 h[8];
@@ -287,6 +293,7 @@ void conv_tc_launch(const ConvTcLaunch& L, cudaStream_t st) {
   a.scale = L.scale; a.shift = L.shift; a.act = L.act;
   a.y16 = L.y16; a.ld16 = L.ld16; a.y32 = L.y32; a.ld32 = L.ld32; a.res = L.res; a.ldr = L.ldr; a.highway = L.highway;
   a.bank = L.bank;
+  a.lengths = (const long long*)L.lengths;
   SAT_REQUIRE(!L.highway || (L.res && L.shift), "highway epilogue needs the layer input (res) and the bias (shift)");
   static bool attr_set = false;
   const int smem = CT_STAGES * CT_STAGE_BYTES + 1024;

@@ -147,8 +147,9 @@ Conv upload_conv_bn(DevPool& pool, const Blob& W, const std::string& P, int k, i
 // shared with postnet.cu
 void conv_bn_act_launch(const float* x, int B, int T, int ldx, const float* w, const float* scale, const float* shift,
                         int k, int cin, int cout, int act, int maxpool2, const float* R, int ldr, float* y, int ldy,
-                        cudaStream_t st) {
+                        cudaStream_t st, const int64_t* row_lengths) {
   GemmArgs g;
+  g.row_lengths = row_lengths;  // optional: input frames t >= length read as zeros
   g.X = x; g.Bn = B; g.T = T; g.Cin = cin; g.ldx = ldx;
   g.W = w; g.taps = k; g.pad_left = (k - 1) / 2; g.N = cout;
   g.scale = scale; g.shift = shift; g.act = act; g.maxpool2 = maxpool2;
@@ -182,6 +183,15 @@ struct sat_encoder {
   std::vector<__half*> hw_img;
   __half* lstm_img = nullptr;
   Scratch ws16;     // haloed fp16 activations of that path
+  // padded frames: 0 = the reference's batched graph (padding flows through the conv layers and the encoder
+  // self-attention unmasked); 1 = every utterance is computed as if it were alone in the batch (frames
+  // past its length are zero for every multi-tap convolution, keys past its length are masked in the self-attention)
+  int mask_padding = 0;
+  int* d_err = nullptr;  // sticky device flag: a symbol id outside [0, num_symbols) was seen
+  int* h_err = nullptr;  // pinned host mirror, refreshed asynchronously at the end of every forward
+  ~sat_encoder() {
+    if (h_err) cudaFreeHost(h_err);
+  }
 };
 
 extern "C" int sat_encoder_create(const sat_hparams* hpp, const sat_tensor* weights, int32_t n_weights, sat_encoder** out) {
@@ -304,12 +314,38 @@ extern "C" int sat_encoder_create(const sat_hparams* hpp, const sat_tensor* weig
         h->hops.push_back(mha_upload(pool, W, P + "/mha", P + "/transform", Ds, Ds, hp.self_attention_num_heads));
       }
     }
+    h->d_err = pool.alloc<int>(1);
+    SAT_CUDA(cudaMemset(h->d_err, 0, sizeof(int)));
+    SAT_CUDA(cudaHostAlloc((void**)&h->h_err, sizeof(int), cudaHostAllocDefault));
+    *h->h_err = 0;
     guard.release();
     *out = h;
   });
 }
 
 extern "C" void sat_encoder_destroy(sat_encoder* h) { delete h; }
+
+extern "C" int sat_encoder_set_mask_padding(sat_encoder* h, int32_t on) {
+  return guarded([&] {
+    SAT_REQUIRE(h, "null argument");
+    h->mask_padding = on ? 1 : 0;
+  });
+}
+
+// waits for the stream, then reports (and clears) the out-of-range-id flag of the forwards issued so far
+extern "C" int sat_encoder_check(sat_encoder* h, void* stream) {
+  return guarded([&] {
+    SAT_REQUIRE(h, "null argument");
+    SAT_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    int flag = 0;
+    SAT_CUDA(cudaMemcpy(&flag, h->d_err, sizeof(int), cudaMemcpyDeviceToHost));
+    if (flag) {
+      SAT_CUDA(cudaMemset(h->d_err, 0, sizeof(int)));
+      *h->h_err = 0;
+      fail(SAT_EINVAL, "a symbol id outside [0, %d) reached the encoder (its embedding was read as zeros)", h->hp.num_symbols);
+    }
+  });
+}
 
 extern "C" int sat_encoder_uses_tensor_cores(sat_encoder* h, int32_t* used) {
   return guarded([&] {
@@ -327,6 +363,12 @@ static int encoder_forward_impl(sat_encoder* h, const int64_t* ids, const float*
     SAT_REQUIRE(sa || (!sa_out && !sa_probs), "ZoneoutEncoderV1 has no self-attention outputs");
     SAT_REQUIRE(!sa || sa_out, "SelfAttentionCBHGEncoder needs sa_out");
     cudaStream_t st = (cudaStream_t)stream;
+    if (*h->h_err) {  // an earlier forward (already finished) saw a bad id: refuse to go on silently
+      *h->h_err = 0;
+      SAT_CUDA(cudaMemsetAsync(h->d_err, 0, sizeof(int), st));
+      fail(SAT_EINVAL, "a symbol id outside [0, %d) reached the encoder in an earlier forward", hp.num_symbols);
+    }
+    const int64_t* mlen = h->mask_padding ? lengths : nullptr;  // masks padded frames (see sat_encoder::mask_padding)
     const size_t rows = (size_t)B * T;
     const int P0 = hp.encoder_prenet_units[0], P1 = hp.encoder_prenet_units[1];
     const int Cb = hp.conv_channels, KW = hp.max_filter_width, half = h->half;
@@ -349,6 +391,7 @@ static int encoder_forward_impl(sat_encoder* h, const int64_t* ids, const float*
       GemmArgs g;
       g.X = ids ? h->emb : embedded; g.Bn = 1; g.T = (int)rows; g.Cin = hp.embedding_dim; g.ldx = hp.embedding_dim;
       g.gather_ids = ids; g.gather_offset = 0;
+      if (ids) { g.gather_rows = hp.num_symbols; g.err_flag = h->d_err; }
       g.W = h->pre_w[0]; g.N = P0; g.shift = h->pre_b[0]; g.act = ACT_RELU; g.C = ws + o_p0; g.ldc = P0;
       gemm_launch(g, st);
       if (!h->tc_full) {
@@ -383,14 +426,14 @@ static int encoder_forward_impl(sat_encoder* h, const int64_t* ids, const float*
         ConvTcLaunch L;  // prenet layer 1: relu(x W + b) -> fp16 (bank input) and fp32 (residual of proj2)
         L.xp = p0_16; L.ldxp = P0; L.B = B; L.T = T; L.cin = P0; L.cout = P1; L.taps = 1; L.pad_left = 0;
         L.wimg = h->pre1_img; L.shift = h->pre_b[1]; L.act = ACT_RELU;
-        L.y16 = x16; L.ld16 = P1; L.y32 = ws + o_p1; L.ld32 = P1;
+        L.y16 = x16; L.ld16 = P1; L.y32 = ws + o_p1; L.ld32 = P1; L.lengths = mlen;
         conv_tc_launch(L, st);
       }
       if (h->bank_img) {
         ConvTcLaunch L;  // all widths of the bank in one launch
         L.xp = x16; L.ldxp = P1; L.B = B; L.T = T; L.cin = P1; L.cout = KW * Cb; L.bank = KW;
         L.wimg = h->bank_img; L.scale = h->bank_scale; L.shift = h->bank_shift; L.act = ACT_RELU;
-        L.y16 = bank16; L.ld16 = ldb;
+        L.y16 = bank16; L.ld16 = ldb; L.lengths = mlen;
         conv_tc_launch(L, st);
       } else {
         for (int k = 1; k <= KW; ++k) {
@@ -398,7 +441,7 @@ static int encoder_forward_impl(sat_encoder* h, const int64_t* ids, const float*
           ConvTcLaunch L;
           L.xp = x16; L.ldxp = P1; L.B = B; L.T = T; L.cin = P1; L.cout = Cb; L.taps = k; L.pad_left = (k - 1) / 2;
           L.wimg = c.wimg; L.scale = c.scale; L.shift = c.shift; L.act = ACT_RELU;
-          L.y16 = bank16 + (size_t)(k - 1) * Cb; L.ld16 = ldb;
+          L.y16 = bank16 + (size_t)(k - 1) * Cb; L.ld16 = ldb; L.lengths = mlen;
           conv_tc_launch(L, st);
         }
       }
@@ -407,7 +450,7 @@ static int encoder_forward_impl(sat_encoder* h, const int64_t* ids, const float*
         ConvTcLaunch L;  // proj1
         L.xp = pool16; L.ldxp = ldb; L.B = B; L.T = T; L.cin = ldb; L.cout = Q1; L.taps = 3; L.pad_left = 1;
         L.wimg = h->proj1.wimg; L.scale = h->proj1.scale; L.shift = h->proj1.shift; L.act = ACT_RELU;
-        L.y16 = q1_16; L.ld16 = Q1;
+        L.y16 = q1_16; L.ld16 = Q1; L.lengths = mlen;
         conv_tc_launch(L, st);
       }
       {
@@ -450,7 +493,7 @@ static int encoder_forward_impl(sat_encoder* h, const int64_t* ids, const float*
           ConvTcLaunch L;  // all widths of the bank in one launch
           L.xp = x16; L.ldxp = P1; L.B = B; L.T = T; L.cin = P1; L.cout = KW * Cb; L.bank = KW;
           L.wimg = h->bank_img; L.scale = h->bank_scale; L.shift = h->bank_shift; L.act = ACT_RELU;
-          L.y16 = bank16; L.ld16 = ldb;
+          L.y16 = bank16; L.ld16 = ldb; L.lengths = mlen;
           conv_tc_launch(L, st);
         } else {
           for (int k = 1; k <= KW; ++k) {
@@ -458,7 +501,7 @@ static int encoder_forward_impl(sat_encoder* h, const int64_t* ids, const float*
             ConvTcLaunch L;
             L.xp = x16; L.ldxp = P1; L.B = B; L.T = T; L.cin = P1; L.cout = Cb; L.taps = k; L.pad_left = (k - 1) / 2;
             L.wimg = c.wimg; L.scale = c.scale; L.shift = c.shift; L.act = ACT_RELU;
-            L.y16 = bank16 + (size_t)(k - 1) * Cb; L.ld16 = ldb;
+            L.y16 = bank16 + (size_t)(k - 1) * Cb; L.ld16 = ldb; L.lengths = mlen;
             conv_tc_launch(L, st);
           }
         }
@@ -466,22 +509,22 @@ static int encoder_forward_impl(sat_encoder* h, const int64_t* ids, const float*
         ConvTcLaunch L;
         L.xp = pool16; L.ldxp = ldb; L.B = B; L.T = T; L.cin = ldb; L.cout = h->proj1.cout; L.taps = 3; L.pad_left = 1;
         L.wimg = h->proj1.wimg; L.scale = h->proj1.scale; L.shift = h->proj1.shift; L.act = ACT_RELU;
-        L.y32 = ws + o_q1; L.ld32 = h->proj1.cout;
+        L.y32 = ws + o_q1; L.ld32 = h->proj1.cout; L.lengths = mlen;
         conv_tc_launch(L, st);
       } else {
         // ---- conv bank -> concat buffer [rows][KW*Cb] (fp32 SIMT form) ----
         for (int k = 1; k <= KW; ++k) {
           const Conv& c = h->bank[k - 1];
           conv_bn_act_launch(ws + o_p1, B, T, P1, c.w, c.scale, c.shift, k, P1, Cb, ACT_RELU, 0, nullptr, 0,
-                             ws + o_bank + (size_t)(k - 1) * Cb, ldb, st);
+                             ws + o_bank + (size_t)(k - 1) * Cb, ldb, st, mlen);
         }
         // ---- maxpool (fused on load) + proj1 ----
         conv_bn_act_launch(ws + o_bank, B, T, ldb, h->proj1.w, h->proj1.scale, h->proj1.shift, 3, ldb, h->proj1.cout, ACT_RELU,
-                           1, nullptr, 0, ws + o_q1, h->proj1.cout, st);
+                           1, nullptr, 0, ws + o_q1, h->proj1.cout, st, mlen);
       }
       // ---- proj2 + residual ----
       conv_bn_act_launch(ws + o_q1, B, T, h->proj1.cout, h->proj2.w, h->proj2.scale, h->proj2.shift, 3, h->proj1.cout,
-                         h->proj2.cout, ACT_NONE, 0, ws + o_p1, P1, ws + o_q2, h->proj2.cout, st);
+                         h->proj2.cout, ACT_NONE, 0, ws + o_p1, P1, ws + o_q2, h->proj2.cout, st, mlen);
       hw_in = ws + o_q2;
       float* ping = ws + o_ha;
       float* pong = ws + o_hb;
@@ -530,11 +573,12 @@ static int encoder_forward_impl(sat_encoder* h, const int64_t* ids, const float*
       for (size_t i = 0; i < h->hops.size(); ++i) {
         float* y = (i + 1 == h->hops.size()) ? sa_out : ws + ((i & 1) ? o_sa0 : o_sa1);
         float* pr = sa_probs ? sa_probs + i * (size_t)H * B * T * T : nullptr;
-        sat_layer_forward(h->hops[i], x, B, T, 0, nullptr, y, pr, ws + o_mha, st, 1);
+        sat_layer_forward(h->hops[i], x, B, T, 0, mlen, y, pr, ws + o_mha, st, 1);
         x = y;
       }
       if (h->hops.empty()) SAT_CUDA(cudaMemcpyAsync(sa_out, x, rows * Ds * sizeof(float), cudaMemcpyDeviceToDevice, st));
     }
+    if (ids) SAT_CUDA(cudaMemcpyAsync(h->h_err, h->d_err, sizeof(int), cudaMemcpyDeviceToHost, st));
   });
 }
 

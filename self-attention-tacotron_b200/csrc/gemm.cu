@@ -34,6 +34,7 @@ struct GemmDev {
   const float* R; int ldr;
   float* C; int ldc;
   const int64_t* row_lengths; const int64_t* gather_ids; long long gather_offset;
+  long long gather_rows; int* err_flag;
   int maxpool2; int vecA; int vecB; long long M;
   int highway;
 };
@@ -44,13 +45,17 @@ __device__ __forceinline__ const float* src_row(const GemmDev& p, long long g, i
   if (g >= p.M) return nullptr;
   if (p.gather_ids) {
     long long r = p.gather_ids[g] - p.gather_offset;
+    if (p.gather_rows > 0 && (r < 0 || r >= p.gather_rows)) {  // id outside the table: zero row + sticky error flag
+      if (p.err_flag) *p.err_flag = 1;
+      return nullptr;
+    }
     return p.X + r * p.ldx;
   }
   int b = (int)(g / p.T), t = (int)(g % p.T) + tap - p.pad_left;
   if (t < 0 || t >= p.T) return nullptr;
   if (p.row_lengths && t >= p.row_lengths[b]) return nullptr;
   const float* row = p.X + ((long long)b * p.T + t) * p.ldx;
-  if (p.maxpool2 && t + 1 < p.T) *next_row = row + p.ldx;
+  if (p.maxpool2 && t + 1 < p.T && !(p.row_lengths && t + 1 >= p.row_lengths[b])) *next_row = row + p.ldx;
   return row;
 }
 
@@ -183,6 +188,7 @@ void gemm_launch(const GemmArgs& a, cudaStream_t st) {
   p.scale = a.scale; p.shift = a.shift; p.act = a.act;
   p.R = a.R; p.ldr = a.ldr; p.C = a.C; p.ldc = a.ldc;
   p.row_lengths = a.row_lengths; p.gather_ids = a.gather_ids; p.gather_offset = a.gather_offset;
+  p.gather_rows = a.gather_rows; p.err_flag = a.err_flag;
   p.maxpool2 = a.maxpool2;
   p.highway = a.highway;
   p.M = (long long)a.Bn * a.T;

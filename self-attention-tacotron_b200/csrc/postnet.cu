@@ -10,7 +10,7 @@
 namespace sat {
 void conv_bn_act_launch(const float* x, int B, int T, int ldx, const float* w, const float* scale, const float* shift,
                         int k, int cin, int cout, int act, int maxpool2, const float* R, int ldr, float* y, int ldy,
-                        cudaStream_t st);
+                        cudaStream_t st, const int64_t* row_lengths = nullptr);
 }
 using namespace sat;
 

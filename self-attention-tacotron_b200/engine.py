@@ -140,6 +140,15 @@ class EncoderHandle:
         check(lib().sat_encoder_uses_tensor_cores(self._h, C.byref(used)))
         return bool(used.value)
 
+    def set_mask_padding(self, on):
+        """True: every utterance is computed as if alone in the batch (the reference's predict runs batch_size=1,
+        predict_mel.py:43-44); False (default): the reference's batched graph, padding unmasked."""
+        check(lib().sat_encoder_set_mask_padding(self._h, int(bool(on))))
+
+    def check(self, stream=None):
+        """Synchronises, then raises ValueError if a symbol id outside [0, num_symbols) reached the encoder."""
+        check(lib().sat_encoder_check(self._h, stream_ptr(stream)))
+
     def forward(self, ids_or_embedded, lengths, want_probs=False, stream=None):
         hp = self.hp
         x = ids_or_embedded

@@ -101,6 +101,13 @@ class ZoneoutEncoderV1:
                                    zoneout_factor_cell, zoneout_factor_output, table.shape[1], table.shape[0])
         self._h = engine.EncoderHandle(self.hp, weights)
 
+    def set_mask_padding(self, on):
+        """see engine.EncoderHandle.set_mask_padding"""
+        self._h.set_mask_padding(on)
+
+    def check(self):
+        self._h.check()
+
     def __call__(self, inputs, input_lengths=None, **kwargs):
         if input_lengths is None:
             raise ValueError("input_lengths is required")
@@ -130,6 +137,13 @@ class SelfAttentionCBHGEncoder:
                                    self_attention_num_heads=self_attention_num_heads,
                                    self_attention_num_hop=self_attention_num_hop)
         self._h = engine.EncoderHandle(self.hp, weights)
+
+    def set_mask_padding(self, on):
+        """see engine.EncoderHandle.set_mask_padding"""
+        self._h.set_mask_padding(on)
+
+    def check(self):
+        self._h.check()
 
     def __call__(self, inputs, input_lengths=None, want_alignments=True, **kwargs):
         if input_lengths is None:

@@ -75,6 +75,11 @@ def predict(hparams, weights, utterances, output_dir=None, batch_size=None, devi
     if device.type != "cuda":
         raise RuntimeError("predict_mel runs on CUDA devices only (no CPU fallback)")
     model = model or tacotron_model_factory(hparams, weights)
+    # The reference's predict forces batch_size=1 (predict_mel.py:43-44), so an utterance never sees padding and stops on
+    # its own stop token.  Batches here keep that per-utterance result: padded encoder frames are masked, and every
+    # row stops by its own rule (the run ends when the last row has stopped).
+    model.encoder.set_mask_padding(True)
+    model.decoder.stop_mode = "per_row"
     batch_size = batch_size or hparams.batch_size
     r = hparams.outputs_per_step
     results = []
@@ -89,6 +94,7 @@ def predict(hparams, weights, utterances, output_dir=None, batch_size=None, devi
         out = model.predict(ids, lengths, target=target if need_target else None, speaker_id=spk,
                             is_validation=mode != "free_run", teacher_forcing=mode == "teacher_forced")
         mel = out["mel"].cpu().numpy()
+        model.encoder.check()  # a symbol id outside the embedding table raises here (tacotron2 Embedding asserts it)
         post = out["mel_postnet"].cpu().numpy() if "mel_postnet" in out else None
         stop_steps = out["stop_steps"].cpu().numpy()
         aligns = [out[k].cpu().numpy() for k in ("alignment", "alignment2") if k in out]
