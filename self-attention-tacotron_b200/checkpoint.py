@@ -311,6 +311,209 @@ def default_name_map(names):
     return out
 
 
+# ---- names of the variables the reference creates, reconstructed ----------------------------------------------------------
+# TF 1.x naming, applied to the constructors of the reference (citations into /root/reference):
+# * a tf.layers.Layer without a name opens variable_scope(None, default_name=snake_case(class)) at its first call, so
+#   siblings are numbered in CALL order inside their enclosing scope: dense, dense_1, ... (MultiHeadAttention calls key,
+#   value, query, output: modules/self_attention.py:103-119; MultiSpeakerPreNet calls dense0, speaker_projection, dense:
+#   modules/multi_speaker_modules.py:27-30; the encoder calls pre_net, pre_net_1, zoneout_cbhg, dense,
+#   self_attention_transformer*: modules/module.py:425-438);
+# * explicit names are kept: conv1d_K{k} / proj1 / proj2 (modules/module.py:51,60,67), memory_layer / query_layer /
+#   attention_v (TF BahdanauAttention), attention_variable / attention_bias / location_features_convolution /
+#   location_features_layer / transition_factor_projection inside scope location_sensitive_attention
+#   (modules/forward_attention.py:17-24,73-90), out_projection / stop_token_projection under decoder/
+#   (modules/module.py:716-723);
+# * tf.layers.batch_normalization -> batch_normalization/{gamma,beta,moving_mean,moving_variance}; LSTMCell ->
+#   lstm_cell/{kernel,bias} (blacklist fragments of models/models.py:165-168); bidirectional_dynamic_rnn ->
+#   bidirectional_rnn/{fw,bw}/...; MultiRNNCell -> multi_rnn_cell/cell_{i}/...
+# Names created inside the absent tacotron2 package (Embedding, PreNet, HighwayNet H / T, ZoneoutLSTMCell, AttentionRNN,
+# DecoderRNNV2, OutputAndStopTokenWrapper) are L-confidence; `resolve_names` therefore matches by FRAGMENT + SHAPE, not
+# by full path, and this function is the single place that states the assumed full paths (used to test the resolver).
+def tf_variable_names(hparams):
+    """{weight-blob name: reconstructed TensorFlow variable name} for every weight of the model."""
+    from .weights import weight_shapes
+    hp = hparams
+    enc = "self_attention_cbhg_encoder" if hp.encoder == "SelfAttentionCBHGEncoder" else "zoneout_encoder_v1"
+    dec = {"ExtendedDecoder": "extended_decoder", "DualSourceDecoder": "dual_source_decoder",
+           "DualSourceTransformerDecoder": "dual_source_transformer_decoder"}[hp.decoder]
+    cbhg = f"{enc}/zoneout_cbhg"
+    num = lambda base, i: base if i == 0 else f"{base}_{i}"  # noqa: E731
+    bn = {"gamma": "gamma", "beta": "beta", "mean": "moving_mean", "var": "moving_variance"}
+    mha = ["key", "value", "query", "output"]
+    ms = hp.use_speaker_embedding and hp.speaker_embedd_to_prenet
+    dual = hp.decoder != "ExtendedDecoder"
+    cell = f"{dec}/decoder/" + ("dual_source_attention_rnn" if dual else "attention_rnn")
+    kinds = []
+    for i in range(2 if dual else 1):
+        a = hp.attention if i == 0 else hp.attention2
+        kinds.append("location_sensitive_attention" if a in ("forward", "location_sensitive") or a.startswith("teacher_forcing_forward")
+                     else "bahdanau_attention")
+    out = {}
+    for k in weight_shapes(hp):
+        q = k.split("/")
+        if k == "embedding":
+            n = "embedding/embedding"
+        elif k == "speaker_embedding":
+            n = "embedding_1/embedding"
+        elif q[0] == "speaker_embedding_projection":
+            n = f"dense/{q[1]}"
+        elif q[:2] == ["encoder", "prenet"]:
+            n = f"{enc}/{num('pre_net', int(q[2].split('_')[1]))}/dense/{q[3]}"
+        elif q[:2] == ["encoder", "cbhg"] and (q[2].startswith("conv1d_K") or q[2] in ("proj1", "proj2")):
+            n = f"{cbhg}/{q[2]}/conv1d/kernel" if q[3] == "kernel" else f"{cbhg}/{q[2]}/batch_normalization/{bn[q[4]]}"
+        elif q[:3] == ["encoder", "cbhg", "adjustment"]:
+            n = f"{cbhg}/dense/{q[3]}"
+        elif q[:2] == ["encoder", "cbhg"] and q[2].startswith("highway_"):
+            n = f"{cbhg}/{num('highway_net', int(q[2].split('_')[1]))}/{q[3]}/{q[4]}"
+        elif q[:2] == ["encoder", "cbhg"] and q[2].startswith("lstm_"):
+            n = f"{cbhg}/bidirectional_rnn/{q[2][5:]}/zoneout_lstm_cell/lstm_cell/{q[3]}"
+        elif q[:2] == ["encoder", "sa_projection"]:
+            n = f"{enc}/dense/{q[2]}"
+        elif q[0] in ("encoder", "decoder") and q[1].startswith("sa_"):
+            scope = (enc if q[0] == "encoder" else f"{dec}/decoder") + "/" + num("self_attention_transformer", int(q[1][3:]))
+            n = (f"{scope}/self_attention/multi_head_attention/{num('dense', mha.index(q[3]))}/{q[4]}" if q[2] == "mha"
+                 else f"{scope}/dense/{q[3]}")
+        elif q[:3] == ["decoder", "prenet", "ms"]:
+            n = f"{cell}/multi_speaker_pre_net/{num('dense', ['dense0', 'speaker_projection', 'dense'].index(q[3]))}/{q[4]}"
+        elif q[:2] == ["decoder", "prenet"]:
+            i = int(q[2].split("_")[1])
+            n = f"{cell}/{num('pre_net', i - 1 if ms else i)}/dense/{q[3]}"
+        elif q[:2] == ["decoder", "attention_lstm"]:
+            n = f"{cell}/attention_wrapper/zoneout_lstm_cell/lstm_cell/{q[2]}"
+        elif q[0] == "decoder" and q[1] in ("lstm_1", "lstm_2"):
+            n = f"{dec}/decoder/decoder_rnn_v2/multi_rnn_cell/cell_{q[1][5:]}/zoneout_lstm_cell/lstm_cell/{q[2]}"
+        elif q[0] == "decoder" and q[1].startswith("attention"):
+            i = int(q[1][9:]) - 1
+            att = f"{cell}/attention_wrapper/{num(kinds[i], sum(1 for j in range(i) if kinds[j] == kinds[i]))}"
+            leaf = {"memory_layer": f"{dec}/{num('memory_layer', i)}/kernel", "query_layer": f"{att}/query_layer/kernel",
+                    "attention_v": f"{att}/" + ("attention_variable" if kinds[i] == "location_sensitive_attention" else "attention_v"),
+                    "attention_bias": f"{att}/attention_bias",
+                    "location_conv": f"{att}/location_features_convolution/{q[-1]}",
+                    "location_layer": f"{att}/location_features_layer/kernel",
+                    "transition": f"{att}/transition_factor_projection/{q[-1]}"}
+            n = leaf[q[2]]
+        elif q[0] == "decoder" and q[1] in ("out_projection", "stop_token_projection"):
+            if dual:
+                n = f"{dec}/decoder/{q[1]}/{q[2]}"  # modules/module.py:716-723
+            else:  # tacotron2 OutputAndStopTokenWrapper: dense (frames), dense_1 (stop token); models/models.py:167
+                n = f"{dec}/decoder/output_and_stop_token_wrapper/{num('dense', int(q[1] == 'stop_token_projection'))}/{q[2]}"
+        elif q[0] == "postnet" and q[1].startswith("conv_"):
+            scope = f"post_net_v2/{num('conv1d', int(q[1][5:]))}"
+            n = f"{scope}/conv1d/kernel" if q[2] == "kernel" else f"{scope}/batch_normalization/{bn[q[3]]}"
+        elif q[:2] == ["postnet", "projection"]:
+            n = f"post_net_v2/dense/{q[2]}"
+        else:
+            raise KeyError(f"no TensorFlow name rule for weight {k}")
+        out[k] = n
+    assert len(set(out.values())) == len(out), "reconstructed names collide"
+    return out
+
+
+def _natural(name):
+    return [int(t) if t.isdigit() else t for t in re.split(r"(\d+)", name)]
+
+
+def resolve_names(hparams, variables):
+    """{checkpoint variable name: weight-blob name} by fragment + shape, for checkpoints written by the reference.
+
+    ``variables``: {name: (dtype, shape)} (``checkpoint_variables``).  Every weight of the model gets a fragment pattern
+    (what any TF naming of that layer must contain) and its expected shape; candidates = variables that match both
+    (singleton axes ignored); several weights sharing pattern and shape (prenet layers, highway layers, the four
+    projections of a MultiHeadAttention, self-attention hops) take their candidates in natural name order -- the order
+    TF numbers sibling scopes in.  Optimiser slots, global_step and beta powers are ignored.  Weights that stay
+    ambiguous or unmatched are left out (``import_weights`` reports them)."""
+    from .weights import weight_shapes
+    hp = hparams
+    shapes = weight_shapes(hp)
+    squeeze = lambda sh: tuple(d for d in sh if d != 1)  # noqa: E731
+    cand = {n: squeeze(sh) for n, (_, sh) in variables.items()
+            if not re.search(r"/Adam(_\d+)?$|^global_step$|beta\d_power$|/ExponentialMovingAverage$", n)}
+    enc_side = lambda n: "decoder" not in n  # noqa: E731
+    dec_side = lambda n: "decoder" in n  # noqa: E731
+    bnp = {"gamma": "gamma", "beta": "beta", "mean": "moving_mean", "var": "moving_variance"}
+
+    def pattern(k):
+        """-> (regex, side predicate or None) for weight-blob name k"""
+        q = k.split("/")
+        leaf = q[-1]
+        if k in ("embedding", "speaker_embedding"):
+            return r"embedding(_\d+)?/[^/]*(embedding|table|kernel)[^/]*$", None
+        if q[0] == "speaker_embedding_projection":
+            return rf"^(?!.*(encoder|decoder|pre_net|highway)).*dense[^/]*/{leaf}$", None
+        if q[:2] == ["encoder", "prenet"]:
+            return rf"pre_?net[^/]*/dense[^/]*/{leaf}$", enc_side
+        if q[:2] == ["encoder", "cbhg"] and (q[2].startswith("conv1d_K") or q[2] in ("proj1", "proj2")):
+            tail = "conv1d[^/]*/kernel" if q[3] == "kernel" else rf"batch_normalization[^/]*/{bnp[q[4]]}"
+            return rf"(^|/){q[2]}/(.*/)?{tail}$", enc_side
+        if q[:3] == ["encoder", "cbhg", "adjustment"]:
+            return rf"cbhg[^/]*/dense[^/]*/{leaf}$", enc_side
+        if q[:2] == ["encoder", "cbhg"] and q[2].startswith("highway_"):
+            return rf"highway[^/]*/{q[3]}[^/]*/{leaf}$", enc_side
+        if q[:2] == ["encoder", "cbhg"] and q[2].startswith("lstm_"):
+            return rf"/{q[2][5:]}/(.*/)?{leaf}$", enc_side
+        if q[:2] == ["encoder", "sa_projection"]:
+            return rf"encoder[^/]*/dense[^/]*/{leaf}$", enc_side
+        if q[0] in ("encoder", "decoder") and q[1].startswith("sa_"):
+            side = enc_side if q[0] == "encoder" else dec_side
+            if q[2] == "mha":
+                return rf"multi_head_attention[^/]*/dense[^/]*/{leaf}$", side
+            return rf"self_attention_transformer[^/]*/dense[^/]*/{leaf}$", side
+        if q[:3] == ["decoder", "prenet", "ms"]:
+            return rf"multi_speaker_pre_?net[^/]*/dense[^/]*/{leaf}$", None
+        if q[:2] == ["decoder", "prenet"]:
+            return rf"(^|/)pre_?net[^/]*/dense[^/]*/{leaf}$", dec_side
+        if q[0] == "decoder" and q[1] in ("attention_lstm", "lstm_1", "lstm_2"):
+            return rf"lstm_cell[^/]*/{leaf}$", dec_side
+        if q[0] == "decoder" and q[1].startswith("attention"):
+            frag = {"memory_layer": "memory_layer[^/]*/kernel", "query_layer": "query_layer[^/]*/kernel",
+                    "attention_v": "(attention_v|attention_variable)", "attention_bias": "attention_bias",
+                    "location_conv": rf"location_features_convolution[^/]*/{leaf}",
+                    "location_layer": "location_features_layer[^/]*/kernel",
+                    "transition": rf"transition_factor_projection[^/]*/{leaf}"}[q[2]]
+            return rf"(^|/){frag}$", None
+        if q[0] == "decoder" and q[1] == "out_projection":
+            return rf"(out_projection/{leaf}|output_and_stop_token_wrapper/dense/{leaf})$", None
+        if q[0] == "decoder" and q[1] == "stop_token_projection":
+            return rf"(stop_token_projection/{leaf}|output_and_stop_token_wrapper/dense_1/{leaf})$", None
+        if q[0] == "postnet" and q[1].startswith("conv_"):
+            tail = "conv1d[^/]*/kernel" if q[2] == "kernel" else rf"batch_normalization[^/]*/{bnp[q[3]]}"
+            return rf"post_?net.*/{tail}$", None
+        if q[:2] == ["postnet", "projection"]:
+            return rf"post_?net[^/]*/dense[^/]*/{leaf}$", None
+        return None, None
+
+    groups = {}
+    for k, (shape, _) in shapes.items():
+        pat, side = pattern(k)
+        if pat is not None:
+            groups.setdefault((pat, side, squeeze(shape)), []).append(k)
+    out, taken = {}, set()
+    # kernels (and everything that is not a bias) first; a bias then follows its kernel into the same TF scope, which
+    # settles groups of equal-shaped biases (the three decoder LSTMs) that name order alone cannot
+    ordered = sorted(groups.items(), key=lambda kv: all(k.endswith("/bias") for k in kv[1]))
+    for (pat, side, shape), ks in ordered:
+        if all(k.endswith("/bias") for k in ks):
+            inv = {k: n for n, k in out.items()}
+            sib = {k: inv[k[:-4] + "kernel"][:-6] + "bias" for k in ks
+                   if k[:-4] + "kernel" in inv and inv[k[:-4] + "kernel"].endswith("kernel")}
+            if len(sib) == len(ks) and all(cand.get(n) == shape and n not in taken for n in sib.values()):
+                for k, n in sib.items():
+                    out[n] = k
+                    taken.add(n)
+                continue
+        rx = re.compile(pat)
+        names = sorted((n for n, sh in cand.items() if sh == shape and rx.search(n) and (side is None or side(n))
+                        and n not in taken), key=_natural)
+        if len(names) != len(ks):
+            continue  # missing or ambiguous: leave to name_map / the error report
+        # blob-side order: the order weight_shapes lists them in IS layer order (prenet 0, 1; highway 0..; key, value,
+        # query, output; hop 0, 1), which is the order TF numbers the sibling scopes in
+        for n, k in zip(names, ks):
+            out[n] = k
+            taken.add(n)
+    return out
+
+
 def import_weights(hparams, prefix, name_map=None, strict=True):
     """Checkpoint ``prefix`` -> weight blob for ``hparams`` (float32, the layouts of include/sat.h).
 
@@ -324,6 +527,10 @@ def import_weights(hparams, prefix, name_map=None, strict=True):
     avail = checkpoint_variables(prefix)
     mapping = {n: n for n in avail if n in shapes}
     mapping.update(default_name_map(avail))
+    # fragment + shape resolution of the TensorFlow-scoped names of a reference checkpoint; never overrides the above
+    for n, k in resolve_names(hparams, avail).items():
+        if n not in mapping and k not in mapping.values():
+            mapping[n] = k
     mapping.update(name_map or {})
     bad = sorted(v for v in mapping.values() if v not in shapes)
     if bad:

@@ -40,11 +40,71 @@ def _make_table():
 _TABLE = _make_table()
 
 
-def crc32c(data: bytes, crc: int = 0) -> int:
+def _crc32c_bytes(data, crc=0):
     c = crc ^ 0xFFFFFFFF
     for b in data:
         c = _TABLE[(c ^ b) & 0xFF] ^ (c >> 8)
     return c ^ 0xFFFFFFFF
+
+
+# Large buffers (checkpoint tensors): the buffer is cut into equal chunks whose CRCs advance in lockstep as one NumPy
+# vector (one table gather per byte position), and the chunk CRCs are joined with the GF(2) "append L zero bytes"
+# operator (the crc32_combine construction: crc(A || B) = shift(crc(A), len(B)) ^ crc(B)).
+def _gf2_times(mat, vec):
+    s, i = 0, 0
+    while vec:
+        if vec & 1:
+            s ^= mat[i]
+        vec >>= 1
+        i += 1
+    return s
+
+
+def _gf2_compose(a, b):
+    return [_gf2_times(a, col) for col in b]
+
+
+_SHIFT_CACHE = {}
+
+
+def _shift_operator(nbytes):
+    """32 columns of the operator that maps crc(A) to crc(A || nbytes zero bytes) (finalised CRC values)."""
+    if nbytes not in _SHIFT_CACHE:
+        op = [0x82F63B78] + [1 << (n - 1) for n in range(1, 32)]  # one zero bit
+        for _ in range(3):
+            op = _gf2_compose(op, op)                             # -> one zero byte
+        total, n = [1 << i for i in range(32)], nbytes
+        while n:
+            if n & 1:
+                total = _gf2_compose(op, total)
+            n >>= 1
+            if n:
+                op = _gf2_compose(op, op)
+        _SHIFT_CACHE[nbytes] = total
+    return _SHIFT_CACHE[nbytes]
+
+
+_FAST_CHUNK = 4096
+
+
+def crc32c(data: bytes, crc: int = 0) -> int:
+    n = len(data)
+    if crc != 0 or n < 64 * _FAST_CHUNK:
+        return _crc32c_bytes(data, crc)
+    import numpy as np
+    L = _FAST_CHUNK
+    chunks = n // L
+    cols = np.frombuffer(data, dtype=np.uint8, count=chunks * L).reshape(chunks, L).T.copy()
+    table = np.asarray(_TABLE, dtype=np.uint32)
+    c = np.full(chunks, 0xFFFFFFFF, dtype=np.uint32)
+    for j in range(L):
+        c = table[(c ^ cols[j]) & 0xFF] ^ (c >> 8)
+    parts = (c ^ np.uint32(0xFFFFFFFF)).tolist()
+    op = _shift_operator(L)
+    total = parts[0]
+    for v in parts[1:]:
+        total = _gf2_times(op, total) ^ v
+    return _crc32c_bytes(memoryview(data)[chunks * L:], total)
 
 
 def masked_crc32c(data: bytes) -> int:

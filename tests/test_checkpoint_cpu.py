@@ -137,3 +137,43 @@ def test_import_with_tensorflow_style_names(tmp_path):
     bad[lc] = "decoder/lstm_1/kernel"
     with pytest.raises((ValueError, KeyError)):
         ck.import_weights(hp, prefix, name_map=bad)
+
+
+@pytest.mark.parametrize("cfg,extra", [("ljspeech_tacotron", {}), ("ljspeech_self_attention", dict(use_postnet_v2=True)),
+                                       ("vctk_self_attention", dict(use_forward_attention_transition_agent=True)),
+                                       ("codes_self_attention", {})])
+def test_import_reference_scoped_checkpoint_without_name_map(cfg, extra, tmp_path):
+    """A whole model written under the TensorFlow-scoped names the reference creates (checkpoint.tf_variable_names:
+    layer scopes numbered in call order, lstm_cell / batch_normalization / memory_layer / ... fragments), with Adam
+    slots and the step counters beside it, imports with NO name_map: every weight is found by fragment + shape, the
+    blob is bit-identical."""
+    hp = sat_b200.config(cfg)
+    hp.override(**extra)
+    W = sat_b200.init_weights(hp, seed=9, stress=True)
+    names = ck.tf_variable_names(hp)
+    assert sorted(names) == sorted(W)
+    tensors = {}
+    for k, v in W.items():
+        tensors[names[k]] = v
+        if k.endswith("kernel"):
+            tensors[names[k] + "/Adam"] = np.zeros_like(v)
+            tensors[names[k] + "/Adam_1"] = np.ones_like(v)
+    tensors["global_step"] = np.asarray(7, dtype=np.int64)
+    tensors["beta1_power"] = np.asarray(0.9, dtype=np.float32)
+    tensors["beta2_power"] = np.asarray(0.999, dtype=np.float32)
+    prefix = str(tmp_path / "model.ckpt-7")
+    ck.write_checkpoint(prefix, tensors)
+    W2 = ck.import_weights(hp, ck.latest_checkpoint(str(tmp_path)))
+    assert sorted(W2) == sorted(W)
+    for k in W:
+        assert W2[k].dtype == np.float32 and np.array_equal(W[k], W2[k]), k
+    # the three decoder LSTM biases share a shape: each must have followed its own kernel
+    m = ck.resolve_names(hp, ck.checkpoint_variables(prefix))
+    assert m[names["decoder/lstm_2/bias"]] == "decoder/lstm_2/bias"
+    assert m[names["decoder/attention_lstm/bias"]] == "decoder/attention_lstm/bias"
+    # a different top-level scope (e.g. a model wrapped in tf.variable_scope("model")) changes nothing
+    ck.write_checkpoint(str(tmp_path / "wrapped.ckpt"), {"model/" + n: v for n, v in tensors.items()
+                                                         if "Adam" not in n and "power" not in n and n != "global_step"},
+                        update_state_file=False)
+    W3 = ck.import_weights(hp, str(tmp_path / "wrapped.ckpt"))
+    assert all(np.array_equal(W[k], W3[k]) for k in W)

@@ -215,3 +215,21 @@ def test_out_of_range_symbol_id_is_reported():
         model.encoder.check()
     model.encoder(_t(np.full((2, 9), 5, dtype=np.int64)), input_lengths=_t(lengths))
     model.encoder.check()  # the flag was cleared; good ids pass
+
+
+def test_predict_from_imported_reference_checkpoint(tmp_path):
+    """a checkpoint under the reference's TensorFlow variable names -> import_weights with no
+    name_map -> predict() equals the run on the weights it was written from."""
+    from sat_b200 import checkpoint as ck
+    from sat_b200.models import tacotron_model_factory
+    hp = small_hp("ljspeech_self_attention")
+    W = sat_b200.init_weights(hp, seed=51, stress=True)
+    names = ck.tf_variable_names(hp)
+    ck.write_checkpoint(str(tmp_path / "model.ckpt-3"), {names[k]: v for k, v in W.items()})
+    W2 = ck.import_weights(hp, ck.latest_checkpoint(str(tmp_path)))
+    ids, lengths, target = _inputs(hp, 2, 19, 6, seed=51)
+    kw = dict(target=_t(target), is_validation=True, teacher_forcing=True)
+    a = tacotron_model_factory(hp, W).predict(_t(ids), _t(lengths), **kw)
+    b = tacotron_model_factory(hp, W2).predict(_t(ids), _t(lengths), **kw)
+    for k in ("mel", "stop_token", "alignment", "alignment2"):
+        np.testing.assert_array_equal(a[k].cpu().numpy(), b[k].cpu().numpy())
