@@ -114,6 +114,9 @@ int sat_encoder_set_mask_padding(sat_encoder* h, int32_t on);
  * (tacotron2 Embedding asserts the range, models/models.py:28; here such an id embeds as zeros and sets a sticky flag,
  * which the next sat_encoder_forward also reports once the offending forward has finished). */
 int sat_encoder_check(sat_encoder* h, void* stream);
+/* The same report without synchronising: covers the forwards that have already finished on the device (each ends by
+ * copying the flag to pinned host memory) -- for pipelined callers that wait on their own events. */
+int sat_encoder_poll_error(sat_encoder* h);
 void sat_encoder_destroy(sat_encoder* h);
 
 /* ---- decoder ---------------------------------------------------------- */

@@ -332,6 +332,19 @@ extern "C" int sat_encoder_set_mask_padding(sat_encoder* h, int32_t on) {
   });
 }
 
+// no synchronisation: reports (and clears) the flag of the forwards that have FINISHED so far (their last operation
+// copies the device flag into pinned host memory)
+extern "C" int sat_encoder_poll_error(sat_encoder* h) {
+  return guarded([&] {
+    SAT_REQUIRE(h, "null argument");
+    if (*h->h_err) {
+      *h->h_err = 0;
+      SAT_CUDA(cudaMemsetAsync(h->d_err, 0, sizeof(int), 0));
+      fail(SAT_EINVAL, "a symbol id outside [0, %d) reached the encoder (its embedding was read as zeros)", h->hp.num_symbols);
+    }
+  });
+}
+
 // waits for the stream, then reports (and clears) the out-of-range-id flag of the forwards issued so far
 extern "C" int sat_encoder_check(sat_encoder* h, void* stream) {
   return guarded([&] {

@@ -149,6 +149,10 @@ class EncoderHandle:
         """Synchronises, then raises ValueError if a symbol id outside [0, num_symbols) reached the encoder."""
         check(lib().sat_encoder_check(self._h, stream_ptr(stream)))
 
+    def poll_error(self):
+        """check() without the synchronisation: reports bad ids of the forwards that have finished on the device"""
+        check(lib().sat_encoder_poll_error(self._h))
+
     def forward(self, ids_or_embedded, lengths, want_probs=False, stream=None):
         hp = self.hp
         x = ids_or_embedded

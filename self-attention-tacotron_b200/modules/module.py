@@ -101,12 +101,18 @@ class ZoneoutEncoderV1:
                                    zoneout_factor_cell, zoneout_factor_output, table.shape[1], table.shape[0])
         self._h = engine.EncoderHandle(self.hp, weights)
 
+    mask_padding = False
+
     def set_mask_padding(self, on):
         """see engine.EncoderHandle.set_mask_padding"""
         self._h.set_mask_padding(on)
+        self.mask_padding = bool(on)
 
     def check(self):
         self._h.check()
+
+    def poll_error(self):
+        self._h.poll_error()
 
     def __call__(self, inputs, input_lengths=None, **kwargs):
         if input_lengths is None:
@@ -138,12 +144,18 @@ class SelfAttentionCBHGEncoder:
                                    self_attention_num_hop=self_attention_num_hop)
         self._h = engine.EncoderHandle(self.hp, weights)
 
+    mask_padding = False
+
     def set_mask_padding(self, on):
         """see engine.EncoderHandle.set_mask_padding"""
         self._h.set_mask_padding(on)
+        self.mask_padding = bool(on)
 
     def check(self):
         self._h.check()
+
+    def poll_error(self):
+        self._h.poll_error()
 
     def __call__(self, inputs, input_lengths=None, want_alignments=True, **kwargs):
         if input_lengths is None:
@@ -206,6 +218,7 @@ class _DecoderBase:
         self.outputs_per_step = outputs_per_step
         self._handles = {}
         self.stop_mode = "all_rows"  # reference rule (helpers.py:156-160); "per_row" retires rows individually
+        self.async_results = False   # True: a free run returns full-length tensors and n_steps as a device tensor
 
     def _handle(self, mechs, speaker_embed):
         kinds = tuple(m.kind for m in mechs)
@@ -287,11 +300,18 @@ class _DecoderBase:
             stop = helper.stop_mode if self.stop_mode == "all_rows" else _lib.STOP_PER_ROW
             out = h.run([m.memory for m in mechs], mechs[0].memory_sequence_length, feed_mode=helper.feed_mode,
                         stop_mode=stop, max_steps=self.max_iters, min_iters=helper.min_iters, **kw)
-        n = int(out["n_steps"].item())  # the one host sync of a run: how many steps the stop rule allowed
+        if is_validation:
+            n = n_ret = min(helper.num_steps, self.max_iters)  # fixed step count: no host sync needed
+        elif self.async_results:
+            # free run without a host sync: full-length buffers, the step count stays on the device (frames past a
+            # row's stop step / past n_steps are unspecified); the caller slices after its own read-back
+            n, n_ret = self.max_iters, out["n_steps"]
+        else:
+            n = n_ret = int(out["n_steps"].item())  # the one host sync of a run: how many steps the stop rule allowed
         mel = out["mel"][:, :n * r]
         stop_token = out["stop"][:, :n, None]
         sa = [p[:, hd, :n, :n] for p in out["self_attention_probs"] for hd in range(p.shape[1])]
-        state = AttentionHistoryState([a[:, :n] for a in out["alignments"]], out["stop_steps"], n, sa)
+        state = AttentionHistoryState([a[:, :n] for a in out["alignments"]], out["stop_steps"], n_ret, sa)
         return mel, stop_token, out["sample_ids"][:, :n], state
 
 

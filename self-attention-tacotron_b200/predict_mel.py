@@ -7,6 +7,7 @@ length-bucketed and sharded over the GPUs of one box (``sharding.py``), inputs a
 PNG plot is written (no plotting stack).  Next to every ``.mfbsp`` a prediction TFRecord is written (:70-74)."""
 import os
 from collections import namedtuple
+from concurrent.futures import ThreadPoolExecutor
 
 import numpy as np
 import torch
@@ -64,13 +65,37 @@ def _pad_batch(utts, hp, device):
             torch.from_numpy(lengths).pin_memory().to(device, non_blocking=True), target, spk)
 
 
+class _HostSlot:
+    """Pinned host buffers for the results of one batch, reused every other batch (two slots = the read-back of batch
+    i overlaps the compute of batch i+1)."""
+
+    def __init__(self):
+        self.bufs = {}
+        self.copied = torch.cuda.Event()
+
+    def fetch(self, name, dev_tensor):
+        """enqueue dev_tensor -> pinned host copy on the current (copy) stream; returns the host tensor"""
+        n = dev_tensor.numel()
+        buf = self.bufs.get(name)
+        if buf is None or buf.numel() < n or buf.dtype != dev_tensor.dtype:
+            buf = torch.empty(max(n, 1), dtype=dev_tensor.dtype).pin_memory()
+            self.bufs[name] = buf
+        host = buf[:n].view(dev_tensor.shape)
+        host.copy_(dev_tensor, non_blocking=True)
+        return host
+
+
 def predict(hparams, weights, utterances, output_dir=None, batch_size=None, device=None, rank=0, world_size=1,
-            mode="free_run", model=None):
+            mode="free_run", model=None, batch_hook=None):
     """Synthesise ``utterances`` (list of Utterance) -> list[PredictedMel] for the ones this rank owns.
 
     mode: 'free_run' (stop-token inference, PREDICT), 'validation' / 'teacher_forced' (EVAL forms).
     With ``hparams.use_forced_alignment_mode`` the two-pass forced alignment of models/models.py:118-134 runs.
-    """
+
+    Batches are pipelined: the results of batch i (mel, post-net mel, stop steps, alignment histories) are read back
+    into pinned host memory on a copy stream while batch i+1 is padded, uploaded and computed; slicing per utterance
+    and the file writes of batch i happen on the host during that compute.  ``batch_hook(i)`` (optional) runs on the
+    compute stream before batch i is launched (bench.py flushes L2 there)."""
     device = device or torch.device("cuda", torch.cuda.current_device())
     if device.type != "cuda":
         raise RuntimeError("predict_mel runs on CUDA devices only (no CPU fallback)")
@@ -78,37 +103,94 @@ def predict(hparams, weights, utterances, output_dir=None, batch_size=None, devi
     # The reference's predict forces batch_size=1 (predict_mel.py:43-44), so an utterance never sees padding and stops on
     # its own stop token.  Batches here keep that per-utterance result: padded encoder frames are masked, and every
     # row stops by its own rule (the run ends when the last row has stopped).
+    saved = (model.encoder.mask_padding, model.decoder.stop_mode, model.decoder.async_results)
     model.encoder.set_mask_padding(True)
     model.decoder.stop_mode = "per_row"
+    model.decoder.async_results = not hparams.use_forced_alignment_mode  # no host sync inside model.predict()
     batch_size = batch_size or hparams.batch_size
     r = hparams.outputs_per_step
     results = []
     buckets = make_buckets([len(u.source) for u in utterances], batch_size, world_size,
                            bucket_width=hparams.batch_bucket_width)
-    for idxs in buckets[rank]:
-        utts = [utterances[i] for i in idxs]
+    copy_stream = torch.cuda.Stream(device=device)
+    slots = [_HostSlot(), _HostSlot()]
+    pool = ThreadPoolExecutor(max_workers=4)
+
+    def launch(i, idxs):
+        utts = [utterances[j] for j in idxs]
         ids, lengths, target, spk = _pad_batch(utts, hparams, device)
         need_target = mode != "free_run" or hparams.use_forced_alignment_mode
         if need_target and target is None:
             raise ValueError(f"mode {mode!r} needs ground-truth mel for every utterance")
+        if batch_hook is not None:
+            batch_hook(i)
         out = model.predict(ids, lengths, target=target if need_target else None, speaker_id=spk,
                             is_validation=mode != "free_run", teacher_forcing=mode == "teacher_forced")
-        mel = out["mel"].cpu().numpy()
-        model.encoder.check()  # a symbol id outside the embedding table raises here (tacotron2 Embedding asserts it)
-        post = out["mel_postnet"].cpu().numpy() if "mel_postnet" in out else None
-        stop_steps = out["stop_steps"].cpu().numpy()
-        aligns = [out[k].cpu().numpy() for k in ("alignment", "alignment2") if k in out]
+        done = torch.cuda.Event()
+        done.record()
+        slot = slots[i % 2]
+        host = {}
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(done)
+            for k in ("mel", "mel_postnet", "stop_steps", "n_steps", "alignment", "alignment2"):
+                v = out.get(k)
+                if not torch.is_tensor(v):
+                    host[k] = v  # n_steps of a fixed-length run is a Python int
+                    continue
+                if k.startswith("alignment"):
+                    v = v.transpose(1, 2)  # back to the contiguous [B, S, T] history the kernel wrote
+                host[k] = slot.fetch(k, v)
+                v.record_stream(copy_stream)
+            slot.copied.record()
+        return utts, [len(u.source) for u in utts], host, slot
+
+    def finish(utts, src_len, host, slot):
+        slot.copied.synchronize()
+        # a symbol id outside the embedding table raises here (tacotron2 Embedding asserts it); no synchronisation:
+        # the batch's forward has finished, the read-back waited for it
+        model.encoder.poll_error()
+        stop_steps = host["stop_steps"].numpy().copy()
+        n_steps = host["n_steps"]
+        if torch.is_tensor(n_steps):
+            n_steps = int(n_steps.numpy().reshape(-1)[0])
+        # ONE copy per result tensor out of the pinned buffers (they are reused two batches later); the utterances of the
+        # batch then share these arrays as views -- 256 separate copies cost 3x as much in page faults
+        # (NumPy copies release the GIL: the tensors are copied side by side on a small thread pool)
+        jobs = {"mel": host["mel"].numpy()[:, :n_steps * r]}
+        if host.get("mel_postnet") is not None:
+            jobs["post"] = host["mel_postnet"].numpy()[:, :n_steps * r]
+        for k in ("alignment", "alignment2"):
+            if host.get(k) is not None:
+                jobs[k] = host[k].numpy()[:, :n_steps]  # [B, S, T]
+        copies = dict(zip(jobs, pool.map(np.array, jobs.values())))
+        mel, post = copies["mel"], copies.get("post")
+        aligns = [copies[k] for k in ("alignment", "alignment2") if k in copies]
         for i, u in enumerate(utts):
             # frames kept per utterance: up to and including its own stop step (free run), else all steps
-            n = out["n_steps"] if (mode != "free_run" or stop_steps[i] < 0) else int(stop_steps[i]) + 1
-            L = int(lengths[i].item())
-            al = [a[i, :L, :n] for a in aligns] + [None] * (6 - len(aligns))
+            n = n_steps if (mode != "free_run" or stop_steps[i] < 0) else int(stop_steps[i]) + 1
+            L = src_len[i]
+            # (T_memory, T_query) like models/models.py:104-115: a transposed VIEW of the batch's history array
+            al = [a[i, :n, :L].T for a in aligns] + [None] * (6 - len(aligns))
             m = mel[i, :n * r]
-            pm = PredictedMel(u.id, u.key, m, post[i, :n * r] if post is not None else None, m.shape[1], m.shape[0],
-                              u.mel, al[0], al[1], al[2], al[3], al[4], al[5], u.source, u.text, None)
+            pm = PredictedMel(u.id, u.key, m, post[i, :n * r] if post is not None else None, m.shape[1],
+                              m.shape[0], u.mel, al[0], al[1], al[2], al[3], al[4], al[5], u.source, u.text, None)
             results.append(pm)
             if output_dir is not None:
                 write_predicted_mel(pm, hparams, output_dir)
+
+    try:
+        pending = None
+        for i, idxs in enumerate(buckets[rank]):
+            cur = launch(i, idxs)  # slot i % 2 is free: batch i - 2 was finished before batch i - 1 was launched
+            if pending is not None:
+                finish(*pending)   # host work of batch i - 1 while batch i computes
+            pending = cur
+        if pending is not None:
+            finish(*pending)
+    finally:
+        pool.shutdown(wait=True)
+        model.encoder.set_mask_padding(saved[0])
+        model.decoder.stop_mode, model.decoder.async_results = saved[1], saved[2]
     return results
 
 
