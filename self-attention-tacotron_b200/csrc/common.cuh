@@ -184,10 +184,27 @@ void conv_tc_maxpool2(const __half* x, int B, int T, int C, __half* y, cudaStrea
 void conv_tc_zero_halo(__half* x, int B, int T, int C, cudaStream_t st);  // C % 8 == 0
 void conv_tc_launch(const ConvTcLaunch& L, cudaStream_t st);
 
+// A time-batched dense layer y[rows, N] = act(x[rows, K] W[K, N] + bias) (+ residual) on the tensor cores with fp32-grade
+// accuracy from fp16 operands: x = xh + xl and W = Wh + Wl as fp16 pairs, y = xh Wh + xl Wh + xh Wl as ONE conv_tc_kernel
+// launch (taps = 1) over the packed activations [xh | xl | xh] (3K columns) and the image [Wh | Wh | Wl] -- the dropped
+// xl Wl term is ~2^-22 relative.  K % 64 == 0; N is padded to a multiple of 128 (Y needs ldy >= Npad columns).
+struct DenseTc3 {
+  const __half* img = nullptr;  // [Npad][3K] K-major
+  const float* bias = nullptr;  // [Npad] (zeros where absent)
+  int K = 0, N = 0, Npad = 0;
+};
+DenseTc3 dense_tc3_upload(DevPool& pool, const float* w, int ldw, const float* bias, int K, int N);  // w: host [K][ldw]
+size_t dense_tc3_pack_halves(size_t rows, int K);  // halves of the packed-activation scratch for `rows` rows
+// lengths / T (optional): rows (b, t) with t >= lengths[b] are packed as zeros (masked memory of the attention keys)
+void dense_tc3_launch(const DenseTc3& d, const float* x, int ldx, size_t rows, int act, const float* res, int ldr, float* y,
+                      int ldy, __half* pack, cudaStream_t st, const int64_t* lengths = nullptr, int T = 0);
+
 // ---- multi-head self-attention (mha.cu) --------------------------------------
 // Device copy of one MultiHeadAttention (modules/self_attention.py:89-128) and, optionally, the
 // tanh transform layer of the enclosing SelfAttentionTransformer (modules/module.py:358).
 struct MhaDev {
+  DenseTc3 tq, to, tt;    // optional tensor-core forms of the three dense layers (dense_tc3_upload) ...
+  __half* xpack = nullptr;  // ... and their packed-activation scratch (dense_tc3_pack_halves(rows, max(Din, D)))
   float* Wqkv = nullptr;  // [Din][3D], column blocks key | value | query
   float* bqkv = nullptr;  // [3D]
   float* Wo = nullptr;    // [D][D]

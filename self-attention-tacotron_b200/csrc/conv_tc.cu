@@ -276,6 +276,72 @@ void conv_tc_maxpool2(const __half* x, int B, int T, int C, __half* y, cudaStrea
   count_launch();
 }
 
+namespace {
+// fp32 [rows][ldx] -> fp16 [halo + rows][3K] = [xh | xl | xh], xh = f16(x), xl = f16(x - xh); optional length mask
+__global__ void pack3_f16_kernel(const float* __restrict__ x, int ldx, size_t rows, int K, int halo, __half* __restrict__ xp,
+                                 const long long* __restrict__ lengths, int T) {
+  const int K4 = K / 4;
+  const size_t n = rows * K4;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const int c4 = (int)(i % K4);
+    const size_t row = i / K4;
+    float4 v = __ldg((const float4*)(x + row * ldx) + c4);
+    if (lengths && (long long)(row % T) >= lengths[row / T]) v = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float f[4] = {v.x, v.y, v.z, v.w};
+    __half h[4], l[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      h[k] = tc::to_f16(f[k]);
+      l[k] = tc::to_f16(f[k] - __half2float(h[k]));
+    }
+    __half* dst = xp + (row + halo) * (size_t)(3 * K) + 4 * c4;
+    const uint2 hv = *(const uint2*)h, lv = *(const uint2*)l;
+    *(uint2*)dst = hv;
+    *(uint2*)(dst + K) = lv;
+    *(uint2*)(dst + 2 * K) = hv;
+  }
+}
+}  // namespace
+
+DenseTc3 dense_tc3_upload(DevPool& pool, const float* w, int ldw, const float* bias, int K, int N) {
+  DenseTc3 d;
+  if (K % 64 != 0 || K <= 0 || N <= 0) return d;
+  d.K = K; d.N = N; d.Npad = (N + 127) / 128 * 128;
+  std::vector<__half> img((size_t)d.Npad * 3 * K, __float2half_rn(0.f));
+  for (int k = 0; k < K; ++k)
+    for (int n = 0; n < N; ++n) {
+      const float v = w[(size_t)k * ldw + n];
+      const __half hi = __float2half_rn(v);
+      __half* row = img.data() + (size_t)n * 3 * K;
+      row[k] = hi;
+      row[K + k] = hi;
+      row[2 * K + k] = __float2half_rn(v - __half2float(hi));
+    }
+  std::vector<float> packed((img.size() + 1) / 2);
+  memcpy(packed.data(), img.data(), img.size() * sizeof(__half));
+  d.img = (const __half*)pool.upload(packed);
+  std::vector<float> b(d.Npad, 0.f);
+  if (bias)
+    for (int n = 0; n < N; ++n) b[n] = bias[n];
+  d.bias = pool.upload(b);
+  return d;
+}
+
+size_t dense_tc3_pack_halves(size_t rows, int K) { return (rows + 2 * CONV_TC_HALO) * (size_t)(3 * K) + 64; }
+
+void dense_tc3_launch(const DenseTc3& d, const float* x, int ldx, size_t rows, int act, const float* res, int ldr, float* y,
+                      int ldy, __half* pack, cudaStream_t st, const int64_t* lengths, int T) {
+  SAT_REQUIRE(d.img && ldy >= d.Npad && rows > 0 && rows < ((size_t)1 << 30), "dense_tc3_launch: bad arguments");
+  const size_t n = rows * (d.K / 4);
+  pack3_f16_kernel<<<(unsigned)std::min<size_t>((n + 255) / 256, 148 * 16), 256, 0, st>>>(
+      x, ldx, rows, d.K, CONV_TC_HALO, pack, (const long long*)lengths, T);
+  count_launch();
+  ConvTcLaunch L;
+  L.xp = pack; L.ldxp = 3 * d.K; L.B = 1; L.T = (int)rows; L.cin = 3 * d.K; L.cout = d.Npad; L.taps = 1; L.pad_left = 0;
+  L.wimg = d.img; L.shift = d.bias; L.act = act; L.y32 = y; L.ld32 = ldy; L.res = res; L.ldr = ldr;
+  conv_tc_launch(L, st);
+}
+
 void conv_tc_launch(const ConvTcLaunch& L, cudaStream_t st) {
   SAT_REQUIRE(conv_tc_supported(L.cin, L.cout), "tensor-core conv needs Cin %% 64 == 0 and Cout %% 128 == 0 (got %d, %d)", L.cin, L.cout);
   const int taps_total = L.bank ? L.bank : L.taps, pad_left = L.bank ? (L.bank - 1) / 2 : L.pad_left;

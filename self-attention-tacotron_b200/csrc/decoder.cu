@@ -164,6 +164,11 @@ struct sat_decoder {
   DevPool pool;
   Scratch ws;
   Scratch ws_tail;  // time-batched buffers of the teacher-forced form
+  Scratch ws_pack;  // packed fp16 activations of the tensor-core dense layers (dense_tc3_launch)
+  // tensor-core forms (fp16 hi + lo operand pairs, fp32-grade) of the time-batched dense layers: attention keys,
+  // multi-speaker dense / prenet layer 1 over all steps, the decoder self-attention projections, frame + stop projection
+  DenseTc3 t_mem[2], t_msd, t_pre1, t_outp, t_qkv[MAX_HOPS], t_o[MAX_HOPS], t_tr[MAX_HOPS];
+  bool dense_tc = true;
   PackedDense pre0, msd, pre1, lstm_a, lstm_1, lstm_2, outp, dq[2];
   PackedDense outp_f;  // outp + prenet layer 0 folded onto the fed-back frame (self feed): [d_out][Mr + 1 + P0]
   bool has_outp_f = false;
@@ -220,6 +225,8 @@ extern "C" int sat_decoder_create(const sat_hparams* hpp, const sat_tensor* weig
                            W.get(D + "prenet/ms/dense0/bias", h->P0), h->Mnf, h->P0);
       h->msd = pack_dense(pool, W.get(D + "prenet/ms/dense/kernel", (int64_t)h->P0 * h->P0),
                           W.get(D + "prenet/ms/dense/bias", h->P0), h->P0, h->P0);
+      h->t_msd = dense_tc3_upload(pool, W.get(D + "prenet/ms/dense/kernel", (int64_t)h->P0 * h->P0), h->P0,
+                                  W.get(D + "prenet/ms/dense/bias", h->P0), h->P0, h->P0);
       h->ms_Ws = pool.upload(W.get(D + "prenet/ms/speaker_projection/kernel", (int64_t)E * h->P0), (size_t)E * h->P0);
       h->ms_bs = pool.upload(W.get(D + "prenet/ms/speaker_projection/bias", h->P0), h->P0);
     } else {
@@ -228,6 +235,9 @@ extern "C" int sat_decoder_create(const sat_hparams* hpp, const sat_tensor* weig
     }
     h->pre1 = pack_dense(pool, W.get(D + "prenet/dense_1/kernel", (int64_t)h->P0 * h->P1),
                          W.get(D + "prenet/dense_1/bias", h->P1), h->P0, h->P1);
+    h->t_pre1 = dense_tc3_upload(pool, W.get(D + "prenet/dense_1/kernel", (int64_t)h->P0 * h->P1), h->P1,
+                                 W.get(D + "prenet/dense_1/bias", h->P1), h->P0, h->P1);
+    if (const char* e = getenv("SAT_DENSE_TC3")) h->dense_tc = atoi(e) != 0;
     // cells
     const int Ka = h->P1 + h->Dctx + A, K1 = A + h->Dctx + Dd, K2 = 2 * Dd;
     h->lstm_a = pack_lstm(pool, W.get(D + "attention_lstm/kernel", (int64_t)Ka * 4 * A), W.get(D + "attention_lstm/bias", 4 * A), Ka, A);
@@ -248,6 +258,7 @@ extern "C" int sat_decoder_create(const sat_hparams* hpp, const sat_tensor* weig
         return pool.upload(v);
       };
       h->mem_layer[i] = padU(W.get(P + "memory_layer/kernel", (int64_t)Dm * U), Dm);
+      h->t_mem[i] = dense_tc3_upload(pool, W.get(P + "memory_layer/kernel", (int64_t)Dm * U), U, nullptr, Dm, U);
       {
         std::vector<int> cm(Up, -1);
         for (int u = 0; u < U; ++u) cm[u] = u;
@@ -302,6 +313,9 @@ extern "C" int sat_decoder_create(const sat_hparams* hpp, const sat_tensor* weig
         for (int n = 0; n < Ds; ++n) b[j * Ds + n] = bb[n];
       }
       h->sa_qkv[i] = pack_dense(pool, w.data(), b.data(), Dd, 3 * Ds);
+      h->t_qkv[i] = dense_tc3_upload(pool, w.data(), 3 * Ds, b.data(), Dd, 3 * Ds);
+      h->t_o[i] = dense_tc3_upload(pool, W.get(P + "mha/output/kernel", (int64_t)Ds * Ds), Ds, W.get(P + "mha/output/bias", Ds), Ds, Ds);
+      h->t_tr[i] = dense_tc3_upload(pool, W.get(P + "transform/kernel", (int64_t)Ds * Ds), Ds, W.get(P + "transform/bias", Ds), Ds, Ds);
       h->sa_o[i] = pack_dense(pool, W.get(P + "mha/output/kernel", (int64_t)Ds * Ds), W.get(P + "mha/output/bias", Ds), Ds, Ds);
       h->sa_tr[i] = pack_dense(pool, W.get(P + "transform/kernel", (int64_t)Ds * Ds), W.get(P + "transform/bias", Ds), Ds, Ds);
       d_out = Ds;
@@ -321,6 +335,7 @@ extern "C" int sat_decoder_create(const sat_hparams* hpp, const sat_tensor* weig
       for (int n = 0; n < h->Mr; ++n) b[n] = bo[n];
       b[h->Mr] = bs[0];
       h->outp = pack_dense(pool, w.data(), b.data(), d_out, N);
+      h->t_outp = dense_tc3_upload(pool, w.data(), N, b.data(), d_out, N);
       // Self feed: the next input frame is the last n_feed_frame frames of this projection, and prenet layer 0 is a
       // dense layer on it -- two GEMVs in sequence on the critical path of every step.  Their composition is one
       // linear map of the decoder output: column Mr + 1 + j = sum_f W_out[:, f0 + f] W_pre0[f][j] (bias likewise),
@@ -697,6 +712,15 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
     p.mel = io.mel; p.stop = io.stop; p.dec_out = io.decoder_outputs; p.stop_steps = io.stop_steps; p.n_steps = io.n_steps;
     p.barrier = h->barrier; p.prof = h->prof;
 
+    // tensor-core form of the time-batched dense layers (dense_tc3_launch): worth it from a few hundred rows on
+    const size_t rows_pack = std::max((size_t)B * T, (size_t)B * S);
+    __half* pack = nullptr;
+    if (h->dense_tc) {
+      int Kmax = std::max(std::max(p.P0, Dd), Ds);
+      for (int i = 0; i < h->n_mech; ++i) Kmax = std::max(Kmax, (int)hp.memory_dim[i]);
+      pack = h->ws_pack.get<__half>(dense_tc3_pack_halves(rows_pack, (Kmax + 63) / 64 * 64));
+    }
+    auto tc3 = [&](const DenseTc3& d, size_t rows) { return pack && d.img && rows >= 256; };
     if (p.ms) {
       spk_term_kernel<<<ceil_div(B * p.P0, 256), 256, 0, st>>>(io.speaker_embed, h->ms_Ws, h->ms_bs, B, hp.speaker_embedding_dim,
                                                               p.P0, ld, ws + o_spk);
@@ -734,11 +758,16 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
         m.teacher_S = io.target_steps;
       } else {
         // keys = (memory * mask) @ memory_layer  (TF BahdanauAttention; computed once per batch)
-        GemmArgs g;
-        g.X = io.memory[i]; g.Bn = B; g.T = T; g.Cin = m.Dv; g.ldx = m.Dv;
-        g.W = h->mem_layer[i]; g.N = m.Up; g.C = ws + o_keys[i]; g.ldc = m.Up;
-        g.row_lengths = io.memory_lengths;
-        gemm_launch(g, st);
+        if (tc3(h->t_mem[i], (size_t)B * T) && h->t_mem[i].Npad == m.Up) {
+          dense_tc3_launch(h->t_mem[i], io.memory[i], m.Dv, (size_t)B * T, ACT_NONE, nullptr, 0, ws + o_keys[i], m.Up, pack,
+                           st, io.memory_lengths, T);
+        } else {
+          GemmArgs g;
+          g.X = io.memory[i]; g.Bn = B; g.T = T; g.Cin = m.Dv; g.ldx = m.Dv;
+          g.W = h->mem_layer[i]; g.N = m.Up; g.C = ws + o_keys[i]; g.ldc = m.Up;
+          g.row_lengths = io.memory_lengths;
+          gemm_launch(g, st);
+        }
         m.keys = ws + o_keys[i];
       }
     }
@@ -754,7 +783,13 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
     // ---- teacher-forced time-batched form: prenet of all steps before the loop, hops + projections after it ----
     bool tail = io.feed_mode == SAT_FEED_TEACHER && io.stop_mode == SAT_STOP_FIXED;
     if (const char* e = getenv("SAT_BATCHED_TAIL")) tail = tail && atoi(e) != 0;
-    auto dense_rows = [&](const PackedDense& d, const float* x, int ldx, size_t rows, int act, float* y) {
+    auto dense_rows = [&](const PackedDense& d, const DenseTc3& t, const float* x, int ldx, size_t rows, int act, float* y,
+                          int ldy) {
+      if (tc3(t, rows) && ldy >= t.Npad) {
+        dense_tc3_launch(t, x, ldx, rows, act, nullptr, 0, y, ldy, pack, st);
+        return;
+      }
+      SAT_REQUIRE(ldy == d.Np, "dense_rows: output stride");
       GemmArgs g;
       g.X = x; g.Bn = 1; g.T = (int)rows; g.Cin = d.K; g.ldx = ldx;
       g.W = d.Wrm; g.N = d.Np; g.shift = d.bias; g.act = act; g.C = y; g.ldc = d.Np;
@@ -762,6 +797,7 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
     };
     const size_t rows_all = (size_t)B * S;
     float *t_dec = nullptr, *t_y[2] = {nullptr, nullptr}, *t_mha = nullptr, *t_proj = nullptr;
+    int ld_proj = h->outp.Np;
     if (tail) {
       for (int i = 0; i < h->hops; ++i)
         tail = tail && h->sa_qkv[i].Np == h->sa_qkv[i].N && h->sa_o[i].Np == h->sa_o[i].N && h->sa_tr[i].Np == h->sa_tr[i].N;
@@ -775,21 +811,22 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
       MhaDev m0;
       m0.D = Ds;
       const size_t o_mha = ttake(h->hops ? mha_scratch_floats(m0, (int64_t)rows_all) : 0);
-      const size_t o_pr = ttake(rows_all * h->outp.Np);
+      ld_proj = tc3(h->t_outp, rows_all) ? h->t_outp.Npad : h->outp.Np;
+      const size_t o_pr = ttake(rows_all * ld_proj);
       float* tw = h->ws_tail.get<float>(toff);
       teacher_inputs_kernel<<<(unsigned)std::min<size_t>((rows_all * p.Mnf + 255) / 256, 148 * 16), 256, 0, st>>>(
           io.target, B, S, io.target_steps, p.Mr, p.Mnf, tw + o_x);
       count_launch();
-      dense_rows(h->pre0, tw + o_x, p.Mnf, rows_all, ACT_RELU, tw + o_a);
+      dense_rows(h->pre0, DenseTc3(), tw + o_x, p.Mnf, rows_all, ACT_RELU, tw + o_a, h->pre0.Np);
       const float* pin = tw + o_a;
       if (p.ms) {
         add_spk_rows_kernel<<<(unsigned)std::min<size_t>((rows_all * p.P0 + 255) / 256, 148 * 16), 256, 0, st>>>(
             tw + o_a, (int)rows_all, B, p.P0, h->pre0.Np, p.spk_term, ld);
         count_launch();
-        dense_rows(h->msd, tw + o_a, h->pre0.Np, rows_all, ACT_RELU, tw + o_b);
+        dense_rows(h->msd, h->t_msd, tw + o_a, h->pre0.Np, rows_all, ACT_RELU, tw + o_b, h->pre0.Np);
         pin = tw + o_b;
       }
-      dense_rows(h->pre1, pin, h->pre0.Np, rows_all, ACT_RELU, tw + o_p1);
+      dense_rows(h->pre1, h->t_pre1, pin, h->pre0.Np, rows_all, ACT_RELU, tw + o_p1, h->pre1.Np);
       p.batched_tail = 1;
       p.p1_all = tw + o_p1;
       p.p1_ld = h->pre1.Np;
@@ -835,12 +872,16 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
         m.Wqkv = h->sa_qkv[i].Wrm; m.bqkv = h->sa_qkv[i].bias; m.Wo = h->sa_o[i].Wrm; m.bo = h->sa_o[i].bias;
         m.Wt = h->sa_tr[i].Wrm; m.bt = h->sa_tr[i].bias;
         m.Din = Dd; m.D = Ds; m.H = hp.decoder_self_attention_num_heads;
+        if (pack && rows_all >= 256) {
+          m.tq = h->t_qkv[i]; m.to = h->t_o[i]; m.tt = h->t_tr[i];
+          m.xpack = pack;
+        }
         sat_layer_forward(m, y, B, S, 1, nullptr, t_y[i & 1], io.self_attention_probs[i], t_mha, st);
         y = t_y[i & 1];
       }
-      dense_rows(h->outp, y, h->outp.K, rows_all, ACT_NONE, t_proj);
+      dense_rows(h->outp, h->t_outp, y, h->outp.K, rows_all, ACT_NONE, t_proj, ld_proj);
       split_projection_kernel<<<(unsigned)std::min<size_t>((rows_all * (p.Mr + 1) + 255) / 256, 148 * 16), 256, 0, st>>>(
-          t_proj, rows_all, h->outp.Np, p.Mr, io.mel, io.stop);
+          t_proj, rows_all, ld_proj, p.Mr, io.mel, io.stop);
       count_launch();
     }
     if (io.sample_ids) {

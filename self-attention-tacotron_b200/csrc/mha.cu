@@ -520,10 +520,14 @@ size_t mha_scratch_floats(const MhaDev& m, int64_t rows) { return (size_t)rows *
 
 static void attention_core(const MhaDev& m, const float* x, int B, int T, int causal, const int64_t* pad_lengths,
                            float* ctx, float* qkv, float* probs, int head_major, cudaStream_t st) {
-  GemmArgs g;
-  g.X = x; g.Bn = 1; g.T = B * T; g.Cin = m.Din; g.ldx = m.Din;
-  g.W = m.Wqkv; g.N = 3 * m.D; g.shift = m.bqkv; g.C = qkv; g.ldc = 3 * m.D;
-  gemm_launch(g, st);
+  if (m.tq.img && m.xpack && m.tq.Npad == 3 * m.D) {
+    dense_tc3_launch(m.tq, x, m.Din, (size_t)B * T, ACT_NONE, nullptr, 0, qkv, 3 * m.D, m.xpack, st);
+  } else {
+    GemmArgs g;
+    g.X = x; g.Bn = 1; g.T = B * T; g.Cin = m.Din; g.ldx = m.Din;
+    g.W = m.Wqkv; g.N = 3 * m.D; g.shift = m.bqkv; g.C = qkv; g.ldc = 3 * m.D;
+    gemm_launch(g, st);
+  }
   const int dh = m.D / m.H, Tpad = (T + 3) & ~3;
   if (mha_tc_ok(T, m.D, m.H)) {
     const int Tp = (T + 15) & ~15;
@@ -562,6 +566,10 @@ void mha_forward(const MhaDev& m, const float* x, int B, int T, int causal, cons
   float* qkv = scratch;
   float* ctx = qkv + rows * 3 * m.D;
   attention_core(m, x, B, T, causal, pad_lengths, ctx, qkv, probs, head_major, st);
+  if (m.to.img && m.xpack && m.to.Npad == m.D) {
+    dense_tc3_launch(m.to, ctx, m.D, rows, ACT_NONE, nullptr, 0, out, m.D, m.xpack, st);
+    return;
+  }
   GemmArgs g;
   g.X = ctx; g.Bn = 1; g.T = (int)rows; g.Cin = m.D; g.ldx = m.D;
   g.W = m.Wo; g.N = m.D; g.shift = m.bo; g.C = out; g.ldc = m.D;
@@ -574,6 +582,10 @@ void sat_layer_forward(const MhaDev& m, const float* x, int B, int T, int causal
   const size_t rows = (size_t)B * T;
   float* a = scratch + rows * 4 * m.D;
   mha_forward(m, x, B, T, causal, pad_lengths, a, probs, scratch, st, head_major);
+  if (m.tt.img && m.xpack && m.tt.Npad == m.D) {
+    dense_tc3_launch(m.tt, a, m.D, rows, ACT_TANH, x, m.D, out, m.D, m.xpack, st);
+    return;
+  }
   GemmArgs g;
   g.X = a; g.Bn = 1; g.T = (int)rows; g.Cin = m.D; g.ldx = m.D;
   g.W = m.Wt; g.N = m.D; g.shift = m.bt; g.act = ACT_TANH; g.R = x; g.ldr = m.D; g.C = out; g.ldc = m.D;
