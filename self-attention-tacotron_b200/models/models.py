@@ -39,6 +39,9 @@ def encoder_factory(params, is_training, weights):
     raise ValueError(f"Unknown encoder: {params.encoder}")
 
 
+MAX_BATCH = 256  # rows of one persistent-kernel launch (csrc/decoder_dev.cuh MAX_B); larger batches run in chunks
+
+
 def decoder_factory(params, weights):
     """models/models.py:349-368 (+ ExtendedDecoder / DualSourceDecoder)."""
     kw = dict(prenet_out_units=params.decoder_prenet_out_units, drop_rate=params.decoder_prenet_drop_rate,
@@ -75,11 +78,37 @@ class SynthesisModel:
         self.postnet = PostNetV2(params.num_mels, params.num_postnet_v2_layers, params.postnet_v2_kernel_size,
                                  params.postnet_v2_out_channels, False, weights=weights) if params.use_postnet_v2 else None
 
+    def _predict_in_chunks(self, source, source_length, target, speaker_id, is_validation, teacher_forcing,
+                           want_enc, want_dec):
+        """Batches beyond one launch's row limit: consecutive chunks of <= MAX_BATCH rows (rows are independent; the
+        all_rows stop rule then applies per chunk), results concatenated with the step / memory axes zero-padded to the
+        longest chunk.  n_steps = the largest chunk's; stop_steps stay per row."""
+        outs = []
+        for b0 in range(0, source.shape[0], MAX_BATCH):
+            sl = slice(b0, b0 + MAX_BATCH)
+            # the padded length is kept: padded frames are part of the reference's batched graph (SURVEY.md A.11)
+            outs.append(self.predict(source[sl], source_length[sl], None if target is None else target[sl],
+                                     None if speaker_id is None else speaker_id[sl], is_validation, teacher_forcing,
+                                     want_enc, want_dec))
+        res = {}
+        for k, v in outs[0].items():
+            vals = [o[k] for o in outs]
+            if k == "n_steps":
+                res[k] = max(int(x.item()) if torch.is_tensor(x) else int(x) for x in vals)
+            elif k == "encoder_alignments":
+                res[k] = [_cat_padded([o[k][i] for o in outs], [1, 2]) for i in range(len(v))]
+            elif torch.is_tensor(v):
+                res[k] = torch.cat(vals, 0) if v.dim() == 1 else _cat_padded(vals, list(range(1, v.dim())))
+        return res
+
     def predict(self, source, source_length, target=None, speaker_id=None, is_validation=False,
                 teacher_forcing=False, want_encoder_alignments=False, want_decoder_self_attention_alignments=False):
         """source int64 ids [B,T_enc] (device), source_length [B]; target [B,T_dec,M] for validation /
         forced alignment.  Returns a dict of device tensors."""
         p = self.params
+        if source.shape[0] > MAX_BATCH:
+            return self._predict_in_chunks(source, source_length, target, speaker_id, is_validation, teacher_forcing,
+                                           want_encoder_alignments, want_decoder_self_attention_alignments)
         self.decoder.want_self_attention_alignments = want_decoder_self_attention_alignments
         if self.dual:
             lstm_out, sa_out, enc_align = self.encoder(source, input_lengths=source_length,
@@ -146,6 +175,18 @@ class SynthesisModel:
         if self.postnet is not None:
             out["mel_postnet"] = self.postnet(mel)
         return out
+
+
+def _cat_padded(ts, dims):
+    """concatenate along the batch axis tensors whose axes `dims` may differ in length (zero padded to the longest)"""
+    tgt = [max(t.shape[d] for t in ts) for d in dims]
+    out = []
+    for t in ts:
+        pad = []
+        for d in range(t.dim() - 1, 0, -1):  # F.pad lists the last axis first
+            pad += [0, tgt[dims.index(d)] - t.shape[d] if d in dims else 0]
+        out.append(torch.nn.functional.pad(t, pad) if any(pad) else t)
+    return torch.cat(out, dim=0)
 
 
 def tacotron_model_factory(hparams, weights):
