@@ -6,7 +6,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libsat.so")
+LIB_PATH = os.environ.get("SAT_LIB", os.path.join(_HERE, "libsat.so"))  # SAT_LIB: A/B timing of another build
 
 SAT_ATT = {"none": 0, "additive": 1, "location_sensitive": 2, "forward": 3,
            "teacher_forcing_forward": 4, "teacher_forcing_additive": 4}
