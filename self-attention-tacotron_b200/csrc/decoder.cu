@@ -51,7 +51,7 @@ void add_row_major(DevPool& pool, PackedDense& d, const float* W, int K, int Nsr
     for (int k = 0; k < K; ++k)
       for (int n = 0; n < N; ++n) rm[r * d.rep_stride + (size_t)k * d.Np + n] = W[(size_t)k * Nsrc + n];
   d.Wrm = pool.upload(rm);
-  d.Np8 = (Nout + 63) / 64 * 64;  // rows of 128-byte multiples: the weight ring streams them with 1-D bulk copies
+  d.Np8 = (Nout + 7) / 8 * 8;
   d.rep_stride16 = ((size_t)K * d.Np8 + 127) / 128 * 128 + 64;
   std::vector<__half> rh(d.rep_stride16 * reps + 8, __float2half(0.f));
   for (int r = 0; r < reps; ++r)
@@ -75,27 +75,6 @@ PackedDense pack_lstm(DevPool& pool, const float* W, const float* bias, int K, i
   PackedDense d = pack_cols(pool, W, bias, K, 4 * units, cm);
   d.N = tiles * TILE_N;
   return d;
-}
-
-// K-major, 128-byte swizzled fp16 images of the 16-column gate tiles of one LSTM for the tensor-core form
-// (decoder_tc.cuh): [units / 4 tiles][ceil(K / 64) chunks][2 KB]; column n of a tile = gate n & 3 of unit
-// 4 tile + 2 (n >> 3) + ((n & 7) >> 2), i.e. the two packed 8-wide tiles of the SIMT form side by side
-const uint8_t* pack_lstm_tc_images(DevPool& pool, const float* W, int K, int units) {
-  if (units % 4) return nullptr;
-  const int tiles = units / 4, kch = ceil_div(K, tc::CHUNK_K16);
-  std::vector<__half> img((size_t)tiles * kch * 1024, __float2half_rn(0.f));
-  for (int t = 0; t < tiles; ++t)
-    for (int n = 0; n < TC_N; ++n) {
-      const int unit = 4 * t + 2 * (n >> 3) + ((n & 7) >> 2), col = (n & 3) * units + unit;
-      for (int k = 0; k < K; ++k) {
-        const size_t off = ((size_t)t * kch + k / tc::CHUNK_K16) * 2048 + tc::sw128_offset16(n, k % tc::CHUNK_K16);
-        const float w = W[(size_t)k * 4 * units + col];
-        img[off / 2] = __float2half_rn(fminf(fmaxf(w, -65504.f), 65504.f));
-      }
-    }
-  std::vector<float> packed((img.size() + 1) / 2);
-  memcpy(packed.data(), img.data(), img.size() * sizeof(__half));
-  return (const uint8_t*)pool.upload(packed);
 }
 
 __global__ void f32_to_f16_kernel(const float* __restrict__ src, __half* __restrict__ dst, size_t n) {
@@ -191,7 +170,6 @@ struct sat_decoder {
   DenseTc3 t_mem[2], t_msd, t_pre1, t_outp, t_qkv[MAX_HOPS], t_o[MAX_HOPS], t_tr[MAX_HOPS];
   bool dense_tc = true;
   PackedDense pre0, msd, pre1, lstm_a, lstm_1, lstm_2, outp, dq[2];
-  const uint8_t* lstm_img[3] = {nullptr, nullptr, nullptr};  // pack_lstm_tc_images of lstm_a, lstm_1, lstm_2
   PackedDense outp_f;  // outp + prenet layer 0 folded onto the fed-back frame (self feed): [d_out][Mr + 1 + P0]
   bool has_outp_f = false;
   PackedDense sa_qkv[MAX_HOPS], sa_o[MAX_HOPS], sa_tr[MAX_HOPS];
@@ -265,9 +243,6 @@ extern "C" int sat_decoder_create(const sat_hparams* hpp, const sat_tensor* weig
     h->lstm_a = pack_lstm(pool, W.get(D + "attention_lstm/kernel", (int64_t)Ka * 4 * A), W.get(D + "attention_lstm/bias", 4 * A), Ka, A);
     h->lstm_1 = pack_lstm(pool, W.get(D + "lstm_1/kernel", (int64_t)K1 * 4 * Dd), W.get(D + "lstm_1/bias", 4 * Dd), K1, Dd);
     h->lstm_2 = pack_lstm(pool, W.get(D + "lstm_2/kernel", (int64_t)K2 * 4 * Dd), W.get(D + "lstm_2/bias", 4 * Dd), K2, Dd);
-    h->lstm_img[0] = pack_lstm_tc_images(pool, W.get(D + "attention_lstm/kernel", (int64_t)Ka * 4 * A), Ka, A);
-    h->lstm_img[1] = pack_lstm_tc_images(pool, W.get(D + "lstm_1/kernel", (int64_t)K1 * 4 * Dd), K1, Dd);
-    h->lstm_img[2] = pack_lstm_tc_images(pool, W.get(D + "lstm_2/kernel", (int64_t)K2 * 4 * Dd), K2, Dd);
     // attention mechanisms
     for (int i = 0; i < h->n_mech; ++i) {
       const std::string P = D + "attention" + std::to_string(i + 1) + "/";
@@ -502,7 +477,8 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
         d.n_tiles = us[i] / 4;
         d.kchunks = ceil_div(Ks[i], tc::CHUNK_K16);
         d.slots = ceil_div(d.n_tiles * RB, h->grid);
-        d.gimg = h->lstm_img[i];
+        d.img_off = off;
+        off += d.slots * d.kchunks * 2048;
       }
       // chunk order: columns produced at least two phases before the LSTM first (requested behind the grid barrier)
       {
@@ -583,29 +559,6 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
     if (const char* e = getenv("SAT_BENCH_BARRIERS")) p.bench_barriers = atoi(e);
     p.tc = use_tc ? 1 : 0;
     if (!use_tc) p.tc_q = p.tc_frame = 0;
-    // ---- weights of the row-split dense layers through the TMA ring (decoder_kernel.cuh: row_dense_ring) ----
-    if (use_tc) {
-      // Measured on B200 (cfg 2, B=256; profiles/README.md round 2): parity green, but slower than the LDG form -- frame
-      // phase 5.5 + 2.8 us -> 7.8 + 3.5 us, step 60 -> 66 us.  With all SMs streaming, both forms sit on the aggregate
-      // L2 rate (~7 TB/s), and the ring gives up a warp to the producer.  Off unless SAT_WRING=1.
-      bool on = false;
-      if (const char* e = getenv("SAT_WRING")) on = atoi(e) != 0;
-      auto layer = [&](const DenseDesc& d, WLayer& L) {
-        L.w = (const uint8_t*)d.Wrm16; L.rowbytes = d.Np8 * 2; L.K = d.K;
-        if (!d.Wrm16 || d.reps != 1 || L.rowbytes > WR_STAGE_BYTES || d.K < 1) return false;
-        L.rpc = std::min(d.K, WR_STAGE_BYTES / L.rowbytes);
-        L.nch = ceil_div(d.K, L.rpc);
-        return true;
-      };
-      const bool room = (size_t)p.scratch_floats * sizeof(float) >= (size_t)WR_OFF_FLOATS * 4 + (size_t)WR_STAGES * WR_STAGE_BYTES;
-      if (on && room && h->n_mech == 1 && !p.tc_q && !io.forced_alignment && layer(h->dq[0].desc(), p.wl[WL_QUERY]) &&
-          al4(2 * A) + 2 * h->dq[0].Np + 2 * NT * 8 <= WR_OFF_FLOATS)
-        p.wr_query = 1;
-      if (on && room && p.fused_prenet0 && !p.ms && h->hops == 0 && !p.tc_frame && layer(p.outp, p.wl[WL_OUT]) &&
-          layer(p.pre1, p.wl[WL_PRE1]) &&
-          frame_smem_floats(p.outp.K, p.outp.Np, p.Mnf, p.pre0.Np, p.pre1.Np) <= WR_OFF_FLOATS)
-        p.wr_frame = 1;
-    }
     if (!use_tc) p.scratch_floats = SCRATCH_FLOATS;
     p.RB = RB;
     p.Ka_pad = ceil_div(Ka, tc::CHUNK_K16) * tc::CHUNK_K16;

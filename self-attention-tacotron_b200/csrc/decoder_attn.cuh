@@ -574,7 +574,7 @@ __device__ __forceinline__ void attention_load_state(const AttMech& m, int b, in
 }
 
 template <int GT>
-__device__ __forceinline__ void attention_item(const AttMech& m, int b, int t, int T, int len, float* sm, int gid = 0,
+__device__ inline void attention_item(const AttMech& m, int b, int t, int T, int len, float* sm, int gid = 0,
                                       int crank = 0, int csize = 1, bool preloaded = false) {
   constexpr int GW = GT / 32;
   const int TS = m.TS;

@@ -21,17 +21,6 @@ constexpr int N_PROF = 48;  // [0,16) phases of a step, [16,24) attention-item s
 constexpr int SCRATCH_FLOATS = (RED_FLOATS > ATT_SMEM_FLOATS ? RED_FLOATS : ATT_SMEM_FLOATS);
 constexpr int TC_SCRATCH_FLOATS = (TC_STAGES * TC_STAGE_BYTES + 1024) / 4;  // ring + alignment slack
 
-// weight stream of the row-split dense layers in tensor-core mode (row_dense_ring below)
-constexpr int WR_STAGES = 6;
-constexpr int WR_STAGE_BYTES = 16384;
-constexpr int WR_OFF_FLOATS = 12288;  // the ring starts 48 KB into the phase scratch
-
-struct WLayer {
-  const uint8_t* w;  // fp16 row-major [K][Np8]
-  int rowbytes, K;
-  int rpc, nch;      // k-rows per chunk, chunks
-};
-
 struct SaHop {
   DenseDesc qkv, o, tr;
   float* kcache;  // [B][H][Smax][dh]
@@ -86,9 +75,6 @@ struct DecParams {
   TcDense tq, tp, tr;
   __half *qx, *px, *rx;     // fp16 hi + lo pairs [RB * 128][ld]: attention-LSTM output, LSTM2 output, prenet layer-0 output
   int qx_ld, px_ld, rx_ld;
-  // ---- tensor-core mode: weights of the row-split dense layers through the TMA ring (row_dense_ring) ----
-  int wr_query, wr_frame;   // query layer (one mechanism) / frame + stop projection with folded prenet 0, then prenet 1
-  WLayer wl[3];             // WL_QUERY, WL_OUT, WL_PRE1
   int cl;                   // cluster size of the launch (1: rows are not split)
   int cl_split[2];          // mechanism i is split over the cluster (else rank 0 takes the whole item)
   const float* cl_wq[2];    // query-layer weights as cl contiguous column slices [cl][A][cl_sw] (fp32)
@@ -374,123 +360,6 @@ __device__ inline void row_dense(const DenseDesc& d, const float* xs, int xs_str
   __syncthreads();
 }
 
-// ---- weight stream of the row-split dense layers (tensor-core mode) ------------------------------------------------
-// The query layer and the frame phase make every CTA read a whole weight matrix for its one or two rows.  Read with
-// LDGs that is a chain of dependent L2 round trips; here the fp16 row-major weights [K][Np8] arrive as 1-D bulk copies
-// (cp.async.bulk, <= 16 KB of whole k-rows per chunk) in a 6-stage ring behind the phase's own arrays, requested by
-// thread 0 -- the first six chunks while the CTA waits at the grid barrier in front of the phase (weights do not
-// depend on it), the rest as stages drain.  full[s]: the bytes have landed; empty[s]: the 15 consumer warps are done.
-struct WRing {
-  uint8_t* base;
-  uint64_t *full, *empty;
-  uint32_t consumed;        // chunks consumed since the start of the run (identical in every thread)
-  uint32_t issued;          // chunks requested (thread 0)
-  int l0, l1;               // layers of the phase being streamed, in order (thread 0): WL_* ids, l1 may be WL_NONE
-  int spos;                 // ... and the next chunk of that stream to request
-};
-enum { WL_NONE = -1, WL_QUERY = 0, WL_OUT = 1, WL_PRE1 = 2 };
-
-// thread 0: request stream positions [r.spos, lim) -- waits for the stage of each to be drained by the consumer warps.
-// wl = the three WLayer descriptors of the launch (DecParams::wl), indexed by WL_* id.
-__device__ __forceinline__ void wr_issue_until(WRing& r, const WLayer* wl, int lim) {
-  while (r.spos < lim) {
-    int pos = r.spos, id = r.l0;
-    if (pos >= wl[id].nch) {
-      pos -= wl[id].nch;
-      id = r.l1;
-    }
-    const uint32_t g = r.issued, s = g % WR_STAGES, use = g / WR_STAGES;
-    if (use > 0) tc::mbar_wait(r.empty + s, (use - 1) & 1);
-    const WLayer L = wl[id];
-    const int r0 = pos * L.rpc;
-    const uint32_t bytes = (uint32_t)(min(L.rpc, L.K - r0) * L.rowbytes);
-    tc::mbar_arrive_expect_tx(r.full + s, bytes);
-    tc::bulk_load(r.base + s * WR_STAGE_BYTES, L.w + (size_t)r0 * L.rowbytes, bytes, r.full + s);
-    r.issued = g + 1;
-    ++r.spos;
-  }
-}
-__device__ __forceinline__ int wr_total(const WRing& r, const WLayer* wl) {
-  return wl[r.l0].nch + (r.l1 >= 0 ? wl[r.l1].nch : 0);
-}
-// thread 0, behind the grid barrier in front of the phase: name the stream and request its first chunks (every stage
-// is free: the previous stream was consumed to the end)
-__device__ __forceinline__ void wr_begin(WRing& r, const WLayer* wl, int l0, int l1) {
-  r.l0 = l0;
-  r.l1 = l1;
-  r.spos = 0;
-  tc::fence_proxy_async();  // the ring's last users were generic-proxy reads and writes of this CTA
-  wr_issue_until(r, wl, min(wr_total(r, wl), WR_STAGES));
-}
-
-// row_dense<RR, true> with the weights taken from the ring: outs[r][n] = act(bias[n] + sum_k xs[r][k] W[k][n]).
-// Warp 0 is the producer (its thread 0 keeps the ring full, up to WR_STAGES chunks past this layer into the next one
-// of the stream); warps 1..15 consume.
-template <int RR>
-__device__ inline void row_dense_ring(const DenseDesc& d, const WLayer* wl, int id, WRing& r, const float* xs, int xs_stride,
-                                      float* part, float* outs, int act) {
-  const WLayer L = wl[id];
-  const int tid = threadIdx.x, lane = tid & 31;
-  const int Np = d.Np8, Cn = Np / 8;
-  const int kparts = min((NT - 32) / Cn, L.rpc);
-  const int ct = tid - 32, kp = ct / Cn, cl = ct - kp * Cn;
-  const uint32_t g0 = r.consumed;
-  if (tid < 32) {
-    if (tid == 0) {
-      const int end = (id == r.l0 ? 0 : wl[r.l0].nch) + L.nch;  // stream position behind this layer
-      wr_issue_until(r, wl, min(wr_total(r, wl), end + WR_STAGES));
-    }
-  } else {
-    float acc[RR][8];
-#pragma unroll
-    for (int q = 0; q < RR; ++q)
-#pragma unroll
-      for (int c = 0; c < 8; ++c) acc[q][c] = 0.f;
-    for (int c = 0; c < L.nch; ++c) {
-      const uint32_t g = g0 + c, s = g % WR_STAGES;
-      tc::mbar_wait(r.full + s, (g / WR_STAGES) & 1);
-      const int r0 = c * L.rpc, rows = min(L.rpc, L.K - r0);
-      if (kp < kparts) {
-        const uint8_t* wb = r.base + s * WR_STAGE_BYTES + cl * 16;
-        for (int j = kp; j < rows; j += kparts) {
-          const uint4 wv = *(const uint4*)(wb + j * L.rowbytes);
-          const float2 a = __half22float2(*(const __half2*)&wv.x), b = __half22float2(*(const __half2*)&wv.y);
-          const float2 e = __half22float2(*(const __half2*)&wv.z), f = __half22float2(*(const __half2*)&wv.w);
-          const float wf[8] = {a.x, a.y, b.x, b.y, e.x, e.y, f.x, f.y};
-#pragma unroll
-          for (int q = 0; q < RR; ++q) {
-            const float x = xs[q * xs_stride + r0 + j];
-#pragma unroll
-            for (int cc = 0; cc < 8; ++cc) acc[q][cc] = fmaf(x, wf[cc], acc[q][cc]);
-          }
-        }
-      }
-      __syncwarp();
-      if (lane == 0) tc::mbar_arrive(r.empty + s);
-    }
-    if (kp < kparts) {
-#pragma unroll
-      for (int q = 0; q < RR; ++q) {
-        float4* dst = (float4*)(part + (size_t)(kp * RR + q) * Np + 8 * cl);
-        dst[0] = make_float4(acc[q][0], acc[q][1], acc[q][2], acc[q][3]);
-        dst[1] = make_float4(acc[q][4], acc[q][5], acc[q][6], acc[q][7]);
-      }
-    }
-  }
-  r.consumed = g0 + L.nch;
-  __syncthreads();
-  const int No = d.Np;  // output row stride (bias is zero-padded to n_tiles * 8 >= Np)
-  for (int i = tid; i < RR * No; i += NT) {
-    const int q = i / No, n = i - q * No;
-    float v = 0.f;
-    for (int k = 0; k < kparts; ++k) v += part[(size_t)(k * RR + q) * Np + n];
-    v += __ldg(d.bias + n);
-    if (act == 1) v = fmaxf(v, 0.f);
-    outs[q * No + n] = v;
-  }
-  __syncthreads();
-}
-
 // shared-memory floats the frame phase needs (checked against the phase scratch on the host)
 __host__ __device__ inline int al4(int x) { return (x + 3) & ~3; }
 __host__ __device__ inline int frame_smem_floats(int Dy, int Np_out, int Mnf, int P0p, int P1p) {
@@ -501,7 +370,7 @@ __host__ __device__ inline int frame_smem_floats(int Dy, int Np_out, int Mnf, in
 // the prenet on it into the attention-LSTM input buffer of step t+1
 template <int RR, bool H>
 __device__ inline void frame_item(const DecParams& p, const int* b, int t, const float* y, int Dy, Act2D p1_dst,
-                                  bool prologue, float* sm, WRing& wr, bool ring) {
+                                  bool prologue, float* sm) {
   const int tid = threadIdx.x, ld = p.ld;
   const int Npo = p.outp.Np, P0p = p.pre0.Np, P1p = p.pre1.Np;
   float* ys = sm;                   // [RR][Dy]        (every region starts 16-byte aligned)
@@ -531,8 +400,7 @@ __device__ inline void frame_item(const DecParams& p, const int* b, int t, const
     }
     __syncthreads();
     stamp();
-    if (H && ring) row_dense_ring<RR>(p.outp, p.wl, WL_OUT, wr, ys, Dy, part, os, 0);
-    else row_dense<RR, H>(p.outp, ys, Dy, part, os, 0);
+    row_dense<RR, H>(p.outp, ys, Dy, part, os, 0);
     stamp();
     for (int i = tid; i < RR * (p.Mr + 1); i += NT) {
       const int r = i / (p.Mr + 1), n = i - r * (p.Mr + 1);
@@ -592,8 +460,7 @@ __device__ inline void frame_item(const DecParams& p, const int* b, int t, const
     row_dense<RR, H>(p.msd, p0s, P0p, part, p0b, 1);
     pin = p0b;
   }
-  if (H && ring) row_dense_ring<RR>(p.pre1, p.wl, WL_PRE1, wr, pin, P0p, part, p1s, 1);
-  else row_dense<RR, H>(p.pre1, pin, P0p, part, p1s, 1);
+  row_dense<RR, H>(p.pre1, pin, P0p, part, p1s, 1);
   ps = 36;
   stamp();
   for (int i = tid; i < RR * p.P1; i += NT) {
@@ -605,16 +472,15 @@ __device__ inline void frame_item(const DecParams& p, const int* b, int t, const
 }
 
 // all rows of the batch through frame_item, two per pass
-__device__ inline void frame_phase(const DecParams& p, int t, const float* y, int Dy, Act2D p1_dst, bool prologue, float* sm,
-                                   WRing& wr, bool ring) {
+__device__ inline void frame_phase(const DecParams& p, int t, const float* y, int Dy, Act2D p1_dst, bool prologue, float* sm) {
   for (int b0 = blockIdx.x; b0 < p.B; b0 += 2 * gridDim.x) {
     int b[2] = {b0, b0 + (int)gridDim.x};
     if (p.tc) {
-      if (b[1] < p.B) frame_item<2, true>(p, b, t, y, Dy, p1_dst, prologue, sm, wr, ring);
-      else frame_item<1, true>(p, b, t, y, Dy, p1_dst, prologue, sm, wr, ring);
+      if (b[1] < p.B) frame_item<2, true>(p, b, t, y, Dy, p1_dst, prologue, sm);
+      else frame_item<1, true>(p, b, t, y, Dy, p1_dst, prologue, sm);
     } else {
-      if (b[1] < p.B) frame_item<2, false>(p, b, t, y, Dy, p1_dst, prologue, sm, wr, false);
-      else frame_item<1, false>(p, b, t, y, Dy, p1_dst, prologue, sm, wr, false);
+      if (b[1] < p.B) frame_item<2, false>(p, b, t, y, Dy, p1_dst, prologue, sm);
+      else frame_item<1, false>(p, b, t, y, Dy, p1_dst, prologue, sm);
     }
   }
 }
@@ -629,17 +495,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
   const int ld = p.ld;
 
   __shared__ __align__(8) uint64_t s_tcbar[2 * TC_STAGES + 1];
-  __shared__ __align__(8) uint64_t s_wrbar[2 * WR_STAGES];
   __shared__ uint32_t s_tmem;
-  WRing wring;
-  // 1024-aligned like the TMA ring: bulk copies whose source or destination is not 128-byte aligned run at a
-  // fraction of the rate (measured: 16 KB chunks at 16-byte alignment took ~1 us each)
-  wring.base = (uint8_t*)((((uintptr_t)scratch + 1023) & ~(uintptr_t)1023) + (size_t)WR_OFF_FLOATS * 4);
-  wring.full = s_wrbar;
-  wring.empty = s_wrbar + WR_STAGES;
-  wring.consumed = wring.issued = 0;
-  wring.l0 = wring.l1 = WL_NONE;
-  wring.spos = 0;
   TcState tcs;
   tcs.ring = (uint8_t*)(((uintptr_t)scratch + 1023) & ~(uintptr_t)1023);
   tcs.wimg = (uint8_t*)(((uintptr_t)wres + 1023) & ~(uintptr_t)1023);
@@ -654,10 +510,6 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
   if (p.tc) {
     if (tid == 0) {
       for (int i = 0; i < 2 * TC_STAGES + 1; ++i) tc::mbar_init(s_tcbar + i, 1);
-      for (int i = 0; i < WR_STAGES; ++i) {
-        tc::mbar_init(s_wrbar + i, 1);
-        tc::mbar_init(s_wrbar + WR_STAGES + i, NW - 1);  // one arrival per consumer warp
-      }
       tc::fence_mbar_init();
     }
     if (tid < 32) tc::tmem_alloc(&s_tmem, 32);
@@ -692,16 +544,10 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
   int ph = 0;
   // next_lstm / next_map: the tensor-core LSTM phase that follows this barrier (null: none) -- its "old" input
   // columns are requested while the CTA waits for the other CTAs
-  // w0 / w1: the weight stream of the row-split phase that follows (row_dense_ring) -- its first chunks are requested
-  // there as well
-  auto phase_end = [&](const TcLstmDesc* next_lstm = nullptr, const CUtensorMap* next_map = nullptr,
-                       int w0 = WL_NONE, int w1 = WL_NONE) {
-    if (next_lstm || w0 >= 0) {
+  auto phase_end = [&](const TcLstmDesc* next_lstm = nullptr, const CUtensorMap* next_map = nullptr) {
+    if (next_lstm) {
       tc::fence_proxy_async();  // every thread: its generic-proxy writes to the scratch precede the TMA writes
-      bar.sync([&] {
-        if (next_lstm) tc_prefill(*next_lstm, next_map, p.RB, tcs);
-        if (w0 >= 0) wr_begin(wring, p.wl, w0, w1);
-      });
+      bar.sync([&] { tc_prefill(*next_lstm, next_map, p.RB, tcs); });
     } else {
       bar.sync();
     }
@@ -723,7 +569,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
   };
   // prenet of the <GO> frame -> attention-LSTM input of step 0
   if (p.batched_tail) copy_prenet(0, Act2D{p.att_in[0], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc});
-  else frame_phase(p, 0, nullptr, 0, Act2D{p.att_in[0], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc}, true, scratch, wring, false);
+  else frame_phase(p, 0, nullptr, 0, Act2D{p.att_in[0], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc}, true, scratch);
   if (p.tc) {
     tc::fence_proxy_async();
     bar.sync([&] { tc_prefill(p.tc_a, p.maps, p.RB, tcs); });
@@ -752,8 +598,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
                   LstmEpi{p.lstm_a.bias, p.A, ld, p.B, p.c_a, p.att_in[cur] + hoff, p.l1_in[cur],
                           p.att_in[nxt] + hoff, nullptr, 0, 0, p.zc, p.zh});
     }
-    if (p.wr_query && (int)blockIdx.x < p.B * p.n_mech) phase_end(nullptr, nullptr, WL_QUERY);
-    else phase_end();
+    phase_end();
     // ---- Q: query layers of all mechanisms as tensor-core tiles ----
     if (p.tc_q) {
       tc::fence_proxy_async();
@@ -836,10 +681,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
             xs[r * p.A + k] = __ldcg(qsrc + (size_t)k * ld + rows[r]);
           }
           __syncthreads();
-          if (p.wr_query) {
-            if (nq == 2) row_dense_ring<2>(dq, p.wl, WL_QUERY, wring, xs, p.A, part, outs, 0);
-            else row_dense_ring<1>(dq, p.wl, WL_QUERY, wring, xs, p.A, part, outs, 0);
-          } else if (p.tc) {
+          if (p.tc) {
             if (nq == 2) row_dense<2, true>(dq, xs, p.A, part, outs, 0);
             else row_dense<1, true>(dq, xs, p.A, part, outs, 0);
           } else {
@@ -926,8 +768,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
                   LstmEpi{p.lstm_2.bias, p.Dd, ld, p.B, p.c_2, p.l2_in[cur] + hoff, p.dout,
                           p.l2_in[nxt] + hoff, p.dec_out, p.max_steps * p.Dd, t * p.Dd, p.zc, p.zh});
     }
-    if (p.wr_frame && (int)blockIdx.x < p.B) phase_end(nullptr, nullptr, WL_OUT, WL_PRE1);
-    else phase_end();
+    phase_end();
     if (!p.batched_tail) {
       // ---- H-K: decoder self-attention hops over the KV cache ----
       const float* y = p.dout;
@@ -961,8 +802,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
                        PrenetTcEpi{p.pre1.bias, p.P1, p.B, Act2D{p.att_in[nxt], 1, p.Ka_pad, 1}});
       } else {
         // ---- L+A+B: frame + stop projection of step t, fed-back frame, prenet of step t+1 (row split) ----
-        frame_phase(p, t, y, p.outp.K, Act2D{p.att_in[nxt], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc}, false, scratch,
-                    wring, p.wr_frame != 0);
+        frame_phase(p, t, y, p.outp.K, Act2D{p.att_in[nxt], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc}, false, scratch);
       }
       if (p.tc && t + 1 < p.max_steps) phase_end(&p.tc_a, p.maps + nxt);
       else phase_end();

@@ -2,10 +2,9 @@
 // utterance batch makes them a real contraction (B >= 64; BASELINE.json north_star).
 //
 // Work split: a CTA owns (column tile of 16 gate columns = 4 units x {i,j,f,o}) x (row block of 128 utterances).
-// The activations X[128 rows][K] (row-major fp16 in HBM/L2) stream through an 8-stage ring of 16 KB TMA boxes
-// {64 k, 128 rows}, each followed by the 2 KB chunk of the tile's W^T slice [16][64 k] (a K-major, 128-byte swizzled
-// fp16 image built once per handle in global memory, fetched by a 1-D bulk copy onto the same mbarrier); one elected
-// thread issues tcgen05.mma kind::f16 (M=128, N=16, K=16) into
+// The W^T slice [16][K] of every LSTM stays resident in shared memory for the whole run as a K-major, 128-byte
+// swizzled fp16 image; the activations X[128 rows][K] (row-major fp16 in HBM/L2) stream through a 6-stage ring of
+// 16 KB TMA boxes {64 k, 128 rows}; one elected thread issues tcgen05.mma kind::f16 (M=128, N=16, K=16) into
 // a 16-column TMEM accumulator; all sixteen warps read it back (tcgen05.ld 32x32b.x4 -> one utterance row and one
 // complete unit per thread) and apply the zoneout cell update in registers.
 // Operands are fp16 with fp32 accumulation: fp16 has the 11-bit significand of tf32 at half the bytes, and the
@@ -17,10 +16,8 @@
 namespace sat {
 namespace dec {
 
-constexpr int TC_STAGES = 8;
-constexpr int TC_X_BYTES = 128 * tc::CHUNK_K16 * 2;      // 16 KB: 128 rows x 64 fp16 of the activations
-constexpr int TC_W_BYTES = 16 * tc::CHUNK_K16 * 2;       // 2 KB: the same 64 k of the tile's 16 gate columns
-constexpr int TC_STAGE_BYTES = TC_X_BYTES + TC_W_BYTES;  // 18 KB (a multiple of 1024: every stage keeps the swizzle alignment)
+constexpr int TC_STAGES = 6;
+constexpr int TC_STAGE_BYTES = 128 * tc::CHUNK_K16 * 2;  // 16 KB: 128 rows x 64 fp16
 constexpr int TC_N = 16;                                 // gate columns per tile
 constexpr int TC_M = 128;                                // utterance rows per tile
 constexpr int TC_STATE_BYTES = 2 * 4 * TC_M * 4;         // per resident item: c and zoned h of 4 units x 128 rows (fp32)
@@ -42,9 +39,7 @@ struct TcLstmDesc {
   const float* bias;  // [units/2 * 8]
   int K, units;
   int n_tiles;        // units / 4 column tiles of 16
-  const uint8_t* gimg;  // global K-major SW128 fp16 images of all tiles: [n_tiles][kchunks][2 KB], built once per handle.
-                        // The chunk of the CTA's tile streams through the ring NEXT TO its activation box (the 62 KB a
-                        // resident copy would pin per CTA are worth more as ring depth for every phase)
+  int img_off;        // byte offset of this layer's resident images inside the TC weight region
   int st_off;         // byte offset of this layer's resident cell state inside the TC weight region
   int slots;          // resident (tile,row block) items per CTA
   int kchunks;        // ceil(K / 64)
@@ -67,9 +62,23 @@ struct TcState {
   long long* prof;     // optional cycle counters (CTA 0): [0] producer loop, [1] wait for the accumulator, [2] cell update
 };
 
-// zero the resident cell state of this CTA's items of one LSTM
+// build this CTA's resident K-major SW128 fp16 image of one LSTM (chunk c of slot s at wimg + img_off +
+// (s*kchunks + c)*2 KB) and zero its cell state
 __device__ inline void tc_load_resident(const TcLstmDesc& d, int RB, const TcState& st) {
   if (d.slots == 0) return;
+  const int n_items = d.n_tiles * RB;
+  int slot = 0;
+  for (int item = blockIdx.x; item < n_items && slot < d.slots; item += gridDim.x, ++slot) {
+    const int tile = item / RB;
+    uint8_t* img = st.wimg + d.img_off + (size_t)slot * d.kchunks * 2048;
+    // column n of the 16-wide tile = column (n & 7) of packed 8-wide tile 2*tile + (n >> 3)
+    for (int i = threadIdx.x; i < d.kchunks * tc::CHUNK_K16 * TC_N; i += NT) {
+      const int n = i & (TC_N - 1), k = i >> 4;
+      float w = 0.f;
+      if (k < d.K) w = __ldg(d.Wp + ((size_t)(2 * tile + (n >> 3)) * d.K + k) * TILE_N + (n & 7));
+      *(__half*)(img + (k / tc::CHUNK_K16) * 2048 + tc::sw128_offset16(n, k % tc::CHUNK_K16)) = tc::to_f16(w);
+    }
+  }
   float* state = (float*)(st.wimg + d.st_off);
   for (int i = threadIdx.x; i < d.slots * (TC_STATE_BYTES / 4); i += NT) state[i] = 0.f;
 }
@@ -80,14 +89,12 @@ __device__ inline void tc_prefill(const TcLstmDesc& d, const CUtensorMap* xmap, 
   const int item = blockIdx.x;
   if (item >= d.n_tiles * RB || d.n_pre == 0) return;
   const int row0 = (item % RB) * TC_M;
-  const uint8_t* gimg = d.gimg + (size_t)(item / RB) * d.kchunks * TC_W_BYTES;
   tc::fence_proxy_async();
   for (int c = 0; c < d.n_pre; ++c) {
     const uint32_t n = st.n_chunks + c, s = n % TC_STAGES, use = n / TC_STAGES;
     if (use > 0) tc::mbar_wait(st.empty + s, (use - 1) & 1);
     tc::mbar_arrive_expect_tx(st.full + s, TC_STAGE_BYTES);
     tc::tma_load_2d(st.ring + s * TC_STAGE_BYTES, xmap, st.full + s, d.order[c] * tc::CHUNK_K16, row0);
-    tc::bulk_load(st.ring + s * TC_STAGE_BYTES + TC_X_BYTES, gimg + d.order[c] * TC_W_BYTES, TC_W_BYTES, st.full + s);
   }
   st.prefilled = d.n_pre;
 }
@@ -152,7 +159,7 @@ __device__ inline void dense_phase_tc(const TcDense& d, const CUtensorMap* xmap,
         const uint32_t n = st.n_chunks + c, s = n % TC_STAGES, use = n / TC_STAGES;
         if (use > 0) tc::mbar_wait(st.empty + s, (use - 1) & 1);
         const int term = c / d.kc, cc = c - term * d.kc;
-        tc::mbar_arrive_expect_tx(st.full + s, TC_X_BYTES);
+        tc::mbar_arrive_expect_tx(st.full + s, TC_STAGE_BYTES);
         tc::tma_load_2d(st.ring + s * TC_STAGE_BYTES, xmap, st.full + s, ((term == 1 ? d.kc : 0) + cc) * tc::CHUNK_K16, row0);
       }
     } else if (tid == 32) {
@@ -200,14 +207,12 @@ __device__ inline void lstm_phase_tc(const TcLstmDesc& d, const TcLstmIO& io, in
   for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++slot) {
     const int tile = item / RB, rb = item % RB;
     const int row0 = rb * TC_M;
-    const uint8_t* gimg = d.gimg + (size_t)tile * d.kchunks * TC_W_BYTES;
+    const uint8_t* img = st.wimg + d.img_off + (size_t)slot * d.kchunks * 2048;
     const bool prof_on = st.prof && blockIdx.x == 0;
     long long t0 = 0;
     if (prof_on) t0 = clock64();
     if (tid == 0) {
       // ---- TMA producer (the first st.prefilled chunks of the first item are already in flight) ----
-      // (two producer threads taking the even / odd chunks were measured: the producer loop shrinks 7.7 -> 5.4 us per
-      // step, "until accumulator ready" stays at 10.9 us -- the stream is bound by the L2, not by the issue rate)
       const int c0 = slot == 0 ? (int)st.prefilled : 0;
       st.prefilled = 0;
       for (int c = c0; c < d.kchunks; ++c) {
@@ -215,7 +220,6 @@ __device__ inline void lstm_phase_tc(const TcLstmDesc& d, const TcLstmIO& io, in
         if (use > 0) tc::mbar_wait(st.empty + s, (use - 1) & 1);
         tc::mbar_arrive_expect_tx(st.full + s, TC_STAGE_BYTES);
         tc::tma_load_2d(st.ring + s * TC_STAGE_BYTES, io.xmap, st.full + s, d.order[c] * tc::CHUNK_K16, row0);
-        tc::bulk_load(st.ring + s * TC_STAGE_BYTES + TC_X_BYTES, gimg + d.order[c] * TC_W_BYTES, TC_W_BYTES, st.full + s);
       }
       if (prof_on) st.prof[0] += clock64() - t0;
     } else if (tid == 32) {
@@ -225,7 +229,7 @@ __device__ inline void lstm_phase_tc(const TcLstmDesc& d, const TcLstmIO& io, in
         const uint32_t n = st.n_chunks + c, s = n % TC_STAGES, use = n / TC_STAGES;
         tc::mbar_wait(st.full + s, use & 1);
         tc::tc_fence_after();
-        const uint32_t a0 = tc::smem_u32(st.ring + s * TC_STAGE_BYTES), b0 = a0 + TC_X_BYTES;
+        const uint32_t a0 = tc::smem_u32(st.ring + s * TC_STAGE_BYTES), b0 = tc::smem_u32(img + d.order[c] * 2048);
 #pragma unroll
         for (int k16 = 0; k16 < tc::CHUNK_K16 / tc::UMMA_K16; ++k16)
           tc::mma_f16(st.tmem, tc::smem_desc_sw128(a0 + k16 * 32), tc::smem_desc_sw128(b0 + k16 * 32), idesc,

@@ -46,18 +46,6 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-// non-blocking test (try_wait may suspend the thread for a system-dependent time before it answers "not yet")
-__device__ __forceinline__ bool mbar_test_wait(uint64_t* bar, uint32_t parity) {
-  uint32_t ok;
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-      "selp.u32 %0, 1, 0, p;\n\t}"
-      : "=r"(ok)
-      : "r"(smem_u32(bar)), "r"(parity)
-      : "memory");
-  return ok != 0;
-}
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   uint32_t n = 0;
   while (!mbar_try_wait(bar, parity))
@@ -176,16 +164,8 @@ __device__ __forceinline__ uint32_t sw128_offset(int n, int kk) {
   return (uint32_t)(n * 128 + ((((kk >> 2) ^ (n & 7)) << 4) | ((kk & 3) << 2)));
 }
 
-// 1-D bulk copy global -> shared (contiguous bytes, multiple of 16, both addresses 16-byte aligned), completion on an
-// mbarrier like a TMA tensor load
-__device__ __forceinline__ void bulk_load(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
-               "l"(src), "r"(bytes), "r"(smem_u32(bar))
-               : "memory");
-}
-
 // the same for an fp16 operand: 64-k chunk image, 2-byte elements
-__host__ __device__ __forceinline__ uint32_t sw128_offset16(int n, int kk) {
+__device__ __forceinline__ uint32_t sw128_offset16(int n, int kk) {
   return (uint32_t)(n * 128 + ((((kk >> 3) ^ (n & 7)) << 4) | ((kk & 7) << 1)));
 }
 

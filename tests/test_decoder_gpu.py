@@ -143,21 +143,6 @@ def test_tensor_core_gate_gemms_full_dims(name, B, T, S):
     print("tensor-core path rel err", name, B, errs)
 
 
-def test_weight_ring_switch(monkeypatch):
-    """SAT_WRING=1 (experiment switch, off by default: slower on B200): the query-layer and frame-phase weights of the
-    self-feeding baseline decoder arrive through a TMA bulk-copy ring filled by a producer warp, the first chunks
-    requested behind the grid barrier; same bar, and equal to the LDG form to fp32 rounding."""
-    monkeypatch.setenv("SAT_WRING", "1")
-    hp = small_hp("ljspeech_tacotron")
-    W = sat_b200.init_weights(hp, seed=17, stress=True)
-    for B, T, S in ((200, 61, 14), (100, 40, 9)):
-        mems, lengths, _, _ = decoder_inputs(hp, B, T, S, seed=17)
-        ref = oracle_decoder(hp, W, mems, lengths, max_iters=S, stop_mode="never")
-        got = run_cuda(hp, W, mems, lengths, feed_mode=1, stop_mode=0, max_steps=S)
-        assert got["tensor_cores"]
-        check_close(got, ref)
-
-
 @pytest.mark.parametrize("name,B,T,S,mode", [("ljspeech_tacotron", 200, 61, 14, "free"),
                                              ("ljspeech_self_attention", 96, 41, 10, "teacher")])
 def test_tensor_core_dense_phases_switch(name, B, T, S, mode, monkeypatch):
