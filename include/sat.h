@@ -171,6 +171,12 @@ int sat_mha_forward_noalloc(const float* wqkv, const float* bqkv, const float* w
                             const float* x, int32_t B, int32_t T, int32_t Din, int32_t D, int32_t H,
                             int32_t causal, const int64_t* lengths, float* out, float* probs, void* stream);
 int64_t sat_mha_noalloc_max_floats(void);
+/* ScaledDotProductAttentionMechanism.__call__ (modules/self_attention.py:45-65, masks :67-86) on already projected
+ * heads: qkv device [B,T,3D] = key | value | query with head h in columns h*(D/H) .. of each block; ctx device [B,T,D]
+ * (heads merged), probs device [B,H,T,T] or null.  softmax(mask(Q K^T / sqrt(D/H))) V; `lengths` (device [B] or null)
+ * enables the padding mask (query rows and key columns past the length), `causal` the subsequent mask.  Asynchronous. */
+int sat_sdpa_forward(const float* qkv, int32_t B, int32_t T, int32_t D, int32_t H, int32_t causal,
+                     const int64_t* lengths, float* ctx, float* probs, void* stream);
 /* SelfAttentionTransformer: prefix/mha/... and prefix/transform/... ; out = x + tanh(Dense(mha(x))) */
 int sat_sat_forward(const sat_tensor* weights, int32_t n_weights, const char* prefix,
                     const float* x, int32_t B, int32_t T, int32_t D, int32_t H, int32_t causal,

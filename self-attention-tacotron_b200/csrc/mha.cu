@@ -518,6 +518,9 @@ MhaDev mha_upload(DevPool& pool, const Blob& W, const std::string& P, const std:
 
 size_t mha_scratch_floats(const MhaDev& m, int64_t rows) { return (size_t)rows * (size_t)(3 * m.D + 2 * m.D) + 64; }
 
+static void scaled_dot_core(const MhaDev& m, const float* qkv, int B, int T, int causal, const int64_t* pad_lengths,
+                            float* ctx, float* probs, int head_major, cudaStream_t st);
+
 static void attention_core(const MhaDev& m, const float* x, int B, int T, int causal, const int64_t* pad_lengths,
                            float* ctx, float* qkv, float* probs, int head_major, cudaStream_t st) {
   if (m.tq.img && m.xpack && m.tq.Npad == 3 * m.D) {
@@ -528,6 +531,13 @@ static void attention_core(const MhaDev& m, const float* x, int B, int T, int ca
     g.W = m.Wqkv; g.N = 3 * m.D; g.shift = m.bqkv; g.C = qkv; g.ldc = 3 * m.D;
     gemm_launch(g, st);
   }
+  scaled_dot_core(m, qkv, B, T, causal, pad_lengths, ctx, probs, head_major, st);
+}
+
+// ScaledDotProductAttentionMechanism.__call__ (modules/self_attention.py:45-65) on projected heads: qkv [B][T][3D]
+// (key | value | query, head h = columns h * dh ..) -> ctx [B][T][D], probs [B][H][T][T]; only m.D and m.H are read
+static void scaled_dot_core(const MhaDev& m, const float* qkv, int B, int T, int causal, const int64_t* pad_lengths,
+                            float* ctx, float* probs, int head_major, cudaStream_t st) {
   const int dh = m.D / m.H, Tpad = (T + 3) & ~3;
   if (mha_tc_ok(T, m.D, m.H)) {
     const int Tp = (T + 15) & ~15;
@@ -608,6 +618,16 @@ extern "C" int sat_mha_forward(const sat_tensor* weights, int32_t n_weights, con
     float* scratch = pool.alloc<float>(mha_scratch_floats(m, (int64_t)B * T), false);
     mha_forward(m, x, B, T, causal, lengths, out, probs, scratch, st);
     SAT_CUDA(cudaStreamSynchronize(st));
+  });
+}
+
+extern "C" int sat_sdpa_forward(const float* qkv, int32_t B, int32_t T, int32_t D, int32_t H, int32_t causal,
+                                const int64_t* lengths, float* ctx, float* probs, void* stream) {
+  return guarded([&] {
+    SAT_REQUIRE(qkv && ctx && B >= 1 && T >= 1 && H >= 1 && D >= H && D % H == 0, "bad argument");
+    MhaDev m;
+    m.D = D; m.H = H; m.Din = D;
+    scaled_dot_core(m, qkv, B, T, causal, lengths, ctx, probs, 0, (cudaStream_t)stream);
   });
 }
 

@@ -256,6 +256,23 @@ def mha_forward(weights, prefix, x, num_heads, model_dim, causal=False, lengths=
     return out, probs
 
 
+def sdpa_forward(query, keys, values, causal=False, lengths=None, want_probs=True, stream=None):
+    """ScaledDotProductAttentionMechanism.__call__ (modules/self_attention.py:45-65) on projected heads
+    [B, H, T, d_head] -> (context [B, H, T, d_head], probs [B, H, T, T]).  The three tensors are interleaved into the
+    kernel's [B, T, 3D] layout (tensor plumbing); the arithmetic is sat_sdpa_forward."""
+    _need_cuda(query, keys, values, lengths)
+    B, H, T, dh = query.shape
+    D = H * dh
+    merge = lambda a: a.float().permute(0, 2, 1, 3).reshape(B, T, D)  # noqa: E731
+    qkv = torch.cat((merge(keys), merge(values), merge(query)), dim=-1).contiguous()
+    ctx = torch.empty((B, T, D), device=query.device, dtype=torch.float32)
+    probs = torch.empty((B, H, T, T), device=query.device, dtype=torch.float32) if want_probs else None
+    if lengths is not None:
+        lengths = lengths.to(device=query.device, dtype=torch.int64).contiguous()
+    check(lib().sat_sdpa_forward(ptr(qkv), B, T, D, H, int(causal), ptr(lengths), ptr(ctx), ptr(probs), stream_ptr(stream)))
+    return ctx.reshape(B, T, H, dh).permute(0, 2, 1, 3), probs
+
+
 def sat_forward(weights, prefix, x, num_heads, causal=False, want_probs=True, stream=None):
     """SelfAttentionTransformer (modules/module.py:363-371): x + tanh(Dense(SelfAttention(x)))."""
     _need_cuda(x)

@@ -8,8 +8,9 @@ def _no_training(is_training):
 
 
 class ScaledDotProductAttentionMechanism:
-    """modules/self_attention.py:13-86.  Kept for name compatibility: the scaled-dot core is fused
-    inside the attention kernel, so this object only records its options."""
+    """modules/self_attention.py:13-86: ``mechanism(query, memory_sequence_length)`` -> (context, alignment) for
+    projected heads [B, H, T, d_head], computed by sat_sdpa_forward (the same kernels MultiHeadAttention uses with the
+    projections fused in front).  Self-attention only: keys, values and query share T."""
 
     def __init__(self, keys, values, num_heads, drop_rate=0.0, is_training=False, use_padding_mask=True,
                  use_subsequent_mask=False):
@@ -27,6 +28,14 @@ class ScaledDotProductAttentionMechanism:
     @property
     def values(self):
         return self._values
+
+    def __call__(self, query, memory_sequence_length=None):
+        if query.shape != self._keys.shape or query.shape[1] != self.num_heads:
+            raise ValueError(f"query {tuple(query.shape)} must match keys {tuple(self._keys.shape)} = [B, num_heads, T, d_head]")
+        lengths = memory_sequence_length if self.use_padding_mask else None
+        if self.use_padding_mask and lengths is None:
+            raise ValueError("use_padding_mask=True needs memory_sequence_length")
+        return engine.sdpa_forward(query, self._keys, self._values, causal=self.use_subsequent_mask, lengths=lengths)
 
 
 class MultiHeadAttention:

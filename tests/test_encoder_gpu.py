@@ -129,6 +129,40 @@ def test_self_attention_module(D, H, T, causal, tc, monkeypatch):
         assert rel_err(aligns[i].cpu().numpy(), ref_p[:, i]) <= TOL
 
 
+@pytest.mark.parametrize("H,T,dh,causal,masked", [(2, 23, 16, False, False), (2, 150, 16, False, True),
+                                                  (2, 70, 128, True, False), (3, 9, 8, True, True),
+                                                  (2, 300, 64, True, False)])
+def test_scaled_dot_product_attention_mechanism(H, T, dh, causal, masked):
+    """modules/self_attention.py:13-86 at its own interface: projected heads [B, H, T, d_head] in, (context, alignment)
+    out -- softmax(mask(Q K^T / sqrt(d_head))) V with the padding (:67-78) and subsequent (:80-86) masks."""
+    from sat_b200.modules.self_attention import ScaledDotProductAttentionMechanism
+    rng = np.random.default_rng(H * T + dh)
+    B = 3
+    q, k, v = (rng.normal(0, 1, size=(B, H, T, dh)).astype(np.float32) for _ in range(3))
+    lengths = np.array([T, max(1, T // 2), max(1, T - 3)], dtype=np.int64)
+    s = (q.astype(np.float64) @ k.astype(np.float64).transpose(0, 1, 3, 2)) / np.sqrt(dh)
+    ok = np.ones((B, 1, T, T), dtype=bool)
+    if masked:
+        m = np.arange(T)[None, :] < lengths[:, None]
+        ok = ok & (m[:, None, :, None] & m[:, None, None, :])
+    if causal:
+        ok = ok & np.tril(np.ones((T, T), dtype=bool))[None, None]
+    s = np.where(ok, s, -np.inf)
+    with np.errstate(invalid="ignore"):
+        p = onn.softmax(s, axis=-1)
+    ref = p @ v.astype(np.float64)
+    mech = ScaledDotProductAttentionMechanism(_t(k), _t(v), H, use_padding_mask=masked, use_subsequent_mask=causal)
+    ctx, align = mech(_t(q), memory_sequence_length=_t(lengths) if masked else None)
+    assert tuple(ctx.shape) == (B, H, T, dh) and tuple(align.shape) == (B, H, T, T)
+    ctx, align = ctx.cpu().numpy(), align.cpu().numpy()
+    for b in range(B):
+        n = int(lengths[b]) if masked else T  # rows past the length are NaN in the reference (0 / 0): compared apart
+        assert rel_err(ctx[b, :, :n], ref[b, :, :n]) <= TOL
+        assert rel_err(align[b, :, :n], p[b, :, :n]) <= TOL
+        if n < T:
+            assert np.isnan(ctx[b, :, n:]).all() and np.isnan(ref[b, :, n:]).all()
+
+
 @pytest.mark.parametrize("D,H,T", [(16, 2, 11), (32, 2, 300), (256, 2, 70)])
 def test_self_attention_padding_mask(D, H, T):
     """use_padding_mask=True (:67-78): rows/columns past the length are -inf; fully masked rows are NaN in the
