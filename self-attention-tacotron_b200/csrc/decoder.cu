@@ -77,27 +77,6 @@ PackedDense pack_lstm(DevPool& pool, const float* W, const float* bias, int K, i
   return d;
 }
 
-// column slices of a dense layer for the cluster form (decoder_kernel.cuh: ClDense): fp16 [CLD][K][Nq] + bias [CLD * Nq]
-ClDense pack_cl_dense(DevPool& pool, const float* W, int ldw, const float* bias, int K, int N) {
-  ClDense d;
-  d.K = K;
-  d.Nq = (ceil_div(N, CLD) + 3) / 4 * 4;
-  std::vector<__half> w((size_t)CLD * K * d.Nq, __float2half_rn(0.f));
-  std::vector<float> b((size_t)CLD * d.Nq, 0.f);
-  for (int r = 0; r < CLD; ++r)
-    for (int n = 0; n < d.Nq; ++n) {
-      const int c = r * d.Nq + n;
-      if (c >= N) continue;
-      if (bias) b[c] = bias[c];
-      for (int k = 0; k < K; ++k) w[((size_t)r * K + k) * d.Nq + n] = __float2half_rn(W[(size_t)k * ldw + c]);
-    }
-  std::vector<float> packed((w.size() + 1) / 2);
-  memcpy(packed.data(), w.data(), w.size() * sizeof(__half));
-  d.W = (const __half*)pool.upload(packed);
-  d.bias = pool.upload(b);
-  return d;
-}
-
 __global__ void f32_to_f16_kernel(const float* __restrict__ src, __half* __restrict__ dst, size_t n) {
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
     dst[i] = tc::to_f16(src[i]);
@@ -190,8 +169,6 @@ struct sat_decoder {
   // multi-speaker dense / prenet layer 1 over all steps, the decoder self-attention projections, frame + stop projection
   DenseTc3 t_mem[2], t_msd, t_pre1, t_outp, t_qkv[MAX_HOPS], t_o[MAX_HOPS], t_tr[MAX_HOPS];
   bool dense_tc = true;
-  ClDense cd_q, cd_o;  // column slices of the query layer (one mechanism) and of the folded frame / stop / prenet-0 projection
-  bool has_cd_q = false, has_cd_o = false;
   PackedDense pre0, msd, pre1, lstm_a, lstm_1, lstm_2, outp, dq[2];
   PackedDense outp_f;  // outp + prenet layer 0 folded onto the fed-back frame (self feed): [d_out][Mr + 1 + P0]
   bool has_outp_f = false;
@@ -318,15 +295,6 @@ extern "C" int sat_decoder_create(const sat_hparams* hpp, const sat_tensor* weig
         }
       }
     }
-    if (h->n_mech == 1) {
-      std::vector<float> wq((size_t)A * h->Up[0], 0.f);  // zero padded to Up columns like the row-major copy
-      const int U = hp.attention_units[0];
-      const float* src = W.get(D + "attention1/query_layer/kernel", (int64_t)A * U);
-      for (int k = 0; k < A; ++k)
-        for (int u = 0; u < U; ++u) wq[(size_t)k * h->Up[0] + u] = src[(size_t)k * U + u];
-      h->cd_q = pack_cl_dense(pool, wq.data(), h->Up[0], nullptr, A, h->Up[0]);
-      h->has_cd_q = true;
-    }
     // decoder self-attention hops (modules/module.py:363-371 inside rnn_wrappers.py:111-124)
     int d_out = Dd;
     for (int i = 0; i < h->hops; ++i) {
@@ -397,8 +365,6 @@ extern "C" int sat_decoder_create(const sat_hparams* hpp, const sat_tensor* weig
       if (NF <= 4 * NT && (size_t)d_out * NF <= (size_t)1 << 22) {
         h->outp_f = pack_dense(pool, wf.data(), bf.data(), d_out, NF);
         h->has_outp_f = true;
-        h->cd_o = pack_cl_dense(pool, wf.data(), NF, bf.data(), d_out, NF);
-        h->has_cd_o = true;
       }
     }
     // launch geometry
@@ -593,48 +559,6 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
     if (const char* e = getenv("SAT_BENCH_BARRIERS")) p.bench_barriers = atoi(e);
     p.tc = use_tc ? 1 : 0;
     if (!use_tc) p.tc_q = p.tc_frame = 0;
-    // ---- column-split query layer / frame projection over clusters of CLD CTAs (decoder_kernel.cuh: ClDense) ----
-    int cld_launch = 1, cld_grid = 0;
-    if (use_tc && h->n_mech == 1) {
-      bool on = true;
-      if (const char* e = getenv("SAT_CLD")) on = atoi(e) != 0;
-      auto fits = [&](const ClDense& d, int extra) {
-        const int G = d.Nq / 4, kparts = std::min((int)NT / G, d.K);
-        return CLD_SLOTS * d.K + al4(CLD_SLOTS * d.Nq) + extra + std::max(kparts * CLD_SLOTS * d.Nq, 2 * (int)NT * 8) <=
-               p.scratch_floats;
-      };
-      const bool q_ok = on && h->has_cd_q && !p.tc_q && !io.forced_alignment && fits(h->cd_q, 0);
-      const bool f_ok = on && h->has_cd_o && p.fused_prenet0 && !p.ms && h->hops == 0 && !p.tc_frame &&
-                        fits(h->cd_o, 2 * p.pre0.Np + 2 * p.pre1.Np);
-      if (q_ok || f_ok) {
-        cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3(h->grid); cfg.blockDim = dim3(NT); cfg.dynamicSmemBytes = smem_bytes; cfg.stream = st;
-        cudaLaunchAttribute at[1];
-        at[0].id = cudaLaunchAttributeClusterDimension;
-        at[0].val.clusterDim.x = CLD; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-        cfg.attrs = at; cfg.numAttrs = 1;
-        int n_cl = 0;
-        const cudaError_t oe = cudaOccupancyMaxActiveClusters(&n_cl, (const void*)decoder_persistent_kernel, &cfg);
-        if (getenv("SAT_DEBUG"))
-          fprintf(stderr, "[sat] cluster-dense: q_ok=%d f_ok=%d occupancy rc=%d clusters=%d smem=%zu\n", (int)q_ok, (int)f_ok,
-                  (int)oe, n_cl, smem_bytes);
-        // Clusters of 4 strand the SMs of GPCs whose SM count is not a multiple of 4 (B200: 33 clusters = 132 CTAs with
-        // one CTA per SM), so the grid shrinks to what is co-resident.  That costs nothing where every CTA has two rows
-        // anyway (B > SM count) or where one row per CTA still fits (B <= clusters * 4); in between it would not pay.
-        const int gc = std::min(n_cl * CLD, h->grid / CLD * CLD);
-        bool grid_ok = oe == cudaSuccess && gc >= CLD && B <= 2 * gc && (B <= gc || B > h->grid);
-        for (const TcLstmDesc* d : {&p.tc_a, &p.tc_1, &p.tc_2}) grid_ok = grid_ok && d->n_tiles * RB <= gc;
-        if (grid_ok) {
-          cld_launch = CLD;
-          cld_grid = gc;
-          p.cld_q = q_ok; p.cld_f = f_ok;
-          if (q_ok) p.cd_q = h->cd_q;
-          if (f_ok) p.cd_o = h->cd_o;
-        } else {
-          cudaGetLastError();
-        }
-      }
-    }
     if (!use_tc) p.scratch_floats = SCRATCH_FLOATS;
     p.RB = RB;
     p.Ka_pad = ceil_div(Ka, tc::CHUNK_K16) * tc::CHUNK_K16;
@@ -679,7 +603,7 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
     if (const char* e = getenv("SAT_ATT_PAIR")) p.att_pair = p.att_pair && atoi(e) != 0;
     // ---- cluster-split attention rows: small batches leave most SMs idle in the row-split phase, so a cluster of 4
     // (or 2) CTAs shares each (row, mechanism) item (DecParams::cl).  fp32 SIMT form only. ----
-    int grid_run = cld_launch > 1 ? cld_grid : h->grid;
+    int grid_run = h->grid;
     p.cl = 1;
     if (!use_tc) {
       int want = 4;
@@ -731,7 +655,7 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
       }
       if (p.cl == 1) smem_bytes = plan_simt(h->grid);
     }
-    h->last_cl = std::max(p.cl, cld_launch);
+    h->last_cl = p.cl;
 
     // ---- workspace carve-up (floats) ----
     size_t off = 0;
@@ -933,9 +857,8 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
       at[0].id = cudaLaunchAttributeCooperative;
       at[0].val.cooperative = 1;
       at[1].id = cudaLaunchAttributeClusterDimension;
-      const int cluster = std::max(p.cl, cld_launch);
-      at[1].val.clusterDim.x = cluster; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
-      cfg.attrs = at; cfg.numAttrs = cluster > 1 ? 2 : 1;
+      at[1].val.clusterDim.x = p.cl; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
+      cfg.attrs = at; cfg.numAttrs = p.cl > 1 ? 2 : 1;
       SAT_CUDA(cudaLaunchKernelExC(&cfg, (const void*)decoder_persistent_kernel, args));
     }
     SAT_CUDA(cudaEventRecord(h->ev1, st));

@@ -21,22 +21,6 @@ constexpr int N_PROF = 48;  // [0,16) phases of a step, [16,24) attention-item s
 constexpr int SCRATCH_FLOATS = (RED_FLOATS > ATT_SMEM_FLOATS ? RED_FLOATS : ATT_SMEM_FLOATS);
 constexpr int TC_SCRATCH_FLOATS = (TC_STAGES * TC_STAGE_BYTES + 1024) / 4;  // ring + alignment slack
 
-// ---- column-split dense layers of the row-split phases (tensor-core mode, one mechanism) -----------------------------
-// Every CTA used to stream a whole weight matrix from L2 for its one or two rows (query layer 131 KB, frame / stop
-// projection with the folded prenet layer 0 213 KB): 60 MB per step through an L2 that delivers ~7 TB/s when all SMs
-// pull.  Launched with a cluster dimension of CLD, the CLD CTAs of a cluster pool their rows (CLD_SLOTS) and each
-// computes 1 / CLD of the COLUMNS for all of them -- a quarter of the bytes per CTA; results go where they are needed:
-// the processed query into global memory (read by the row's own CTA after one cluster barrier), the prenet activations
-// into the owning CTA's shared memory (DSMEM), mel frames / stop logits straight to their output tensors.
-constexpr int CLD = 4;
-constexpr int CLD_SLOTS = 2 * CLD;
-
-struct ClDense {
-  const __half* W;    // [CLD][K][Nq] fp16: column slice r holds columns r * Nq .. of the layer (zero padded)
-  const float* bias;  // [CLD * Nq]
-  int K, Nq;          // Nq: columns per slice, a multiple of 4
-};
-
 struct SaHop {
   DenseDesc qkv, o, tr;
   float* kcache;  // [B][H][Smax][dh]
@@ -91,8 +75,6 @@ struct DecParams {
   TcDense tq, tp, tr;
   __half *qx, *px, *rx;     // fp16 hi + lo pairs [RB * 128][ld]: attention-LSTM output, LSTM2 output, prenet layer-0 output
   int qx_ld, px_ld, rx_ld;
-  int cld_q, cld_f;         // column-split query layer / frame + stop projection over clusters of CLD CTAs (see ClDense)
-  ClDense cd_q, cd_o;
   int cl;                   // cluster size of the launch (1: rows are not split)
   int cl_split[2];          // mechanism i is split over the cluster (else rank 0 takes the whole item)
   const float* cl_wq[2];    // query-layer weights as cl contiguous column slices [cl][A][cl_sw] (fp32)
@@ -489,118 +471,6 @@ __device__ inline void frame_item(const DecParams& p, const int* b, int t, const
   stamp();
 }
 
-// outs[s][n] = bias[n] + sum_k xs[s][k] W_slice[k][n] for the NS pooled rows of the cluster and this CTA's column slice.
-// A lane owns 4 columns (one 8-byte load per k), NT / (Nq / 4) k-slices; part needs kparts * NS * Nq floats.
-template <int NS>
-__device__ inline void row_dense_slice(const ClDense& d, int crank, const float* xs, int xs_stride, float* part, float* outs) {
-  const int tid = threadIdx.x;
-  const int Nq = d.Nq, G = Nq >> 2, K = d.K;
-  const int kparts = min(NT / G, K), kper = (K + kparts - 1) / kparts;
-  const int kp = tid / G, g = tid - kp * G;
-  if (kp < kparts) {
-    float acc[NS][4];
-#pragma unroll
-    for (int q = 0; q < NS; ++q)
-#pragma unroll
-      for (int c = 0; c < 4; ++c) acc[q][c] = 0.f;
-    const int k0 = kp * kper, k1 = min(K, k0 + kper);
-    const uint2* w = (const uint2*)(d.W + (size_t)crank * K * Nq) + (size_t)k0 * G + g;
-    for (int k = k0; k < k1; k += 8, w += 8 * G) {
-      uint2 wv[8];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) wv[j] = (k + j < k1) ? __ldg(w + (size_t)j * G) : make_uint2(0u, 0u);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        if (k + j >= k1) break;
-        const float2 a = __half22float2(*(const __half2*)&wv[j].x), b = __half22float2(*(const __half2*)&wv[j].y);
-#pragma unroll
-        for (int q = 0; q < NS; ++q) {
-          const float x = xs[q * xs_stride + k + j];
-          acc[q][0] = fmaf(x, a.x, acc[q][0]); acc[q][1] = fmaf(x, a.y, acc[q][1]);
-          acc[q][2] = fmaf(x, b.x, acc[q][2]); acc[q][3] = fmaf(x, b.y, acc[q][3]);
-        }
-      }
-    }
-#pragma unroll
-    for (int q = 0; q < NS; ++q)
-      *(float4*)(part + (size_t)(kp * NS + q) * Nq + 4 * g) = make_float4(acc[q][0], acc[q][1], acc[q][2], acc[q][3]);
-  }
-  __syncthreads();
-  for (int i = tid; i < NS * Nq; i += NT) {
-    const int q = i / Nq, n = i - q * Nq;
-    float v = __ldg(d.bias + crank * Nq + n);
-    for (int k = 0; k < kparts; ++k) v += part[(size_t)(k * NS + q) * Nq + n];
-    outs[i] = v;
-  }
-  __syncthreads();
-}
-
-// rows pooled by the cluster of this CTA: slot s belongs to CTA s >> 1 of the cluster (its first or second row)
-__device__ __forceinline__ int cld_row(int slot) {
-  return (int)(blockIdx.x - cluster_ctarank()) + (slot >> 1) + (int)gridDim.x * (slot & 1);
-}
-
-// frame phase, column-split form (self feed with prenet layer 0 folded into the projection): see ClDense
-__device__ inline void frame_phase_cluster(const DecParams& p, int t, const float* y, Act2D p1_dst, float* sm) {
-  const int tid = threadIdx.x, ld = p.ld, crank = (int)cluster_ctarank();
-  if ((int)blockIdx.x - crank >= p.B) return;  // no row in this cluster (uniform over its CTAs)
-  const int K = p.cd_o.K, Nq = p.cd_o.Nq, P0p = p.pre0.Np, P1p = p.pre1.Np;
-  float* xs = sm;                           // [CLD_SLOTS][K] decoder outputs of the pooled rows
-  float* so = xs + CLD_SLOTS * K;           // [CLD_SLOTS][Nq] this CTA's column slice of the projection
-  float* p0s = so + al4(CLD_SLOTS * Nq);    // [2][P0p] prenet layer-0 activations of the OWN rows (filled by the cluster)
-  float* p1s = p0s + 2 * P0p;               // [2][P1p]
-  float* part = p1s + 2 * P1p;
-  for (int i = tid; i < CLD_SLOTS * K; i += NT) {
-    const int s = i / K, k = i - s * K, r = cld_row(s);
-    xs[i] = r < p.B ? __ldcg(y + (size_t)k * ld + r) : 0.f;
-  }
-  __syncthreads();
-  row_dense_slice<CLD_SLOTS>(p.cd_o, crank, xs, K, part, so);
-  const int N = p.Mr + 1 + p.P0;
-  for (int i = tid; i < CLD_SLOTS * Nq; i += NT) {
-    const int s = i / Nq, n = i - s * Nq, c = crank * Nq + n, r = cld_row(s);
-    if (r >= p.B || c >= N) continue;
-    const float v = so[i];
-    if (c < p.Mr) p.mel[((size_t)r * p.max_steps + t) * p.Mr + c] = v;
-    else if (c == p.Mr) p.stop[(size_t)r * p.max_steps + t] = v;
-    else st_cluster_f32(p0s + (s & 1) * P0p + (c - p.Mr - 1), (uint32_t)(s >> 1), fmaxf(v, 0.f));  // -> the row's owner
-  }
-  cluster_sync_all();  // every CTA now holds relu(prenet layer 0) of its own rows
-  const int b0 = blockIdx.x, b1 = b0 + gridDim.x;
-  if (b0 < p.B) {
-    const int rr = b1 < p.B ? 2 : 1;
-    if (rr == 2) row_dense<2, true>(p.pre1, p0s, P0p, part, p1s, 1);
-    else row_dense<1, true>(p.pre1, p0s, P0p, part, p1s, 1);
-    for (int i = tid; i < rr * p.P1; i += NT) {
-      const int q = i / p.P1, n = i - q * p.P1;
-      p1_dst.put(n, q ? b1 : b0, p1s[q * P1p + n]);
-    }
-    __syncthreads();
-  }
-}
-
-// query layer, column-split form: processed queries of the cluster's pooled rows -> global pq (row-major [b][Up])
-__device__ inline void query_cluster(const DecParams& p, const float* qsrc, float* sm) {
-  const int tid = threadIdx.x, ld = p.ld, crank = (int)cluster_ctarank();
-  if ((int)blockIdx.x - crank >= p.B) return;
-  const int K = p.cd_q.K, Nq = p.cd_q.Nq;
-  float* xs = sm;                  // [CLD_SLOTS][A]
-  float* so = xs + CLD_SLOTS * K;  // [CLD_SLOTS][Nq]
-  float* part = so + al4(CLD_SLOTS * Nq);
-  for (int i = tid; i < CLD_SLOTS * K; i += NT) {
-    const int s = i / K, k = i - s * K, r = cld_row(s);
-    xs[i] = r < p.B ? __ldcg(qsrc + (size_t)k * ld + r) : 0.f;
-  }
-  __syncthreads();
-  row_dense_slice<CLD_SLOTS>(p.cd_q, crank, xs, K, part, so);
-  const AttMech& m = p.mech[0];
-  for (int i = tid; i < CLD_SLOTS * Nq; i += NT) {
-    const int s = i / Nq, n = i - s * Nq, c = crank * Nq + n, r = cld_row(s);
-    if (r < p.B && c < m.Up) const_cast<float*>(m.pq)[(size_t)c * m.pq_su + (size_t)r * m.pq_sb] = so[i];
-  }
-  cluster_sync_all();  // release / acquire at cluster scope: the four slices of pq are visible to the row's own CTA
-}
-
 // all rows of the batch through frame_item, two per pass
 __device__ inline void frame_phase(const DecParams& p, int t, const float* y, int Dy, Act2D p1_dst, bool prologue, float* sm) {
   for (int b0 = blockIdx.x; b0 < p.B; b0 += 2 * gridDim.x) {
@@ -789,7 +659,6 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
     } else {
       const float* qsrc = p.tc ? p.qfm : p.l1_in[cur];  // feature-major [A][ld]
       const int n_items = p.B * p.n_mech;
-      if (p.cld_q) query_cluster(p, qsrc, scratch);
       for (int i0 = blockIdx.x; i0 < n_items; i0 += 2 * gridDim.x) {
         const int i1 = i0 + gridDim.x;
         const int nit = i1 < n_items ? 2 : 1;
@@ -797,7 +666,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
         const int mi0 = i0 % p.n_mech;
         // the items of one CTA share the mechanism whenever gridDim.x is a multiple of n_mech; otherwise one at a time
         const bool pair = nit == 2 && (i1 % p.n_mech) == mi0;
-        for (int q0 = 0; q0 < nit && !p.tc_q && !p.cld_q; q0 += pair ? 2 : 1) {
+        for (int q0 = 0; q0 < nit && !p.tc_q; q0 += pair ? 2 : 1) {
           const int nq = pair ? 2 : 1;
           const int mi = items[q0] % p.n_mech;
           if (p.mech[mi].kind == SAT_ATT_TEACHER_FORCING) continue;
@@ -931,9 +800,6 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
         __syncthreads();
         dense_phase_tc(p.tr, p.maps + 8, p.RB, tcs,
                        PrenetTcEpi{p.pre1.bias, p.P1, p.B, Act2D{p.att_in[nxt], 1, p.Ka_pad, 1}});
-      } else if (p.cld_f) {
-        // ---- the same with the projection split by columns over clusters of CTAs ----
-        frame_phase_cluster(p, t, y, Act2D{p.att_in[nxt], 1, p.Ka_pad, 1}, scratch);
       } else {
         // ---- L+A+B: frame + stop projection of step t, fed-back frame, prenet of step t+1 (row split) ----
         frame_phase(p, t, y, p.outp.K, Act2D{p.att_in[nxt], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc}, false, scratch);
