@@ -14,6 +14,7 @@
 // The BiLSTM input projection is one time-batched GEMM; the recurrence runs in a kernel where each
 // CTA owns a few (row, direction) sequences for all T steps (rows are independent -> no grid sync).
 #include "common.cuh"
+#include "tc.cuh"
 #include <cstdlib>
 
 namespace sat {
@@ -112,6 +113,37 @@ void bilstm_launch(const float* xproj, const float* Wh, const long long* lengths
   bilstm_kernel<U, ROWS><<<grid, LSTM_NT, smem, st>>>(xproj, Wh, lengths, B, T, zc, zh, out);
 }
 
+// The encoder prenet (two relu Dense layers, dropout off at inference: SURVEY.md A.1) is applied to the EMBEDDING of a
+// symbol, so for id inputs it is a function of the id alone: prenet(embedding[id]) is tabulated per symbol when the
+// weights are loaded (double accumulation) and the two GEMMs of the hot path become one gather.
+// y32 [B*T][P] fp32 (residual of proj2); y16 (optional) the zero-haloed fp16 conv input [B][T + 2 halo][P].
+// ids outside [0, rows) read as a zero row and set *err (tacotron2 Embedding asserts the range); with `lengths` the
+// frames t >= lengths[b] are zeros (sat_encoder::mask_padding).
+__global__ void prenet_table_gather_kernel(const long long* __restrict__ ids, const float* __restrict__ tab, int n_sym, int B,
+                                           int T, int P, int Tp, int halo, const long long* __restrict__ lengths,
+                                           float* __restrict__ y32, __half* __restrict__ y16, int* __restrict__ err) {
+  const int P4 = P / 4;
+  const size_t n = (size_t)B * T * P4;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const int c4 = (int)(i % P4);
+    const size_t row = i / P4;
+    const int b = (int)(row / T), t = (int)(row % T);
+    const long long id = ids[row];
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (id < 0 || id >= n_sym) {
+      if (c4 == 0) *err = 1;
+    } else if (!lengths || t < lengths[b]) {
+      v = __ldg((const float4*)(tab + (size_t)id * P) + c4);
+    }
+    *((float4*)(y32 + row * P) + c4) = v;
+    if (y16) {
+      __half2* dst = (__half2*)(y16 + ((size_t)b * Tp + halo + t) * P + 4 * c4);
+      dst[0] = __halves2half2(tc::to_f16(v.x), tc::to_f16(v.y));
+      dst[1] = __halves2half2(tc::to_f16(v.z), tc::to_f16(v.w));
+    }
+  }
+}
+
 struct Conv {
   __half* wimg = nullptr;  // K-major fp16 image for the tensor-core path (null when the shape is not supported)
   float* w = nullptr;      // [k][cin][cout]
@@ -177,6 +209,7 @@ struct sat_encoder {
   int half = 0, cin = 0, sm_count = 148;
   bool tc = false;  // conv bank + proj1 on the tensor cores (fp16 operands, fp32 accumulation)
   bool tc_full = false;  // ... and prenet layer 1, proj2, the highway layers and the BiLSTM input projection as well
+  float* pre_tab = nullptr;    // [num_symbols][P1]: prenet(embedding[id]) per symbol (prenet_table_gather_kernel)
   __half* pre1_img = nullptr;
   __half* bank_img = nullptr;  // all widths in one image (conv_tc_bank_image): the bank is ONE launch
   float *bank_scale = nullptr, *bank_shift = nullptr;
@@ -221,6 +254,29 @@ extern "C" int sat_encoder_create(const sat_hparams* hpp, const sat_tensor* weig
       d = u;
     }
     h->cin = d;
+    {
+      const int P0 = hp.encoder_prenet_units[0], P1 = hp.encoder_prenet_units[1], S = hp.num_symbols;
+      const float* emb = W.get("embedding", (int64_t)S * E);
+      const float *w0 = W.get("encoder/prenet/dense_0/kernel", (int64_t)E * P0), *b0 = W.get("encoder/prenet/dense_0/bias", P0);
+      const float *w1 = W.get("encoder/prenet/dense_1/kernel", (int64_t)P0 * P1), *b1 = W.get("encoder/prenet/dense_1/bias", P1);
+      std::vector<float> tab((size_t)S * P1);
+      std::vector<double> a0(P0), a1(P1);
+      for (int sym = 0; sym < S; ++sym) {
+        for (int j = 0; j < P0; ++j) a0[j] = b0[j];
+        for (int k = 0; k < E; ++k) {
+          const double x = emb[(size_t)sym * E + k];
+          for (int j = 0; j < P0; ++j) a0[j] += x * (double)w0[(size_t)k * P0 + j];
+        }
+        for (int j = 0; j < P1; ++j) a1[j] = b1[j];
+        for (int k = 0; k < P0; ++k) {
+          const double x = a0[k] > 0.0 ? a0[k] : 0.0;
+          for (int j = 0; j < P1; ++j) a1[j] += x * (double)w1[(size_t)k * P1 + j];
+        }
+        for (int j = 0; j < P1; ++j) tab[(size_t)sym * P1 + j] = (float)(a1[j] > 0.0 ? a1[j] : 0.0);
+      }
+      if (P1 % 4 == 0) h->pre_tab = pool.upload(tab);
+      if (const char* e = getenv("SAT_ENC_PRENET_TABLE")) if (atoi(e) == 0) h->pre_tab = nullptr;
+    }
     h->half = hp.cbhg_out_units / 2;
     SAT_REQUIRE(hp.cbhg_out_units % 2 == 0, "cbhg_out_units must be even");
     SAT_REQUIRE(h->half == 128, "the BiLSTM kernel is built for 128 units per direction (cbhg_out_units=256), got %d", h->half);
@@ -399,8 +455,15 @@ static int encoder_forward_impl(sat_encoder* h, const int64_t* ids, const float*
       o_mha = take(mha_scratch_floats(h->hops.empty() ? MhaDev() : h->hops[0], (int64_t)rows));
     }
     float* ws = h->ws.get<float>(off);
-    // ---- embedding gather fused into prenet layer 0 ----
-    {
+    // ---- prenet: per-symbol table for id inputs, else the two dense layers (embedding gather fused into layer 0) ----
+    const bool use_tab = ids && h->pre_tab;
+    if (use_tab && !h->tc_full) {
+      const size_t n = rows * (P1 / 4);
+      prenet_table_gather_kernel<<<(unsigned)std::min<size_t>((n + 255) / 256, 148 * 16), 256, 0, st>>>(
+          (const long long*)ids, h->pre_tab, hp.num_symbols, B, T, P1, 0, 0, (const long long*)mlen, ws + o_p1, nullptr, h->d_err);
+      count_launch();
+    }
+    if (!use_tab) {
       GemmArgs g;
       g.X = ids ? h->emb : embedded; g.Bn = 1; g.T = (int)rows; g.Cin = hp.embedding_dim; g.ldx = hp.embedding_dim;
       g.gather_ids = ids; g.gather_offset = 0;
@@ -434,8 +497,14 @@ static int encoder_forward_impl(sat_encoder* h, const int64_t* ids, const float*
       conv_tc_zero_halo(x16, B, T, P1, st);
       conv_tc_zero_halo(pool16, B, T, ldb, st);
       conv_tc_zero_halo(q1_16, B, T, Q1, st);
-      conv_tc_pack(ws + o_p0, P0, B, T, P0, p0_16, P0, st);
-      {
+      if (use_tab) {
+        const size_t n = rows * (P1 / 4);
+        prenet_table_gather_kernel<<<(unsigned)std::min<size_t>((n + 255) / 256, 148 * 16), 256, 0, st>>>(
+            (const long long*)ids, h->pre_tab, hp.num_symbols, B, T, P1, Tp, CONV_TC_HALO, (const long long*)mlen, ws + o_p1, x16,
+            h->d_err);
+        count_launch();
+      } else {
+        conv_tc_pack(ws + o_p0, P0, B, T, P0, p0_16, P0, st);
         ConvTcLaunch L;  // prenet layer 1: relu(x W + b) -> fp16 (bank input) and fp32 (residual of proj2)
         L.xp = p0_16; L.ldxp = P0; L.B = B; L.T = T; L.cin = P0; L.cout = P1; L.taps = 1; L.pad_left = 0;
         L.wimg = h->pre1_img; L.shift = h->pre_b[1]; L.act = ACT_RELU;

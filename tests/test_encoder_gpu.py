@@ -83,7 +83,9 @@ def test_zoneout_encoder_v1_and_embedded_input():
     assert rel_err(out.cpu().numpy(), ref) <= TOL
     emb = _t(W["embedding"][ids])
     out2, _, _ = h.forward(emb, _t(lengths))
-    assert torch.equal(out, out2)
+    # id inputs take the per-symbol prenet table (exact), embedded inputs the two dense layers: same bar for both
+    assert rel_err(out2.cpu().numpy(), ref) <= TOL
+    assert rel_err(out2.cpu().numpy(), out.cpu().numpy()) <= TOL
 
 
 def test_encoder_two_hops_and_adjustment_free_dims():
