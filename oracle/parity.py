@@ -179,6 +179,10 @@ def free_run_report(got, ref, stop_mode, r, max_iters, first_n=200, tol=1e-3):
     n = min(int(got["n_steps"]), n_ref)
     # per-row number of compared steps: N = min(stop step + 1, first_n, n)
     per_row = np.where(ss_ref >= 0, ss_ref + 1, n)
+    if stop_mode == "per_row":
+        # a row whose stop decision is inside the fp tolerance may stop a step apart in the two runs; a retired row emits
+        # nothing after ITS stop, so the compared window ends at the earlier of the two
+        per_row = np.minimum(per_row, np.where(ss_got >= 0, ss_got + 1, n))
     per_row = np.minimum(np.minimum(per_row, first_n), n)
     al_g, al_r = np.asarray(got["alignment"])[:, :n], np.asarray(ref["alignments"][0])[:, :n]
     valid = np.arange(n)[None, :] < per_row[:, None]
@@ -196,8 +200,13 @@ def free_run_report(got, ref, stop_mode, r, max_iters, first_n=200, tol=1e-3):
     mel_g = np.asarray(got["mel"])[:, :n * r].reshape(B, n, r * M)
     mel_r = np.asarray(ref["mel"])[:, :n * r].reshape(B, n, r * M)
     rep["mel_rel_err_first_n"] = rel_err(np.where(valid[..., None], mel_g, 0), np.where(valid[..., None], mel_r, 0))
-    rep["mel_rel_err_all_steps"] = rel_err(mel_g, mel_r)
-    rep["stop_rel_err"] = rel_err(np.asarray(got["stop"])[:, :n], ref_stop[:, :n])
+    # every step a row emits: all n under the all_rows / never rules, up to its own stop step under the per-row rule
+    # (a retired row writes nothing afterwards)
+    own = (np.minimum(np.where(ss_ref >= 0, ss_ref + 1, n), np.where(ss_got >= 0, ss_got + 1, n))
+           if stop_mode == "per_row" else np.full(B, n))
+    emitted = np.arange(n)[None, :] < np.minimum(own, n)[:, None]
+    rep["mel_rel_err_all_steps"] = rel_err(np.where(emitted[..., None], mel_g, 0), np.where(emitted[..., None], mel_r, 0))
+    rep["stop_rel_err"] = rel_err(np.where(emitted, np.asarray(got["stop"])[:, :n], 0), np.where(emitted, ref_stop[:, :n], 0))
     ref_max = float(np.max(np.abs(mel_r)))
     rep["mel_rel_err_at_step"] = {str(s): float(np.max(np.abs(mel_g[:, s - 1] - mel_r[:, s - 1])) / ref_max)
                                   for s in CHECK_STEPS if s <= n}

@@ -375,7 +375,8 @@ extern "C" int sat_decoder_create(const sat_hparams* hpp, const sat_tensor* weig
     SAT_REQUIRE(prop.cooperativeLaunch, "device lacks cooperative launch");
     h->sm_count = prop.multiProcessorCount;
     h->max_dyn_smem = prop.sharedMemPerBlockOptin - 4096;
-    SAT_CUDA(cudaFuncSetAttribute(decoder_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->max_dyn_smem));
+    SAT_CUDA(cudaFuncSetAttribute(decoder_persistent_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->max_dyn_smem));
+    SAT_CUDA(cudaFuncSetAttribute(decoder_persistent_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->max_dyn_smem));
     h->grid = h->sm_count;
     h->barrier = pool.alloc<unsigned>(1);
     h->prof = pool.alloc<long long>(N_PROF);
@@ -445,6 +446,9 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
     p.P0 = h->P0; p.P1 = h->P1; p.A = A; p.Dd = Dd; p.Dctx = h->Dctx; p.n_mech = h->n_mech;
     p.hops = h->hops; p.heads = hp.decoder_self_attention_num_heads; p.Ds = Ds; p.ms = hp.multi_speaker_prenet;
     p.feed_mode = io.feed_mode; p.stop_mode = io.stop_mode; p.max_steps = S; p.min_iters = io.min_iters;
+    p.retire = io.stop_mode == SAT_STOP_PER_ROW && h->hops == 0;  // (the KV-cached hops walk all rows: SIMT dense phases)
+    if (const char* e = getenv("SAT_RETIRE")) p.retire = p.retire && atoi(e) != 0;
+    const void* kernel_fn = p.retire ? (const void*)decoder_persistent_kernel<true> : (const void*)decoder_persistent_kernel<false>;
     p.S_target = io.target_steps; p.Smax = S;
     p.zc = hp.zoneout_factor_cell; p.zh = hp.zoneout_factor_output;
     p.pre0 = h->pre0.desc(); p.pre1 = h->pre1.desc(); p.outp = h->outp.desc();
@@ -639,7 +643,7 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
           at[0].val.clusterDim.x = cl; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
           cfg.attrs = at; cfg.numAttrs = 1;
           int n_cl = 0;
-          if (cudaOccupancyMaxActiveClusters(&n_cl, (const void*)decoder_persistent_kernel, &cfg) != cudaSuccess) {
+          if (cudaOccupancyMaxActiveClusters(&n_cl, kernel_fn, &cfg) != cudaSuccess) {
             cudaGetLastError();
             break;
           }
@@ -859,7 +863,7 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
       at[1].id = cudaLaunchAttributeClusterDimension;
       at[1].val.clusterDim.x = p.cl; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
       cfg.attrs = at; cfg.numAttrs = p.cl > 1 ? 2 : 1;
-      SAT_CUDA(cudaLaunchKernelExC(&cfg, (const void*)decoder_persistent_kernel, args));
+      SAT_CUDA(cudaLaunchKernelExC(&cfg, kernel_fn, args));
     }
     SAT_CUDA(cudaEventRecord(h->ev1, st));
     h->last_B = B; h->last_T = T; h->last_S = S;

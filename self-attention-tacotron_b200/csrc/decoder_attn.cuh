@@ -574,8 +574,8 @@ __device__ __forceinline__ void attention_load_state(const AttMech& m, int b, in
 }
 
 template <int GT>
-__device__ inline void attention_item(const AttMech& m, int b, int t, int T, int len, float* sm, int gid = 0,
-                                      int crank = 0, int csize = 1, bool preloaded = false) {
+__device__ __forceinline__ void attention_item_inl(const AttMech& m, int b, int t, int T, int len, float* sm, int gid = 0,
+                                                   int crank = 0, int csize = 1, bool preloaded = false) {
   constexpr int GW = GT / 32;
   const int TS = m.TS;
   float* e = sm;                         // [TS] energies -> softmax probs a
@@ -838,6 +838,14 @@ __device__ inline void attention_item(const AttMech& m, int b, int t, int T, int
   }
   group_sync<GT>(gid);
   stamp();
+}
+
+// The same, left to the compiler's inlining heuristics (the instantiation of the kernel without row retirement sits on
+// the 128-register limit and spills less this way; the one with it would otherwise keep the AttMech copy in local memory).
+template <int GT>
+__device__ inline void attention_item(const AttMech& m, int b, int t, int T, int len, float* sm, int gid = 0, int crank = 0,
+                                      int csize = 1, bool preloaded = false) {
+  attention_item_inl<GT>(m, b, t, T, len, sm, gid, crank, csize, preloaded);
 }
 
 }  // namespace dec

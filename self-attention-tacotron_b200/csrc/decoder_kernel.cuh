@@ -75,6 +75,7 @@ struct DecParams {
   TcDense tq, tp, tr;
   __half *qx, *px, *rx;     // fp16 hi + lo pairs [RB * 128][ld]: attention-LSTM output, LSTM2 output, prenet layer-0 output
   int qx_ld, px_ld, rx_ld;
+  int retire;               // per-row stop rule: stopped rows leave the row-split phases (s_live in the kernel)
   int cl;                   // cluster size of the launch (1: rows are not split)
   int cl_split[2];          // mechanism i is split over the cluster (else rank 0 takes the whole item)
   const float* cl_wq[2];    // query-layer weights as cl contiguous column slices [cl][A][cl_sw] (fp32)
@@ -472,24 +473,38 @@ __device__ inline void frame_item(const DecParams& p, const int* b, int t, const
 }
 
 // all rows of the batch through frame_item, two per pass
-__device__ inline void frame_phase(const DecParams& p, int t, const float* y, int Dy, Act2D p1_dst, bool prologue, float* sm) {
-  for (int b0 = blockIdx.x; b0 < p.B; b0 += 2 * gridDim.x) {
-    int b[2] = {b0, b0 + (int)gridDim.x};
+// live[0 .. n_live): the rows that still decode (RETIRE: the per-row stop rule has retired the others; else all rows)
+template <bool RETIRE>
+__device__ inline void frame_phase(const DecParams& p, int t, const float* y, int Dy, Act2D p1_dst, bool prologue, float* sm,
+                                   const short* live, int n_live) {
+  for (int l0 = blockIdx.x; l0 < n_live; l0 += 2 * gridDim.x) {
+    const int l1 = l0 + (int)gridDim.x;
+    const bool two = l1 < n_live;
+    int b[2] = {RETIRE ? (int)live[l0] : l0, RETIRE ? (two ? (int)live[l1] : 0) : l1};
     if (p.tc) {
-      if (b[1] < p.B) frame_item<2, true>(p, b, t, y, Dy, p1_dst, prologue, sm);
+      if (two) frame_item<2, true>(p, b, t, y, Dy, p1_dst, prologue, sm);
       else frame_item<1, true>(p, b, t, y, Dy, p1_dst, prologue, sm);
     } else {
-      if (b[1] < p.B) frame_item<2, false>(p, b, t, y, Dy, p1_dst, prologue, sm);
+      if (two) frame_item<2, false>(p, b, t, y, Dy, p1_dst, prologue, sm);
       else frame_item<1, false>(p, b, t, y, Dy, p1_dst, prologue, sm);
     }
   }
 }
 
+// RETIRE: the per-row stop rule retires stopped rows from the row-split phases (a separate instantiation, so that the
+// indirection through the live-row list costs the other stop rules nothing)
+template <bool RETIRE>
 __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_constant__ DecParams p) {
   extern __shared__ __align__(16) float smem[];
   float* scratch = smem;                  // SCRATCH_FLOATS: reduction / row-phase scratch
   float* wres = smem + p.scratch_floats;  // resident LSTM tiles / tensor-core weight images
   __shared__ int s_stopped[MAX_B];
+  // Row retirement (per-row stop rule): s_live[0 .. s_nlive) = the rows that have not stopped, in row order.  The
+  // row-split phases (query layer + attention, frame phase) hand out live rows only, so a stopped row costs nothing there
+  // and the live ones spread over all CTAs again; the LSTM phases work on 128-row tensor tiles and keep running every
+  // row (a retired row's state simply stops mattering).  Frames after a row's own stop step are not written.
+  __shared__ short s_live[MAX_B];
+  __shared__ int s_nlive, s_cnt[MAX_B / 32];
   GridBarrier bar{p.barrier, 0u};
   const int tid = threadIdx.x;
   const int ld = p.ld;
@@ -531,7 +546,11 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
     load_resident(p.lstm_1, wres);
     load_resident(p.lstm_2, wres);
   }
-  for (int i = tid; i < MAX_B; i += NT) s_stopped[i] = -1;
+  for (int i = tid; i < MAX_B; i += NT) {
+    s_stopped[i] = -1;
+    s_live[i] = (short)i;
+  }
+  if (tid == 0) s_nlive = p.B;
   __syncthreads();
 
   if (p.bench_barriers > 0 && p.prof) {
@@ -569,7 +588,8 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
   };
   // prenet of the <GO> frame -> attention-LSTM input of step 0
   if (p.batched_tail) copy_prenet(0, Act2D{p.att_in[0], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc});
-  else frame_phase(p, 0, nullptr, 0, Act2D{p.att_in[0], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc}, true, scratch);
+  else frame_phase<RETIRE>(p, 0, nullptr, 0, Act2D{p.att_in[0], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc}, true, scratch, s_live, p.B);
+  auto row_of = [&](int li) { return RETIRE ? (int)s_live[li] : li; };
   if (p.tc) {
     tc::fence_proxy_async();
     bar.sync([&] { tc_prefill(p.tc_a, p.maps, p.RB, tcs); });
@@ -614,9 +634,9 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
     if (p.cl > 1) {
       // cluster-split form (fp32 SIMT mode only): item = cluster index, every CTA of the cluster works on it
       const float* qsrc = p.l1_in[cur];  // feature-major [A][ld]
-      const int n_items = p.B * p.n_mech, ncl = gridDim.x / p.cl, crank = (int)cluster_ctarank();
+      const int n_items = (RETIRE ? s_nlive : p.B) * p.n_mech, ncl = gridDim.x / p.cl, crank = (int)cluster_ctarank();
       for (int item = blockIdx.x / p.cl; item < n_items; item += ncl) {
-        const int mi = item % p.n_mech, b = item / p.n_mech;
+        const int mi = item % p.n_mech, b = row_of(item / p.n_mech);
         const bool split = p.cl_split[mi] != 0;
         AttMech m = p.mech[mi];
         const int coff = mi ? p.mech[0].Dv : 0;
@@ -658,7 +678,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
       }
     } else {
       const float* qsrc = p.tc ? p.qfm : p.l1_in[cur];  // feature-major [A][ld]
-      const int n_items = p.B * p.n_mech;
+      const int n_items = (RETIRE ? s_nlive : p.B) * p.n_mech;  // item i = (live row i / n_mech, mechanism i % n_mech)
       for (int i0 = blockIdx.x; i0 < n_items; i0 += 2 * gridDim.x) {
         const int i1 = i0 + gridDim.x;
         const int nit = i1 < n_items ? 2 : 1;
@@ -675,7 +695,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
           float* outs = xs + al4(2 * p.A);     // [2][Np]
           float* part = outs + 2 * dq.Np;      // [2 * NT * 8]
           int rows[2];
-          for (int r = 0; r < nq; ++r) rows[r] = items[q0 + r] / p.n_mech;
+          for (int r = 0; r < nq; ++r) rows[r] = row_of(items[q0 + r] / p.n_mech);
           for (int i = tid; i < nq * p.A; i += NT) {
             const int r = i / p.A, k = i - r * p.A;
             xs[r * p.A + k] = __ldcg(qsrc + (size_t)k * ld + rows[r]);
@@ -720,15 +740,17 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
           const int gid = tid / (NT / 2);
           AttMech m;
           setup(items[gid], m);
-          const int b = items[gid] / p.n_mech;
-          attention_item<NT / 2>(m, b, t, p.T, (int)p.lengths[b], scratch + gid * p.att_row_floats, gid);
+          const int b = row_of(items[gid] / p.n_mech);
+          if (RETIRE) attention_item_inl<NT / 2>(m, b, t, p.T, (int)p.lengths[b], scratch + gid * p.att_row_floats, gid);
+          else attention_item<NT / 2>(m, b, t, p.T, (int)p.lengths[b], scratch + gid * p.att_row_floats, gid);
           __syncthreads();  // both halves are done with the scratch
         } else {
           for (int q = 0; q < nit; ++q) {
             AttMech m;
             setup(items[q], m);
-            const int b = items[q] / p.n_mech;
-            attention_item<NT>(m, b, t, p.T, (int)p.lengths[b], scratch);
+            const int b = row_of(items[q] / p.n_mech);
+            if (RETIRE) attention_item_inl<NT>(m, b, t, p.T, (int)p.lengths[b], scratch);
+            else attention_item<NT>(m, b, t, p.T, (int)p.lengths[b], scratch);
           }
         }
       }
@@ -802,7 +824,8 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
                        PrenetTcEpi{p.pre1.bias, p.P1, p.B, Act2D{p.att_in[nxt], 1, p.Ka_pad, 1}});
       } else {
         // ---- L+A+B: frame + stop projection of step t, fed-back frame, prenet of step t+1 (row split) ----
-        frame_phase(p, t, y, p.outp.K, Act2D{p.att_in[nxt], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc}, false, scratch);
+        frame_phase<RETIRE>(p, t, y, p.outp.K, Act2D{p.att_in[nxt], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc}, false, scratch,
+                            s_live, RETIRE ? s_nlive : p.B);
       }
       if (p.tc && t + 1 < p.max_steps) phase_end(&p.tc_a, p.maps + nxt);
       else phase_end();
@@ -824,6 +847,24 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
       if (p.stop_mode == SAT_STOP_ALL_ROWS ? all_term : all_stopped) {
         ++t;
         break;
+      }
+      if (RETIRE) {
+        // compact the rows that are still decoding (every CTA derives the same list from the same stop logits)
+        const bool alive = tid < p.B && s_stopped[tid] < 0;
+        const unsigned bal = __ballot_sync(0xffffffffu, alive);
+        if (tid < MAX_B && (tid & 31) == 0) s_cnt[tid >> 5] = __popc(bal);
+        __syncthreads();
+        if (alive) {
+          int off = __popc(bal & ((1u << (tid & 31)) - 1u));
+          for (int w = 0; w < (tid >> 5); ++w) off += s_cnt[w];
+          s_live[off] = (short)tid;
+        }
+        if (tid == 0) {
+          int n = 0;
+          for (int w = 0; w < MAX_B / 32; ++w) n += s_cnt[w];
+          s_nlive = n;
+        }
+        __syncthreads();
       }
     }
   }

@@ -69,9 +69,12 @@ class DecoderHandle:
         io.forced_alignment = int(forced_alignment)
         io.feed_mode, io.stop_mode, io.max_steps, io.min_iters = feed_mode, stop_mode, max_steps, min_iters
         S = max_steps
-        mel = torch.empty((B, S * r, M), device=dev, dtype=torch.float32)
-        stop = torch.empty((B, S), device=dev, dtype=torch.float32)
-        aligns = [torch.empty((B, S, T), device=dev, dtype=torch.float32) if want_alignments else None
+        # per-row stop rule: a row leaves the row-split phases at its own stop step, nothing is written for it
+        # afterwards -- the buffers start at zero so that those frames are well defined
+        new = torch.zeros if stop_mode == _lib.STOP_PER_ROW else torch.empty
+        mel = new((B, S * r, M), device=dev, dtype=torch.float32)
+        stop = new((B, S), device=dev, dtype=torch.float32)
+        aligns = [new((B, S, T), device=dev, dtype=torch.float32) if want_alignments else None
                   for _ in range(self.n_mech)]
         ids = torch.empty((B, S, r), device=dev, dtype=torch.int32) if want_sample_ids else None
         dout = torch.empty((B, S, hp.decoder_out_units), device=dev, dtype=torch.float32) if want_decoder_outputs else None

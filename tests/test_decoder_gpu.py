@@ -217,9 +217,52 @@ def test_extended_decoder_free_run_stop(stop_mode):
     got = run_cuda(hp, W, mems, lengths, feed_mode=1, stop_mode=1 if stop_mode == "all_rows" else 2, max_steps=40)
     assert got["n_steps"] == ref["n_steps"]
     np.testing.assert_array_equal(got["stop_steps"], ref["stop_steps"])
+    n, r = got["n_steps"], hp.outputs_per_step
+    if stop_mode == "per_row":
+        # a stopped row is retired from the row-split phases: it emits up to its own stop step, zeros afterwards
+        assert len(set(ref["stop_steps"].tolist())) > 1, "rows should stop at different steps"
+        for b, ss in enumerate(ref["stop_steps"]):
+            m = n if ss < 0 else ss + 1
+            assert rel_err(got["mel"][b, :m * r], ref["mel"][b, :m * r]) <= TOL
+            assert rel_err(got["stop"][b, :m], ref["stop"][b, :m]) <= TOL
+            assert rel_err(got["alignments"][0][b, :m], ref["alignments"][0][b, :m]) <= TOL
+            np.testing.assert_array_equal(np.argmax(got["alignments"][0][b, :m], -1), np.argmax(ref["alignments"][0][b, :m], -1))
+            assert not got["mel"][b, m * r:].any() and not got["alignments"][0][b, m:].any()
+        return
     check_close(got, ref)
-    n = got["n_steps"]
     np.testing.assert_array_equal(np.argmax(got["alignments"][0][:, :n], -1), np.argmax(ref["alignments"][0][:, :n], -1))
+
+
+def test_row_retirement_tensor_core_path():
+    """Per-row stop rule at B = 200 (tcgen05 gate GEMMs, paired attention rows): rows stop at spread-out steps, leave the
+    row-split phases, and every row's frames up to its own stop step equal the oracle's; SAT_RETIRE=0 (all rows keep
+    running) gives the same frames there."""
+    hp = small_hp("ljspeech_tacotron")
+    W = sat_b200.init_weights(hp, seed=19, stress=True)
+    W["decoder/stop_token_projection/kernel"] *= 8.0
+    B, T, S = 200, 37, 30
+    mems, lengths, _, _ = decoder_inputs(hp, B, T, 1, seed=19)
+    probe = oracle_decoder(hp, W, mems, lengths, stop_mode="never", max_iters=S)
+    W["decoder/stop_token_projection/bias"] -= np.float32(np.median(probe["stop"][:, 11:, 0].max(axis=1)))
+    ref = oracle_decoder(hp, W, mems, lengths, stop_mode="per_row", max_iters=S)
+    got = run_cuda(hp, W, mems, lengths, feed_mode=1, stop_mode=2, max_steps=S)
+    assert got["tensor_cores"] and got["n_steps"] == ref["n_steps"]
+    stops = ref["stop_steps"]
+    assert 20 < int((stops >= 0).sum()) < B
+    # a stop logit within fp tolerance of 0 cannot be pinned: compare the rows whose decision is clear in the oracle
+    logit = ref["stop"][:, :, 0]
+    scale = np.abs(logit).max()
+    r = hp.outputs_per_step
+    n_checked = 0
+    for b in range(B):
+        m = got["n_steps"] if stops[b] < 0 else stops[b] + 1
+        if np.abs(logit[b, 11:m]).min() < 4 * TOL * scale:
+            continue
+        n_checked += 1
+        assert got["stop_steps"][b] == stops[b]
+        assert rel_err(got["mel"][b, :m * r], ref["mel"][b, :m * r]) <= TOL
+        assert not got["mel"][b, m * r:].any()
+    assert n_checked > B // 2
 
 
 @pytest.mark.parametrize("kind,cumulative,agent", [("location_sensitive", False, False),
