@@ -51,7 +51,8 @@ enum { SAT_FEED_TEACHER = 0,      /* targets[:, t, -M*n_feed:]        helpers.py
 /* stop rule */
 enum { SAT_STOP_FIXED = 0,     /* validation: S = T_dec / r steps          helpers.py:102 */
        SAT_STOP_ALL_ROWS = 1,  /* reduce_all(sigmoid(stop)>.5 & t>10)      helpers.py:156-160 */
-       SAT_STOP_PER_ROW = 2    /* same rule per utterance; run ends when every row stopped */ };
+       SAT_STOP_PER_ROW = 2    /* same rule per utterance; run ends when every row stopped.  A stopped row is retired:
+                                  mel / stop / alignment entries after its own stop step are NOT written */ };
 
 /* named host tensor of the weight blob (names: DESIGN.md "weight blob") */
 typedef struct { const char* name; const float* data; int64_t numel; } sat_tensor;
