@@ -118,8 +118,12 @@ __global__ void __launch_bounds__(MHA_WARPS * 32) mha_attn_kernel(const float* _
 // (V as hi + lo) accumulates in TMEM columns [256, 256 + dh) and is written back as fp32.
 constexpr int MT_THREADS = 128;
 
+// The fp32 Q tile and the K / V blocks of the head arrive by TMA (three un-swizzled boxes of the [B*T, 3D] projection
+// output into a staging area, one mbarrier); the threads then split them into the swizzled fp16 hi / lo operands.
+// use_tma = 0 (staging does not fit next to the operands: wide heads) reads them with plain loads instead.
 __global__ void __launch_bounds__(MT_THREADS, 1)
-mha_tc_kernel(const float* __restrict__ qkv, int T, int Tp, int D, int H, int causal, const long long* __restrict__ lengths,
+mha_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_kv, int use_tma,
+              const float* __restrict__ qkv, int T, int Tp, int D, int H, int causal, const long long* __restrict__ lengths,
               float* __restrict__ ctx, float* __restrict__ probs, int head_major) {
   extern __shared__ __align__(1024) uint8_t mt_smem[];
   uint8_t* base = (uint8_t*)(((uintptr_t)mt_smem + 1023) & ~(uintptr_t)1023);
@@ -131,7 +135,10 @@ mha_tc_kernel(const float* __restrict__ qkv, int T, int Tp, int D, int H, int ca
   uint8_t* Vh = Kl + (size_t)256 * 128;              // nchunk x [dh rows][128 B]
   uint8_t* Vl = Vh + (size_t)nchunk * dh * 128;
   uint8_t* P = (uint8_t*)(((uintptr_t)(Vl + (size_t)nchunk * dh * 128) + 1023) & ~(uintptr_t)1023);  // nchunk x 16 KB
-  __shared__ __align__(8) uint64_t bars[2];
+  float* Qst = (float*)(P + (size_t)nchunk * 16384);  // TMA staging: [128][dh], [Tp][dh], [Tp][dh] fp32
+  float* Kst = Qst + 128 * dh;
+  float* Vst = Kst + (size_t)Tp * dh;
+  __shared__ __align__(8) uint64_t bars[3];
   __shared__ uint32_t tmem_slot;
   const int tid = threadIdx.x, warp = tid >> 5;
   const int b = blockIdx.y / H, h = blockIdx.y % H, q0 = blockIdx.x * 128;
@@ -142,7 +149,15 @@ mha_tc_kernel(const float* __restrict__ qkv, int T, int Tp, int D, int H, int ca
   if (tid == 0) {
     tc::mbar_init(bars, 1);
     tc::mbar_init(bars + 1, 1);
+    tc::mbar_init(bars + 2, 1);
     tc::fence_mbar_init();
+    if (use_tma) {
+      // rows past this utterance (the next one's, or out of bounds = zeros) are masked below like in the plain form
+      tc::mbar_arrive_expect_tx(bars + 2, (uint32_t)((128 + 2 * Tp) * dh * 4));
+      tc::tma_load_2d(Qst, &map_q, bars + 2, 2 * D + h * dh, b * T + q0);
+      tc::tma_load_2d(Kst, &map_kv, bars + 2, h * dh, b * T);
+      tc::tma_load_2d(Vst, &map_kv, bars + 2, D + h * dh, b * T);
+    }
   }
   if (warp == 0) tc::tmem_alloc(&tmem_slot, 512);
   auto split_store = [](uint8_t* hi, uint8_t* lo, uint32_t off, float x) {
@@ -150,17 +165,22 @@ mha_tc_kernel(const float* __restrict__ qkv, int T, int Tp, int D, int H, int ca
     *(__half*)(hi + off) = xh;
     *(__half*)(lo + off) = tc::to_f16(x - __half2float(xh));
   };
+  if (use_tma) {
+    __syncthreads();  // the barrier initialisation is visible to the waiting threads
+    tc::mbar_wait(bars + 2, 0);
+  }
   for (int i = tid; i < 128 * dh; i += MT_THREADS) {
     const int r = i / dh, d = i - r * dh;
-    const float x = (q0 + r < T) ? __ldg(src + (size_t)(q0 + r) * ld + 2 * D + d) * scale : 0.f;
+    const float x = (q0 + r < T) ? (use_tma ? Qst[i] : __ldg(src + (size_t)(q0 + r) * ld + 2 * D + d)) * scale : 0.f;
     split_store(Qh, Ql, tc::sw128_offset16(r, d), x);
   }
   for (int i = tid; i < Tp * dh; i += MT_THREADS) {
     const int j = i / dh, d = i - j * dh;
     const bool ok = j < T;
-    split_store(Kh, Kl, tc::sw128_offset16(j, d), ok ? __ldg(src + (size_t)j * ld + d) : 0.f);
+    split_store(Kh, Kl, tc::sw128_offset16(j, d), ok ? (use_tma ? Kst[i] : __ldg(src + (size_t)j * ld + d)) : 0.f);
     // V^T: row d, key j -> chunk j / 64
-    split_store(Vh, Vl, (uint32_t)((j >> 6) * dh * 128) + tc::sw128_offset16(d, j & 63), ok ? __ldg(src + (size_t)j * ld + D + d) : 0.f);
+    split_store(Vh, Vl, (uint32_t)((j >> 6) * dh * 128) + tc::sw128_offset16(d, j & 63),
+                ok ? (use_tma ? Vst[i] : __ldg(src + (size_t)j * ld + D + d)) : 0.f);
   }
   tc::fence_proxy_async();
   tc::tc_fence_before();
@@ -541,11 +561,22 @@ static void scaled_dot_core(const MhaDev& m, const float* qkv, int B, int T, int
   const int dh = m.D / m.H, Tpad = (T + 3) & ~3;
   if (mha_tc_ok(T, m.D, m.H)) {
     const int Tp = (T + 15) & ~15;
-    const size_t smem = mha_tc_smem_bytes(Tp, dh);
+    size_t smem = mha_tc_smem_bytes(Tp, dh);
+    const size_t staging = (size_t)(128 + 2 * Tp) * dh * sizeof(float);
+    int use_tma = smem + staging <= 200 * 1024 && (((uintptr_t)qkv) & 15) == 0;
+    if (const char* e = getenv("SAT_MHA_TMA")) use_tma = use_tma && atoi(e) != 0;
+    CUtensorMap map_q, map_kv;
+    memset(&map_q, 0, sizeof(map_q));
+    memset(&map_kv, 0, sizeof(map_kv));
+    if (use_tma) {
+      smem += staging;
+      make_tensor_map_2d_plain(&map_q, qkv, (uint64_t)B * T, (uint64_t)3 * m.D, (uint64_t)3 * m.D, (uint32_t)dh, 128);
+      make_tensor_map_2d_plain(&map_kv, qkv, (uint64_t)B * T, (uint64_t)3 * m.D, (uint64_t)3 * m.D, (uint32_t)dh, (uint32_t)Tp);
+    }
     SAT_CUDA(cudaFuncSetAttribute(mha_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid((unsigned)ceil_div(T, 128), (unsigned)(B * m.H));
-    mha_tc_kernel<<<grid, MT_THREADS, smem, st>>>(qkv, T, Tp, m.D, m.H, causal, (const long long*)pad_lengths, ctx, probs,
-                                                  head_major);
+    mha_tc_kernel<<<grid, MT_THREADS, smem, st>>>(map_q, map_kv, use_tma, qkv, T, Tp, m.D, m.H, causal,
+                                                  (const long long*)pad_lengths, ctx, probs, head_major);
     count_launch();
     check_launch("mha_tc_kernel");
     return;

@@ -175,6 +175,9 @@ __device__ __forceinline__ uint32_t sw128_offset16(int n, int kk) {
 // 128-byte swizzle (tc_host.cu)
 void make_tensor_map_2d(CUtensorMap* map, const float* base, uint64_t rows, uint64_t cols, uint64_t row_stride_floats,
                         uint32_t box_rows);
+// un-swizzled fp32 box {box_cols, box_rows} (box_cols * 4 a multiple of 16 bytes): staging loads
+void make_tensor_map_2d_plain(CUtensorMap* map, const float* base, uint64_t rows, uint64_t cols, uint64_t row_stride_floats,
+                              uint32_t box_cols, uint32_t box_rows);
 // the same over a row-major fp16 matrix, box = {64 halves, box_rows}
 void make_tensor_map_2d_f16(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t row_stride_elems,
                             uint32_t box_rows);

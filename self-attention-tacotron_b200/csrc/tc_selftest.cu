@@ -37,6 +37,19 @@ void encode_2d(CUtensorMap* map, CUtensorMapDataType dt, size_t elem, uint32_t b
 }
 }  // namespace
 
+// un-swizzled fp32 box {box_cols, box_rows}: a staging load (the consumer converts / re-lays-out in shared memory)
+void make_tensor_map_2d_plain(CUtensorMap* map, const float* base, uint64_t rows, uint64_t cols, uint64_t row_stride_floats,
+                              uint32_t box_cols, uint32_t box_rows) {
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {row_stride_floats * 4};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = encode_tiled()(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) fail(SAT_ECUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+}
+
 void make_tensor_map_2d(CUtensorMap* map, const float* base, uint64_t rows, uint64_t cols, uint64_t row_stride_floats,
                         uint32_t box_rows) {
   encode_2d(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, tc::CHUNK_K, base, rows, cols, row_stride_floats, box_rows);
