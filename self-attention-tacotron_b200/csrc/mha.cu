@@ -300,8 +300,12 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__
 constexpr int MF_THREADS = 128;
 constexpr int MF_KEYS = 64;
 
+// use_tma: the fp32 Q tile and every 64-key chunk of K (and V in pass 2) arrive by TMA (un-swizzled boxes of the
+// [B*T, 3D] projection output) in a staging area; the box of the NEXT chunk is requested as soon as the threads have
+// split the current one into the fp16 hi / lo operands, so the load runs under the chunk's MMAs and softmax.
 __global__ void __launch_bounds__(MF_THREADS, 1)
-mha_flash_tc_kernel(const float* __restrict__ qkv, int T, int D, int H, int causal, const long long* __restrict__ lengths,
+mha_flash_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_kv, int use_tma,
+                    const float* __restrict__ qkv, int T, int D, int H, int causal, const long long* __restrict__ lengths,
                     float* __restrict__ ctx, float* __restrict__ probs, int head_major) {
   extern __shared__ __align__(1024) uint8_t mf_smem[];
   uint8_t* base = (uint8_t*)(((uintptr_t)mf_smem + 1023) & ~(uintptr_t)1023);
@@ -313,7 +317,9 @@ mha_flash_tc_kernel(const float* __restrict__ qkv, int T, int D, int H, int caus
   uint8_t* Vh = Kl + (size_t)nkc * 8192;       // V^T: [dh rows][64 keys] (16 KB reserved)
   uint8_t* Vl = Vh + 16384;
   uint8_t* P = Vl + 16384;                     // [128 rows][64 keys]
-  __shared__ __align__(8) uint64_t bars[2];
+  float* stg = (float*)(P + 16384);            // TMA staging: Q [128][dh], then K [64][dh] | V [64][dh] per chunk (fp32)
+  __shared__ __align__(8) uint64_t bars[3];
+  uint32_t phs = 0;
   __shared__ uint32_t tmem_slot;
   const int tid = threadIdx.x, warp = tid >> 5;
   const int b = blockIdx.y / H, h = blockIdx.y % H, q0 = blockIdx.x * 128;
@@ -324,7 +330,12 @@ mha_flash_tc_kernel(const float* __restrict__ qkv, int T, int D, int H, int caus
   if (tid == 0) {
     tc::mbar_init(bars, 1);
     tc::mbar_init(bars + 1, 1);
+    tc::mbar_init(bars + 2, 1);
     tc::fence_mbar_init();
+    if (use_tma) {
+      tc::mbar_arrive_expect_tx(bars + 2, (uint32_t)(128 * dh * 4));
+      tc::tma_load_2d(stg, &map_q, bars + 2, 2 * D + h * dh, b * T + q0);
+    }
   }
   if (warp == 0) tc::tmem_alloc(&tmem_slot, 256);
   auto split_store = [](uint8_t* hi, uint8_t* lo, uint32_t off, float x) {
@@ -332,9 +343,14 @@ mha_flash_tc_kernel(const float* __restrict__ qkv, int T, int D, int H, int caus
     *(__half*)(hi + off) = xh;
     *(__half*)(lo + off) = tc::to_f16(x - __half2float(xh));
   };
+  if (use_tma) {
+    __syncthreads();  // the barrier initialisation is visible to the waiting threads
+    tc::mbar_wait(bars + 2, phs);
+    phs ^= 1;
+  }
   for (int i = tid; i < 128 * dh; i += MF_THREADS) {
     const int r = i / dh, d = i - r * dh;
-    const float x = (q0 + r < T) ? __ldg(src + (size_t)(q0 + r) * ld + 2 * D + d) * scale : 0.f;
+    const float x = (q0 + r < T) ? (use_tma ? stg[i] : __ldg(src + (size_t)(q0 + r) * ld + 2 * D + d)) * scale : 0.f;
     split_store(Qh, Ql, (uint32_t)((d >> 6) * 16384) + tc::sw128_offset16(r, d & 63), x);
   }
   tc::fence_proxy_async();
@@ -352,17 +368,35 @@ mha_flash_tc_kernel(const float* __restrict__ qkv, int T, int D, int H, int caus
   const int nchunks = (kmax + MF_KEYS - 1) / MF_KEYS;
   uint32_t ph0 = 0, ph1 = 0;
 
+  // thread 0: request the staging boxes of chunk c (rows past the utterance are masked when they are split)
+  auto request = [&](int c, bool with_values) {
+    tc::mbar_arrive_expect_tx(bars + 2, (uint32_t)((with_values ? 2 : 1) * MF_KEYS * dh * 4));
+    tc::tma_load_2d(stg, &map_kv, bars + 2, h * dh, b * T + c * MF_KEYS);
+    if (with_values) tc::tma_load_2d(stg + MF_KEYS * dh, &map_kv, bars + 2, D + h * dh, b * T + c * MF_KEYS);
+  };
+  if (use_tma && tid == 0) request(0, false);  // (the Q tile has been split: the staging area is free)
   auto load_keys = [&](int c, bool with_values) {
+    if (use_tma) {
+      tc::mbar_wait(bars + 2, phs);
+      phs ^= 1;
+    }
     for (int i = tid; i < MF_KEYS * dh; i += MF_THREADS) {
       const int j = i / dh, d = i - j * dh, kj = c * MF_KEYS + j;
       const bool ok = kj < T;
-      split_store(Kh, Kl, (uint32_t)((d >> 6) * 8192) + tc::sw128_offset16(j, d & 63), ok ? __ldg(src + (size_t)kj * ld + d) : 0.f);
-      if (with_values) split_store(Vh, Vl, tc::sw128_offset16(d, j), ok ? __ldg(src + (size_t)kj * ld + D + d) : 0.f);
+      split_store(Kh, Kl, (uint32_t)((d >> 6) * 8192) + tc::sw128_offset16(j, d & 63),
+                  ok ? (use_tma ? stg[i] : __ldg(src + (size_t)kj * ld + d)) : 0.f);
+      if (with_values)
+        split_store(Vh, Vl, tc::sw128_offset16(d, j), ok ? (use_tma ? stg[MF_KEYS * dh + i] : __ldg(src + (size_t)kj * ld + D + d)) : 0.f);
     }
     tc::fence_proxy_async();
     tc::tc_fence_before();
     __syncthreads();
     tc::tc_fence_after();
+    if (use_tma && tid == 0) {
+      // the staging area has been read by every thread: the next chunk's boxes travel under this chunk's MMAs / softmax
+      if (c + 1 < nchunks) request(c + 1, with_values);
+      else if (!with_values) request(0, true);
+    }
   };
   auto scores = [&]() {  // S[128 x 64] = Q K_c^T into TMEM columns [0, 64)
     if (tid == 0) {
@@ -582,11 +616,22 @@ static void scaled_dot_core(const MhaDev& m, const float* qkv, int B, int T, int
     return;
   }
   if (mha_flash_ok(T, m.D, m.H)) {
-    const size_t smem = mha_flash_smem_bytes(dh);
+    size_t smem = mha_flash_smem_bytes(dh);
+    const size_t staging = (size_t)128 * dh * sizeof(float);  // Q tile = K + V chunk
+    int use_tma = smem + staging <= 220 * 1024 && (((uintptr_t)qkv) & 15) == 0;
+    if (const char* e = getenv("SAT_MHA_TMA")) use_tma = use_tma && atoi(e) != 0;
+    CUtensorMap map_q, map_kv;
+    memset(&map_q, 0, sizeof(map_q));
+    memset(&map_kv, 0, sizeof(map_kv));
+    if (use_tma) {
+      smem += staging;
+      make_tensor_map_2d_plain(&map_q, qkv, (uint64_t)B * T, (uint64_t)3 * m.D, (uint64_t)3 * m.D, (uint32_t)dh, 128);
+      make_tensor_map_2d_plain(&map_kv, qkv, (uint64_t)B * T, (uint64_t)3 * m.D, (uint64_t)3 * m.D, (uint32_t)dh, MF_KEYS);
+    }
     SAT_CUDA(cudaFuncSetAttribute(mha_flash_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid((unsigned)ceil_div(T, 128), (unsigned)(B * m.H));
-    mha_flash_tc_kernel<<<grid, MF_THREADS, smem, st>>>(qkv, T, m.D, m.H, causal, (const long long*)pad_lengths, ctx, probs,
-                                                        head_major);
+    mha_flash_tc_kernel<<<grid, MF_THREADS, smem, st>>>(map_q, map_kv, use_tma, qkv, T, m.D, m.H, causal,
+                                                        (const long long*)pad_lengths, ctx, probs, head_major);
     count_launch();
     check_launch("mha_flash_tc_kernel");
     return;
