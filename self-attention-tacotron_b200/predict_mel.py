@@ -65,6 +65,9 @@ def _pad_batch(utts, hp, device):
             torch.from_numpy(lengths).pin_memory().to(device, non_blocking=True), target, spk)
 
 
+COPY_THREADS = max(2, min(8, (os.cpu_count() or 8) // 2))  # host threads that copy results out of the pinned buffers
+
+
 class _HostSlot:
     """Pinned host buffers for the results of one batch, reused every other batch (two slots = the read-back of batch
     i overlaps the compute of batch i+1)."""
@@ -114,7 +117,7 @@ def predict(hparams, weights, utterances, output_dir=None, batch_size=None, devi
                            bucket_width=hparams.batch_bucket_width)
     copy_stream = torch.cuda.Stream(device=device)
     slots = [_HostSlot(), _HostSlot()]
-    pool = ThreadPoolExecutor(max_workers=4)
+    pool = ThreadPoolExecutor(max_workers=COPY_THREADS)
 
     def launch(i, idxs):
         utts = [utterances[j] for j in idxs]
@@ -162,7 +165,12 @@ def predict(hparams, weights, utterances, output_dir=None, batch_size=None, devi
         for k in ("alignment", "alignment2"):
             if host.get(k) is not None:
                 jobs[k] = host[k].numpy()[:, :n_steps]  # [B, S, T]
-        copies = dict(zip(jobs, pool.map(np.array, jobs.values())))
+        copies = {k: np.empty(v.shape, dtype=v.dtype) for k, v in jobs.items()}
+        parts = []
+        for k, v in jobs.items():  # row blocks of every tensor, so that all pool threads fault in and fill pages
+            step = max(1, -(-v.shape[0] // COPY_THREADS))
+            parts += [(copies[k][a:a + step], v[a:a + step]) for a in range(0, v.shape[0], step)]
+        list(pool.map(lambda dv: np.copyto(dv[0], dv[1]), parts))
         mel, post = copies["mel"], copies.get("post")
         aligns = [copies[k] for k in ("alignment", "alignment2") if k in copies]
         for i, u in enumerate(utts):
