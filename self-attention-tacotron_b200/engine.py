@@ -28,7 +28,7 @@ class DecoderHandle:
         self.n_mech = 1 if hp.decoder == "ExtendedDecoder" else 2
 
     def __del__(self):
-        if getattr(self, "_h", None) and self._h.value:
+        if getattr(self, "_h", None) and self._h.value and lib is not None:  # (module globals are gone at interpreter exit)
             lib().sat_decoder_destroy(self._h)
             self._h = C.c_void_p()
 
@@ -134,7 +134,7 @@ class EncoderHandle:
         self.self_attention = hp.encoder == "SelfAttentionCBHGEncoder"
 
     def __del__(self):
-        if getattr(self, "_h", None) and self._h.value:
+        if getattr(self, "_h", None) and self._h.value and lib is not None:  # (module globals are gone at interpreter exit)
             lib().sat_encoder_destroy(self._h)
             self._h = C.c_void_p()
 
@@ -195,7 +195,7 @@ class PostnetHandle:
         check(lib().sat_postnet_create(C.byref(s), arr, n, C.byref(self._h)))
 
     def __del__(self):
-        if getattr(self, "_h", None) and self._h.value:
+        if getattr(self, "_h", None) and self._h.value and lib is not None:  # (module globals are gone at interpreter exit)
             lib().sat_postnet_destroy(self._h)
             self._h = C.c_void_p()
 
