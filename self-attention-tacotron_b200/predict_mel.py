@@ -81,7 +81,7 @@ class _HostSlot:
         n = dev_tensor.numel()
         buf = self.bufs.get(name)
         if buf is None or buf.numel() < n or buf.dtype != dev_tensor.dtype:
-            buf = torch.empty(max(n, 1), dtype=dev_tensor.dtype).pin_memory()
+            buf = torch.empty(max(n, 1), dtype=dev_tensor.dtype, pin_memory=True)
             self.bufs[name] = buf
         host = buf[:n].view(dev_tensor.shape)
         host.copy_(dev_tensor, non_blocking=True)
@@ -89,7 +89,7 @@ class _HostSlot:
 
 
 def predict(hparams, weights, utterances, output_dir=None, batch_size=None, device=None, rank=0, world_size=1,
-            mode="free_run", model=None, batch_hook=None):
+            mode="free_run", model=None, batch_hook=None, pinned_results=False):
     """Synthesise ``utterances`` (list of Utterance) -> list[PredictedMel] for the ones this rank owns.
 
     mode: 'free_run' (stop-token inference, PREDICT), 'validation' / 'teacher_forced' (EVAL forms).
@@ -98,7 +98,13 @@ def predict(hparams, weights, utterances, output_dir=None, batch_size=None, devi
     Batches are pipelined: the results of batch i (mel, post-net mel, stop steps, alignment histories) are read back
     into pinned host memory on a copy stream while batch i+1 is padded, uploaded and computed; slicing per utterance
     and the file writes of batch i happen on the host during that compute.  ``batch_hook(i)`` (optional) runs on the
-    compute stream before batch i is launched (bench.py flushes L2 there)."""
+    compute stream before batch i is launched (bench.py flushes L2 there).
+
+    ``pinned_results``: False (default) -- two pinned buffer sets are reused and every batch's results are copied out
+    of them into ordinary arrays (host threads, in row blocks); right for a one-shot run that keeps all its results.
+    True -- every batch gets its own pinned tensors and the returned arrays are VIEWS of them (no second host copy);
+    right for a serving loop that drops results after use: torch's caching host allocator then recycles the blocks,
+    whereas a caller that accumulates results pays a cudaHostAlloc (~80 ms per 184 MB) per batch."""
     device = device or torch.device("cuda", torch.cuda.current_device())
     if device.type != "cuda":
         raise RuntimeError("predict_mel runs on CUDA devices only (no CPU fallback)")
@@ -131,7 +137,7 @@ def predict(hparams, weights, utterances, output_dir=None, batch_size=None, devi
                             is_validation=mode != "free_run", teacher_forcing=mode == "teacher_forced")
         done = torch.cuda.Event()
         done.record()
-        slot = slots[i % 2]
+        slot = _HostSlot() if pinned_results else slots[i % 2]
         host = {}
         with torch.cuda.stream(copy_stream):
             copy_stream.wait_event(done)
@@ -160,17 +166,21 @@ def predict(hparams, weights, utterances, output_dir=None, batch_size=None, devi
         # batch then share these arrays as views -- 256 separate copies cost 3x as much in page faults
         # (NumPy copies release the GIL: the tensors are copied side by side on a small thread pool)
         jobs = {"mel": host["mel"].numpy()[:, :n_steps * r]}
+        views = pinned_results
         if host.get("mel_postnet") is not None:
             jobs["post"] = host["mel_postnet"].numpy()[:, :n_steps * r]
         for k in ("alignment", "alignment2"):
             if host.get(k) is not None:
                 jobs[k] = host[k].numpy()[:, :n_steps]  # [B, S, T]
-        copies = {k: np.empty(v.shape, dtype=v.dtype) for k, v in jobs.items()}
-        parts = []
-        for k, v in jobs.items():  # row blocks of every tensor, so that all pool threads fault in and fill pages
-            step = max(1, -(-v.shape[0] // COPY_THREADS))
-            parts += [(copies[k][a:a + step], v[a:a + step]) for a in range(0, v.shape[0], step)]
-        list(pool.map(lambda dv: np.copyto(dv[0], dv[1]), parts))
+        if views:
+            copies = jobs  # the arrays keep the batch's pinned tensors alive
+        else:
+            copies = {k: np.empty(v.shape, dtype=v.dtype) for k, v in jobs.items()}
+            parts = []
+            for k, v in jobs.items():  # row blocks of every tensor, so that all pool threads fault in and fill pages
+                step = max(1, -(-v.shape[0] // COPY_THREADS))
+                parts += [(copies[k][a:a + step], v[a:a + step]) for a in range(0, v.shape[0], step)]
+            list(pool.map(lambda dv: np.copyto(dv[0], dv[1]), parts))
         mel, post = copies["mel"], copies.get("post")
         aligns = [copies[k] for k in ("alignment", "alignment2") if k in copies]
         for i, u in enumerate(utts):

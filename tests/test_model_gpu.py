@@ -132,6 +132,11 @@ def test_predict_mel_free_run_writes_mfbsp(tmp_path):
         np.testing.assert_array_equal(p.mel, v.predicted_mel)
         np.testing.assert_array_equal(p.source, utts[i].source)
     assert len(set(stops)) > 1, "the utterances should stop at different steps"
+    # serving-loop form: results as views of per-batch pinned tensors -- the same numbers
+    res2 = predict(hp, W, utts, batch_size=8, pinned_results=True)
+    for a, b in zip(res, res2):
+        np.testing.assert_array_equal(a.predicted_mel, b.predicted_mel)
+        np.testing.assert_array_equal(a.alignment, b.alignment)
 
 
 def test_predict_mel_from_reference_tfrecords(tmp_path):
