@@ -423,7 +423,7 @@ def run_ours(args, rank, world, local_rank):
     # reference's batch_size=1 predict); frames are counted as returned.
     from sat_b200.predict_mel import predict, Utterance
     model = tacotron_model_factory(hp, W)
-    k2 = max(2, min(args.steps, 5))
+    k2 = max(2, min(args.steps, 8))
     utts = [Utterance(b + j * B, f"u{b + j * B}", ids_np[b, :len_np[b]]) for j in range(k2) for b in range(B)]
     h2d = [0]
 

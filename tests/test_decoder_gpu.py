@@ -117,6 +117,24 @@ def test_cluster_split_attention_rows(name, B, T, S, mode, monkeypatch):
     print("cluster", got["cluster"], name, B, T, {k: rel_err(got[k], ref[k]) for k in ("mel", "stop")})
 
 
+@pytest.mark.parametrize("B,T,want", [(6, 400, "2"), (4, 600, None), (3, 1000, None), (40, 90, None), (7, 64, "2")])
+def test_cluster_split_edge_shapes(B, T, want, monkeypatch):
+    """Cluster size 2 (SAT_CLUSTER=2), long memories (T_enc = 400 splits; from T_enc ~ 600 on the row's shared-memory
+    plan no longer fits behind the query-layer arrays -> one CTA per row), and a batch too large for any split
+    (B x mechanisms x 2 > SM count)."""
+    if want:
+        monkeypatch.setenv("SAT_CLUSTER", want)
+    hp = small_hp("ljspeech_self_attention")
+    W = sat_b200.init_weights(hp, seed=23, stress=True)
+    mems, lengths, target, _ = decoder_inputs(hp, B, T, 5, seed=23)
+    ref = oracle_decoder(hp, W, mems, lengths, target=target, is_validation=True, teacher_forcing=True)
+    got = run_cuda(hp, W, mems, lengths, target=target, feed_mode=0, stop_mode=0, max_steps=5)
+    print("cluster size", got["cluster"], "for B, T =", B, T)
+    if want:
+        assert got["cluster"] == int(want)
+    check_close(got, ref)
+
+
 @pytest.mark.parametrize("B", [130, 256])
 def test_extended_decoder_two_row_groups(B):
     hp = small_hp("ljspeech_tacotron", **SMALL)
