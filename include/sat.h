@@ -148,6 +148,15 @@ typedef struct {
 
 int sat_decoder_create(const sat_hparams* hp, const sat_tensor* weights, int32_t n_weights, sat_decoder** out);
 int sat_decoder_run(sat_decoder* h, const sat_decoder_io* io, void* stream);
+/* One decoder step with the recurrent state kept in the handle -- the RNN-cell contract of the reference
+ * (`cell(inputs, state) -> (output, new_state)`: modules/rnn_wrappers.py:74-124,210-214, tacotron2 DecoderRNNV2 /
+ * AttentionRNN) for debugging and step-by-step parity.  `io` describes the WHOLE run exactly as for sat_decoder_run
+ * (buffers sized for max_steps); the call executes step `step` only and writes its frames, stop logit and alignments
+ * at position `step` of those buffers.  step 0 initialises the state; step k > 0 must follow step k - 1 of the same
+ * run on the same handle (SAT_EINVAL otherwise).  n_steps receives step + 1; `finished` (device int32, may be null)
+ * receives 1 if the stop rule (io->stop_mode) ended the run at this step, else 0.  Runs the fp32 form at every batch
+ * size (the tensor-core form keeps the cell state on the SMs for the length of a launch). */
+int sat_decoder_step(sat_decoder* h, const sat_decoder_io* io, int32_t step, int32_t* finished, void* stream);
 /* average algorithmic bytes one decoder step moves for the last run (SURVEY.md 8d formula) */
 double sat_decoder_step_bytes(const sat_decoder* h, int32_t B, int32_t T_enc, int32_t avg_cache_len);
 void sat_decoder_destroy(sat_decoder* h);

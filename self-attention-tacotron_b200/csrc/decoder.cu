@@ -188,6 +188,7 @@ struct sat_decoder {
   CUtensorMap hmaps[9];
   CUtensorMap* dmaps = nullptr;  // device copy, 64-byte aligned
   int last_tc = 0, last_cl = 1;
+  int step_next = -1;  // sat_decoder_step: the step the state in the workspace is ready for
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;  // bracket the persistent launch of the last run
   int last_B = 0, last_T = 0, last_S = 0;
   ~sat_decoder() {
@@ -421,9 +422,12 @@ extern "C" double sat_decoder_step_bytes(const sat_decoder* h, int32_t B, int32_
   return w * 4.0 + B * (per_utt + state + io);
 }
 
-extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* stream) {
+// steps [t_begin, t_begin + t_count) of the run `iop` describes; t_count < 0: the whole run
+static int decoder_run_impl(sat_decoder* h, const sat_decoder_io* iop, void* stream, int t_begin, int t_count,
+                            int32_t* finished = nullptr) {
   return guarded([&] {
     SAT_REQUIRE(h && iop, "null argument");
+    const bool stepping = t_count >= 0;
     const sat_decoder_io& io = *iop;
     const sat_hparams& hp = h->hp;
     cudaStream_t st = (cudaStream_t)stream;
@@ -446,7 +450,13 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
     p.P0 = h->P0; p.P1 = h->P1; p.A = A; p.Dd = Dd; p.Dctx = h->Dctx; p.n_mech = h->n_mech;
     p.hops = h->hops; p.heads = hp.decoder_self_attention_num_heads; p.Ds = Ds; p.ms = hp.multi_speaker_prenet;
     p.feed_mode = io.feed_mode; p.stop_mode = io.stop_mode; p.max_steps = S; p.min_iters = io.min_iters;
-    p.retire = io.stop_mode == SAT_STOP_PER_ROW && h->hops == 0;  // (the KV-cached hops walk all rows: SIMT dense phases)
+    p.retire = io.stop_mode == SAT_STOP_PER_ROW && h->hops == 0 && !stepping;  // (the KV-cached hops walk all rows)
+    p.finished = finished;
+    p.t_begin = stepping ? t_begin : 0;
+    p.t_end = stepping ? std::min(S, t_begin + t_count) : S;
+    SAT_REQUIRE(!stepping || (t_begin >= 0 && t_begin < S && t_count >= 1), "step %d is outside [0, max_steps)", t_begin);
+    SAT_REQUIRE(!stepping || t_begin == 0 || (h->step_next == t_begin && h->last_B == B && h->last_T == T && h->last_S == S),
+                "sat_decoder_step: step %d does not continue the handle's run (next step %d)", t_begin, h->step_next);
     if (const char* e = getenv("SAT_RETIRE")) p.retire = p.retire && atoi(e) != 0;
     const void* kernel_fn = p.retire ? (const void*)decoder_persistent_kernel<true> : (const void*)decoder_persistent_kernel<false>;
     p.S_target = io.target_steps; p.Smax = S;
@@ -467,6 +477,7 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
     // ---- tensor-core mode for the gate GEMMs once the batch makes them a real contraction ----
     bool use_tc = B >= 64;
     if (const char* e = getenv("SAT_TC")) use_tc = atoi(e) != 0;
+    if (stepping) use_tc = false;  // the tensor-core form keeps the cell state in shared memory for the length of a launch
     use_tc = use_tc && (A % 4 == 0) && (Dd % 4 == 0);
     const int RB = ceil_div(Bp, TC_M);
     size_t smem_bytes = 0;
@@ -700,9 +711,10 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
       o_vc[i] = take((size_t)B * Ds * S);
     }
     float* ws = h->ws.get<float>(off);
-    SAT_CUDA(cudaMemsetAsync(ws, 0, state_floats * sizeof(float), st));
+    const bool fresh = p.t_begin == 0;  // a continued run keeps the state the previous launch left in the workspace
+    if (fresh) SAT_CUDA(cudaMemsetAsync(ws, 0, state_floats * sizeof(float), st));
     SAT_CUDA(cudaMemsetAsync(h->barrier, 0, sizeof(unsigned), st));
-    SAT_CUDA(cudaMemsetAsync(io.stop_steps, 0xff, sizeof(int32_t) * B, st));
+    if (fresh) SAT_CUDA(cudaMemsetAsync(io.stop_steps, 0xff, sizeof(int32_t) * B, st));
 
     p.xin = ws + o_xin; p.p0 = ws + o_p0; p.p0b = ws + o_p0b;
     p.att_in[0] = ws + o_att0; p.att_in[1] = ws + o_att1;
@@ -775,8 +787,10 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
         m.keys = ws + o_keys[i];
       }
     }
-    init_state_kernel<<<ceil_div(B, 128), 128, 0, st>>>(ws + o_sap[0], ws + o_sap[1], ws + o_su[0], ws + o_su[1], B, T);
-    count_launch();
+    if (fresh) {
+      init_state_kernel<<<ceil_div(B, 128), 128, 0, st>>>(ws + o_sap[0], ws + o_sap[1], ws + o_su[0], ws + o_su[1], B, T);
+      count_launch();
+    }
     for (int i = 0; i < h->hops; ++i) {
       p.hop[i].qkv = h->sa_qkv[i].desc(); p.hop[i].o = h->sa_o[i].desc(); p.hop[i].tr = h->sa_tr[i].desc();
       plan_rows(p.hop[i].qkv, false); plan_rows(p.hop[i].o, false); plan_rows(p.hop[i].tr, false);
@@ -785,7 +799,7 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
     }
 
     // ---- teacher-forced time-batched form: prenet of all steps before the loop, hops + projections after it ----
-    bool tail = io.feed_mode == SAT_FEED_TEACHER && io.stop_mode == SAT_STOP_FIXED;
+    bool tail = io.feed_mode == SAT_FEED_TEACHER && io.stop_mode == SAT_STOP_FIXED && !stepping;
     if (const char* e = getenv("SAT_BATCHED_TAIL")) tail = tail && atoi(e) != 0;
     auto dense_rows = [&](const PackedDense& d, const DenseTc3& t, const float* x, int ldx, size_t rows, int act, float* y,
                           int ldy) {
@@ -867,6 +881,7 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
     }
     SAT_CUDA(cudaEventRecord(h->ev1, st));
     h->last_B = B; h->last_T = T; h->last_S = S;
+    h->step_next = stepping ? p.t_end : -1;
     count_launch();
     if (tail) {
       // decoder self-attention hops as causal time-batched attention, then the frame + stop projection
@@ -895,6 +910,14 @@ extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* 
     }
     check_launch("decoder_persistent_kernel");
   });
+}
+
+extern "C" int sat_decoder_run(sat_decoder* h, const sat_decoder_io* iop, void* stream) {
+  return decoder_run_impl(h, iop, stream, 0, -1);
+}
+
+extern "C" int sat_decoder_step(sat_decoder* h, const sat_decoder_io* iop, int32_t step, int32_t* finished, void* stream) {
+  return decoder_run_impl(h, iop, stream, step, 1, finished);
 }
 
 // cycles per phase accumulated by CTA 0 over all runs since the last reset (debug / profiling aid)

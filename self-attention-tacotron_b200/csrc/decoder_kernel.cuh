@@ -76,6 +76,9 @@ struct DecParams {
   __half *qx, *px, *rx;     // fp16 hi + lo pairs [RB * 128][ld]: attention-LSTM output, LSTM2 output, prenet layer-0 output
   int qx_ld, px_ld, rx_ld;
   int retire;               // per-row stop rule: stopped rows leave the row-split phases (s_live in the kernel)
+  int* finished;            // optional (sat_decoder_step): 1 if the stop rule ended the run inside this launch, else 0
+  int t_begin, t_end;       // decoder steps [t_begin, t_end) of the run (sat_decoder_step: one step per launch, the state
+                            // of the fp32 form lives in the workspace between launches); normally [0, max_steps)
   int cl;                   // cluster size of the launch (1: rows are not split)
   int cl_split[2];          // mechanism i is split over the cluster (else rank 0 takes the whole item)
   const float* cl_wq[2];    // query-layer weights as cl contiguous column slices [cl][A][cl_sw] (fp32)
@@ -547,7 +550,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
     load_resident(p.lstm_2, wres);
   }
   for (int i = tid; i < MAX_B; i += NT) {
-    s_stopped[i] = -1;
+    s_stopped[i] = (p.t_begin > 0 && i < p.B) ? p.stop_steps[i] : -1;  // a continued run keeps its stop decisions
     s_live[i] = (short)i;
   }
   if (tid == 0) s_nlive = p.B;
@@ -587,7 +590,9 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
     }
   };
   // prenet of the <GO> frame -> attention-LSTM input of step 0
-  if (p.batched_tail) copy_prenet(0, Act2D{p.att_in[0], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc});
+  if (p.t_begin > 0) {
+    // continued run: the previous launch left the prenet of this step's input frame in place
+  } else if (p.batched_tail) copy_prenet(0, Act2D{p.att_in[0], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc});
   else frame_phase<RETIRE>(p, 0, nullptr, 0, Act2D{p.att_in[0], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc}, true, scratch, s_live, p.B);
   auto row_of = [&](int li) { return RETIRE ? (int)s_live[li] : li; };
   if (p.tc) {
@@ -597,8 +602,8 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
     bar.sync();
   }
 
-  int t = 0;
-  for (; t < p.max_steps; ++t) {
+  int t = p.t_begin, fired = 0;
+  for (; t < p.t_end; ++t) {
     const int cur = t & 1, nxt = cur ^ 1;
     ph = 0;
     if (p.prof && blockIdx.x == 0 && tid == 0) tprev = clock64();
@@ -846,6 +851,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
       const int all_stopped = __syncthreads_and(stopped ? 1 : 0);
       if (p.stop_mode == SAT_STOP_ALL_ROWS ? all_term : all_stopped) {
         ++t;
+        fired = 1;
         break;
       }
       if (RETIRE) {
@@ -868,7 +874,10 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
       }
     }
   }
-  if (blockIdx.x == 0 && tid == 0) *p.n_steps = t;
+  if (blockIdx.x == 0 && tid == 0) {
+    *p.n_steps = t;
+    if (p.finished) *p.finished = fired;
+  }
   if (p.tc) {
     if (tid == 0) {
       // a stop decision can leave the prefetch for the next step in flight: let it land before the CTA exits

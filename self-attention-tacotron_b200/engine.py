@@ -35,7 +35,7 @@ class DecoderHandle:
     def run(self, memories, lengths, *, target=None, teacher_alignments=None, speaker_embed=None,
             feed_mode, stop_mode, max_steps, forced_alignment=False, min_iters=10,
             want_alignments=True, want_sample_ids=False, want_decoder_outputs=False,
-            want_self_attention_probs=False, stream=None):
+            want_self_attention_probs=False, stream=None, step_by_step=False):
         hp = self.hp
         if not isinstance(memories, (tuple, list)):
             memories = (memories,)
@@ -91,7 +91,15 @@ class DecoderHandle:
             sa_probs = [torch.empty((B, hp.decoder_self_attention_num_heads, S, S), device=dev, dtype=torch.float32)
                         for _ in range(hp.decoder_self_attention_num_hop)]
         io.self_attention_probs = (C.c_void_p * 2)(*[a.data_ptr() for a in sa_probs] + [0] * (2 - len(sa_probs)))
-        check(lib().sat_decoder_run(self._h, C.byref(io), stream_ptr(stream)))
+        if step_by_step:
+            # sat_decoder_step: the same run, one launch per decoder step (state kept in the handle)
+            fin = torch.zeros((1,), device=dev, dtype=torch.int32)
+            for t in range(S):
+                check(lib().sat_decoder_step(self._h, C.byref(io), t, ptr(fin), stream_ptr(stream)))
+                if stop_mode != _lib.STOP_FIXED and int(fin.item()):
+                    break  # the stop rule ended the run at step t
+        else:
+            check(lib().sat_decoder_run(self._h, C.byref(io), stream_ptr(stream)))
         return {"mel": mel, "stop": stop, "alignments": aligns, "sample_ids": ids, "decoder_outputs": dout,
                 "self_attention_probs": sa_probs,
                 "stop_steps": stop_steps, "n_steps": n_steps, "_keep": (memories, lengths, target, tas, speaker_embed)}

@@ -117,6 +117,44 @@ def test_cluster_split_attention_rows(name, B, T, S, mode, monkeypatch):
     print("cluster", got["cluster"], name, B, T, {k: rel_err(got[k], ref[k]) for k in ("mel", "stop")})
 
 
+@pytest.mark.parametrize("name,B,mode", [("ljspeech_tacotron", 5, "free"), ("ljspeech_self_attention", 3, "teacher"),
+                                         ("ljspeech_tacotron", 70, "free_stop")])
+def test_decoder_step_by_step(name, B, mode, monkeypatch):
+    """sat_decoder_step (the RNN-cell contract: one step per call, state kept in the handle) reproduces sat_decoder_run:
+    free run bit for bit in the fp32 form, the teacher-forced run (whose one-launch form batches the tail over time)
+    within the bar; at B = 70 the one-launch form runs the tensor-core gate GEMMs and the stepped one the fp32 form."""
+    hp = small_hp(name, max_iters=40)
+    W = sat_b200.init_weights(hp, seed=27, stress=True)
+    S = 14
+    mems, lengths, target, _ = decoder_inputs(hp, B, 31, S, seed=27)
+    if mode == "teacher":
+        kw = dict(target=target, feed_mode=0, stop_mode=0, max_steps=S)
+        ref = oracle_decoder(hp, W, mems, lengths, target=target, is_validation=True, teacher_forcing=True)
+    elif mode == "free":
+        kw = dict(feed_mode=1, stop_mode=0, max_steps=S)
+        ref = oracle_decoder(hp, W, mems, lengths, max_iters=S, stop_mode="never")
+    else:
+        W["decoder/stop_token_projection/kernel"] *= 8.0
+        probe = oracle_decoder(hp, W, mems, lengths, stop_mode="never", max_iters=40)
+        W["decoder/stop_token_projection/bias"] -= np.float32(np.median(probe["stop"][:, 11:, 0].max(axis=1)))
+        kw = dict(feed_mode=1, stop_mode=2, max_steps=40)
+        ref = oracle_decoder(hp, W, mems, lengths, stop_mode="per_row", max_iters=40)
+    one = run_cuda(hp, W, mems, lengths, **kw)
+    stepped = run_cuda(hp, W, mems, lengths, step_by_step=True, **kw)
+    assert stepped["n_steps"] == one["n_steps"] == ref["n_steps"] and not stepped["tensor_cores"]
+    if mode == "free":
+        np.testing.assert_array_equal(stepped["mel"], one["mel"])
+        np.testing.assert_array_equal(stepped["alignments"][0], one["alignments"][0])
+    if mode == "free_stop":
+        np.testing.assert_array_equal(stepped["stop_steps"], ref["stop_steps"])
+        n, r = stepped["n_steps"], hp.outputs_per_step
+        for b, ss in enumerate(ref["stop_steps"]):  # the stepped form keeps every row running; compare up to its stop
+            m = n if ss < 0 else ss + 1
+            assert rel_err(stepped["mel"][b, :m * r], ref["mel"][b, :m * r]) <= TOL
+    else:
+        check_close(stepped, ref)
+
+
 @pytest.mark.parametrize("B,T,want", [(6, 400, "2"), (4, 600, None), (3, 1000, None), (40, 90, None), (7, 64, "2")])
 def test_cluster_split_edge_shapes(B, T, want, monkeypatch):
     """Cluster size 2 (SAT_CLUSTER=2), long memories (T_enc = 400 splits; from T_enc ~ 600 on the row's shared-memory
