@@ -91,6 +91,13 @@ const char* sat_last_error(void);
 int64_t sat_launch_count(void);
 void sat_launch_count_reset(void);
 
+/* Host helper of the sharded predict path (no reference counterpart: the reference buckets with
+ * tf.data bucket_by_sequence_length, datasets/dataset.py): batch cuts of `n` utterance lengths sorted longest first,
+ * minimising sum over batches of longest * (c0 + c1 * batch size) with at most batch_size utterances per batch.
+ * cut[i] = size of the batch that starts at i in the optimal cutting of lengths[i..n) (follow it from i = 0).  CPU
+ * only; no device work. */
+int sat_bucket_cuts(const int64_t* sorted_lengths, int64_t n, int32_t batch_size, double c0, double c1, int32_t* cut);
+
 /* ---- encoder ---------------------------------------------------------- */
 int sat_encoder_create(const sat_hparams* hp, const sat_tensor* weights, int32_t n_weights, sat_encoder** out);
 /* ids [B,T] int64 (device), lengths [B] int64 (device).

@@ -16,8 +16,9 @@ def run(cfg, B, T, S, feed, reps=3):
     lengths = torch.from_numpy(rng.integers(T * 2 // 3, T + 1, size=B).astype(np.int64)).to(dev)
     target = torch.from_numpy(rng.normal(0, 1, size=(B, S * hp.outputs_per_step, hp.num_mels)).astype(np.float32)).to(dev)
     h = DecoderHandle(hp, W)
-    kw = dict(target=target, feed_mode=feed, stop_mode=0, max_steps=S)
-    h.run(mems, lengths, **kw); torch.cuda.synchronize()
+    kw = dict(target=target, feed_mode=feed, stop_mode=int(os.environ.get("SAT_DEV_STOP", "0")), max_steps=S)
+    o = h.run(mems, lengths, **kw); torch.cuda.synchronize()
+    print("n_steps", int(o["n_steps"].item()), "rows stopped", int((o["stop_steps"] >= 0).sum().item()))
     h.profile(reset=True)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()

@@ -59,6 +59,30 @@ extern "C" const char* sat_last_error(void) { return g_last_error.c_str(); }
 extern "C" int64_t sat_launch_count(void) { return g_launches; }
 extern "C" void sat_launch_count_reset(void) { g_launches = 0; }
 
+// Host-side helper of the sharded path (sharding.make_buckets): cuts of one rank's share, sorted longest first, into
+// batches of at most batch_size utterances minimising sum_batches longest * (c0 + c1 * size) -- an O(n * batch_size)
+// dynamic programme from the back (ties: the smaller batch), written here because it sits in front of the first launch
+// of every predict() call.
+extern "C" int sat_bucket_cuts(const int64_t* sorted_lengths, int64_t n, int32_t batch_size, double c0, double c1,
+                               int32_t* cut) {
+  return guarded([&] {
+    SAT_REQUIRE(n >= 0 && batch_size > 0 && (n == 0 || (sorted_lengths && cut)), "bad argument");
+    std::vector<double> best((size_t)n + 1, 0.0);
+    for (int64_t i = n - 1; i >= 0; --i) {
+      const double L = (double)sorted_lengths[i];
+      const int64_t kmax = std::min<int64_t>(batch_size, n - i);
+      double bc = 0.0;
+      int32_t bk = 0;
+      for (int64_t k = 1; k <= kmax; ++k) {
+        const double c = L * (c0 + c1 * (double)k) + best[i + k];
+        if (bk == 0 || c < bc) bc = c, bk = (int32_t)k;
+      }
+      best[i] = bc;
+      cut[i] = bk;
+    }
+  });
+}
+
 extern "C" int sat_dense_forward(const float* kernel_host, const float* bias_host, int32_t K, int32_t N, int32_t act,
                                  const float* x, int64_t rows, float* y, void* stream) {
   return guarded([&] {

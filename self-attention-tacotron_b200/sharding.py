@@ -13,6 +13,32 @@ import numpy as np
 STEP_US0, STEP_US1 = 30.0, 0.27
 
 
+def _bucket_cuts_numpy(L, batch_size, c0, c1):
+    """the dynamic programme of make_buckets, one NumPy row per utterance (what sat_bucket_cuts does natively)"""
+    n = len(L)
+    L = L.astype(np.float64)
+    best = np.zeros(n + 1)
+    cut = np.zeros(n, dtype=np.int32)
+    for i in range(n - 1, -1, -1):
+        ks = np.arange(1, min(batch_size, n - i) + 1)
+        c = L[i] * (c0 + c1 * ks) + best[i + ks]
+        j = int(np.argmin(c))
+        best[i], cut[i] = c[j], ks[j]
+    return cut
+
+
+def _bucket_cuts(L, batch_size, c0, c1):
+    """cut[i] = size of the batch starting at i; libsat.so's sat_bucket_cuts (the programme is O(n * batch_size) and sits
+    in front of the first launch of every predict() call: 10 ms per 2048 utterances in NumPy, 0.2 ms natively)"""
+    import ctypes as C
+    from . import _lib
+    L = np.ascontiguousarray(L, dtype=np.int64)
+    cut = np.zeros(len(L), dtype=np.int32)
+    _lib.check(_lib.lib().sat_bucket_cuts(L.ctypes.data_as(C.c_void_p), C.c_int64(len(L)), C.c_int32(batch_size),
+                                          C.c_double(c0), C.c_double(c1), cut.ctypes.data_as(C.c_void_p)))
+    return cut
+
+
 def make_buckets(lengths, batch_size, world_size=1, bucket_width=50, cost_model=(STEP_US0, STEP_US1)):
     """-> per-rank list of batches; each batch is a list of utterance indices of similar length.
 
@@ -41,18 +67,10 @@ def make_buckets(lengths, batch_size, world_size=1, bucket_width=50, cost_model=
         if n == 0:
             continue
         if cost_model is not None:
-            c0, c1 = cost_model
-            L = lengths[share].astype(np.float64)
-            best = np.zeros(n + 1)
-            cut = np.zeros(n, dtype=np.int64)
-            for i in range(n - 1, -1, -1):
-                ks = np.arange(1, min(batch_size, n - i) + 1)
-                c = L[i] * (c0 + c1 * ks) + best[i + ks]
-                j = int(np.argmin(c))
-                best[i], cut[i] = c[j], ks[j]
+            cut = _bucket_cuts(lengths[share], batch_size, *cost_model)
             i = 0
             while i < n:
-                per_rank[k].append([int(x) for x in share[i:i + cut[i]]])
+                per_rank[k].append(share[i:i + cut[i]].tolist())
                 i += int(cut[i])
             continue
         cur, cur_bucket = [], None

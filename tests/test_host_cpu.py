@@ -151,6 +151,12 @@ def test_cost_model_buckets_never_cost_more_than_fixed_width():
     lens4 = np.array([10, 10, 10, 200])
     per_utt = make_buckets(lens4, 4, 1, cost_model=(0.0, 1.0))[0]  # the long utterance must not drag the short ones
     assert sum(int(lens4[b].max()) * len(b) for b in per_utt) == 230 and [3] in per_utt
+    # the native dynamic programme (libsat.so: sat_bucket_cuts) and its NumPy statement cut alike
+    from sat_b200.sharding import _bucket_cuts, _bucket_cuts_numpy
+    for n, bs in ((1, 4), (5, 8), (700, 128), (2048, 256)):
+        L = np.sort(rng.integers(20, 300, size=n))[::-1].copy()
+        np.testing.assert_array_equal(_bucket_cuts(L, bs, STEP_US0, STEP_US1), _bucket_cuts_numpy(L, bs, STEP_US0, STEP_US1))
+    assert make_buckets([], 8, 2) == [[], []]
 
 
 def test_two_rank_gloo_shard_and_gather(tmp_path):
