@@ -60,11 +60,11 @@ GROUPS = {
                              dec("ljspeech_tacotron", 4, 30, 13, 1, stop=2),
                              dec("ljspeech_tacotron", 37, 19, 3, 1, stop=1),
                              dec("codes_self_attention", 2, 17, 3, 2)),
-    # tensor-core form: tcgen05 gate GEMMs with the TMA ring, paired attention rows (B > 148), the experiment switch
+    # tensor-core form: tcgen05 gate GEMMs with the TMA ring, paired attention rows (B > 148), two activation ring shapes
     "decoder_tc": lambda: (dec("ljspeech_tacotron", 64, 20, 3, 1),
                            dec("ljspeech_tacotron", 150, 24, 2, 1),
                            dec("ljspeech_self_attention", 66, 18, 2, 1),
-                           dec("ljspeech_tacotron", 130, 20, 2, 1, env={"SAT_TC_DENSE": "1"})),
+                           dec("ljspeech_tacotron", 130, 20, 2, 1, env={"SAT_TC_G": "1", "SAT_TC_STAGES": "3"})),
     # encoder: conv_tc_kernel (fused bank, proj, highway, LSTM projection), bilstm_kernel, mha_tc_kernel
     "encoder": lambda: (enc("ljspeech_self_attention", 2, 40), enc("ljspeech_tacotron", 3, 33)),
 }

@@ -185,8 +185,6 @@ struct sat_decoder {
   unsigned* barrier = nullptr;
   long long* prof = nullptr;
   size_t max_dyn_smem = 0;
-  CUtensorMap hmaps[9];
-  CUtensorMap* dmaps = nullptr;  // device copy, 64-byte aligned
   int last_tc = 0, last_cl = 1;
   int step_next = -1;  // sat_decoder_step: the step the state in the workspace is ready for
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;  // bracket the persistent launch of the last run
@@ -381,7 +379,6 @@ extern "C" int sat_decoder_create(const sat_hparams* hpp, const sat_tensor* weig
     h->grid = h->sm_count;
     h->barrier = pool.alloc<unsigned>(1);
     h->prof = pool.alloc<long long>(N_PROF);
-    h->dmaps = (CUtensorMap*)(((uintptr_t)pool.alloc<uint8_t>(9 * sizeof(CUtensorMap) + 64) + 63) & ~(uintptr_t)63);
     SAT_CUDA(cudaEventCreate(&h->ev0));
     SAT_CUDA(cudaEventCreate(&h->ev1));
     guard.release();
@@ -495,74 +492,48 @@ static int decoder_run_impl(sat_decoder* h, const sat_decoder_io* iop, void* str
         d.img_off = off;
         off += d.slots * d.kchunks * 2048;
       }
-      // chunk order: columns produced at least two phases before the LSTM first (requested behind the grid barrier)
-      {
-        struct Range { int lo, hi; };
-        const Range old_a[1] = {{p.P1, Ka}}, old_1[2] = {{0, A}, {A + p.Dctx, K1}}, old_2[1] = {{Dd, K2}};
-        const Range* olds[3] = {old_a, old_1, old_2};
-        const int nold[3] = {1, 2, 1};
-        for (int i = 0; i < 3; ++i) {
-          TcLstmDesc& d = *td[i];
-          if (d.kchunks > 48) { use_tc = false; break; }
-          int n = 0, n_old = 0;
-          for (int pass = 0; pass < 2; ++pass)
-            for (int c = 0; c < d.kchunks; ++c) {
-              const int lo = c * tc::CHUNK_K16, hi = std::min(lo + tc::CHUNK_K16, Ks[i]);
-              bool old = false;
-              for (int r = 0; r < nold[i]; ++r) old = old || (lo >= olds[i][r].lo && hi <= olds[i][r].hi);
-              if (old == (pass == 0)) { d.order[n++] = (unsigned char)c; n_old += pass == 0; }
-            }
-          // measured on B200 (cfg 2, B=256): requesting these chunks behind the grid barrier shortens the LSTM phases by
-          // ~0.7 us each but lengthens the phases whose barrier hosts the requests by as much (net 0), so it is
-          // off unless SAT_TC_PREFILL=<chunks> asks for it
-          d.n_pre = 0;
-          if (const char* e = getenv("SAT_TC_PREFILL")) d.n_pre = std::min(std::min(n_old, (int)TC_STAGES), atoi(e));
-        }
-      }
       for (int i = 0; i < 3; ++i) {  // cell state of the CTA's own items, after the images
         td[i]->st_off = off;
         off += td[i]->slots * TC_STATE_BYTES;
       }
-      // ---- the row-local dense layers as tensor-core tile phases (dense_phase_tc): query layers always, frame / stop
-      // projection + prenet when prenet layer 0 is folded into the projection (self feed, no speaker term, no hops) ----
-      // Measured on B200 (cfg 2, B=256, profiles/README.md round 2): parity green, but every TMA-fed tile phase costs
-      // ~6 us (grid barrier + two TMA round trips + epilogue) -- Q 6.1 us against 5.5 us inside the attention rows,
-      // P + R 22 us against the 11.8 us row-split frame phase; step 59.4 -> 72.4 us.  Off unless SAT_TC_DENSE=1.
-      bool dense_tc = false;
-      if (const char* e = getenv("SAT_TC_DENSE")) dense_tc = use_tc && atoi(e) != 0;
-      auto plan_dense = [&](TcDense& d, int K, int terms) {  // one resident slot per CTA, or not at all
-        d.K = K; d.kc = ceil_div(K, tc::CHUNK_K16); d.terms = terms;
-        d.n_tiles = d.nt[0] + d.nt[1];
-        d.slots = 1; d.img_off = off;
-        if (d.n_tiles * RB > h->grid) return false;
-        off += (terms == 3 ? 2 : 1) * d.kc * 2048;
-        return true;
-      };
-      if (dense_tc && !io.forced_alignment) {
-        bool ok = true;
-        for (int i = 0; i < h->n_mech; ++i) {
-          ok = ok && h->Up[i] % TC_N == 0 && h->dq[i].Wrm;
-          p.tq.W[i] = h->dq[i].Wrm; p.tq.ldw[i] = h->dq[i].Np; p.tq.nt[i] = h->Up[i] / TC_N; p.tq.ncol[i] = h->Up[i];
+      // activation ring: `stages` bulk copies of G operand tiles (16 KB each) in flight.  The SM's TMA unit retires one
+      // copy per ~0.28 us whatever its size (scripts/dev/tma_bench.cu), so the ring takes the largest copies that fit:
+      // 2 x 64 KB, else 2 x 48 KB, 2 x 32 KB, 2 x 16 KB (SAT_TC_G / SAT_TC_STAGES override)
+      const long long room = (long long)h->max_dyn_smem - 1024 - off - 1024;
+      int G = 0, stages = 2;
+      for (int g : {4, 3, 2, 1})
+        if (G == 0 && (long long)stages * g * TC_TILE_BYTES <= room) G = g;
+      if (const char* e = getenv("SAT_TC_G")) G = std::max(1, std::min(8, atoi(e)));
+      if (const char* e = getenv("SAT_TC_STAGES")) stages = std::max(1, std::min((int)TC_MAX_STAGES, atoi(e)));
+      const size_t scratch_bytes = std::max((size_t)SCRATCH_FLOATS * sizeof(float), (size_t)stages * G * TC_TILE_BYTES + 1024);
+      p.tc_G = G; p.tc_stages = stages;
+      // copy order: copies whose columns were all produced at least two phases before the LSTM go first and are requested
+      // behind the grid barrier in front of the phase, at most one per ring stage (SAT_TC_PREFILL=0 switches that off)
+      if (G > 0) {
+        struct Range { int lo, hi; };
+        const Range old_a[1] = {{p.P1, Ka}}, old_1[2] = {{0, A}, {A + p.Dctx, K1}}, old_2[1] = {{Dd, K2}};
+        const Range* olds[3] = {old_a, old_1, old_2};
+        const int nold[3] = {1, 2, 1};
+        int pre_max = stages;
+        if (const char* e = getenv("SAT_TC_PREFILL")) pre_max = std::min(stages, std::max(0, atoi(e)));
+        for (int i = 0; i < 3; ++i) {
+          TcLstmDesc& d = *td[i];
+          d.ncopy = ceil_div(d.kchunks, G);
+          if (d.ncopy > 16) { G = 0; break; }
+          int n = 0, n_old = 0;
+          for (int pass = 0; pass < 2; ++pass)
+            for (int c = 0; c < d.ncopy; ++c) {
+              const int lo = c * G * tc::CHUNK_K16, hi = std::min(lo + G * tc::CHUNK_K16, Ks[i]);
+              bool old = false;
+              for (int r = 0; r < nold[i]; ++r) old = old || (lo >= olds[i][r].lo && hi <= olds[i][r].hi);
+              if (old == (pass == 0)) { d.order[n++] = (unsigned char)c; n_old += pass == 0; }
+            }
+          d.n_pre = std::min(n_old, pre_max);
         }
-        const int off0 = off;
-        if (ok && plan_dense(p.tq, A, 2)) p.tc_q = 1;
-        else off = off0;
       }
-      if (dense_tc && p.fused_prenet0 && !p.ms && h->hops == 0) {
-        const int off0 = off;
-        p.tp.W[0] = p.outp.Wrm; p.tp.ldw[0] = p.outp.Np; p.tp.ncol[0] = p.Mr + 1 + p.P0;
-        p.tp.nt[0] = ceil_div(p.tp.ncol[0], TC_N); p.tp.bias = p.outp.bias;
-        p.tr.W[0] = p.pre1.Wrm; p.tr.ldw[0] = p.pre1.Np; p.tr.ncol[0] = p.P1;
-        p.tr.nt[0] = ceil_div(p.P1, TC_N); p.tr.bias = p.pre1.bias;
-        if (plan_dense(p.tp, p.outp.K, 3) && plan_dense(p.tr, p.P0, 2)) p.tc_frame = 1;
-        else off = off0;
-      }
-      p.scratch_floats = std::max((int)SCRATCH_FLOATS, (int)TC_SCRATCH_FLOATS);
-      smem_bytes = p.scratch_floats * sizeof(float) + 1024 + (size_t)off;
-      if (smem_bytes > h->max_dyn_smem) {  // resident images do not fit: SIMT form
-        use_tc = false;
-        p.tc_q = p.tc_frame = 0;
-      }
+      p.scratch_floats = (int)(scratch_bytes / sizeof(float));
+      smem_bytes = scratch_bytes + 1024 + (size_t)off;
+      if (G == 0 || smem_bytes > h->max_dyn_smem) use_tc = false;  // resident images do not fit: SIMT form
     }
     {
       const int need = frame_smem_floats(p.outp.K, p.outp.Np, p.Mnf, p.pre0.Np, p.pre1.Np);
@@ -573,7 +544,6 @@ static int decoder_run_impl(sat_decoder* h, const sat_decoder_io* iop, void* str
     }
     if (const char* e = getenv("SAT_BENCH_BARRIERS")) p.bench_barriers = atoi(e);
     p.tc = use_tc ? 1 : 0;
-    if (!use_tc) p.tc_q = p.tc_frame = 0;
     if (!use_tc) p.scratch_floats = SCRATCH_FLOATS;
     p.RB = RB;
     p.Ka_pad = ceil_div(Ka, tc::CHUNK_K16) * tc::CHUNK_K16;
@@ -684,10 +654,6 @@ static int decoder_run_impl(sat_decoder* h, const sat_decoder_io* iop, void* str
     const size_t o_l10 = take(n_l1), o_l11 = take(n_l1);
     const size_t o_l20 = take(n_l2), o_l21 = take(n_l2);
     const size_t o_qfm = take((size_t)A * ld);
-    // fp16 hi + lo activation pairs of the tensor-core dense phases (zeroed per run: padding rows / columns stay zero)
-    p.qx_ld = 2 * p.tq.kc * tc::CHUNK_K16; p.px_ld = 2 * p.tp.kc * tc::CHUNK_K16; p.rx_ld = 2 * p.tr.kc * tc::CHUNK_K16;
-    const size_t o_qx = take(p.tc_q ? rows_tc * p.qx_ld / 2 : 0), o_px = take(p.tc_frame ? rows_tc * p.px_ld / 2 : 0);
-    const size_t o_rx = take(p.tc_frame ? rows_tc * p.rx_ld / 2 : 0);
     const size_t o_ca = take((size_t)A * ld), o_c1 = take((size_t)Dd * ld), o_c2 = take((size_t)Dd * ld);
     const size_t o_dout = take((size_t)Dd * ld);
     const size_t o_saq = take((size_t)Ds * ld), o_sactx = take((size_t)Ds * ld), o_saa = take((size_t)Ds * ld);
@@ -721,7 +687,6 @@ static int decoder_run_impl(sat_decoder* h, const sat_decoder_io* iop, void* str
     p.l1_in[0] = ws + o_l10; p.l1_in[1] = ws + o_l11;
     p.l2_in[0] = ws + o_l20; p.l2_in[1] = ws + o_l21;
     p.qfm = ws + o_qfm;
-    p.qx = (__half*)(ws + o_qx); p.px = (__half*)(ws + o_px); p.rx = (__half*)(ws + o_rx);
     p.c_a = ws + o_ca; p.c_1 = ws + o_c1; p.c_2 = ws + o_c2; p.dout = ws + o_dout;
     p.sa_q = ws + o_saq; p.sa_ctx = ws + o_sactx; p.sa_a = ws + o_saa; p.sa_y[0] = ws + o_say0; p.sa_y[1] = ws + o_say1;
     p.target = io.target; p.lengths = (const long long*)io.memory_lengths;
@@ -853,19 +818,6 @@ static int decoder_run_impl(sat_decoder* h, const sat_decoder_io* iop, void* str
       t_y[0] = tw + o_y0; t_y[1] = tw + o_y1; t_mha = tw + o_mha; t_proj = tw + o_pr;
     }
 
-    if (use_tc) {
-      float* bufs[6] = {p.att_in[0], p.att_in[1], p.l1_in[0], p.l1_in[1], p.l2_in[0], p.l2_in[1]};
-      const int pads[6] = {p.Ka_pad, p.Ka_pad, p.K1_pad, p.K1_pad, p.K2_pad, p.K2_pad};
-      for (int i = 0; i < 6; ++i)
-        make_tensor_map_2d_f16(&h->hmaps[i], bufs[i], rows_tc, (uint64_t)pads[i], (uint64_t)pads[i], TC_M);
-      if (p.tc_q) make_tensor_map_2d_f16(&h->hmaps[6], p.qx, rows_tc, (uint64_t)p.qx_ld, (uint64_t)p.qx_ld, TC_M);
-      if (p.tc_frame) {
-        make_tensor_map_2d_f16(&h->hmaps[7], p.px, rows_tc, (uint64_t)p.px_ld, (uint64_t)p.px_ld, TC_M);
-        make_tensor_map_2d_f16(&h->hmaps[8], p.rx, rows_tc, (uint64_t)p.rx_ld, (uint64_t)p.rx_ld, TC_M);
-      }
-      SAT_CUDA(cudaMemcpyAsync(h->dmaps, h->hmaps, sizeof(h->hmaps), cudaMemcpyHostToDevice, st));
-      p.maps = h->dmaps;
-    }
     void* args[] = {&p};
     SAT_CUDA(cudaEventRecord(h->ev0, st));
     {

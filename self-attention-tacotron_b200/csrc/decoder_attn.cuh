@@ -54,7 +54,8 @@ struct AttMech {
   const __half* values16;  // optional fp16 copy of `values` (tensor-core mode)
   void* ctx_dst[2];     // context element (d, b) written at ctx_dst[i][d * ctx_sd[i] + b * ctx_sb[i]]; may be null
   int ctx_sd[2], ctx_sb[2];
-  int ctx_f16;          // 1: the context destinations are fp16 buffers feeding tensor-core GEMMs, 0: fp32
+  int ctx_f16;          // 1: the context destinations are fp16 operand-tile buffers of the tensor-core GEMMs (element
+                        // tc_act_index(ctx_sd[i] + d, b, ctx_sb[i]): ctx_sd = feature offset, ctx_sb = chunks per row), 0: fp32
   // shared-memory plan of the row phase: TS = capacity of the per-position arrays (>= T, multiple of 16; MAX_T for the
   // stand-alone entry point), FB = floats of the location-feature / context-partial buffer (>= 8 TS and >= 16 Dv)
   int TS, FB;
@@ -780,9 +781,8 @@ __device__ __forceinline__ void attention_item_inl(const AttMech& m, int b, int 
 #pragma unroll
         for (int i = 0; i < 2; ++i)
           if (m.ctx_dst[i]) {
-            const size_t o = (size_t)(w0 + d) * m.ctx_sd[i] + (size_t)b * m.ctx_sb[i];
-            if (m.ctx_f16) ((__half*)m.ctx_dst[i])[o] = tc::to_f16(ctx);
-            else ((float*)m.ctx_dst[i])[o] = ctx;
+            if (m.ctx_f16) ((__half*)m.ctx_dst[i])[tc_act_index(m.ctx_sd[i] + w0 + d, b, m.ctx_sb[i])] = tc::to_f16(ctx);
+            else ((float*)m.ctx_dst[i])[(size_t)(w0 + d) * m.ctx_sd[i] + (size_t)b * m.ctx_sb[i]] = ctx;
           }
       }
       group_sync<GT>(gid);
@@ -822,9 +822,8 @@ __device__ __forceinline__ void attention_item_inl(const AttMech& m, int b, int 
 #pragma unroll
     for (int i = 0; i < 2; ++i)
       if (m.ctx_dst[i]) {
-        const size_t o = (size_t)d * m.ctx_sd[i] + (size_t)b * m.ctx_sb[i];
-        if (m.ctx_f16) ((__half*)m.ctx_dst[i])[o] = tc::to_f16(ctx);
-        else ((float*)m.ctx_dst[i])[o] = ctx;
+        if (m.ctx_f16) ((__half*)m.ctx_dst[i])[tc_act_index(m.ctx_sd[i] + d, b, m.ctx_sb[i])] = tc::to_f16(ctx);
+        else ((float*)m.ctx_dst[i])[(size_t)d * m.ctx_sd[i] + (size_t)b * m.ctx_sb[i]] = ctx;
       }
   }
   if (GT == NT && fwd && m.agent) {

@@ -22,6 +22,14 @@ constexpr int RED_FLOATS = NW * TILE_N * ROWS_PER_GROUP;  // cross-warp reductio
 constexpr int MAX_HOPS = 2;
 constexpr int MAX_B = 256;
 
+// element (feature n, utterance row b) of a tensor-core activation buffer (B >= 64 form; fp16, `kc` 64-k chunks per row):
+// index in halves into [row block of 128][chunk][128 rows][64 k], every [128][64] tile in the 128-byte-swizzled order
+// the tcgen05 A operand has in shared memory -- a row block is then one contiguous run that bulk copies move verbatim
+__device__ __forceinline__ size_t tc_act_index(int n, int b, int kc) {
+  const int r = b & 127, kk = n & 63;
+  return ((size_t)((b >> 7) * kc + (n >> 6)) << 13) + (size_t)(r * 64 + ((((kk >> 3) ^ (r & 7)) << 3) | (kk & 7)));
+}
+
 struct DenseDesc {
   const float* Wp;    // [n_tiles][K][8] packed (global)
   const float* bias;  // [n_tiles*8] packed (zeros where absent)

@@ -19,7 +19,6 @@ namespace dec {
 
 constexpr int N_PROF = 48;  // [0,16) phases of a step, [16,24) attention-item stages, [24,27) tc, [32,40) frame-item stages (CTA 0)
 constexpr int SCRATCH_FLOATS = (RED_FLOATS > ATT_SMEM_FLOATS ? RED_FLOATS : ATT_SMEM_FLOATS);
-constexpr int TC_SCRATCH_FLOATS = (TC_STAGES * TC_STAGE_BYTES + 1024) / 4;  // ring + alignment slack
 
 struct SaHop {
   DenseDesc qkv, o, tr;
@@ -46,8 +45,10 @@ struct DecParams {
   int *stop_steps, *n_steps;
   unsigned* barrier;
   long long* prof;  // [N_PROF] accumulated SM cycles per phase (CTA 0), may be null
-  // ---- tensor-core mode (B >= 64): LSTM inputs att_in / l1_in / l2_in are ROW-major fp16 [RB*128][K*_pad] ----
+  // ---- tensor-core mode (B >= 64): LSTM inputs att_in / l1_in / l2_in are fp16 in operand-tile order
+  // [RB row blocks][K*_pad / 64 chunks][128 rows][64 k] (tc_act_index) ----
   int tc, RB, Ka_pad, K1_pad, K2_pad;
+  int tc_G, tc_stages;      // 64-k chunks per bulk copy and copies in flight of the gate GEMMs' activation ring
   // ---- teacher-forced time-batched form (feed_mode teacher + fixed step count): everything that does not feed the
   // recurrence leaves the loop.  The prenet of all (known) input frames is precomputed into p1_all[S][B][p1_ld]; the
   // loop runs C, D+E, F, G only and records the LSTM2 outputs in dec_out; the decoder self-attention hops (as ONE
@@ -59,7 +60,6 @@ struct DecParams {
   int bench_barriers;       // diagnostic: time this many empty grid barriers before the loop (prof[30])
   int scratch_floats;       // phase scratch at the head of dynamic smem (>= SCRATCH_FLOATS; holds the TMA ring in tc mode)
   TcLstmDesc tc_a, tc_1, tc_2;
-  const CUtensorMap* maps;  // [9]: att_in[0,1], l1_in[0,1], l2_in[0,1], qx, px, rx
   float* qfm;               // feature-major copy of the attention-LSTM output (query) for the SIMT query layers
   int fused_prenet0;        // 1: `outp` carries P0 extra columns = prenet layer 0 applied to the fed-back frame, folded
                             //    into the projection (self feed only): column Mr + 1 + j = sum_f W_out[:, f0 + f] W_pre0[f][j]
@@ -68,13 +68,6 @@ struct DecParams {
   // ---- cluster-split attention rows (small batches: B * n_mech * cl <= grid; launched with cluster dimension cl) ----
   // The cl CTAs of a cluster share one (row, mechanism) item: each computes Up / cl columns of the query layer, the
   // energies of those units (partials all-gathered through distributed shared memory) and Dv / cl context columns.
-  // ---- tensor-core mode: the row-local dense layers as tile phases of their own (dense_phase_tc) instead of per-row
-  // GEMVs that make every CTA stream the whole weight matrix from L2 ----
-  int tc_q;                 // query layers of all mechanisms: phase Q between the attention LSTM and the attention rows
-  int tc_frame;             // frame / stop projection (+ folded prenet layer 0) and prenet layer 1: phases P and R
-  TcDense tq, tp, tr;
-  __half *qx, *px, *rx;     // fp16 hi + lo pairs [RB * 128][ld]: attention-LSTM output, LSTM2 output, prenet layer-0 output
-  int qx_ld, px_ld, rx_ld;
   int retire;               // per-row stop rule: stopped rows leave the row-split phases (s_live in the kernel)
   int* finished;            // optional (sat_decoder_step): 1 if the stop rule ended the run inside this launch, else 0
   int t_begin, t_end;       // decoder steps [t_begin, t_end) of the run (sat_decoder_step: one step per launch, the state
@@ -143,54 +136,6 @@ struct QkvEpi {
       const int hd = d / dh, dd = d % dh;
       float* dst = (which == 0 ? kc : vc) + (((size_t)b * H + hd) * Smax + t) * dh + dd;
       *(float4*)dst = make_float4(v[0], v[1], v[2], v[3]);
-    }
-  }
-};
-
-// epilogues of the tensor-core dense phases (dense_phase_tc): one utterance row x four columns per call
-struct QueryTcEpi {  // processed queries of up to two mechanisms, row-major [b][Up]
-  float* pq[2];
-  int Up[2], nt0, B;
-  __device__ __forceinline__ void operator()(int b, int tile, int ul, const float* g) const {
-    if (b >= B) return;
-    const int grp = tile < nt0 ? 0 : 1, n = (tile - (grp ? nt0 : 0)) * TC_N + ul * 4;
-    *(float4*)(pq[grp] + (size_t)b * Up[grp] + n) = make_float4(g[0], g[1], g[2], g[3]);
-  }
-};
-struct FrameTcEpi {  // frame + stop projection with prenet layer 0 folded in (self feed): [mel (Mr) | stop | relu -> p0]
-  const float* bias;
-  int Mr, P0, N, B, t, max_steps;
-  float *mel, *stop;
-  __half* rx;
-  int rx_ld, rx_lo;
-  __device__ __forceinline__ void operator()(int b, int tile, int ul, const float* g) const {
-    if (b >= B) return;
-#pragma unroll
-    for (int c = 0; c < 4; ++c) {
-      const int n = tile * TC_N + ul * 4 + c;
-      if (n >= N) continue;
-      const float v = g[c] + __ldg(bias + n);
-      if (n < Mr) mel[((size_t)b * max_steps + t) * Mr + n] = v;
-      else if (n == Mr) stop[(size_t)b * max_steps + t] = v;
-      else {
-        const float r = fmaxf(v, 0.f);
-        const __half hh = tc::to_f16(r);
-        rx[(size_t)b * rx_ld + (n - Mr - 1)] = hh;
-        rx[(size_t)b * rx_ld + rx_lo + (n - Mr - 1)] = tc::to_f16(r - __half2float(hh));
-      }
-    }
-  }
-};
-struct PrenetTcEpi {  // prenet layer 1 -> the attention-LSTM input of the next step
-  const float* bias;
-  int N, B;
-  Act2D dst;
-  __device__ __forceinline__ void operator()(int b, int tile, int ul, const float* g) const {
-    if (b >= B) return;
-#pragma unroll
-    for (int c = 0; c < 4; ++c) {
-      const int n = tile * TC_N + ul * 4 + c;
-      if (n < N) dst.put(n, b, fmaxf(g[c] + __ldg(bias + n), 0.f));
     }
   }
 };
@@ -512,14 +457,16 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
   const int tid = threadIdx.x;
   const int ld = p.ld;
 
-  __shared__ __align__(8) uint64_t s_tcbar[2 * TC_STAGES + 1];
+  __shared__ __align__(8) uint64_t s_tcbar[2 * TC_MAX_STAGES + 1];
   __shared__ uint32_t s_tmem;
   TcState tcs;
+  tcs.G = p.tc_G;
+  tcs.stages = p.tc_stages;
   tcs.ring = (uint8_t*)(((uintptr_t)scratch + 1023) & ~(uintptr_t)1023);
   tcs.wimg = (uint8_t*)(((uintptr_t)wres + 1023) & ~(uintptr_t)1023);
   tcs.full = s_tcbar;
-  tcs.empty = s_tcbar + TC_STAGES;
-  tcs.done = s_tcbar + 2 * TC_STAGES;
+  tcs.empty = s_tcbar + TC_MAX_STAGES;
+  tcs.done = s_tcbar + 2 * TC_MAX_STAGES;
   tcs.tmem = 0;
   tcs.n_chunks = 0;
   tcs.n_items = 0;
@@ -527,18 +474,13 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
   tcs.prof = p.prof ? p.prof + 24 : nullptr;
   if (p.tc) {
     if (tid == 0) {
-      for (int i = 0; i < 2 * TC_STAGES + 1; ++i) tc::mbar_init(s_tcbar + i, 1);
+      for (int i = 0; i < 2 * TC_MAX_STAGES + 1; ++i) tc::mbar_init(s_tcbar + i, 1);
       tc::fence_mbar_init();
     }
     if (tid < 32) tc::tmem_alloc(&s_tmem, 32);
     tc_load_resident(p.tc_a, p.RB, tcs);
     tc_load_resident(p.tc_1, p.RB, tcs);
     tc_load_resident(p.tc_2, p.RB, tcs);
-    if (p.tc_q) tc_load_dense_resident(p.tq, p.RB, tcs);
-    if (p.tc_frame) {
-      tc_load_dense_resident(p.tp, p.RB, tcs);
-      tc_load_dense_resident(p.tr, p.RB, tcs);
-    }
     tc::fence_proxy_async();
     tc::tc_fence_before();
     __syncthreads();
@@ -564,16 +506,17 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
   }
   long long tprev = 0;
   int ph = 0;
-  // next_lstm / next_map: the tensor-core LSTM phase that follows this barrier (null: none) -- its "old" input
-  // columns are requested while the CTA waits for the other CTAs
-  auto phase_end = [&](const TcLstmDesc* next_lstm = nullptr, const CUtensorMap* next_map = nullptr) {
-    if (next_lstm) {
-      tc::fence_proxy_async();  // every thread: its generic-proxy writes to the scratch precede the TMA writes
-      bar.sync([&] { tc_prefill(*next_lstm, next_map, p.RB, tcs); });
+  // next_lstm / next_x: the tensor-core LSTM phase that follows this barrier (null: none) -- the copies of its "old"
+  // input columns are requested while the CTA waits for the other CTAs
+  auto phase_end = [&](const TcLstmDesc* next_lstm = nullptr, const float* next_x = nullptr) {
+    if (next_lstm && next_lstm->n_pre > 0) {
+      tc::fence_proxy_async();  // every thread: its generic-proxy writes to the scratch precede the bulk-copy writes
+      bar.sync([&] { tc_prefill(*next_lstm, (const __half*)next_x, p.RB, tcs); });
+      tcs.prefilled = blockIdx.x < next_lstm->n_tiles * p.RB ? next_lstm->n_pre : 0;
     } else {
       bar.sync();
     }
-    if (p.prof && blockIdx.x == 0 && tid == 0) {
+    if (p.prof && blockIdx.x == 0 && tid == 0 && tprev) {  // (tprev == 0: the barrier in front of the first step)
       const long long now = clock64();
       p.prof[ph] += now - tprev;
       tprev = now;
@@ -592,15 +535,11 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
   // prenet of the <GO> frame -> attention-LSTM input of step 0
   if (p.t_begin > 0) {
     // continued run: the previous launch left the prenet of this step's input frame in place
-  } else if (p.batched_tail) copy_prenet(0, Act2D{p.att_in[0], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc});
-  else frame_phase<RETIRE>(p, 0, nullptr, 0, Act2D{p.att_in[0], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc}, true, scratch, s_live, p.B);
+  } else if (p.batched_tail) copy_prenet(0, Act2D{p.att_in[0], p.tc ? 0 : ld, p.tc ? p.Ka_pad / 64 : 1, p.tc});
+  else frame_phase<RETIRE>(p, 0, nullptr, 0, Act2D{p.att_in[0], p.tc ? 0 : ld, p.tc ? p.Ka_pad / 64 : 1, p.tc}, true, scratch, s_live, p.B);
   auto row_of = [&](int li) { return RETIRE ? (int)s_live[li] : li; };
-  if (p.tc) {
-    tc::fence_proxy_async();
-    bar.sync([&] { tc_prefill(p.tc_a, p.maps, p.RB, tcs); });
-  } else {
-    bar.sync();
-  }
+  if (p.tc) phase_end(&p.tc_a, p.att_in[p.t_begin & 1]);
+  else bar.sync();
 
   int t = p.t_begin, fired = 0;
   for (; t < p.t_end; ++t) {
@@ -611,9 +550,8 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
     if (p.tc) {
       // fp16 row-major buffers: att_in = [prenet | context | zoned h], l1_in = [h_a | context | zoned h1]
       const int h0 = p.P1 + p.Dctx;
-      TcLstmIO io{p.maps + cur, Act2D{p.l1_in[cur], 1, p.K1_pad, 1}, Act2D{p.tc_q ? nullptr : p.qfm, ld, 1, 0},
-                  Act2D{(__half*)p.att_in[nxt] + h0, 1, p.Ka_pad, 1}, nullptr, 0, 0,
-                  p.tc_q ? p.qx : nullptr, p.qx_ld, p.qx_ld / 2};
+      TcLstmIO io{(const __half*)p.att_in[cur], Act2D{p.l1_in[cur], 0, p.K1_pad / 64, 1}, Act2D{p.qfm, ld, 1, 0},
+                  Act2D{p.att_in[nxt], h0, p.Ka_pad / 64, 1}, nullptr, 0, 0};
       tc::fence_proxy_async();
       __syncthreads();
       lstm_phase_tc(p.tc_a, io, p.B, p.Bp, p.RB, p.zc, p.zh, tcs);
@@ -624,15 +562,6 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
                           p.att_in[nxt] + hoff, nullptr, 0, 0, p.zc, p.zh});
     }
     phase_end();
-    // ---- Q: query layers of all mechanisms as tensor-core tiles ----
-    if (p.tc_q) {
-      tc::fence_proxy_async();
-      __syncthreads();
-      dense_phase_tc(p.tq, p.maps + 6, p.RB, tcs,
-                     QueryTcEpi{{const_cast<float*>(p.mech[0].pq), const_cast<float*>(p.mech[1].pq)},
-                                {p.mech[0].Up, p.mech[1].Up}, p.tq.nt[0], p.B});
-      phase_end();
-    }
     // ---- D+E: query layers and attention mechanisms (row split, no barrier in between) ----
     // The processed query of a row is a row-local dense on the attention-LSTM output, so the CTA that owns the row's
     // attention item computes it itself (two rows per pass share one stream of the query-layer weights from L2).
@@ -691,7 +620,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
         const int mi0 = i0 % p.n_mech;
         // the items of one CTA share the mechanism whenever gridDim.x is a multiple of n_mech; otherwise one at a time
         const bool pair = nit == 2 && (i1 % p.n_mech) == mi0;
-        for (int q0 = 0; q0 < nit && !p.tc_q; q0 += pair ? 2 : 1) {
+        for (int q0 = 0; q0 < nit; q0 += pair ? 2 : 1) {
           const int nq = pair ? 2 : 1;
           const int mi = items[q0] % p.n_mech;
           if (p.mech[mi].kind == SAT_ATT_TEACHER_FORCING) continue;
@@ -725,11 +654,13 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
           m = p.mech[mi];
           const int coff = mi ? p.mech[0].Dv : 0;
           if (p.tc) {
-            m.ctx_dst[0] = (__half*)p.att_in[nxt] + p.P1 + coff;
-            m.ctx_dst[1] = (__half*)p.l1_in[cur] + p.A + coff;
-            m.ctx_sd[0] = m.ctx_sd[1] = 1;
-            m.ctx_sb[0] = p.Ka_pad;
-            m.ctx_sb[1] = p.K1_pad;
+            // fp16 operand-tile order (tc_act_index): ctx_sd = feature offset of the context, ctx_sb = chunks per row
+            m.ctx_dst[0] = p.att_in[nxt];
+            m.ctx_dst[1] = p.l1_in[cur];
+            m.ctx_sd[0] = p.P1 + coff;
+            m.ctx_sd[1] = p.A + coff;
+            m.ctx_sb[0] = p.Ka_pad / 64;
+            m.ctx_sb[1] = p.K1_pad / 64;
             m.ctx_f16 = 1;
           } else {
             m.ctx_f16 = 0;
@@ -760,15 +691,15 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
         }
       }
     }
-    if (p.tc) phase_end(&p.tc_1, p.maps + 2 + cur);
+    if (p.tc) phase_end(&p.tc_1, p.l1_in[cur]);
     else phase_end();
     // ---- F: decoder LSTM 1 ----
     if (p.batched_tail && t + 1 < p.max_steps)
-      copy_prenet(t + 1, Act2D{p.att_in[nxt], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc});
+      copy_prenet(t + 1, Act2D{p.att_in[nxt], p.tc ? 0 : ld, p.tc ? p.Ka_pad / 64 : 1, p.tc});
     if (p.tc) {
       const int h0 = p.A + p.Dctx;
-      TcLstmIO io{p.maps + 2 + cur, Act2D{p.l2_in[cur], 1, p.K2_pad, 1}, Act2D{nullptr, 0, 0, 0},
-                  Act2D{(__half*)p.l1_in[nxt] + h0, 1, p.K1_pad, 1}, nullptr, 0, 0, nullptr, 0, 0};
+      TcLstmIO io{(const __half*)p.l1_in[cur], Act2D{p.l2_in[cur], 0, p.K2_pad / 64, 1}, Act2D{nullptr, 0, 0, 0},
+                  Act2D{p.l1_in[nxt], h0, p.K1_pad / 64, 1}, nullptr, 0, 0};
       tc::fence_proxy_async();
       __syncthreads();
       lstm_phase_tc(p.tc_1, io, p.B, p.Bp, p.RB, p.zc, p.zh, tcs);
@@ -778,14 +709,13 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
                   LstmEpi{p.lstm_1.bias, p.Dd, ld, p.B, p.c_1, p.l1_in[cur] + hoff, p.l2_in[cur],
                           p.l1_in[nxt] + hoff, nullptr, 0, 0, p.zc, p.zh});
     }
-    if (p.tc) phase_end(&p.tc_2, p.maps + 4 + cur);
+    if (p.tc) phase_end(&p.tc_2, p.l2_in[cur]);
     else phase_end();
     // ---- G: decoder LSTM 2 ----
     if (p.tc) {
       const int h0 = p.Dd;
-      TcLstmIO io{p.maps + 4 + cur, Act2D{p.tc_frame ? nullptr : p.dout, ld, 1, 0}, Act2D{nullptr, 0, 0, 0},
-                  Act2D{(__half*)p.l2_in[nxt] + h0, 1, p.K2_pad, 1}, p.dec_out, p.max_steps * p.Dd, t * p.Dd,
-                  p.tc_frame ? p.px : nullptr, p.px_ld, p.px_ld / 2};
+      TcLstmIO io{(const __half*)p.l2_in[cur], Act2D{p.dout, ld, 1, 0}, Act2D{nullptr, 0, 0, 0},
+                  Act2D{p.l2_in[nxt], h0, p.K2_pad / 64, 1}, p.dec_out, p.max_steps * p.Dd, t * p.Dd};
       tc::fence_proxy_async();
       __syncthreads();
       lstm_phase_tc(p.tc_2, io, p.B, p.Bp, p.RB, p.zc, p.zh, tcs);
@@ -795,7 +725,8 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
                   LstmEpi{p.lstm_2.bias, p.Dd, ld, p.B, p.c_2, p.l2_in[cur] + hoff, p.dout,
                           p.l2_in[nxt] + hoff, p.dec_out, p.max_steps * p.Dd, t * p.Dd, p.zc, p.zh});
     }
-    phase_end();
+    if (p.tc && p.batched_tail && t + 1 < p.t_end) phase_end(&p.tc_a, p.att_in[nxt]);
+    else phase_end();
     if (!p.batched_tail) {
       // ---- H-K: decoder self-attention hops over the KV cache ----
       const float* y = p.dout;
@@ -815,46 +746,34 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
         phase_end();
         y = p.sa_y[hi & 1];
       }
-      if (p.tc_frame) {
-        // ---- P: frame + stop projection of step t with prenet layer 0 folded in; R: prenet layer 1 of step t+1 ----
-        tc::fence_proxy_async();
-        __syncthreads();
-        dense_phase_tc(p.tp, p.maps + 7, p.RB, tcs,
-                       FrameTcEpi{p.outp.bias, p.Mr, p.P0, p.Mr + 1 + p.P0, p.B, t, p.max_steps, p.mel, p.stop, p.rx,
-                                  p.rx_ld, p.rx_ld / 2});
-        phase_end();
-        tc::fence_proxy_async();
-        __syncthreads();
-        dense_phase_tc(p.tr, p.maps + 8, p.RB, tcs,
-                       PrenetTcEpi{p.pre1.bias, p.P1, p.B, Act2D{p.att_in[nxt], 1, p.Ka_pad, 1}});
-      } else {
-        // ---- L+A+B: frame + stop projection of step t, fed-back frame, prenet of step t+1 (row split) ----
-        frame_phase<RETIRE>(p, t, y, p.outp.K, Act2D{p.att_in[nxt], p.tc ? 1 : ld, p.tc ? p.Ka_pad : 1, p.tc}, false, scratch,
-                            s_live, RETIRE ? s_nlive : p.B);
-      }
-      if (p.tc && t + 1 < p.max_steps) phase_end(&p.tc_a, p.maps + nxt);
+      // ---- L+A+B: frame + stop projection of step t, fed-back frame, prenet of step t+1 (row split) ----
+      frame_phase<RETIRE>(p, t, y, p.outp.K, Act2D{p.att_in[nxt], p.tc ? 0 : ld, p.tc ? p.Ka_pad / 64 : 1, p.tc}, false, scratch,
+                          s_live, RETIRE ? s_nlive : p.B);
+      if (p.tc && t + 1 < p.t_end) phase_end(&p.tc_a, p.att_in[nxt]);
       else phase_end();
     }
     // ---- stop rule (every CTA evaluates the same data -> same decision) ----
     if (p.stop_mode != SAT_STOP_FIXED) {
-      bool term = true, stopped = true;
+      bool term = true, stopped = true, fresh = false;
       if (tid < p.B) {
         const float logit = __ldcg(p.stop + (size_t)tid * p.max_steps + t);
         term = (sigmoidf_(logit) > 0.5f) && (t > p.min_iters);
         if (term && s_stopped[tid] < 0) {
           s_stopped[tid] = t;
+          fresh = true;
           if (blockIdx.x == 0) p.stop_steps[tid] = t;
         }
         stopped = s_stopped[tid] >= 0;
       }
-      const int all_term = __syncthreads_and(term ? 1 : 0);
+      // RETIRE runs under the per-row rule only: its first vote asks whether any row stopped at this step
+      const int all_term = RETIRE ? __syncthreads_or(fresh ? 1 : 0) : __syncthreads_and(term ? 1 : 0);
       const int all_stopped = __syncthreads_and(stopped ? 1 : 0);
-      if (p.stop_mode == SAT_STOP_ALL_ROWS ? all_term : all_stopped) {
+      if ((!RETIRE && p.stop_mode == SAT_STOP_ALL_ROWS) ? all_term : all_stopped) {
         ++t;
         fired = 1;
         break;
       }
-      if (RETIRE) {
+      if (RETIRE && all_term) {
         // compact the rows that are still decoding (every CTA derives the same list from the same stop logits)
         const bool alive = tid < p.B && s_stopped[tid] < 0;
         const unsigned bal = __ballot_sync(0xffffffffu, alive);
@@ -880,10 +799,10 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
   }
   if (p.tc) {
     if (tid == 0) {
-      // a stop decision can leave the prefetch for the next step in flight: let it land before the CTA exits
+      // a stop decision can leave the requests for the next step in flight: let them land before the CTA exits
       for (uint32_t c = 0; c < tcs.prefilled; ++c) {
         const uint32_t n = tcs.n_chunks + c;
-        tc::mbar_wait(tcs.full + n % TC_STAGES, (n / TC_STAGES) & 1);
+        tc::mbar_wait(tcs.full + n % tcs.stages, (n / tcs.stages) & 1);
       }
     }
     tc::tc_fence_before();

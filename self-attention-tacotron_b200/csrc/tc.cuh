@@ -60,6 +60,15 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, u
       "l"(map), "r"(smem_u32(bar)), "r"(x), "r"(y)
       : "memory");
 }
+// 1-D bulk copy global -> shared (src and dst 16-byte aligned, bytes a multiple of 16), completing on the mbarrier.
+// Measured on B200 (scripts/dev/tma_bench.cu): the SM's TMA unit retires ONE copy or tensor box per ~0.28 us whatever
+// its size up to 32 KB (64 / 128 / 256-row boxes alike, 1 or 148 CTAs, 2 or 12 in flight) and moves larger copies at
+// 130 - 220 GB/s -- so a stream is paid for in instructions: few, large copies.
+__device__ __forceinline__ void bulk_load_1d(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
 }
@@ -106,6 +115,32 @@ __device__ __forceinline__ void mma_f16(uint32_t tmem_d, uint64_t adesc, uint64_
       "setp.ne.b32 p, %4, 0;\n\t"
       "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// The same, called by EVERY lane of a warp with warp-uniform arguments; one elected lane issues.  A loop run by a single
+// thread (if (tid == 32)) keeps descriptors and addresses in per-thread registers, and every tcgen05.mma then pays for
+// R2UR transfers behind elect loops: ~130 cycles per instruction on B200 instead of ~20 -- with N = 16 tiles that issue
+// time, not the data, bounded the gate GEMMs.
+// alo / blo: low words of the SW128 operand descriptors ((shared address & 0x3FFFF) >> 4; consecutive K-steps of 32
+// bytes are +2); the high word is the same for every K-major SW128 operand
+constexpr uint32_t DESC_SW128_HI = (1024u >> 4) | (1u << 14) | (2u << 29);
+__device__ __forceinline__ uint32_t desc_lo(uint32_t saddr) { return (saddr & 0x3FFFFu) >> 4; }
+__device__ __forceinline__ void mma_f16_warp(uint32_t tmem_d, uint32_t alo, uint32_t blo, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\t.reg .b64 da, db;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "mov.b64 da, {%1, %5};\n\t"
+      "mov.b64 db, {%2, %5};\n\t"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %3, p;\n\t}" ::"r"(tmem_d),
+      "r"(alo), "r"(blo), "r"(idesc), "r"(accumulate), "r"(DESC_SW128_HI)
+      : "memory");
+}
+__device__ __forceinline__ void mma_commit_warp(uint64_t* bar) {
+  asm volatile(
+      "{\n\t.reg .pred q;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(smem_u32(bar))
       : "memory");
 }
 __device__ __forceinline__ void mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {

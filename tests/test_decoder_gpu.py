@@ -200,12 +200,17 @@ def test_tensor_core_gate_gemms_full_dims(name, B, T, S):
 
 
 @pytest.mark.parametrize("name,B,T,S,mode", [("ljspeech_tacotron", 200, 61, 14, "free"),
+                                             ("ljspeech_tacotron", 70, 33, 9, "teacher"),
                                              ("ljspeech_self_attention", 96, 41, 10, "teacher")])
-def test_tensor_core_dense_phases_switch(name, B, T, S, mode, monkeypatch):
-    """SAT_TC_DENSE=1 (an experiment switch, off by default: slower on B200, see profiles/README.md) runs the query
-    layers -- and, for the self-feeding baseline decoder, the frame / stop projection with the folded prenet layer 0
-    and prenet layer 1 -- as tcgen05 tile phases with fp16 hi + lo operand pairs; same bar."""
-    monkeypatch.setenv("SAT_TC_DENSE", "1")
+@pytest.mark.parametrize("chunks,stages", [(None, None), ("1", "3"), ("3", "2")])
+def test_tensor_core_activation_ring_shapes(name, B, T, S, mode, chunks, stages, monkeypatch):
+    """The activation stream of the tcgen05 gate GEMMs -- fp16 operand tiles laid out in HBM in their shared-memory
+    byte order, moved by 1-D bulk copies of SAT_TC_G tiles with SAT_TC_STAGES copies in flight (default: the largest
+    copies that fit, 2 x 64 KB) -- meets the bar for every ring shape, with a ragged last row block and K ranges that
+    are not a multiple of the copy size."""
+    if chunks is not None:
+        monkeypatch.setenv("SAT_TC_G", chunks)
+        monkeypatch.setenv("SAT_TC_STAGES", stages)
     hp = small_hp(name)
     W = sat_b200.init_weights(hp, seed=13, stress=True)
     mems, lengths, target, _ = decoder_inputs(hp, B, T, S, seed=13)
