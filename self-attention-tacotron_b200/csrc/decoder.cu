@@ -640,6 +640,10 @@ static int decoder_run_impl(sat_decoder* h, const sat_decoder_io* iop, void* str
       }
       if (p.cl == 1) smem_bytes = plan_simt(h->grid);
     }
+    if (getenv("SAT_DEBUG_PLAN"))
+      fprintf(stderr, "[sat decoder plan] B=%d T=%d tc=%d G=%d stages=%d att_pair=%d att_row_floats=%d scratch_floats=%d smem=%zu cl=%d "
+                      "grid=%d\n", B, T, (int)use_tc, p.tc_G, p.tc_stages, p.att_pair, p.att_row_floats, p.scratch_floats, smem_bytes, p.cl,
+              grid_run);
     h->last_cl = p.cl;
 
     // ---- workspace carve-up (floats) ----
