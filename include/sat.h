@@ -219,7 +219,9 @@ int sat_dense_forward(const float* kernel_host, const float* bias_host, int32_t 
 int sat_embedding_lookup(const float* table_host, int64_t table_rows, int32_t dim, int64_t index_offset,
                          const int64_t* ids, int64_t n, float* out, void* stream);
 /* cycles accumulated by CTA 0 of the persistent decoder kernel (profiling aid): 48 host slots,
- * [0,16) phases of a step, [16,24) stages of the attention item, [24,27) tensor-core LSTM, [32,40) frame-item stages */
+ * [0,16) phases of a step, [16,24) stages of the attention item, [24,27) tensor-core LSTM, [32,40) frame-item stages.
+ * The counters cost ~2 % of a step, so they only run from the first call of this function on the handle onwards (or with
+ * SAT_PROF=1 in the environment): call it once (reset = 1) before the runs to be profiled. */
 int sat_decoder_profile(sat_decoder* h, int64_t* out16, int32_t reset);
 /* device time (ms) of the persistent decoder kernel of the last sat_decoder_run, from CUDA events recorded on the
  * launching stream around that launch; blocks until the kernel has finished */
@@ -231,6 +233,11 @@ int sat_decoder_used_tensor_cores(sat_decoder* h, int32_t* used);
  * ForwardAttention.__call__, modules/forward_attention.py:88-122) was split over a cluster of CTAs (small batches:
  * B * mechanisms * size <= SM count, fp32 form), 1 when each row ran on one CTA */
 int sat_decoder_cluster_size(sat_decoder* h, int32_t* size);
+/* SAT_STOP_PER_ROW only: 1 (default) = a row leaves the row-split phases at its own stop step (the retirement
+ * instantiation of the kernel: ~10 % slower per step while no row has stopped, up to ~12 % faster once rows stop far
+ * apart), 0 = stopped rows keep running until the last row has stopped (same results up to each row's own stop step).
+ * No reference counterpart: the reference synthesises one utterance per run (predict_mel.py:43-44). */
+int sat_decoder_set_row_retirement(sat_decoder* h, int32_t on);
 
 /* diagnostic: one-CTA self-test of the tcgen05 / TMA / TMEM building blocks (csrc/tc.cuh):
  * D[128,16] = A[128,K] . Wt[16,K]^T in TF32 with fp32 accumulation; all pointers device, K % 32 == 0, K <= 1024 */

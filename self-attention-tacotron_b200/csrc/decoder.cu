@@ -183,6 +183,8 @@ struct sat_decoder {
   int n_mech = 1, hops = 0, sm_count = 0, grid = 0;
   int P0 = 0, P1 = 0, Dctx = 0, Mr = 0, Mnf = 0;
   unsigned* barrier = nullptr;
+  bool prof_on = false;  // phase counters requested (sat_decoder_profile)
+  bool retire_rows = true;  // per-row stop rule: retire stopped rows (sat_decoder_set_row_retirement)
   long long* prof = nullptr;
   size_t max_dyn_smem = 0;
   int last_tc = 0, last_cl = 1;
@@ -376,6 +378,7 @@ extern "C" int sat_decoder_create(const sat_hparams* hpp, const sat_tensor* weig
     h->max_dyn_smem = prop.sharedMemPerBlockOptin - 4096;
     SAT_CUDA(cudaFuncSetAttribute(decoder_persistent_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->max_dyn_smem));
     SAT_CUDA(cudaFuncSetAttribute(decoder_persistent_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->max_dyn_smem));
+    SAT_CUDA(cudaFuncSetAttribute(decoder_persistent_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->max_dyn_smem));
     h->grid = h->sm_count;
     h->barrier = pool.alloc<unsigned>(1);
     h->prof = pool.alloc<long long>(N_PROF);
@@ -447,7 +450,7 @@ static int decoder_run_impl(sat_decoder* h, const sat_decoder_io* iop, void* str
     p.P0 = h->P0; p.P1 = h->P1; p.A = A; p.Dd = Dd; p.Dctx = h->Dctx; p.n_mech = h->n_mech;
     p.hops = h->hops; p.heads = hp.decoder_self_attention_num_heads; p.Ds = Ds; p.ms = hp.multi_speaker_prenet;
     p.feed_mode = io.feed_mode; p.stop_mode = io.stop_mode; p.max_steps = S; p.min_iters = io.min_iters;
-    p.retire = io.stop_mode == SAT_STOP_PER_ROW && h->hops == 0 && !stepping;  // (the KV-cached hops walk all rows)
+    p.retire = io.stop_mode == SAT_STOP_PER_ROW && h->retire_rows && h->hops == 0 && !stepping;  // (the KV-cached hops walk all rows)
     p.finished = finished;
     p.t_begin = stepping ? t_begin : 0;
     p.t_end = stepping ? std::min(S, t_begin + t_count) : S;
@@ -455,7 +458,12 @@ static int decoder_run_impl(sat_decoder* h, const sat_decoder_io* iop, void* str
     SAT_REQUIRE(!stepping || t_begin == 0 || (h->step_next == t_begin && h->last_B == B && h->last_T == T && h->last_S == S),
                 "sat_decoder_step: step %d does not continue the handle's run (next step %d)", t_begin, h->step_next);
     if (const char* e = getenv("SAT_RETIRE")) p.retire = p.retire && atoi(e) != 0;
-    const void* kernel_fn = p.retire ? (const void*)decoder_persistent_kernel<true> : (const void*)decoder_persistent_kernel<false>;
+    // the phase counters (sat_decoder_profile / SAT_PROF=1) run in an instantiation of their own, without row retirement
+    const bool prof_run = h->prof_on || getenv("SAT_PROF");
+    if (prof_run) p.retire = 0;
+    const void* kernel_fn = prof_run   ? (const void*)decoder_persistent_kernel<false, true>
+                            : p.retire ? (const void*)decoder_persistent_kernel<true>
+                                       : (const void*)decoder_persistent_kernel<false>;
     p.S_target = io.target_steps; p.Smax = S;
     p.zc = hp.zoneout_factor_cell; p.zh = hp.zoneout_factor_output;
     p.pre0 = h->pre0.desc(); p.pre1 = h->pre1.desc(); p.outp = h->outp.desc();
@@ -695,7 +703,7 @@ static int decoder_run_impl(sat_decoder* h, const sat_decoder_io* iop, void* str
     p.sa_q = ws + o_saq; p.sa_ctx = ws + o_sactx; p.sa_a = ws + o_saa; p.sa_y[0] = ws + o_say0; p.sa_y[1] = ws + o_say1;
     p.target = io.target; p.lengths = (const long long*)io.memory_lengths;
     p.mel = io.mel; p.stop = io.stop; p.dec_out = io.decoder_outputs; p.stop_steps = io.stop_steps; p.n_steps = io.n_steps;
-    p.barrier = h->barrier; p.prof = h->prof;
+    p.barrier = h->barrier; p.prof = prof_run ? h->prof : nullptr;
 
     // tensor-core form of the time-batched dense layers (dense_tc3_launch): worth it from a few hundred rows on
     const size_t rows_pack = std::max((size_t)B * T, (size_t)B * S);
@@ -880,6 +888,7 @@ extern "C" int sat_decoder_step(sat_decoder* h, const sat_decoder_io* iop, int32
 extern "C" int sat_decoder_profile(sat_decoder* h, int64_t* out16 /* N_PROF = 48 slots */, int32_t reset) {
   return guarded([&] {
     SAT_REQUIRE(h && out16, "null argument");
+    h->prof_on = true;  // the counters run from the next sat_decoder_run on
     SAT_CUDA(cudaDeviceSynchronize());
     SAT_CUDA(cudaMemcpy(out16, h->prof, sizeof(long long) * N_PROF, cudaMemcpyDeviceToHost));
     if (reset) SAT_CUDA(cudaMemset(h->prof, 0, sizeof(long long) * N_PROF));
@@ -892,6 +901,13 @@ extern "C" int sat_decoder_used_tensor_cores(sat_decoder* h, int32_t* used) {
   return guarded([&] {
     SAT_REQUIRE(h && used, "null argument");
     *used = h->last_tc;
+  });
+}
+
+extern "C" int sat_decoder_set_row_retirement(sat_decoder* h, int32_t on) {
+  return guarded([&] {
+    SAT_REQUIRE(h, "null argument");
+    h->retire_rows = on != 0;
   });
 }
 

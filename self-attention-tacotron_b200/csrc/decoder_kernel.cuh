@@ -317,7 +317,7 @@ __host__ __device__ inline int frame_smem_floats(int Dy, int Np_out, int Mnf, in
 
 // rows b[0..RR): (unless `prologue`) project y -> frame + stop token of step t, form the next input frame, and run
 // the prenet on it into the attention-LSTM input buffer of step t+1
-template <int RR, bool H>
+template <int RR, bool H, bool PROF>
 __device__ inline void frame_item(const DecParams& p, const int* b, int t, const float* y, int Dy, Act2D p1_dst,
                                   bool prologue, float* sm) {
   const int tid = threadIdx.x, ld = p.ld;
@@ -332,7 +332,7 @@ __device__ inline void frame_item(const DecParams& p, const int* b, int t, const
   float* part = s32 + 64;           // [2 * NT * 8]
   long long tp = 0;
   int ps = 32;
-  const bool profiling = p.prof && blockIdx.x == 0 && tid == 0 && !prologue;
+  const bool profiling = PROF && p.prof && blockIdx.x == 0 && tid == 0 && !prologue;
   if (profiling) tp = clock64();
   auto stamp = [&]() {
     if (profiling) {
@@ -422,27 +422,44 @@ __device__ inline void frame_item(const DecParams& p, const int* b, int t, const
 
 // all rows of the batch through frame_item, two per pass
 // live[0 .. n_live): the rows that still decode (RETIRE: the per-row stop rule has retired the others; else all rows)
-template <bool RETIRE>
+template <bool RETIRE, bool PROF>
 __device__ inline void frame_phase(const DecParams& p, int t, const float* y, int Dy, Act2D p1_dst, bool prologue, float* sm,
                                    const short* live, int n_live) {
   for (int l0 = blockIdx.x; l0 < n_live; l0 += 2 * gridDim.x) {
     const int l1 = l0 + (int)gridDim.x;
     const bool two = l1 < n_live;
-    int b[2] = {RETIRE ? (int)live[l0] : l0, RETIRE ? (two ? (int)live[l1] : 0) : l1};
+    int bl[2] = {l0, l1};
+    const int* b = bl;
+    if (RETIRE) {
+      // the live rows' indices stay in shared memory (re-read where needed): as two more registers through the whole item
+      // they cost the dense layers of this instantiation 17 % at the 128-register limit
+      __shared__ int s_fb[2];
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        s_fb[0] = live[l0];
+        s_fb[1] = two ? (int)live[l1] : 0;
+      }
+      __syncthreads();
+      b = s_fb;
+    }
     if (p.tc) {
-      if (two) frame_item<2, true>(p, b, t, y, Dy, p1_dst, prologue, sm);
-      else frame_item<1, true>(p, b, t, y, Dy, p1_dst, prologue, sm);
+      if (two) frame_item<2, true, PROF>(p, b, t, y, Dy, p1_dst, prologue, sm);
+      else frame_item<1, true, PROF>(p, b, t, y, Dy, p1_dst, prologue, sm);
     } else {
-      if (two) frame_item<2, false>(p, b, t, y, Dy, p1_dst, prologue, sm);
-      else frame_item<1, false>(p, b, t, y, Dy, p1_dst, prologue, sm);
+      if (two) frame_item<2, false, PROF>(p, b, t, y, Dy, p1_dst, prologue, sm);
+      else frame_item<1, false, PROF>(p, b, t, y, Dy, p1_dst, prologue, sm);
     }
   }
 }
 
 // RETIRE: the per-row stop rule retires stopped rows from the row-split phases (a separate instantiation, so that the
 // indirection through the live-row list costs the other stop rules nothing)
-template <bool RETIRE>
+// PROF: the per-phase cycle counters of CTA 0 (sat_decoder_profile).  A separate instantiation: compiled in, they cost the
+// plain kernel 2 % even when switched off at run time (registers and code at the 128-register limit, measured by an A/B
+// of two builds on one box); the profiling instantiation exists for the plain stop rules only.
+template <bool RETIRE, bool PROF = false>
 __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_constant__ DecParams p) {
+  long long* const kprof = PROF ? p.prof : nullptr;
   extern __shared__ __align__(16) float smem[];
   float* scratch = smem;                  // SCRATCH_FLOATS: reduction / row-phase scratch
   float* wres = smem + p.scratch_floats;  // resident LSTM tiles / tensor-core weight images
@@ -471,7 +488,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
   tcs.n_chunks = 0;
   tcs.n_items = 0;
   tcs.prefilled = 0;
-  tcs.prof = p.prof ? p.prof + 24 : nullptr;
+  tcs.prof = kprof ? kprof + 24 : nullptr;
   if (p.tc) {
     if (tid == 0) {
       for (int i = 0; i < 2 * TC_MAX_STAGES + 1; ++i) tc::mbar_init(s_tcbar + i, 1);
@@ -498,11 +515,11 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
   if (tid == 0) s_nlive = p.B;
   __syncthreads();
 
-  if (p.bench_barriers > 0 && p.prof) {
+  if (p.bench_barriers > 0 && kprof) {
     bar.sync();
     const long long c0 = clock64();
     for (int i = 0; i < p.bench_barriers; ++i) bar.sync();
-    if (blockIdx.x == 0 && tid == 0) p.prof[30] += clock64() - c0;
+    if (blockIdx.x == 0 && tid == 0) kprof[30] += clock64() - c0;
   }
   long long tprev = 0;
   int ph = 0;
@@ -516,9 +533,9 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
     } else {
       bar.sync();
     }
-    if (p.prof && blockIdx.x == 0 && tid == 0 && tprev) {  // (tprev == 0: the barrier in front of the first step)
+    if (kprof && blockIdx.x == 0 && tid == 0 && tprev) {  // (tprev == 0: the barrier in front of the first step)
       const long long now = clock64();
-      p.prof[ph] += now - tprev;
+      kprof[ph] += now - tprev;
       tprev = now;
     }
     ++ph;
@@ -536,7 +553,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
   if (p.t_begin > 0) {
     // continued run: the previous launch left the prenet of this step's input frame in place
   } else if (p.batched_tail) copy_prenet(0, Act2D{p.att_in[0], p.tc ? 0 : ld, p.tc ? p.Ka_pad / 64 : 1, p.tc});
-  else frame_phase<RETIRE>(p, 0, nullptr, 0, Act2D{p.att_in[0], p.tc ? 0 : ld, p.tc ? p.Ka_pad / 64 : 1, p.tc}, true, scratch, s_live, p.B);
+  else frame_phase<RETIRE, PROF>(p, 0, nullptr, 0, Act2D{p.att_in[0], p.tc ? 0 : ld, p.tc ? p.Ka_pad / 64 : 1, p.tc}, true, scratch, s_live, p.B);
   auto row_of = [&](int li) { return RETIRE ? (int)s_live[li] : li; };
   if (p.tc) phase_end(&p.tc_a, p.att_in[p.t_begin & 1]);
   else bar.sync();
@@ -545,7 +562,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
   for (; t < p.t_end; ++t) {
     const int cur = t & 1, nxt = cur ^ 1;
     ph = 0;
-    if (p.prof && blockIdx.x == 0 && tid == 0) tprev = clock64();
+    if (kprof && blockIdx.x == 0 && tid == 0) tprev = clock64();
     // ---- C: attention LSTM ----
     if (p.tc) {
       // fp16 row-major buffers: att_in = [prenet | context | zoned h], l1_in = [h_a | context | zoned h1]
@@ -579,7 +596,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
         m.ctx_dst[1] = p.l1_in[cur] + (size_t)(p.A + coff) * ld;
         m.ctx_sd[0] = m.ctx_sd[1] = ld;
         m.ctx_sb[0] = m.ctx_sb[1] = 1;
-        m.prof = p.prof ? p.prof + 16 : nullptr;
+        m.prof = kprof ? kprof + 16 : nullptr;
         if (split || crank == 0) {
           // the row's attention state goes in flight together with the query-layer input
           attention_load_state<NT>(m, b, p.T, scratch + p.cl_att_off);
@@ -669,7 +686,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
             m.ctx_sd[0] = m.ctx_sd[1] = ld;
             m.ctx_sb[0] = m.ctx_sb[1] = 1;
           }
-          m.prof = p.prof ? p.prof + 16 : nullptr;
+          m.prof = kprof ? kprof + 16 : nullptr;
         };
         if (p.att_pair && pair && att_row_pairable(p.mech[mi0])) {
           // two rows of the same mechanism: one per half of the CTA, concurrently (named barriers 1 / 2)
@@ -677,7 +694,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
           AttMech m;
           setup(items[gid], m);
           const int b = row_of(items[gid] / p.n_mech);
-          if (RETIRE) attention_item_inl<NT / 2>(m, b, t, p.T, (int)p.lengths[b], scratch + gid * p.att_row_floats, gid);
+          if (RETIRE || PROF) attention_item_inl<NT / 2>(m, b, t, p.T, (int)p.lengths[b], scratch + gid * p.att_row_floats, gid);
           else attention_item<NT / 2>(m, b, t, p.T, (int)p.lengths[b], scratch + gid * p.att_row_floats, gid);
           __syncthreads();  // both halves are done with the scratch
         } else {
@@ -685,7 +702,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
             AttMech m;
             setup(items[q], m);
             const int b = row_of(items[q] / p.n_mech);
-            if (RETIRE) attention_item_inl<NT>(m, b, t, p.T, (int)p.lengths[b], scratch);
+            if (RETIRE || PROF) attention_item_inl<NT>(m, b, t, p.T, (int)p.lengths[b], scratch);
             else attention_item<NT>(m, b, t, p.T, (int)p.lengths[b], scratch);
           }
         }
@@ -747,7 +764,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
         y = p.sa_y[hi & 1];
       }
       // ---- L+A+B: frame + stop projection of step t, fed-back frame, prenet of step t+1 (row split) ----
-      frame_phase<RETIRE>(p, t, y, p.outp.K, Act2D{p.att_in[nxt], p.tc ? 0 : ld, p.tc ? p.Ka_pad / 64 : 1, p.tc}, false, scratch,
+      frame_phase<RETIRE, PROF>(p, t, y, p.outp.K, Act2D{p.att_in[nxt], p.tc ? 0 : ld, p.tc ? p.Ka_pad / 64 : 1, p.tc}, false, scratch,
                           s_live, RETIRE ? s_nlive : p.B);
       if (p.tc && t + 1 < p.t_end) phase_end(&p.tc_a, p.att_in[nxt]);
       else phase_end();

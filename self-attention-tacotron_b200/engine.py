@@ -117,6 +117,10 @@ class DecoderHandle:
         check(lib().sat_decoder_used_tensor_cores(self._h, C.byref(used)))
         return bool(used.value)
 
+    def set_row_retirement(self, on):
+        """per-row stop rule: retire stopped rows from the row-split phases (default) or let them run on"""
+        check(lib().sat_decoder_set_row_retirement(self._h, C.c_int32(1 if on else 0)))
+
     def cluster_size(self):
         size = C.c_int32()
         check(lib().sat_decoder_cluster_size(self._h, C.byref(size)))

@@ -219,6 +219,7 @@ class _DecoderBase:
         self._handles = {}
         self.stop_mode = "all_rows"  # reference rule (helpers.py:156-160); "per_row" retires rows individually
         self.async_results = False   # True: a free run returns full-length tensors and n_steps as a device tensor
+        self.retire_rows = True      # "per_row": stopped rows leave the row-split phases (False: they run on; same results)
 
     def _handle(self, mechs, speaker_embed):
         kinds = tuple(m.kind for m in mechs)
@@ -298,6 +299,7 @@ class _DecoderBase:
         else:
             helper = helpers.StopTokenBasedInferenceHelper(B, hp.num_mels, r, n_feed_frame=hp.n_feed_frame)
             stop = helper.stop_mode if self.stop_mode == "all_rows" else _lib.STOP_PER_ROW
+            h.set_row_retirement(self.retire_rows)
             out = h.run([m.memory for m in mechs], mechs[0].memory_sequence_length, feed_mode=helper.feed_mode,
                         stop_mode=stop, max_steps=self.max_iters, min_iters=helper.min_iters, **kw)
         if is_validation:

@@ -88,8 +88,11 @@ class _HostSlot:
         return host
 
 
+RETIRE_SPREAD = 0.7  # predict(): rows are retired in batches whose shortest source is below this fraction of the longest
+
+
 def predict(hparams, weights, utterances, output_dir=None, batch_size=None, device=None, rank=0, world_size=1,
-            mode="free_run", model=None, batch_hook=None, pinned_results=False):
+            mode="free_run", model=None, batch_hook=None, pinned_results=False, retire_rows=None):
     """Synthesise ``utterances`` (list of Utterance) -> list[PredictedMel] for the ones this rank owns.
 
     mode: 'free_run' (stop-token inference, PREDICT), 'validation' / 'teacher_forced' (EVAL forms).
@@ -99,6 +102,9 @@ def predict(hparams, weights, utterances, output_dir=None, batch_size=None, devi
     into pinned host memory on a copy stream while batch i+1 is padded, uploaded and computed; slicing per utterance
     and the file writes of batch i happen on the host during that compute.  ``batch_hook(i)`` (optional) runs on the
     compute stream before batch i is launched (bench.py flushes L2 there).
+
+    ``retire_rows``: None (default) -- per batch, by the spread of the source lengths (RETIRE_SPREAD); True / False force it.
+    The results are the same either way (frames up to each row's own stop step).
 
     ``pinned_results``: False (default) -- two pinned buffer sets are reused and every batch's results are copied out
     of them into ordinary arrays (host threads, in row blocks); right for a one-shot run that keeps all its results.
@@ -112,7 +118,7 @@ def predict(hparams, weights, utterances, output_dir=None, batch_size=None, devi
     # The reference's predict forces batch_size=1 (predict_mel.py:43-44), so an utterance never sees padding and stops on
     # its own stop token.  Batches here keep that per-utterance result: padded encoder frames are masked, and every
     # row stops by its own rule (the run ends when the last row has stopped).
-    saved = (model.encoder.mask_padding, model.decoder.stop_mode, model.decoder.async_results)
+    saved = (model.encoder.mask_padding, model.decoder.stop_mode, model.decoder.async_results, model.decoder.retire_rows)
     model.encoder.set_mask_padding(True)
     model.decoder.stop_mode = "per_row"
     model.decoder.async_results = not hparams.use_forced_alignment_mode  # no host sync inside model.predict()
@@ -133,6 +139,11 @@ def predict(hparams, weights, utterances, output_dir=None, batch_size=None, devi
             raise ValueError(f"mode {mode!r} needs ground-truth mel for every utterance")
         if batch_hook is not None:
             batch_hook(i)
+        # Row retirement costs ~10 % per step until rows stop and pays once they stop far apart.  Output length follows
+        # source length, and the buckets hold utterances of similar length: retire only in batches whose shortest source
+        # is less than RETIRE_SPREAD of the longest (ragged tails, small corpora, fixed-width buckets).
+        model.decoder.retire_rows = (retire_rows if retire_rows is not None else
+                                     min(len(u.source) for u in utts) < RETIRE_SPREAD * max(len(u.source) for u in utts))
         out = model.predict(ids, lengths, target=target if need_target else None, speaker_id=spk,
                             is_validation=mode != "free_run", teacher_forcing=mode == "teacher_forced")
         done = torch.cuda.Event()
@@ -208,7 +219,7 @@ def predict(hparams, weights, utterances, output_dir=None, batch_size=None, devi
     finally:
         pool.shutdown(wait=True)
         model.encoder.set_mask_padding(saved[0])
-        model.decoder.stop_mode, model.decoder.async_results = saved[1], saved[2]
+        model.decoder.stop_mode, model.decoder.async_results, model.decoder.retire_rows = saved[1], saved[2], saved[3]
     return results
 
 

@@ -137,6 +137,13 @@ def test_predict_mel_free_run_writes_mfbsp(tmp_path):
     for a, b in zip(res, res2):
         np.testing.assert_array_equal(a.predicted_mel, b.predicted_mel)
         np.testing.assert_array_equal(a.alignment, b.alignment)
+    # row retirement is a scheduling choice (predict() picks it per batch from the spread of the source lengths: on for
+    # this ragged batch): forced on or off, every utterance keeps its frames up to its own stop step
+    for forced in (True, False):
+        res3 = predict(hp, W, utts, batch_size=8, retire_rows=forced)
+        for a, b in zip(res, res3):
+            assert a.predicted_mel.shape == b.predicted_mel.shape
+            assert rel_err(b.predicted_mel, a.predicted_mel) <= 1e-6
 
 
 def test_predict_mel_from_reference_tfrecords(tmp_path):
