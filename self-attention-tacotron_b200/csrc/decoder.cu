@@ -379,6 +379,8 @@ extern "C" int sat_decoder_create(const sat_hparams* hpp, const sat_tensor* weig
     SAT_CUDA(cudaFuncSetAttribute(decoder_persistent_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->max_dyn_smem));
     SAT_CUDA(cudaFuncSetAttribute(decoder_persistent_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->max_dyn_smem));
     SAT_CUDA(cudaFuncSetAttribute(decoder_persistent_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->max_dyn_smem));
+    SAT_CUDA(cudaFuncSetAttribute(decoder_persistent_kernel<false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)h->max_dyn_smem));
     h->grid = h->sm_count;
     h->barrier = pool.alloc<unsigned>(1);
     h->prof = pool.alloc<long long>(N_PROF);
@@ -841,7 +843,11 @@ static int decoder_run_impl(sat_decoder* h, const sat_decoder_io* iop, void* str
       at[1].id = cudaLaunchAttributeClusterDimension;
       at[1].val.clusterDim.x = p.cl; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
       cfg.attrs = at; cfg.numAttrs = p.cl > 1 ? 2 : 1;
-      SAT_CUDA(cudaLaunchKernelExC(&cfg, kernel_fn, args));
+      // the specialised instantiation of the plain kernel: tensor-core form, no cluster-split rows, no KV-cached hops
+      const void* launch_fn = kernel_fn;
+      if (!prof_run && !p.retire && p.tc && p.cl == 1 && p.hops == 0 && !getenv("SAT_NO_SPEC"))
+        launch_fn = (const void*)decoder_persistent_kernel<false, false, true>;
+      SAT_CUDA(cudaLaunchKernelExC(&cfg, launch_fn, args));
     }
     SAT_CUDA(cudaEventRecord(h->ev1, st));
     h->last_B = B; h->last_T = T; h->last_S = S;

@@ -422,7 +422,7 @@ __device__ inline void frame_item(const DecParams& p, const int* b, int t, const
 
 // all rows of the batch through frame_item, two per pass
 // live[0 .. n_live): the rows that still decode (RETIRE: the per-row stop rule has retired the others; else all rows)
-template <bool RETIRE, bool PROF>
+template <bool RETIRE, bool PROF, bool SPEC>
 __device__ inline void frame_phase(const DecParams& p, int t, const float* y, int Dy, Act2D p1_dst, bool prologue, float* sm,
                                    const short* live, int n_live) {
   for (int l0 = blockIdx.x; l0 < n_live; l0 += 2 * gridDim.x) {
@@ -442,7 +442,7 @@ __device__ inline void frame_phase(const DecParams& p, int t, const float* y, in
       __syncthreads();
       b = s_fb;
     }
-    if (p.tc) {
+    if (SPEC || p.tc) {
       if (two) frame_item<2, true, PROF>(p, b, t, y, Dy, p1_dst, prologue, sm);
       else frame_item<1, true, PROF>(p, b, t, y, Dy, p1_dst, prologue, sm);
     } else {
@@ -457,9 +457,14 @@ __device__ inline void frame_phase(const DecParams& p, int t, const float* y, in
 // PROF: the per-phase cycle counters of CTA 0 (sat_decoder_profile).  A separate instantiation: compiled in, they cost the
 // plain kernel 2 % even when switched off at run time (registers and code at the 128-register limit, measured by an A/B
 // of two builds on one box); the profiling instantiation exists for the plain stop rules only.
-template <bool RETIRE, bool PROF = false>
+// SPEC: the instantiation for the tensor-core form without cluster-split rows and without KV-cached hops (the baseline
+// Tacotron decoder at B >= 64, what bench.py times): those run-time switches become constants and the fp32 SIMT forms of
+// the phases drop out of the kernel, which at the 128-register limit is worth a few per cent.
+template <bool RETIRE, bool PROF = false, bool SPEC = false>
 __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_constant__ DecParams p) {
   long long* const kprof = PROF ? p.prof : nullptr;
+  const bool k_tc = SPEC ? true : p.tc != 0;
+  const int k_cl = SPEC ? 1 : p.cl, k_hops = SPEC ? 0 : p.hops;
   extern __shared__ __align__(16) float smem[];
   float* scratch = smem;                  // SCRATCH_FLOATS: reduction / row-phase scratch
   float* wres = smem + p.scratch_floats;  // resident LSTM tiles / tensor-core weight images
@@ -489,7 +494,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
   tcs.n_items = 0;
   tcs.prefilled = 0;
   tcs.prof = kprof ? kprof + 24 : nullptr;
-  if (p.tc) {
+  if (k_tc) {
     if (tid == 0) {
       for (int i = 0; i < 2 * TC_MAX_STAGES + 1; ++i) tc::mbar_init(s_tcbar + i, 1);
       tc::fence_mbar_init();
@@ -552,10 +557,10 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
   // prenet of the <GO> frame -> attention-LSTM input of step 0
   if (p.t_begin > 0) {
     // continued run: the previous launch left the prenet of this step's input frame in place
-  } else if (p.batched_tail) copy_prenet(0, Act2D{p.att_in[0], p.tc ? 0 : ld, p.tc ? p.Ka_pad / 64 : 1, p.tc});
-  else frame_phase<RETIRE, PROF>(p, 0, nullptr, 0, Act2D{p.att_in[0], p.tc ? 0 : ld, p.tc ? p.Ka_pad / 64 : 1, p.tc}, true, scratch, s_live, p.B);
+  } else if (p.batched_tail) copy_prenet(0, Act2D{p.att_in[0], k_tc ? 0 : ld, k_tc ? p.Ka_pad / 64 : 1, k_tc});
+  else frame_phase<RETIRE, PROF, SPEC>(p, 0, nullptr, 0, Act2D{p.att_in[0], k_tc ? 0 : ld, k_tc ? p.Ka_pad / 64 : 1, k_tc}, true, scratch, s_live, p.B);
   auto row_of = [&](int li) { return RETIRE ? (int)s_live[li] : li; };
-  if (p.tc) phase_end(&p.tc_a, p.att_in[p.t_begin & 1]);
+  if (k_tc) phase_end(&p.tc_a, p.att_in[p.t_begin & 1]);
   else bar.sync();
 
   int t = p.t_begin, fired = 0;
@@ -564,7 +569,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
     ph = 0;
     if (kprof && blockIdx.x == 0 && tid == 0) tprev = clock64();
     // ---- C: attention LSTM ----
-    if (p.tc) {
+    if (k_tc) {
       // fp16 row-major buffers: att_in = [prenet | context | zoned h], l1_in = [h_a | context | zoned h1]
       const int h0 = p.P1 + p.Dctx;
       TcLstmIO io{(const __half*)p.att_in[cur], Act2D{p.l1_in[cur], 0, p.K1_pad / 64, 1}, Act2D{p.qfm, ld, 1, 0},
@@ -582,11 +587,11 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
     // ---- D+E: query layers and attention mechanisms (row split, no barrier in between) ----
     // The processed query of a row is a row-local dense on the attention-LSTM output, so the CTA that owns the row's
     // attention item computes it itself (two rows per pass share one stream of the query-layer weights from L2).
-    if (p.cl > 1) {
+    if (k_cl > 1) {
       // cluster-split form (fp32 SIMT mode only): item = cluster index, every CTA of the cluster works on it
       const float* qsrc = p.l1_in[cur];  // feature-major [A][ld]
-      const int n_items = (RETIRE ? s_nlive : p.B) * p.n_mech, ncl = gridDim.x / p.cl, crank = (int)cluster_ctarank();
-      for (int item = blockIdx.x / p.cl; item < n_items; item += ncl) {
+      const int n_items = (RETIRE ? s_nlive : p.B) * p.n_mech, ncl = gridDim.x / k_cl, crank = (int)cluster_ctarank();
+      for (int item = blockIdx.x / k_cl; item < n_items; item += ncl) {
         const int mi = item % p.n_mech, b = row_of(item / p.n_mech);
         const bool split = p.cl_split[mi] != 0;
         AttMech m = p.mech[mi];
@@ -622,13 +627,13 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
             __syncthreads();
           }
           attention_item<NT>(m, b, t, p.T, (int)p.lengths[b], scratch + p.cl_att_off, 0, split ? crank : 0,
-                             split ? p.cl : 1, true);
+                             split ? k_cl : 1, true);
         }
         // the next item's remote partial energies must not land while a CTA of the cluster still reads this item's
         if (item + ncl < n_items) cluster_sync_all();
       }
     } else {
-      const float* qsrc = p.tc ? p.qfm : p.l1_in[cur];  // feature-major [A][ld]
+      const float* qsrc = k_tc ? p.qfm : p.l1_in[cur];  // feature-major [A][ld]
       const int n_items = (RETIRE ? s_nlive : p.B) * p.n_mech;  // item i = (live row i / n_mech, mechanism i % n_mech)
       for (int i0 = blockIdx.x; i0 < n_items; i0 += 2 * gridDim.x) {
         const int i1 = i0 + gridDim.x;
@@ -652,7 +657,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
             xs[r * p.A + k] = __ldcg(qsrc + (size_t)k * ld + rows[r]);
           }
           __syncthreads();
-          if (p.tc) {
+          if (k_tc) {
             if (nq == 2) row_dense<2, true>(dq, xs, p.A, part, outs, 0);
             else row_dense<1, true>(dq, xs, p.A, part, outs, 0);
           } else {
@@ -670,7 +675,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
           const int mi = item % p.n_mech;
           m = p.mech[mi];
           const int coff = mi ? p.mech[0].Dv : 0;
-          if (p.tc) {
+          if (k_tc) {
             // fp16 operand-tile order (tc_act_index): ctx_sd = feature offset of the context, ctx_sb = chunks per row
             m.ctx_dst[0] = p.att_in[nxt];
             m.ctx_dst[1] = p.l1_in[cur];
@@ -708,12 +713,12 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
         }
       }
     }
-    if (p.tc) phase_end(&p.tc_1, p.l1_in[cur]);
+    if (k_tc) phase_end(&p.tc_1, p.l1_in[cur]);
     else phase_end();
     // ---- F: decoder LSTM 1 ----
     if (p.batched_tail && t + 1 < p.max_steps)
-      copy_prenet(t + 1, Act2D{p.att_in[nxt], p.tc ? 0 : ld, p.tc ? p.Ka_pad / 64 : 1, p.tc});
-    if (p.tc) {
+      copy_prenet(t + 1, Act2D{p.att_in[nxt], k_tc ? 0 : ld, k_tc ? p.Ka_pad / 64 : 1, k_tc});
+    if (k_tc) {
       const int h0 = p.A + p.Dctx;
       TcLstmIO io{(const __half*)p.l1_in[cur], Act2D{p.l2_in[cur], 0, p.K2_pad / 64, 1}, Act2D{nullptr, 0, 0, 0},
                   Act2D{p.l1_in[nxt], h0, p.K1_pad / 64, 1}, nullptr, 0, 0};
@@ -726,10 +731,10 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
                   LstmEpi{p.lstm_1.bias, p.Dd, ld, p.B, p.c_1, p.l1_in[cur] + hoff, p.l2_in[cur],
                           p.l1_in[nxt] + hoff, nullptr, 0, 0, p.zc, p.zh});
     }
-    if (p.tc) phase_end(&p.tc_2, p.l2_in[cur]);
+    if (k_tc) phase_end(&p.tc_2, p.l2_in[cur]);
     else phase_end();
     // ---- G: decoder LSTM 2 ----
-    if (p.tc) {
+    if (k_tc) {
       const int h0 = p.Dd;
       TcLstmIO io{(const __half*)p.l2_in[cur], Act2D{p.dout, ld, 1, 0}, Act2D{nullptr, 0, 0, 0},
                   Act2D{p.l2_in[nxt], h0, p.K2_pad / 64, 1}, p.dec_out, p.max_steps * p.Dd, t * p.Dd};
@@ -742,12 +747,12 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
                   LstmEpi{p.lstm_2.bias, p.Dd, ld, p.B, p.c_2, p.l2_in[cur] + hoff, p.dout,
                           p.l2_in[nxt] + hoff, p.dec_out, p.max_steps * p.Dd, t * p.Dd, p.zc, p.zh});
     }
-    if (p.tc && p.batched_tail && t + 1 < p.t_end) phase_end(&p.tc_a, p.att_in[nxt]);
+    if (k_tc && p.batched_tail && t + 1 < p.t_end) phase_end(&p.tc_a, p.att_in[nxt]);
     else phase_end();
     if (!p.batched_tail) {
       // ---- H-K: decoder self-attention hops over the KV cache ----
       const float* y = p.dout;
-      for (int hi = 0; hi < p.hops; ++hi) {
+      for (int hi = 0; hi < k_hops; ++hi) {
         const SaHop& h = p.hop[hi];
         dense_phase(h.qkv, y, ld, p.Bp, wres, scratch,
                     QkvEpi{h.qkv.bias, p.Ds, p.Ds / p.heads, p.heads, p.Smax, t, ld, p.B, h.kcache, h.vcache, p.sa_q});
@@ -764,9 +769,9 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
         y = p.sa_y[hi & 1];
       }
       // ---- L+A+B: frame + stop projection of step t, fed-back frame, prenet of step t+1 (row split) ----
-      frame_phase<RETIRE, PROF>(p, t, y, p.outp.K, Act2D{p.att_in[nxt], p.tc ? 0 : ld, p.tc ? p.Ka_pad / 64 : 1, p.tc}, false, scratch,
+      frame_phase<RETIRE, PROF, SPEC>(p, t, y, p.outp.K, Act2D{p.att_in[nxt], k_tc ? 0 : ld, k_tc ? p.Ka_pad / 64 : 1, k_tc}, false, scratch,
                           s_live, RETIRE ? s_nlive : p.B);
-      if (p.tc && t + 1 < p.t_end) phase_end(&p.tc_a, p.att_in[nxt]);
+      if (k_tc && t + 1 < p.t_end) phase_end(&p.tc_a, p.att_in[nxt]);
       else phase_end();
     }
     // ---- stop rule (every CTA evaluates the same data -> same decision) ----
@@ -814,7 +819,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
     *p.n_steps = t;
     if (p.finished) *p.finished = fired;
   }
-  if (p.tc) {
+  if (k_tc) {
     if (tid == 0) {
       // a stop decision can leave the requests for the next step in flight: let them land before the CTA exits
       for (uint32_t c = 0; c < tcs.prefilled; ++c) {
