@@ -843,9 +843,10 @@ static int decoder_run_impl(sat_decoder* h, const sat_decoder_io* iop, void* str
       at[1].id = cudaLaunchAttributeClusterDimension;
       at[1].val.clusterDim.x = p.cl; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
       cfg.attrs = at; cfg.numAttrs = p.cl > 1 ? 2 : 1;
-      // the specialised instantiation of the plain kernel: tensor-core form, no cluster-split rows, no KV-cached hops
+      // the specialised instantiation of the plain kernel (free-running baseline decoder, B >= 64; decoder_kernel.cuh)
       const void* launch_fn = kernel_fn;
-      if (!prof_run && !p.retire && p.tc && p.cl == 1 && p.hops == 0 && !getenv("SAT_NO_SPEC"))
+      if (!prof_run && !p.retire && p.tc && p.cl == 1 && p.hops == 0 && p.n_mech == 1 && !p.batched_tail && p.fused_prenet0 && !p.ms &&
+          !getenv("SAT_NO_SPEC"))
         launch_fn = (const void*)decoder_persistent_kernel<false, false, true>;
       SAT_CUDA(cudaLaunchKernelExC(&cfg, launch_fn, args));
     }

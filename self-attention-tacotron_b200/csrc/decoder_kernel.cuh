@@ -317,7 +317,7 @@ __host__ __device__ inline int frame_smem_floats(int Dy, int Np_out, int Mnf, in
 
 // rows b[0..RR): (unless `prologue`) project y -> frame + stop token of step t, form the next input frame, and run
 // the prenet on it into the attention-LSTM input buffer of step t+1
-template <int RR, bool H, bool PROF>
+template <int RR, bool H, bool PROF, bool SPEC = false>
 __device__ inline void frame_item(const DecParams& p, const int* b, int t, const float* y, int Dy, Act2D p1_dst,
                                   bool prologue, float* sm) {
   const int tid = threadIdx.x, ld = p.ld;
@@ -358,7 +358,7 @@ __device__ inline void frame_item(const DecParams& p, const int* b, int t, const
       else p.mel[((size_t)b[r] * p.max_steps + t) * p.Mr + n] = v;
     }
     const int f0 = p.Mr - p.Mnf;
-    if (p.fused_prenet0) {
+    if (SPEC || p.fused_prenet0) {
       // self feed with prenet layer 0 folded into the projection: its pre-activations are columns Mr + 1 .. of `os`
       for (int i = tid; i < RR * p.P0; i += NT) {
         const int r = i / p.P0, n = i - r * p.P0;
@@ -396,10 +396,10 @@ __device__ inline void frame_item(const DecParams& p, const int* b, int t, const
   __syncthreads();
   ps = 34;
   stamp();
-  if (prologue || !p.fused_prenet0) row_dense<RR, H>(p.pre0, fr, p.Mnf, part, p0s, 1);
+  if (prologue || !(SPEC || p.fused_prenet0)) row_dense<RR, H>(p.pre0, fr, p.Mnf, part, p0s, 1);
   stamp();
   const float* pin = p0s;
-  if (p.ms) {
+  if (!SPEC && p.ms) {
     // MultiSpeakerPreNet: relu(dense0(x)) + softsign(speaker projection), then a second relu dense
     for (int i = tid; i < RR * p.P0; i += NT) {
       const int r = i / p.P0, n = i - r * p.P0;
@@ -443,8 +443,8 @@ __device__ inline void frame_phase(const DecParams& p, int t, const float* y, in
       b = s_fb;
     }
     if (SPEC || p.tc) {
-      if (two) frame_item<2, true, PROF>(p, b, t, y, Dy, p1_dst, prologue, sm);
-      else frame_item<1, true, PROF>(p, b, t, y, Dy, p1_dst, prologue, sm);
+      if (two) frame_item<2, true, PROF, SPEC>(p, b, t, y, Dy, p1_dst, prologue, sm);
+      else frame_item<1, true, PROF, SPEC>(p, b, t, y, Dy, p1_dst, prologue, sm);
     } else {
       if (two) frame_item<2, false, PROF>(p, b, t, y, Dy, p1_dst, prologue, sm);
       else frame_item<1, false, PROF>(p, b, t, y, Dy, p1_dst, prologue, sm);
@@ -457,14 +457,16 @@ __device__ inline void frame_phase(const DecParams& p, int t, const float* y, in
 // PROF: the per-phase cycle counters of CTA 0 (sat_decoder_profile).  A separate instantiation: compiled in, they cost the
 // plain kernel 2 % even when switched off at run time (registers and code at the 128-register limit, measured by an A/B
 // of two builds on one box); the profiling instantiation exists for the plain stop rules only.
-// SPEC: the instantiation for the tensor-core form without cluster-split rows and without KV-cached hops (the baseline
-// Tacotron decoder at B >= 64, what bench.py times): those run-time switches become constants and the fp32 SIMT forms of
+// SPEC: the instantiation for the free-running baseline Tacotron decoder at B >= 64 (what bench.py times): tensor-core
+// form, one attention mechanism, no cluster-split rows, no KV-cached hops, no time-batched tail, self feed with prenet
+// layer 0 folded into the projection, no speaker term.  Those run-time switches become constants and the other forms of
 // the phases drop out of the kernel, which at the 128-register limit is worth a few per cent.
 template <bool RETIRE, bool PROF = false, bool SPEC = false>
 __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_constant__ DecParams p) {
   long long* const kprof = PROF ? p.prof : nullptr;
   const bool k_tc = SPEC ? true : p.tc != 0;
-  const int k_cl = SPEC ? 1 : p.cl, k_hops = SPEC ? 0 : p.hops;
+  const int k_cl = SPEC ? 1 : p.cl, k_hops = SPEC ? 0 : p.hops, k_nmech = SPEC ? 1 : p.n_mech;
+  const bool k_tail = SPEC ? false : p.batched_tail != 0;
   extern __shared__ __align__(16) float smem[];
   float* scratch = smem;                  // SCRATCH_FLOATS: reduction / row-phase scratch
   float* wres = smem + p.scratch_floats;  // resident LSTM tiles / tensor-core weight images
@@ -557,7 +559,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
   // prenet of the <GO> frame -> attention-LSTM input of step 0
   if (p.t_begin > 0) {
     // continued run: the previous launch left the prenet of this step's input frame in place
-  } else if (p.batched_tail) copy_prenet(0, Act2D{p.att_in[0], k_tc ? 0 : ld, k_tc ? p.Ka_pad / 64 : 1, k_tc});
+  } else if (k_tail) copy_prenet(0, Act2D{p.att_in[0], k_tc ? 0 : ld, k_tc ? p.Ka_pad / 64 : 1, k_tc});
   else frame_phase<RETIRE, PROF, SPEC>(p, 0, nullptr, 0, Act2D{p.att_in[0], k_tc ? 0 : ld, k_tc ? p.Ka_pad / 64 : 1, k_tc}, true, scratch, s_live, p.B);
   auto row_of = [&](int li) { return RETIRE ? (int)s_live[li] : li; };
   if (k_tc) phase_end(&p.tc_a, p.att_in[p.t_begin & 1]);
@@ -590,9 +592,9 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
     if (k_cl > 1) {
       // cluster-split form (fp32 SIMT mode only): item = cluster index, every CTA of the cluster works on it
       const float* qsrc = p.l1_in[cur];  // feature-major [A][ld]
-      const int n_items = (RETIRE ? s_nlive : p.B) * p.n_mech, ncl = gridDim.x / k_cl, crank = (int)cluster_ctarank();
+      const int n_items = (RETIRE ? s_nlive : p.B) * k_nmech, ncl = gridDim.x / k_cl, crank = (int)cluster_ctarank();
       for (int item = blockIdx.x / k_cl; item < n_items; item += ncl) {
-        const int mi = item % p.n_mech, b = row_of(item / p.n_mech);
+        const int mi = item % k_nmech, b = row_of(item / k_nmech);
         const bool split = p.cl_split[mi] != 0;
         AttMech m = p.mech[mi];
         const int coff = mi ? p.mech[0].Dv : 0;
@@ -634,24 +636,24 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
       }
     } else {
       const float* qsrc = k_tc ? p.qfm : p.l1_in[cur];  // feature-major [A][ld]
-      const int n_items = (RETIRE ? s_nlive : p.B) * p.n_mech;  // item i = (live row i / n_mech, mechanism i % n_mech)
+      const int n_items = (RETIRE ? s_nlive : p.B) * k_nmech;  // item i = (live row i / n_mech, mechanism i % n_mech)
       for (int i0 = blockIdx.x; i0 < n_items; i0 += 2 * gridDim.x) {
         const int i1 = i0 + gridDim.x;
         const int nit = i1 < n_items ? 2 : 1;
         const int items[2] = {i0, i1};
-        const int mi0 = i0 % p.n_mech;
+        const int mi0 = i0 % k_nmech;
         // the items of one CTA share the mechanism whenever gridDim.x is a multiple of n_mech; otherwise one at a time
-        const bool pair = nit == 2 && (i1 % p.n_mech) == mi0;
+        const bool pair = nit == 2 && (i1 % k_nmech) == mi0;
         for (int q0 = 0; q0 < nit; q0 += pair ? 2 : 1) {
           const int nq = pair ? 2 : 1;
-          const int mi = items[q0] % p.n_mech;
+          const int mi = items[q0] % k_nmech;
           if (p.mech[mi].kind == SAT_ATT_TEACHER_FORCING) continue;
           const DenseDesc& dq = p.dq[mi];
           float* xs = scratch;                 // [2][A]
           float* outs = xs + al4(2 * p.A);     // [2][Np]
           float* part = outs + 2 * dq.Np;      // [2 * NT * 8]
           int rows[2];
-          for (int r = 0; r < nq; ++r) rows[r] = row_of(items[q0 + r] / p.n_mech);
+          for (int r = 0; r < nq; ++r) rows[r] = row_of(items[q0 + r] / k_nmech);
           for (int i = tid; i < nq * p.A; i += NT) {
             const int r = i / p.A, k = i - r * p.A;
             xs[r * p.A + k] = __ldcg(qsrc + (size_t)k * ld + rows[r]);
@@ -672,7 +674,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
           __syncthreads();
         }
         auto setup = [&](int item, AttMech& m) {
-          const int mi = item % p.n_mech;
+          const int mi = item % k_nmech;
           m = p.mech[mi];
           const int coff = mi ? p.mech[0].Dv : 0;
           if (k_tc) {
@@ -698,7 +700,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
           const int gid = tid / (NT / 2);
           AttMech m;
           setup(items[gid], m);
-          const int b = row_of(items[gid] / p.n_mech);
+          const int b = row_of(items[gid] / k_nmech);
           if (RETIRE || PROF) attention_item_inl<NT / 2>(m, b, t, p.T, (int)p.lengths[b], scratch + gid * p.att_row_floats, gid);
           else attention_item<NT / 2>(m, b, t, p.T, (int)p.lengths[b], scratch + gid * p.att_row_floats, gid);
           __syncthreads();  // both halves are done with the scratch
@@ -706,7 +708,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
           for (int q = 0; q < nit; ++q) {
             AttMech m;
             setup(items[q], m);
-            const int b = row_of(items[q] / p.n_mech);
+            const int b = row_of(items[q] / k_nmech);
             if (RETIRE || PROF) attention_item_inl<NT>(m, b, t, p.T, (int)p.lengths[b], scratch);
             else attention_item<NT>(m, b, t, p.T, (int)p.lengths[b], scratch);
           }
@@ -716,7 +718,7 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
     if (k_tc) phase_end(&p.tc_1, p.l1_in[cur]);
     else phase_end();
     // ---- F: decoder LSTM 1 ----
-    if (p.batched_tail && t + 1 < p.max_steps)
+    if (k_tail && t + 1 < p.max_steps)
       copy_prenet(t + 1, Act2D{p.att_in[nxt], k_tc ? 0 : ld, k_tc ? p.Ka_pad / 64 : 1, k_tc});
     if (k_tc) {
       const int h0 = p.A + p.Dctx;
@@ -747,9 +749,9 @@ __global__ void __launch_bounds__(NT, 1) decoder_persistent_kernel(const __grid_
                   LstmEpi{p.lstm_2.bias, p.Dd, ld, p.B, p.c_2, p.l2_in[cur] + hoff, p.dout,
                           p.l2_in[nxt] + hoff, p.dec_out, p.max_steps * p.Dd, t * p.Dd, p.zc, p.zh});
     }
-    if (k_tc && p.batched_tail && t + 1 < p.t_end) phase_end(&p.tc_a, p.att_in[nxt]);
+    if (k_tc && k_tail && t + 1 < p.t_end) phase_end(&p.tc_a, p.att_in[nxt]);
     else phase_end();
-    if (!p.batched_tail) {
+    if (!k_tail) {
       // ---- H-K: decoder self-attention hops over the KV cache ----
       const float* y = p.dout;
       for (int hi = 0; hi < k_hops; ++hi) {
